@@ -1,0 +1,169 @@
+/* lbmff.h -- C ABI of the B200-native LBM-Ferrofluid solver path (liblbmff.so).
+ *
+ * Plain pointers and sizes only: no torch / ATen types cross this boundary.
+ * Every pointer is a DEVICE pointer (fp32 unless stated; flags are uint8 with
+ * FLUID = 1, OBSTACLE = 2, reference src/LBM/utils/types.py:7-15).  Tensors use
+ * the reference's contiguous layout [B][C][D][H][W], x (W) fastest; 2-D grids
+ * pass D = 1 and use the *_d2q9 entry points.  `stream` is a cudaStream_t.
+ * Every function returns 0 on success or a cudaError_t value;
+ * lbmff_last_error_string() describes the last failure of the calling thread.
+ * Outputs never alias inputs unless a parameter is documented "in place".
+ *
+ * Each entry point names the reference interface (file:line under
+ * /root/reference) that a binding would replace with it.  The reference is
+ * pure Python/PyTorch, so "the FFI a maintainer would add" is a ctypes call
+ * from the body of the named method -- see INTEGRATION.md.
+ */
+#ifndef LBMFF_H
+#define LBMFF_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* lbmff_stream_t; /* cudaStream_t */
+
+/* rho -> density affine map parameters and the lattice scales, shared by many
+ * calls (reference: constructor kwargs of every op, LBM_collision_3d.py:12-28). */
+/* Scalars are doubles, like the Python floats of the reference: derived constants
+ * (c = dx/dt, cs2, 1 - 0.5/tau, ...) are formed in double on the host and rounded
+ * to fp32 once, exactly where the reference's scalar-times-tensor ops round them. */
+typedef struct lbmff_fluid_params {
+  double dx, dt;
+  double density_liquid, density_gas, rho_liquid, rho_gas;
+  double kappa;
+  double tau;          /* single-phase / magnetic relaxation time (self._tau) */
+  double tau_f, tau_g; /* HCZ relaxation times */
+  double gravity;      /* scalar given to set_gravity(); acts along -y */
+  double cot_theta;    /* tan(pi/2 - contact_angle) as the reference evaluates it in fp32, HCZ_3d.py:97 */
+} lbmff_fluid_params;
+
+const char* lbmff_last_error_string(void);
+int lbmff_version(void);
+
+/* ---- a1/a2  LBMPropagation{2,3}d.propagation / rebounce_obstacle
+ *      (LBM_propagation_3d.py:18-111,113-142; LBM_propagation_2d.py:18-68,70-86) */
+int lbmff_propagation_d2q9(const float* f, float* f_out, int B, int H, int W, lbmff_stream_t stream);
+int lbmff_propagation_d3q19(const float* f, float* f_out, int B, int D, int H, int W, lbmff_stream_t stream);
+int lbmff_rebounce_obstacle_d2q9(const float* f, const uint8_t* flags, float* f_out, int B, int H, int W,
+                                 lbmff_stream_t stream);
+int lbmff_rebounce_obstacle_d3q19(const float* f, const uint8_t* flags, float* f_out, int B, int D, int H, int W,
+                                  lbmff_stream_t stream);
+
+/* ---- a3  LBMMacroCompute{2,3}d.macro_compute (LBM_macro_compute_3d.py:73-120, _2d.py:65-107)
+ *      density_out may be NULL (single-phase form). */
+int lbmff_macro_compute_d2q9(const float* f, const float* rho, const float* vel, const uint8_t* flags,
+                             float* rho_out, float* vel_out, float* density_out, const lbmff_fluid_params* p, int B,
+                             int H, int W, lbmff_stream_t stream);
+int lbmff_macro_compute_d3q19(const float* f, const float* rho, const float* vel, const uint8_t* flags,
+                              float* rho_out, float* vel_out, float* density_out, const lbmff_fluid_params* p, int B,
+                              int D, int H, int W, lbmff_stream_t stream);
+
+/* ---- a4  get_pressure (order 0: LBM_macro_compute_3d.py:59-71) /
+ *          equation_of_states (order 1: LBM_collision_3d.py:105-122); n = element count */
+int lbmff_equation_of_states(const float* rho, float* out, long long n, double dx, double dt, int order,
+                             lbmff_stream_t stream);
+
+/* ---- a5/a6/a14  get_feq_ / get_geq_ / compute_Gamma
+ *      (LBM_collision_3d.py:133-207, LBM_collision_2d.py:113-181, HCZ_3d.py:271-281)
+ *      force may be NULL; feq_in may be NULL (then geq builds feq itself from rho, vel, force, tau). */
+int lbmff_get_feq_d2q9(const float* rho, const float* vel, const float* force, double tau, double dx, double dt,
+                       float* feq, int B, int H, int W, lbmff_stream_t stream);
+int lbmff_get_feq_d3q19(const float* rho, const float* vel, const float* force, double tau, double dx, double dt,
+                        float* feq, int B, int D, int H, int W, lbmff_stream_t stream);
+int lbmff_get_geq_d2q9(const float* rho, const float* vel, const float* density, const float* pressure,
+                       const float* force, const float* feq_in, double tau, double dx, double dt, float* geq, int B,
+                       int H, int W, lbmff_stream_t stream);
+int lbmff_get_geq_d3q19(const float* rho, const float* vel, const float* density, const float* pressure,
+                        const float* force, const float* feq_in, double tau, double dx, double dt, float* geq, int B,
+                        int D, int H, int W, lbmff_stream_t stream);
+int lbmff_compute_gamma_d2q9(const float* vel, double dx, double dt, float* gamma, int B, int H, int W,
+                             lbmff_stream_t stream);
+int lbmff_compute_gamma_d3q19(const float* vel, double dx, double dt, float* gamma, int B, int D, int H, int W,
+                              lbmff_stream_t stream);
+
+/* ---- a13  smooth_phi (HCZ_3d.py:265-269, LBM_magnetic_3d.py:119-123) */
+int lbmff_smooth_phi(const float* phi, float* out, long long n, double eps, lbmff_stream_t stream);
+
+/* ---- a7/a8  get_grad (static) / get_laplacian
+ *      (LBM_collision_3d.py:209-318, LBM_collision_2d.py:183-256); out of grad is [B][dim][...] */
+int lbmff_get_grad_2d(const float* in, const uint8_t* flags, float* out, double dx, int B, int H, int W,
+                      lbmff_stream_t stream);
+int lbmff_get_grad_3d(const float* in, const uint8_t* flags, float* out, double dx, int B, int D, int H, int W,
+                      lbmff_stream_t stream);
+int lbmff_get_laplacian_2d(const float* in, float* out, double dx, int B, int H, int W, lbmff_stream_t stream);
+int lbmff_get_laplacian_3d(const float* in, float* out, double dx, int B, int D, int H, int W,
+                           lbmff_stream_t stream);
+
+/* ---- a17  get_staggered_x/_y/_z (src/LBM/utils/grid.py:7-49); axis 0 = x, 1 = y, 2 = z.
+ *      in: [BC][D][H][W] -> out with extent + 1 along `axis`. */
+int lbmff_get_staggered(const float* in, float* out, int axis, int BC, int D, int H, int W, lbmff_stream_t stream);
+
+/* ---- get_vort (LBM_macro_compute_2d.py:109-117) */
+int lbmff_get_vort_2d(const float* vel, float* out, double dx, int B, int H, int W, lbmff_stream_t stream);
+
+/* ---- a9  LBMCollision{2,3}d.collision: BGK with velocity-shift forcing
+ *      (LBM_collision_3d.py:320-346, LBM_collision_2d.py:258-287) */
+int lbmff_collision_bgk_d2q9(const float* f, const float* rho, const float* vel, const uint8_t* flags,
+                             const float* force, double tau, double dx, double dt, float* f_out, int B, int H, int W,
+                             lbmff_stream_t stream);
+int lbmff_collision_bgk_d3q19(const float* f, const float* rho, const float* vel, const uint8_t* flags,
+                              const float* force, double tau, double dx, double dt, float* f_out, int B, int D, int H,
+                              int W, lbmff_stream_t stream);
+
+/* ---- a10  LBMCollisionMRT2d.get_s_by_KBC / collision (LBM_collision_MRT_2d.py:62-182,184-226)
+ *      kbc != 0: centred moments, s = {T, N, Pi_xy} (every KBC_* type, types.py:72-107);
+ *      kbc == 0: raw moments, s = {T, Pi_xy, Q_xxy, Q_xyy, A} (KBC_type None / LBGK). */
+int lbmff_get_s_by_kbc_d2q9(const float* f, const float* rho, const float* vel, int kbc, double dx, double dt,
+                            float* s_out, int B, int H, int W, lbmff_stream_t stream);
+int lbmff_collision_kbc_d2q9(const float* f, const float* rho, const float* vel, const uint8_t* flags,
+                             const float* force, double tau, int kbc, double dx, double dt, float* f_out, int B, int H,
+                             int W, lbmff_stream_t stream);
+
+/* ---- a11  LBMCollisionSC2d.calculate_force / collision (LBM_collision_SC_2d.py:22-97,99-137) */
+int lbmff_sc_force_d2q9(const float* density, const uint8_t* flags, double density_liquid, double density_gas,
+                        double dx, double dt, float* force_out, int B, int H, int W, lbmff_stream_t stream);
+
+/* ---- a12  LBMCollisionHCZ{2,3}d.capillary_process (HCZ_3d.py:21-263, HCZ_2d.py:21-173)
+ *      rho: IN PLACE (wetting boundary on the shell).  H2 / phi may both be NULL (no Kelvin force).
+ *      workspace: >= 4 * B*D*H*W floats of scratch.  Outputs: vel_out [dim], density_out, pressure_out,
+ *      force_out [dim], dfai_out [dim], dprho_out [dim]. */
+int lbmff_capillary_process_d2q9(float* rho, const float* vel, const uint8_t* flags, const float* g,
+                                 const float* density, const float* pressure, const float* H2, const float* phi,
+                                 const lbmff_fluid_params* p, float* vel_out, float* density_out,
+                                 float* pressure_out, float* force_out, float* dfai_out, float* dprho_out,
+                                 float* workspace, int B, int H, int W, lbmff_stream_t stream);
+int lbmff_capillary_process_d3q19(float* rho, const float* vel, const uint8_t* flags, const float* g,
+                                  const float* density, const float* pressure, const float* H2, const float* phi,
+                                  const lbmff_fluid_params* p, float* vel_out, float* density_out,
+                                  float* pressure_out, float* force_out, float* dfai_out, float* dprho_out,
+                                  float* workspace, int B, int D, int H, int W, lbmff_stream_t stream);
+
+/* ---- a15  LBMCollisionHCZ{2,3}d.collision (HCZ_3d.py:283-361, HCZ_2d.py:193-286)
+ *      kbc_on_g: 2-D only, entropic KBC relaxation of g (KBC_type is not None). */
+int lbmff_collision_hcz_d2q9(const float* f, const float* g, const float* rho, const float* vel,
+                             const float* density, const uint8_t* flags, const float* force, const float* pressure,
+                             const float* dfai, const float* dprho, const lbmff_fluid_params* p, int kbc_on_g,
+                             float* f_out, float* g_out, int B, int H, int W, lbmff_stream_t stream);
+int lbmff_collision_hcz_d3q19(const float* f, const float* g, const float* rho, const float* vel,
+                              const float* density, const uint8_t* flags, const float* force,
+                              const float* pressure, const float* dfai, const float* dprho,
+                              const lbmff_fluid_params* p, float* f_out, float* g_out, int B, int D, int H, int W,
+                              lbmff_stream_t stream);
+
+/* ---- a16  LBMMagnetic{2,3}d.get_H_int (LBM_magnetic_3d.py:125-188, LBM_magnetic_2d.py:105-164)
+ *      H_ext_mac_*: face arrays (W+1 / H+1 / D+1 along their axis); hz may be NULL in 2-D.
+ *      psi_ws: B*D*H*W floats of scratch (receives psi).  Outputs H_int [dim], h_out [Q]. */
+int lbmff_get_H_int_d2q9(const float* phi, const uint8_t* flags, const float* Hx, const float* Hy, const float* h,
+                         double tau, double dx, double dt, float* H_int, float* h_out, float* psi_ws, int B, int H,
+                         int W, lbmff_stream_t stream);
+int lbmff_get_H_int_d3q19(const float* phi, const uint8_t* flags, const float* Hx, const float* Hy,
+                          const float* Hz, const float* h, double tau, double dx, double dt, float* H_int,
+                          float* h_out, float* psi_ws, int B, int D, int H, int W, lbmff_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LBMFF_H */
