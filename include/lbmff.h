@@ -163,6 +163,91 @@ int lbmff_get_H_int_d3q19(const float* phi, const uint8_t* flags, const float* H
                           const float* Hz, const float* h, double tau, double dx, double dt, float* H_int,
                           float* h_out, float* psi_ws, int B, int D, int H, int W, lbmff_stream_t stream);
 
+/* =====================================================================================
+ * Fused step tier.  The reference has no counterpart function: its time loop lives in the
+ * demo scripts (demo_3d_LBM_Rosensweig_instability.py:151-209, demo_2d_LBM.py:101-121).
+ * These entry points execute the same sequence of reference ops with far fewer passes over
+ * HBM; lbm_ferrofluid_b200.solver drives them.  State between steps: post-collision f, g
+ * (pre-stream), rho (shell values persist), pressure, vel, and the magnetic lattice.
+ * ===================================================================================== */
+
+/* rho <- sum_q f_q(x - e_q) on non-OBSTACLE cells, in place (propagation + macro_compute). */
+int lbmff_hcz_moments_d2q9(const float* f, const uint8_t* flags, float* rho, int B, int H, int W,
+                           lbmff_stream_t stream);
+int lbmff_hcz_moments_d3q19(const float* f, const uint8_t* flags, float* rho, int B, int D, int H, int W,
+                            lbmff_stream_t stream);
+
+/* Sweep-invariant magnetic source rhs (LBM_magnetic_3d.py:161-179) and chi, from rho via
+ * density -> phi (demo :162) -> chi.  chi_out may be NULL. */
+int lbmff_magnetic_source_2d(const float* rho, const uint8_t* mflags, const float* Hx, const float* Hy,
+                             const lbmff_fluid_params* p, float* rhs_out, float* chi_out, int B, int H, int W,
+                             lbmff_stream_t stream);
+int lbmff_magnetic_source_3d(const float* rho, const uint8_t* mflags, const float* Hx, const float* Hy,
+                             const float* Hz, const lbmff_fluid_params* p, float* rhs_out, float* chi_out, int B,
+                             int D, int H, int W, lbmff_stream_t stream);
+
+/* n_sweeps population-faithful sweeps (propagation + rebounce_obstacle + get_H_int collision per sweep,
+ * one pass over h each).  Ping-pong hA -> hB -> hA ...: the result is in hA if n_sweeps is even, else hB.
+ * psi_out receives psi of the LAST sweep (the one H_int is taken from, demo :166-178). */
+int lbmff_magnetic_sweeps_d2q9(float* hA, float* hB, const uint8_t* mflags, const float* rhs, float* psi_out,
+                               int n_sweeps, double tau, double dx, double dt, int B, int H, int W,
+                               lbmff_stream_t stream);
+int lbmff_magnetic_sweeps_d3q19(float* hA, float* hB, const uint8_t* mflags, const float* rhs, float* psi_out,
+                                int n_sweeps, double tau, double dx, double dt, int B, int D, int H, int W,
+                                lbmff_stream_t stream);
+
+/* tau == 1 scalar form of the same sweeps (valid when every OBSTACLE cell of mflags is on the outer
+ * shell): state a[2][N] = outgoing value of the axis / diagonal weight class.  aA holds the latest state,
+ * aB the one before; result in aA if n_sweeps is even, else aB (the other buffer then holds "one before").
+ * Bit-identical psi to lbmff_magnetic_sweeps_* on non-OBSTACLE cells. */
+int lbmff_magnetic_sweeps_scalar_2d(float* aA, float* aB, const uint8_t* mflags, const float* rhs, float* psi_out,
+                                    int n_sweeps, double dx, double dt, int B, int H, int W,
+                                    lbmff_stream_t stream);
+int lbmff_magnetic_sweeps_scalar_3d(float* aA, float* aB, const uint8_t* mflags, const float* rhs, float* psi_out,
+                                    int n_sweeps, double dx, double dt, int B, int D, int H, int W,
+                                    lbmff_stream_t stream);
+/* Rebuild the Q-population h from the scalar state (a_cur latest, a_prev one sweep earlier). */
+int lbmff_magnetic_materialize_h_2d(const float* a_cur, const float* a_prev, const float* psi, const float* rhs,
+                                    const uint8_t* mflags, float* h_out, double dx, double dt, int B, int H, int W,
+                                    lbmff_stream_t stream);
+int lbmff_magnetic_materialize_h_3d(const float* a_cur, const float* a_prev, const float* psi, const float* rhs,
+                                    const uint8_t* mflags, float* h_out, double dx, double dt, int B, int D, int H,
+                                    int W, lbmff_stream_t stream);
+
+/* capillary_process part 1: ordered wetting boundary (rho IN PLACE) then ws = [lap(density) | fai | prho],
+ * 3 * B*D*H*W floats (HCZ_3d.py:73-220).  `pressure` is the previous step's. */
+int lbmff_hcz_capillary_fields_2d(float* rho, const uint8_t* flags, const float* pressure,
+                                  const lbmff_fluid_params* p, float* ws, int B, int H, int W,
+                                  lbmff_stream_t stream);
+int lbmff_hcz_capillary_fields_3d(float* rho, const uint8_t* flags, const float* pressure,
+                                  const lbmff_fluid_params* p, float* ws, int B, int D, int H, int W,
+                                  lbmff_stream_t stream);
+
+/* propagation + rebounce_obstacle of f and g, capillary_process part 2 (forces, vel, pressure) and the
+ * HCZ collision, in one pass: reads f_in/g_in (pulled), writes f_out/g_out.  chi/psi/mflags NULL = no
+ * magnetic force.  H_ext: cell-centred [B][dim][...] or NULL with H_uniform[dim].  vel, pressure are
+ * updated IN PLACE on FLUID cells; force_out may be NULL. */
+int lbmff_hcz_collide_stream_d2q9(const float* f_in, const float* g_in, float* f_out, float* g_out,
+                                  const float* rho, const uint8_t* flags, const uint8_t* mflags, const float* ws,
+                                  const float* chi, const float* psi, const float* H_ext, const double* H_uniform,
+                                  const lbmff_fluid_params* p, int kbc_on_g, float* vel, float* pressure,
+                                  float* force_out, int B, int H, int W, lbmff_stream_t stream);
+int lbmff_hcz_collide_stream_d3q19(const float* f_in, const float* g_in, float* f_out, float* g_out,
+                                   const float* rho, const uint8_t* flags, const uint8_t* mflags, const float* ws,
+                                   const float* chi, const float* psi, const float* H_ext, const double* H_uniform,
+                                   const lbmff_fluid_params* p, float* vel, float* pressure, float* force_out,
+                                   int B, int D, int H, int W, lbmff_stream_t stream);
+
+/* Single-phase step in one pass: propagation + macro_compute + rebounce_obstacle + collision
+ * (demo_2d_LBM.py:101-121).  kbc < 0: BGK; kbc = 0 / 1: LBGK-split / KBC entropic collision (D2Q9).
+ * rho, vel updated IN PLACE on non-OBSTACLE cells; force may be NULL. */
+int lbmff_stream_collide_d2q9(const float* f_in, float* f_out, const uint8_t* flags, const float* force, float* rho,
+                              float* vel, double tau, int kbc, double dx, double dt, int B, int H, int W,
+                              lbmff_stream_t stream);
+int lbmff_stream_collide_d3q19(const float* f_in, float* f_out, const uint8_t* flags, const float* force,
+                               float* rho, float* vel, double tau, double dx, double dt, int B, int D, int H, int W,
+                               lbmff_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

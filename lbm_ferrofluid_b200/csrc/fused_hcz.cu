@@ -1,0 +1,361 @@
+// Fused tier, hydrodynamic part of one outer step (demo_3d_LBM_Rosensweig_instability.py:151-209):
+//
+//  k_hcz_moments        rho = sum_q f_q(x - e_q) on non-OBSTACLE cells          (stream + macro_compute)
+//  k_hcz_fields         after the ordered wetting kernels: lap(density), fai, prho  (capillary_process, part 1)
+//  k_hcz_collide_stream pull f,g; bounce on OBSTACLE; on FLUID: forces, vel, pressure, f and g collisions;
+//                       write the other f,g buffers (stream + bounce + capillary_process part 2 + collision)
+//  k_stream_collide     single-phase D2Q9 / D3Q19: stream + macro + bounce + BGK / KBC in one pass
+//
+// Populations stay in the reference's [Q][z][y][x] SoA layout: the thread index runs along x, so every
+// population load (shifted by at most one cell) and store is unit-stride.  State between steps is the
+// post-collision, pre-stream f,g -- the same state the reference holds at the end of a step.
+#include "capi.cuh"
+#include "capillary.cuh"
+#include "collide.cuh"
+
+namespace lbmff {
+
+template <int DIM>
+struct Nbr {  // periodic neighbour coordinates of a cell
+  int x[3], y[3], z[3];  // index 0: -1, 1: 0, 2: +1
+  __device__ __forceinline__ Nbr(const Cell& c, const Grid& g) {
+    x[0] = wrap(c.x - 1, g.W); x[1] = c.x; x[2] = wrap(c.x + 1, g.W);
+    y[0] = wrap(c.y - 1, g.H); y[1] = c.y; y[2] = wrap(c.y + 1, g.H);
+    z[0] = DIM == 3 ? wrap(c.z - 1, g.D) : 0; z[1] = c.z; z[2] = DIM == 3 ? wrap(c.z + 1, g.D) : 0;
+  }
+  // linear index of x - s*e_q  (s = +1: pull source; s = -1: x + e_q)
+  __device__ __forceinline__ long long at(const Grid& g, int q, int s) const {
+    using L = Lat<DIM>;
+    return lin(g, x[1 - s * L::ex(q)], y[1 - s * L::ey(q)], z[1 - s * L::ez(q)]);
+  }
+};
+
+template <int DIM>
+__global__ void __launch_bounds__(kThreads) k_hcz_moments(const float* __restrict__ f,
+                                                          const uint8_t* __restrict__ flags, float* __restrict__ rho,
+                                                          Grid g) {
+  using L = Lat<DIM>;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.N) return;
+  const long long b = blockIdx.y;
+  if (flags[b * g.N + i] == LBMFF_OBSTACLE) return;  // old rho kept (LBM_macro_compute_3d.py:93-98)
+  const Nbr<DIM> nb(cell_of(i, g), g);
+  const float* fb = f + b * L::Q * g.N;
+  float s = 0.0f;
+#pragma unroll
+  for (int q = 0; q < L::Q; ++q) s += __ldg(fb + q * g.N + nb.at(g, q, 1));
+  rho[b * g.N + i] = s;
+}
+
+struct AffineRho {
+  const float* __restrict__ rho;
+  Affine A;
+  Grid g;
+  __device__ __forceinline__ float operator()(int x, int y, int z) const {
+    return affine_density(__ldg(rho + lin(g, x, y, z)), A);
+  }
+};
+
+// ws = [lap | fai | prho], N floats each
+template <int DIM>
+__global__ void __launch_bounds__(kThreads) k_hcz_fields(const float* __restrict__ rho,
+                                                         const float* __restrict__ pressure, float* __restrict__ ws,
+                                                         Consts k, Grid g) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.N) return;
+  const long long b = blockIdx.y;
+  const Cell c = cell_of(i, g);
+  const float* r = rho + b * g.N;
+  float* w = ws + b * 3 * g.N;
+  const bool shell = c.x == 0 || c.x == g.W - 1 || c.y == 0 || c.y == g.H - 1 ||
+                     (DIM == 3 && (c.z == 0 || c.z == g.D - 1));
+  w[i] = shell ? 0.0f : laplacian_at<DIM>(AffineRho{r, k.aff, g}, c.x, c.y, c.z, k.dx2);
+  const long long j = lin(g, interior(c.x, g.W), interior(c.y, g.H), DIM == 3 ? interior(c.z, g.D) : 0);
+  const float rj = r[j];
+  w[g.N + i] = eos_cs(rj, k.cs2, k.a_eos, 1) - rj * k.cs2;
+  // density of the previous macro_compute at an interior cell = affine(rho) there (wetting touches the shell only)
+  w[2 * g.N + i] = pressure[b * g.N + j] - k.cs2 * affine_density(rj, k.aff);
+}
+
+struct HextUniform {
+  float v[3];
+};
+
+template <int DIM, bool MAGNETIC>
+__global__ void __launch_bounds__(kThreads, 2)
+k_hcz_collide_stream(const float* __restrict__ f_in, const float* __restrict__ g_in, float* __restrict__ f_out,
+                     float* __restrict__ g_out, const float* __restrict__ rho_, const uint8_t* __restrict__ flags,
+                     const uint8_t* __restrict__ mflags, const float* __restrict__ ws,
+                     const float* __restrict__ chi, const float* __restrict__ psi, const float* __restrict__ Hext,
+                     HextUniform Hu, float* __restrict__ vel, float* __restrict__ pressure,
+                     float* __restrict__ force_out, Consts k, int kbc_on_g, KbcScalars K, Grid g) {
+  using L = Lat<DIM>;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.N) return;
+  const long long b = blockIdx.y;
+  const Cell c = cell_of(i, g);
+  const Nbr<DIM> nb(c, g);
+  const float* fi = f_in + b * L::Q * g.N;
+  const float* gi = g_in + b * L::Q * g.N;
+  float* fo = f_out + b * L::Q * g.N;
+  float* go = g_out + b * L::Q * g.N;
+  const uint8_t fl = flags[b * g.N + i];
+  if (fl == LBMFF_OBSTACLE) {
+    // stream then full-way bounce: out_q(x) = in_opp(q)(x + e_q); walls never collide
+#pragma unroll
+    for (int q = 0; q < L::Q; ++q) {
+      const long long j = L::opp(q) * g.N + nb.at(g, q, -1);
+      fo[q * g.N + i] = __ldg(fi + j);
+      go[q * g.N + i] = __ldg(gi + j);
+    }
+    return;
+  }
+  float gv[L::Q];
+#pragma unroll
+  for (int q = 0; q < L::Q; ++q) gv[q] = __ldg(gi + q * g.N + nb.at(g, q, 1));
+  if (fl != LBMFF_FLUID) {  // streamed only (HCZ collides FLUID cells only, HCZ_3d.py:357-359)
+#pragma unroll
+    for (int q = 0; q < L::Q; ++q) {
+      go[q * g.N + i] = gv[q];
+      fo[q * g.N + i] = __ldg(fi + q * g.N + nb.at(g, q, 1));
+    }
+    return;
+  }
+  // ---- capillary_process part 2 at a FLUID cell (HCZ_3d.py:217-261)
+  const uint8_t* flb = flags + b * g.N;
+  const float* w = ws + b * 3 * g.N;
+  const int x = interior(c.x, g.W), y = interior(c.y, g.H), z = DIM == 3 ? interior(c.z, g.D) : 0;
+  float glap[3], gfai[3], gprho[3];
+  grad_at<DIM>(ObstacleClampedField{w, flb, g}, x, y, z, k.dx, glap);
+  grad_at<DIM>(ObstacleClampedField{w + g.N, flb, g}, x, y, z, k.dx, gfai);
+  grad_at<DIM>(ObstacleClampedField{w + 2 * g.N, flb, g}, x, y, z, k.dx, gprho);
+  const float rho = rho_[b * g.N + i];
+  const float dn = affine_density(rho, k.aff);
+  float F[DIM];
+#pragma unroll
+  for (int a = 0; a < DIM; ++a) {
+    F[a] = k.kappa * dn * glap[a];
+    if (a == 1) F[a] += k.grav_y * dn;
+  }
+  if (MAGNETIC) {
+    float gchi[3], gpsi[3], H2 = 0.0f;
+    grad_at<DIM>(ObstacleClampedField{chi + b * g.N, flb, g}, x, y, z, k.dx, gchi);
+    grad_at<DIM>(ObstacleClampedField{psi + b * g.N, mflags + b * g.N, g}, x, y, z, k.dx, gpsi);
+#pragma unroll
+    for (int a = 0; a < DIM; ++a) {
+      const float he = Hext ? __ldg(Hext + (b * DIM + a) * g.N + i) : Hu.v[a];
+      const float ht = he + (-gpsi[a]);  // H_ext + H_int, H_int = -grad(psi) (LBM_magnetic_3d.py:184)
+      H2 += ht * ht;
+    }
+#pragma unroll
+    for (int a = 0; a < DIM; ++a) F[a] += k.kelvin * H2 * gchi[a];
+  }
+  float s = 0.f, m[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+  for (int q = 0; q < L::Q; ++q) {
+    s += gv[q];
+    if (L::ex(q) != 0) m[0] += gv[q] * (float)L::ex(q);
+    if (L::ey(q) != 0) m[1] += gv[q] * (float)L::ey(q);
+    if (DIM == 3 && L::ez(q) != 0) m[2] += gv[q] * (float)L::ez(q);
+  }
+  float u[DIM], dot = 0.f;
+#pragma unroll
+  for (int a = 0; a < DIM; ++a) {
+    u[a] = (m[a] * k.c + k.half_dt_RT * F[a]) / k.cs2 / dn;
+    vel[(b * DIM + a) * g.N + i] = u[a];
+    if (force_out) force_out[(b * DIM + a) * g.N + i] = F[a];
+    dot += u[a] * gprho[a];
+  }
+  const float p = s - k.half_dt * dot;
+  pressure[b * g.N + i] = p;
+  // ---- HCZ collision (HCZ_3d.py:283-361), f loaded only now to keep register pressure down
+  float fv[L::Q];
+#pragma unroll
+  for (int q = 0; q < L::Q; ++q) fv[q] = __ldg(fi + q * g.N + nb.at(g, q, 1));
+  hcz_collide_cell<DIM>(fv, gv, rho, u, dn, p, F, gfai, gprho, k, kbc_on_g, K);
+#pragma unroll
+  for (int q = 0; q < L::Q; ++q) {
+    fo[q * g.N + i] = fv[q];
+    go[q * g.N + i] = gv[q];
+  }
+}
+
+// ---- single-phase: stream + macro + bounce + BGK/KBC (demo_2d_LBM.py:101-121) -------------------
+template <int DIM, int MODE>  // MODE 0: BGK, 1: KBC (D2Q9)
+__global__ void __launch_bounds__(kThreads) k_stream_collide(const float* __restrict__ f_in,
+                                                             float* __restrict__ f_out,
+                                                             const uint8_t* __restrict__ flags,
+                                                             const float* __restrict__ force, float* __restrict__ rho_,
+                                                             float* __restrict__ vel, int kbc, Consts k,
+                                                             KbcScalars K, Grid g) {
+  using L = Lat<DIM>;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.N) return;
+  const long long b = blockIdx.y;
+  const Nbr<DIM> nb(cell_of(i, g), g);
+  const float* fi = f_in + b * L::Q * g.N;
+  float* fo = f_out + b * L::Q * g.N;
+  if (flags[b * g.N + i] == LBMFF_OBSTACLE) {
+#pragma unroll
+    for (int q = 0; q < L::Q; ++q) fo[q * g.N + i] = __ldg(fi + L::opp(q) * g.N + nb.at(g, q, -1));
+    return;  // rho, vel keep their old values on OBSTACLE cells
+  }
+  float fv[L::Q], s = 0.f, m[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+  for (int q = 0; q < L::Q; ++q) {
+    fv[q] = __ldg(fi + q * g.N + nb.at(g, q, 1));
+    s += fv[q];
+    if (L::ex(q) != 0) m[0] += fv[q] * (float)L::ex(q);
+    if (L::ey(q) != 0) m[1] += fv[q] * (float)L::ey(q);
+    if (DIM == 3 && L::ez(q) != 0) m[2] += fv[q] * (float)L::ez(q);
+  }
+  const float rho = s, scale = k.c / rho;
+  rho_[b * g.N + i] = rho;
+  float u0[DIM], u[DIM];
+#pragma unroll
+  for (int a = 0; a < DIM; ++a) {
+    u0[a] = m[a] * scale;
+    vel[(b * DIM + a) * g.N + i] = u0[a];
+    u[a] = force ? u0[a] + k.tau * force[(b * DIM + a) * g.N + i] / rho : u0[a];
+  }
+  const FeqFactors<DIM> F = feq_factors<DIM>(u, k.c);
+  if constexpr (MODE == 1) {
+    float fe[9], o[9];
+#pragma unroll
+    for (int q = 0; q < 9; ++q) fe[q] = feq_q<DIM>(F, rho, q);
+    kbc_relax(fv, fe, rho, u0, k.c, kbc, K, o);
+#pragma unroll
+    for (int q = 0; q < 9; ++q) fo[q * g.N + i] = o[q];
+  } else {
+#pragma unroll
+    for (int q = 0; q < L::Q; ++q) fo[q * g.N + i] = k.keep * fv[q] + feq_q<DIM>(F, rho, q) / k.tau;
+  }
+}
+
+static Consts consts_of(const lbmff_fluid_params* p) {
+  return make_consts(p->dx, p->dt, p->tau, p->tau_f, p->tau_g, p->density_liquid, p->density_gas, p->rho_liquid,
+                     p->rho_gas, p->kappa, p->gravity, p->cot_theta);
+}
+
+template <int DIM>
+static int moments_impl(const float* f, const uint8_t* flags, float* rho, int B, int D, int H, int W,
+                        cudaStream_t st, const char* where) {
+  if (!(f && flags && rho)) return bad_arg(where, "null pointer");
+  const Grid g = make_grid(B, D, H, W);
+  k_hcz_moments<DIM><<<dim3(blocks_for(g.N), (unsigned)B), kThreads, 0, st>>>(f, flags, rho, g);
+  return check_launch(where);
+}
+
+template <int DIM>
+static int fields_impl(float* rho, const uint8_t* flags, const float* pressure, const lbmff_fluid_params* p,
+                       float* ws, int B, int D, int H, int W, cudaStream_t st, const char* where) {
+  if (!(rho && flags && pressure && p && ws)) return bad_arg(where, "null pointer");
+  if (W < 4 || H < 4 || (DIM == 3 && D < 4)) return bad_arg(where, "every extent must be >= 4");
+  const Grid g = make_grid(B, D, H, W);
+  const Consts k = consts_of(p);
+  launch_wetting<DIM>(rho, flags, k.cot, g, st);
+  k_hcz_fields<DIM><<<dim3(blocks_for(g.N), (unsigned)B), kThreads, 0, st>>>(rho, pressure, ws, k, g);
+  return check_launch(where);
+}
+
+template <int DIM>
+static int collide_stream_impl(const float* f_in, const float* g_in, float* f_out, float* g_out, const float* rho,
+                               const uint8_t* flags, const uint8_t* mflags, const float* ws, const float* chi,
+                               const float* psi, const float* Hext, const double* Hu, const lbmff_fluid_params* p,
+                               int kbc_on_g, float* vel, float* pressure, float* force_out, int B, int D, int H,
+                               int W, cudaStream_t st, const char* where) {
+  if (!(f_in && g_in && f_out && g_out && rho && flags && ws && p && vel && pressure))
+    return bad_arg(where, "null pointer");
+  if (f_in == f_out || g_in == g_out) return bad_arg(where, "in and out population buffers must differ");
+  const bool magnetic = chi != nullptr;
+  if (magnetic && !(psi && mflags && (Hext || Hu))) return bad_arg(where, "magnetic inputs incomplete");
+  const Grid g = make_grid(B, D, H, W);
+  const Consts k = consts_of(p);
+  HextUniform hu{{0.f, 0.f, 0.f}};
+  if (Hu) for (int a = 0; a < DIM; ++a) hu.v[a] = (float)Hu[a];
+  const dim3 grid(blocks_for(g.N), (unsigned)B);
+  if (magnetic)
+    k_hcz_collide_stream<DIM, true><<<grid, kThreads, 0, st>>>(f_in, g_in, f_out, g_out, rho, flags, mflags, ws, chi,
+                                                               psi, Hext, hu, vel, pressure, force_out, k, kbc_on_g,
+                                                               make_kbc(p->tau_g), g);
+  else
+    k_hcz_collide_stream<DIM, false><<<grid, kThreads, 0, st>>>(f_in, g_in, f_out, g_out, rho, flags, mflags, ws,
+                                                                chi, psi, Hext, hu, vel, pressure, force_out, k,
+                                                                kbc_on_g, make_kbc(p->tau_g), g);
+  return check_launch(where);
+}
+
+template <int DIM>
+static int stream_collide_impl(const float* f_in, float* f_out, const uint8_t* flags, const float* force, float* rho,
+                               float* vel, double tau, int kbc, double dx, double dt, int B, int D, int H, int W,
+                               cudaStream_t st, const char* where) {
+  if (!(f_in && f_out && f_in != f_out && flags && rho && vel)) return bad_arg(where, "null or aliased pointer");
+  if (!(tau > 0)) return bad_arg(where, "tau must be positive");
+  if (DIM == 3 && kbc >= 0) return bad_arg(where, "KBC collision exists for D2Q9 only");
+  const Grid g = make_grid(B, D, H, W);
+  const Consts k = make_consts(dx, dt, tau);
+  const dim3 grid(blocks_for(g.N), (unsigned)B);
+  if constexpr (DIM == 2) {
+    if (kbc >= 0) {
+      k_stream_collide<2, 1><<<grid, kThreads, 0, st>>>(f_in, f_out, flags, force, rho, vel, kbc, k, make_kbc(tau), g);
+      return check_launch(where);
+    }
+  }
+  k_stream_collide<DIM, 0><<<grid, kThreads, 0, st>>>(f_in, f_out, flags, force, rho, vel, 0, k, make_kbc(tau), g);
+  return check_launch(where);
+}
+
+}  // namespace lbmff
+
+using namespace lbmff;
+
+extern "C" {
+
+int lbmff_hcz_moments_d2q9(const float* f, const uint8_t* flags, float* rho, int B, int H, int W,
+                           lbmff_stream_t stream) {
+  return moments_impl<2>(f, flags, rho, B, 1, H, W, (cudaStream_t)stream, __func__);
+}
+int lbmff_hcz_moments_d3q19(const float* f, const uint8_t* flags, float* rho, int B, int D, int H, int W,
+                            lbmff_stream_t stream) {
+  return moments_impl<3>(f, flags, rho, B, D, H, W, (cudaStream_t)stream, __func__);
+}
+int lbmff_hcz_capillary_fields_2d(float* rho, const uint8_t* flags, const float* pressure,
+                                  const lbmff_fluid_params* p, float* ws, int B, int H, int W,
+                                  lbmff_stream_t stream) {
+  return fields_impl<2>(rho, flags, pressure, p, ws, B, 1, H, W, (cudaStream_t)stream, __func__);
+}
+int lbmff_hcz_capillary_fields_3d(float* rho, const uint8_t* flags, const float* pressure,
+                                  const lbmff_fluid_params* p, float* ws, int B, int D, int H, int W,
+                                  lbmff_stream_t stream) {
+  return fields_impl<3>(rho, flags, pressure, p, ws, B, D, H, W, (cudaStream_t)stream, __func__);
+}
+int lbmff_hcz_collide_stream_d2q9(const float* f_in, const float* g_in, float* f_out, float* g_out,
+                                  const float* rho, const uint8_t* flags, const uint8_t* mflags, const float* ws,
+                                  const float* chi, const float* psi, const float* H_ext, const double* H_uniform,
+                                  const lbmff_fluid_params* p, int kbc_on_g, float* vel, float* pressure,
+                                  float* force_out, int B, int H, int W, lbmff_stream_t stream) {
+  return collide_stream_impl<2>(f_in, g_in, f_out, g_out, rho, flags, mflags, ws, chi, psi, H_ext, H_uniform, p,
+                                kbc_on_g, vel, pressure, force_out, B, 1, H, W, (cudaStream_t)stream, __func__);
+}
+int lbmff_hcz_collide_stream_d3q19(const float* f_in, const float* g_in, float* f_out, float* g_out,
+                                   const float* rho, const uint8_t* flags, const uint8_t* mflags, const float* ws,
+                                   const float* chi, const float* psi, const float* H_ext, const double* H_uniform,
+                                   const lbmff_fluid_params* p, float* vel, float* pressure, float* force_out,
+                                   int B, int D, int H, int W, lbmff_stream_t stream) {
+  return collide_stream_impl<3>(f_in, g_in, f_out, g_out, rho, flags, mflags, ws, chi, psi, H_ext, H_uniform, p, 0,
+                                vel, pressure, force_out, B, D, H, W, (cudaStream_t)stream, __func__);
+}
+int lbmff_stream_collide_d2q9(const float* f_in, float* f_out, const uint8_t* flags, const float* force, float* rho,
+                              float* vel, double tau, int kbc, double dx, double dt, int B, int H, int W,
+                              lbmff_stream_t stream) {
+  return stream_collide_impl<2>(f_in, f_out, flags, force, rho, vel, tau, kbc, dx, dt, B, 1, H, W,
+                                (cudaStream_t)stream, __func__);
+}
+int lbmff_stream_collide_d3q19(const float* f_in, float* f_out, const uint8_t* flags, const float* force,
+                               float* rho, float* vel, double tau, double dx, double dt, int B, int D, int H, int W,
+                               lbmff_stream_t stream) {
+  return stream_collide_impl<3>(f_in, f_out, flags, force, rho, vel, tau, -1, dx, dt, B, D, H, W,
+                                (cudaStream_t)stream, __func__);
+}
+
+}  // extern "C"

@@ -1,0 +1,316 @@
+// Fused tier, magnetic subsystem: the 30 Poisson-lattice relaxation sweeps per outer step
+// (demo_3d_LBM_Rosensweig_instability.py:163-173 -> LBM_propagation_3d.py:18-142 + LBM_magnetic_3d.py:125-188).
+//
+//  k_mag_source      sweep-invariant source rhs and chi from rho, once per outer step
+//  k_mag_sweep       population-faithful sweep: stream + bounce + psi + collide in ONE pass over h
+//                    (A/B buffers; 2*Q*4 B per cell per sweep = 152 B D3Q19, 72 B D2Q9)
+//  k_mag_sweep_scalar  tau == 1 collapse: the post-collision state of a cell is (w' psi + w S), so only the
+//                    two distinct outgoing values per cell (axis / diagonal weight class) are stored:
+//                    8 B written + 8 B read (unique) per cell per sweep.  Arithmetic is the same uncontracted
+//                    sequence as k_mag_sweep -> bit-identical psi on non-OBSTACLE cells.
+#include "capi.cuh"
+#include "magnetic.cuh"
+
+namespace lbmff {
+
+struct ChiOfRho {
+  const float* __restrict__ rho;
+  Affine A;
+  Smooth sm;
+  Grid g;
+  __device__ __forceinline__ float operator()(int x, int y, int z) const {
+    return susceptibility(phase_field(affine_density(__ldg(rho + lin(g, x, y, z)), A), A), sm);
+  }
+};
+
+// rhs (FLUID cells of mflags, else 0) and chi, from rho via density -> phi -> chi
+template <int DIM>
+__global__ void __launch_bounds__(kThreads) k_mag_source(const float* __restrict__ rho,
+                                                         const uint8_t* __restrict__ mflags, HextFaces Hf,
+                                                         float* __restrict__ rhs, float* __restrict__ chi_out,
+                                                         Consts k, Grid g) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.N) return;
+  const long long b = blockIdx.y;
+  const Cell c = cell_of(i, g);
+  ChiOfRho chi{rho + b * g.N, k.aff, k.sm, g};
+  HextFaces Hb = Hf;
+  Hb.x += b * (long long)g.D * g.H * (g.W + 1);
+  Hb.y += b * (long long)g.D * (g.H + 1) * g.W;
+  if (DIM == 3) Hb.z += b * (long long)(g.D + 1) * g.H * g.W;
+  float r = 0.0f;
+  if (mflags[b * g.N + i] == LBMFF_FLUID) r = magnetic_rhs_at<DIM>(chi, Hb, c.x, c.y, c.z, g, k.dx);
+  rhs[b * g.N + i] = r;
+  if (chi_out) chi_out[b * g.N + i] = chi(c.x, c.y, c.z);
+}
+
+// ---- population-faithful fused sweep ----------------------------------------------------------
+// OBSTACLE cell x: out_q(x) = in_opp(q)(x + e_q)   (stream, then bounce; walls never collide)
+// other cells:     h_q = in_q(x - e_q); psi = sum_{q>=1} h_q / (1 - w0); out_q = collide(h_q, psi, rhs)
+template <int DIM, bool WRITE_PSI>
+__global__ void __launch_bounds__(kThreads) k_mag_sweep(const float* __restrict__ hin, float* __restrict__ hout,
+                                                        const uint8_t* __restrict__ mflags,
+                                                        const float* __restrict__ rhs, float* __restrict__ psi_out,
+                                                        Consts k, Grid g) {
+  using L = Lat<DIM>;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.N) return;
+  const long long b = blockIdx.y;
+  const float* in = hin + b * L::Q * g.N;
+  float* out = hout + b * L::Q * g.N;
+  const Cell c = cell_of(i, g);
+  const int xm = wrap(c.x - 1, g.W), xp = wrap(c.x + 1, g.W);
+  const int ym = wrap(c.y - 1, g.H), yp = wrap(c.y + 1, g.H);
+  const int zm = DIM == 3 ? wrap(c.z - 1, g.D) : 0, zp = DIM == 3 ? wrap(c.z + 1, g.D) : 0;
+  const bool obst = mflags[b * g.N + i] == LBMFF_OBSTACLE;
+  float hv[L::Q];
+  if (!obst) {
+#pragma unroll
+    for (int q = 0; q < L::Q; ++q) {
+      const int sx = L::ex(q) == 1 ? xm : (L::ex(q) == -1 ? xp : c.x);
+      const int sy = L::ey(q) == 1 ? ym : (L::ey(q) == -1 ? yp : c.y);
+      const int sz = L::ez(q) == 1 ? zm : (L::ez(q) == -1 ? zp : c.z);
+      hv[q] = __ldg(in + q * g.N + lin(g, sx, sy, sz));
+    }
+  } else {  // walls are rare: divergence only in warps that touch one
+#pragma unroll
+    for (int q = 0; q < L::Q; ++q) {
+      const int sx = L::ex(q) == 1 ? xp : (L::ex(q) == -1 ? xm : c.x);
+      const int sy = L::ey(q) == 1 ? yp : (L::ey(q) == -1 ? ym : c.y);
+      const int sz = L::ez(q) == 1 ? zp : (L::ez(q) == -1 ? zm : c.z);
+      hv[q] = __ldg(in + L::opp(q) * g.N + lin(g, sx, sy, sz));
+    }
+  }
+  const float psi = psi_of<DIM>(hv);
+  if (WRITE_PSI) psi_out[b * g.N + i] = psi;
+  if (!obst) {
+    const float r = rhs[b * g.N + i];
+#pragma unroll
+    for (int q = 0; q < L::Q; ++q) hv[q] = mag_collide_q<DIM>(q, hv[q], psi, r, k);
+  }
+#pragma unroll
+  for (int q = 0; q < L::Q; ++q) out[q * g.N + i] = hv[q];
+}
+
+// ---- tau == 1 scalar sweep ---------------------------------------------------------------------
+// a[0] = outgoing value of the axis-weight populations, a[1] = of the diagonal-weight populations.
+// cur = state after the previous sweep, prev = state one sweep earlier AND the output buffer: a population
+// that comes back from a wall cell is this cell's own outgoing value of two sweeps ago (full-way bounce-back
+// = one sweep of delay), i.e. prev at the SAME cell, read by the same thread before it overwrites it.
+template <int DIM, bool WRITE_PSI>
+__global__ void __launch_bounds__(kThreads) k_mag_sweep_scalar(const float* __restrict__ cur, float* prev_out,
+                                                               const uint8_t* __restrict__ mflags,
+                                                               const float* __restrict__ rhs,
+                                                               float* __restrict__ psi_out, Consts k, Grid g) {
+  using L = Lat<DIM>;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.N) return;
+  const long long b = blockIdx.y;
+  const float* ca = cur + b * 2 * g.N;
+  float* pa = prev_out + b * 2 * g.N;
+  const uint8_t* fl = mflags + b * g.N;
+  if (fl[i] == LBMFF_OBSTACLE) return;  // wall state is implicit (never observed: get_grad masks it)
+  const Cell c = cell_of(i, g);
+  const int xm = wrap(c.x - 1, g.W), xp = wrap(c.x + 1, g.W);
+  const int ym = wrap(c.y - 1, g.H), yp = wrap(c.y + 1, g.H);
+  const int zm = DIM == 3 ? wrap(c.z - 1, g.D) : 0, zp = DIM == 3 ? wrap(c.z + 1, g.D) : 0;
+  float hv[L::Q];
+  hv[0] = 0.0f;
+  bool need_prev = false;
+  long long src[L::Q];
+#pragma unroll
+  for (int q = 1; q < L::Q; ++q) {
+    const int sx = L::ex(q) == 1 ? xm : (L::ex(q) == -1 ? xp : c.x);
+    const int sy = L::ey(q) == 1 ? ym : (L::ey(q) == -1 ? yp : c.y);
+    const int sz = L::ez(q) == 1 ? zm : (L::ez(q) == -1 ? zp : c.z);
+    src[q] = lin(g, sx, sy, sz);
+  }
+  // walls lie on the outer shell only (checked by the host), so only shell-adjacent cells test flags
+  const bool near_shell = c.x <= 1 || c.x >= g.W - 2 || c.y <= 1 || c.y >= g.H - 2 ||
+                          (DIM == 3 && (c.z <= 1 || c.z >= g.D - 2));
+  unsigned wall_mask = 0;
+  if (near_shell) {
+#pragma unroll
+    for (int q = 1; q < L::Q; ++q)
+      if (fl[src[q]] == LBMFF_OBSTACLE) wall_mask |= 1u << q;
+    need_prev = wall_mask != 0;
+  }
+  float p_axis = 0.f, p_diag = 0.f;
+  if (need_prev) {
+    p_axis = pa[i];
+    p_diag = pa[g.N + i];
+  }
+#pragma unroll
+  for (int q = 1; q < L::Q; ++q) {
+    const bool axis = (L::ex(q) != 0) + (L::ey(q) != 0) + (L::ez(q) != 0) == 1;
+    const float v = __ldg(ca + (axis ? 0 : g.N) + src[q]);
+    hv[q] = (wall_mask >> q) & 1u ? (axis ? p_axis : p_diag) : v;
+  }
+  const float psi = psi_of<DIM>(hv);
+  if (WRITE_PSI) psi_out[b * g.N + i] = psi;
+  const float r = rhs[b * g.N + i];
+  // representative populations of the two weight classes: q = 1 (axis), q = 5 (diagonal) in both lattices
+  pa[i] = mag_collide_q<DIM>(1, 0.0f, psi, r, k);
+  pa[g.N + i] = mag_collide_q<DIM>(5, 0.0f, psi, r, k);
+}
+
+// Rebuild the population-faithful h from the scalar state (for API users that ask for h).
+// cur = state after the last sweep, prev = one sweep earlier, psi = psi of the last sweep.
+template <int DIM>
+__global__ void __launch_bounds__(kThreads) k_mag_materialize(const float* __restrict__ cur,
+                                                              const float* __restrict__ prev,
+                                                              const float* __restrict__ psi,
+                                                              const float* __restrict__ rhs,
+                                                              const uint8_t* __restrict__ mflags,
+                                                              float* __restrict__ h, Consts k, Grid g) {
+  using L = Lat<DIM>;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.N) return;
+  const long long b = blockIdx.y;
+  const float* ca = cur + b * 2 * g.N;
+  const float* pa = prev + b * 2 * g.N;
+  const uint8_t* fl = mflags + b * g.N;
+  float* out = h + b * L::Q * g.N;
+  const Cell c = cell_of(i, g);
+  if (fl[i] != LBMFF_OBSTACLE) {
+    out[i] = mag_collide_q<DIM>(0, 0.0f, psi[b * g.N + i], rhs[b * g.N + i], k);
+#pragma unroll
+    for (int q = 1; q < L::Q; ++q) {
+      const bool axis = (L::ex(q) != 0) + (L::ey(q) != 0) + (L::ez(q) != 0) == 1;
+      out[q * g.N + i] = ca[(axis ? 0 : g.N) + i];
+    }
+  } else {
+    // wall cell s: h_q(s) = (h of one sweep earlier)_{opp q}(s + e_q) when that neighbour is not a wall;
+    // chains between wall cells carry values older than the two kept levels and are left at zero
+    out[i] = 0.0f;
+#pragma unroll
+    for (int q = 1; q < L::Q; ++q) {
+      const bool axis = (L::ex(q) != 0) + (L::ey(q) != 0) + (L::ez(q) != 0) == 1;
+      const long long j = lin(g, wrap(c.x + L::ex(q), g.W), wrap(c.y + L::ey(q), g.H),
+                              DIM == 3 ? wrap(c.z + L::ez(q), g.D) : 0);
+      out[q * g.N + i] = fl[j] != LBMFF_OBSTACLE ? pa[(axis ? 0 : g.N) + j] : 0.0f;
+    }
+  }
+}
+
+template <int DIM>
+static int sweeps_impl(float* hA, float* hB, const uint8_t* mflags, const float* rhs, float* psi_out, int n,
+                       double tau, double dx, double dt, int B, int D, int H, int W, cudaStream_t st,
+                       const char* where) {
+  if (!(hA && hB && hA != hB && mflags && rhs && psi_out)) return bad_arg(where, "null or aliased pointer");
+  if (n < 1) return bad_arg(where, "n_sweeps must be >= 1");
+  if (!(tau > 0)) return bad_arg(where, "tau must be positive");
+  const Grid g = make_grid(B, D, H, W);
+  const Consts k = make_consts(dx, dt, tau);
+  const dim3 grid(blocks_for(g.N), (unsigned)B);
+  for (int s = 0; s < n; ++s) {
+    const float* in = (s & 1) ? hB : hA;
+    float* out = (s & 1) ? hA : hB;
+    if (s == n - 1)
+      k_mag_sweep<DIM, true><<<grid, kThreads, 0, st>>>(in, out, mflags, rhs, psi_out, k, g);
+    else
+      k_mag_sweep<DIM, false><<<grid, kThreads, 0, st>>>(in, out, mflags, rhs, psi_out, k, g);
+  }
+  return check_launch(where);
+}
+
+template <int DIM>
+static int sweeps_scalar_impl(float* aA, float* aB, const uint8_t* mflags, const float* rhs, float* psi_out, int n,
+                              double dx, double dt, int B, int D, int H, int W, cudaStream_t st,
+                              const char* where) {
+  if (!(aA && aB && aA != aB && mflags && rhs && psi_out)) return bad_arg(where, "null or aliased pointer");
+  if (n < 1) return bad_arg(where, "n_sweeps must be >= 1");
+  const Grid g = make_grid(B, D, H, W);
+  const Consts k = make_consts(dx, dt, 1.0);
+  const dim3 grid(blocks_for(g.N), (unsigned)B);
+  for (int s = 0; s < n; ++s) {
+    const float* cur = (s & 1) ? aB : aA;
+    float* prev = (s & 1) ? aA : aB;
+    if (s == n - 1)
+      k_mag_sweep_scalar<DIM, true><<<grid, kThreads, 0, st>>>(cur, prev, mflags, rhs, psi_out, k, g);
+    else
+      k_mag_sweep_scalar<DIM, false><<<grid, kThreads, 0, st>>>(cur, prev, mflags, rhs, psi_out, k, g);
+  }
+  return check_launch(where);
+}
+
+template <int DIM>
+static int source_impl(const float* rho, const uint8_t* mflags, const float* Hx, const float* Hy, const float* Hz,
+                       const lbmff_fluid_params* p, float* rhs, float* chi, int B, int D, int H, int W,
+                       cudaStream_t st, const char* where) {
+  if (!(rho && mflags && Hx && Hy && (DIM == 2 || Hz) && p && rhs)) return bad_arg(where, "null pointer");
+  if (W < 3 || H < 3 || (DIM == 3 && D < 3)) return bad_arg(where, "every extent must be >= 3");
+  const Grid g = make_grid(B, D, H, W);
+  const Consts k = make_consts(p->dx, p->dt, p->tau, p->tau_f, p->tau_g, p->density_liquid, p->density_gas,
+                               p->rho_liquid, p->rho_gas, p->kappa, p->gravity, p->cot_theta);
+  k_mag_source<DIM><<<dim3(blocks_for(g.N), (unsigned)B), kThreads, 0, st>>>(rho, mflags, HextFaces{Hx, Hy, Hz},
+                                                                             rhs, chi, k, g);
+  return check_launch(where);
+}
+
+template <int DIM>
+static int materialize_impl(const float* cur, const float* prev, const float* psi, const float* rhs,
+                            const uint8_t* mflags, float* h, double dx, double dt, int B, int D, int H, int W,
+                            cudaStream_t st, const char* where) {
+  if (!(cur && prev && psi && rhs && mflags && h)) return bad_arg(where, "null pointer");
+  const Grid g = make_grid(B, D, H, W);
+  k_mag_materialize<DIM><<<dim3(blocks_for(g.N), (unsigned)B), kThreads, 0, st>>>(cur, prev, psi, rhs, mflags, h,
+                                                                                  make_consts(dx, dt, 1.0), g);
+  return check_launch(where);
+}
+
+}  // namespace lbmff
+
+using namespace lbmff;
+
+extern "C" {
+
+int lbmff_magnetic_source_2d(const float* rho, const uint8_t* mflags, const float* Hx, const float* Hy,
+                             const lbmff_fluid_params* p, float* rhs_out, float* chi_out, int B, int H, int W,
+                             lbmff_stream_t stream) {
+  return source_impl<2>(rho, mflags, Hx, Hy, nullptr, p, rhs_out, chi_out, B, 1, H, W, (cudaStream_t)stream,
+                        __func__);
+}
+int lbmff_magnetic_source_3d(const float* rho, const uint8_t* mflags, const float* Hx, const float* Hy,
+                             const float* Hz, const lbmff_fluid_params* p, float* rhs_out, float* chi_out, int B,
+                             int D, int H, int W, lbmff_stream_t stream) {
+  return source_impl<3>(rho, mflags, Hx, Hy, Hz, p, rhs_out, chi_out, B, D, H, W, (cudaStream_t)stream, __func__);
+}
+int lbmff_magnetic_sweeps_d2q9(float* hA, float* hB, const uint8_t* mflags, const float* rhs, float* psi_out,
+                               int n_sweeps, double tau, double dx, double dt, int B, int H, int W,
+                               lbmff_stream_t stream) {
+  return sweeps_impl<2>(hA, hB, mflags, rhs, psi_out, n_sweeps, tau, dx, dt, B, 1, H, W, (cudaStream_t)stream,
+                        __func__);
+}
+int lbmff_magnetic_sweeps_d3q19(float* hA, float* hB, const uint8_t* mflags, const float* rhs, float* psi_out,
+                                int n_sweeps, double tau, double dx, double dt, int B, int D, int H, int W,
+                                lbmff_stream_t stream) {
+  return sweeps_impl<3>(hA, hB, mflags, rhs, psi_out, n_sweeps, tau, dx, dt, B, D, H, W, (cudaStream_t)stream,
+                        __func__);
+}
+int lbmff_magnetic_sweeps_scalar_2d(float* aA, float* aB, const uint8_t* mflags, const float* rhs, float* psi_out,
+                                    int n_sweeps, double dx, double dt, int B, int H, int W,
+                                    lbmff_stream_t stream) {
+  return sweeps_scalar_impl<2>(aA, aB, mflags, rhs, psi_out, n_sweeps, dx, dt, B, 1, H, W, (cudaStream_t)stream,
+                               __func__);
+}
+int lbmff_magnetic_sweeps_scalar_3d(float* aA, float* aB, const uint8_t* mflags, const float* rhs, float* psi_out,
+                                    int n_sweeps, double dx, double dt, int B, int D, int H, int W,
+                                    lbmff_stream_t stream) {
+  return sweeps_scalar_impl<3>(aA, aB, mflags, rhs, psi_out, n_sweeps, dx, dt, B, D, H, W, (cudaStream_t)stream,
+                               __func__);
+}
+int lbmff_magnetic_materialize_h_2d(const float* a_cur, const float* a_prev, const float* psi, const float* rhs,
+                                    const uint8_t* mflags, float* h_out, double dx, double dt, int B, int H, int W,
+                                    lbmff_stream_t stream) {
+  return materialize_impl<2>(a_cur, a_prev, psi, rhs, mflags, h_out, dx, dt, B, 1, H, W, (cudaStream_t)stream,
+                             __func__);
+}
+int lbmff_magnetic_materialize_h_3d(const float* a_cur, const float* a_prev, const float* psi, const float* rhs,
+                                    const uint8_t* mflags, float* h_out, double dx, double dt, int B, int D, int H,
+                                    int W, lbmff_stream_t stream) {
+  return materialize_impl<3>(a_cur, a_prev, psi, rhs, mflags, h_out, dx, dt, B, D, H, W, (cudaStream_t)stream,
+                             __func__);
+}
+
+}  // extern "C"

@@ -129,7 +129,9 @@ struct ObstacleClampedField {
   Grid g;
   __device__ __forceinline__ float operator()(int x, int y, int z) const {
     long long i = lin(g, x, y, z);
-    if (flags[i] == LBMFF_OBSTACLE) {
+    // the interior clamp is the identity off the shell, so only shell cells need their flag read
+    const bool shell = x == 0 || x == g.W - 1 || y == 0 || y == g.H - 1 || (g.D > 1 && (z == 0 || z == g.D - 1));
+    if (shell && flags[i] == LBMFF_OBSTACLE) {
       i = lin(g, interior(x, g.W), interior(y, g.H), interior(z, g.D));
     }
     return __ldg(p + i);

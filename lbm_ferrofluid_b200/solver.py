@@ -1,0 +1,285 @@
+"""Fused time-stepping drivers on top of the C ABI's fused tier (include/lbmff.h, second half).
+
+The reference has no solver object: each demo script owns the state tensors and spells the step out
+op by op (demo_3d_LBM_Rosensweig_instability.py:151-209).  ``FerroSolver.step`` executes exactly that
+sequence -- stream f,g / macro / bounce / phi / n_sweeps x (stream h, bounce h, get_H_int) / H2 /
+capillary_process / HCZ collision -- with 9 + n_sweeps kernel launches instead of ~4400, and
+``SinglePhaseSolver.step`` the demo_2d_LBM(_KBC) loop with one launch.  The op-by-op classes in this
+package remain the drop-in API; these drivers are what bench.py times.
+"""
+from __future__ import annotations
+
+import ctypes
+import math
+from typing import Optional, Sequence
+
+import torch
+
+from . import _host as H
+from .collision import LBMCollision2d, LBMCollision3d
+from .grid import get_staggered
+from .macro_compute import LBMMacroCompute2d, LBMMacroCompute3d
+from .types import CellType, KBCType
+
+FLUID, OBSTACLE = int(CellType.FLUID), int(CellType.OBSTACLE)
+
+
+def _res(t):
+    return tuple(t.shape[2:])
+
+
+class FerroSolver:
+    """HCZ two-phase flow (+ optional ferrofluid magnetic subsystem), D2Q9 or D3Q19.
+
+    Parameters mirror the demos: ``flags`` / ``magnetic_flags`` uint8 [B,1,(D,)H,W]; ``H_ext`` either a
+    cell-centred field [B,dim,...] (then its staggered faces are built with get_staggered, as the demos
+    do) or a uniform vector of ``dim`` floats; ``gravity`` the scalar given to set_gravity.
+    ``magnetic_path``: "faithful" (population lattice h, any tau), "scalar" (tau == 1 collapse, walls on
+    the shell only; bit-identical psi) or "auto" (scalar when valid).
+    """
+
+    def __init__(self, flags: torch.Tensor, *, density_liquid=0.2508, density_gas=0.02381, rho_liquid=0.2508,
+                 rho_gas=0.02381, kappa=0.01, tau_f=0.68, tau_g=0.68, tau=1.0, contact_angle=0.5 * math.pi,
+                 gravity=1e-4, dx=1.0, dt=1.0, magnetic_flags: Optional[torch.Tensor] = None,
+                 H_ext=None, n_sweeps: int = 30, KBC_type: Optional[int] = None, magnetic_path: str = "auto",
+                 keep_force: bool = True):
+        self.flags = H.need_cuda(flags, "flags", torch.uint8)
+        self.device = self.flags.device
+        self.dim, self.B, _, self.D, self.Hh, self.W = H.dims(self.flags)
+        self.res = _res(self.flags)
+        self.Q = 9 if self.dim == 2 else 19
+        self.dx, self.dt = float(dx), float(dt)
+        self._density_liquid, self._density_gas = density_liquid, density_gas
+        self._rho_liquid, self._rho_gas = rho_liquid, rho_gas
+        self._kappa, self._tau_f, self._tau_g, self._tau = kappa, tau_f, tau_g, tau
+        self.gravity = float(gravity)
+        self.cot = H.cot_of_contact_angle(contact_angle)
+        self.n_sweeps = int(n_sweeps)
+        self.KBC_type = KBC_type
+        if self.dim == 3 or KBC_type is None:
+            self._kbc_mode = 0
+        else:
+            self._kbc_mode = 1 if KBCType.is_KBC(KBC_type) else 2
+        bad = ((self.flags != FLUID) & (self.flags != OBSTACLE)).any().item()
+        if bad:
+            raise RuntimeError("FerroSolver supports FLUID / OBSTACLE flags only; use the op-by-op API otherwise")
+        self.params = H.fluid_params(self, self.dx, self.dt, cot=self.cot, gravity=self.gravity)
+        self.magnetic = magnetic_flags is not None
+        opts = dict(dtype=torch.float32, device=self.device)
+        sc = lambda c: torch.zeros((self.B, c, *self.res), **opts)  # noqa: E731
+        self.rho, self.pressure, self.vel = sc(1), sc(1), sc(self.dim)
+        self.force = sc(self.dim) if keep_force else None
+        self._ws = sc(3)
+        self._f = [sc(self.Q), sc(self.Q)]
+        self._g = [sc(self.Q), sc(self.Q)]
+        self._cur = 0
+        self.steps_done = 0
+        if self.magnetic:
+            self.mflags = H.need_cuda(magnetic_flags, "magnetic_flags", torch.uint8)
+            if H_ext is None:
+                raise RuntimeError("magnetic_flags given without H_ext")
+            if torch.is_tensor(H_ext):
+                self.H_ext = H.need_cuda(H_ext, "H_ext")
+                self._H_uniform = None
+            else:
+                vec = [float(v) for v in H_ext]
+                if len(vec) != self.dim:
+                    raise RuntimeError(f"uniform H_ext needs {self.dim} components")
+                self._H_uniform = (ctypes.c_double * 3)(*(vec + [0.0] * (3 - self.dim)))
+                self.H_ext = None
+                full = torch.empty((self.B, self.dim, *self.res), **opts)
+                for a, v in enumerate(vec):
+                    full[:, a] = v
+                H_ext = full
+            self.H_ext_mac = get_staggered(H_ext if torch.is_tensor(H_ext) else full, mode="replicate")
+            inner = self.mflags[(slice(None), slice(None)) + (slice(1, -1),) * self.dim]
+            walls_on_shell = not (inner == OBSTACLE).any().item()
+            scalar_ok = float(tau) == 1.0 and walls_on_shell
+            if magnetic_path == "auto":
+                magnetic_path = "scalar" if scalar_ok else "faithful"
+            if magnetic_path == "scalar" and not scalar_ok:
+                raise RuntimeError("magnetic_path='scalar' needs tau == 1 and every OBSTACLE cell of "
+                                   "magnetic_flags on the outer shell")
+            if magnetic_path not in ("scalar", "faithful"):
+                raise ValueError("magnetic_path must be 'auto', 'faithful' or 'scalar'")
+            self.magnetic_path = magnetic_path
+            self.psi, self._rhs, self._chi = sc(1), sc(1), sc(1)
+            if magnetic_path == "faithful":
+                self._h = [sc(self.Q), sc(self.Q)]
+            else:
+                self._a = [sc(2), sc(2)]
+            self._mcur = 0
+        else:
+            self.magnetic_path = None
+            self.mflags = None
+
+    # ---- state ------------------------------------------------------------------------------
+    @property
+    def f(self):
+        return self._f[self._cur]
+
+    @property
+    def g(self):
+        return self._g[self._cur]
+
+    @property
+    def density(self):
+        """density = affine(rho), the map macro_compute / capillary_process apply (HCZ_3d.py:213-215)."""
+        dg, dl, rg, rl = self._density_gas, self._density_liquid, self._rho_gas, self._rho_liquid
+        return dg + (dl - dg) * ((self.rho - rg) / (rl - rg))
+
+    @property
+    def phi(self):
+        """Order parameter the demos render (demo_3d...Rosensweig...py:162)."""
+        dg, dl = self._density_gas, self._density_liquid
+        return -(2.0 * (self.density - dg) / (dl - dg) - 1.0)
+
+    @property
+    def h(self):
+        """Magnetic lattice populations; rebuilt from the scalar state when the scalar path is active."""
+        if not self.magnetic:
+            return None
+        if self.magnetic_path == "faithful":
+            return self._h[self._mcur]
+        out = torch.empty((self.B, self.Q, *self.res), dtype=torch.float32, device=self.device)
+        H.launch(f"lbmff_magnetic_materialize_h_{self.dim}d", self.device, H.ptr(self._a[self._mcur]),
+                 H.ptr(self._a[1 - self._mcur]), H.ptr(self.psi), H.ptr(self._rhs), H.ptr(self.mflags), H.ptr(out),
+                 self.dx, self.dt, *H.sizes(self.dim, self.B, self.D, self.Hh, self.W))
+        return out
+
+    def initialize(self, rho: torch.Tensor, density: Optional[torch.Tensor] = None,
+                   vel: Optional[torch.Tensor] = None):
+        """Initial pressure, f, g from rho / density / vel exactly as the demos do
+        (demo_3d_LBM_Rosensweig_instability.py:128-145): p = EOS(density), f = feq(density, vel),
+        g = geq(rho, vel, density, p, feq = f); h = 0."""
+        rho = H.need_cuda(rho, "rho")
+        density = rho if density is None else H.need_cuda(density, "density")
+        self.rho.copy_(rho)
+        if vel is not None:
+            self.vel.copy_(H.need_cuda(vel, "vel"))
+        else:
+            self.vel.zero_()
+        kw = dict(density_liquid=self._density_liquid, density_gas=self._density_gas, rho_liquid=self._rho_liquid,
+                  rho_gas=self._rho_gas, device=self.device)
+        macro = (LBMMacroCompute2d if self.dim == 2 else LBMMacroCompute3d)(**kw)
+        col = (LBMCollision2d if self.dim == 2 else LBMCollision3d)(tau=1.0, **kw)
+        self.pressure.copy_(macro.get_pressure(dx=self.dx, dt=self.dt, density=density))
+        zero = torch.zeros_like(self.vel)
+        f0 = col.get_feq_(dx=self.dx, dt=self.dt, rho=density, vel=self.vel, force=zero)
+        g0 = col.get_geq_(dx=self.dx, dt=self.dt, rho=self.rho, vel=self.vel, density=density,
+                          pressure=self.pressure, force=zero, feq=f0)
+        self._cur = 0
+        self._f[0].copy_(f0)
+        self._g[0].copy_(g0)
+        if self.magnetic:
+            for t in (self._h if self.magnetic_path == "faithful" else self._a):
+                t.zero_()
+            self.psi.zero_()
+            self._mcur = 0
+        self.steps_done = 0
+        return self
+
+    # ---- stepping ---------------------------------------------------------------------------
+    def _sizes(self):
+        return H.sizes(self.dim, self.B, self.D, self.Hh, self.W)
+
+    def _step_once(self):
+        d, sz, suf = self.dim, self._sizes(), H.suffix(self.dim)
+        cur, nxt = self._cur, 1 - self._cur
+        dev = self.device
+        H.launch("lbmff_hcz_moments_" + suf, dev, H.ptr(self._f[cur]), H.ptr(self.flags), H.ptr(self.rho), *sz)
+        chi = psi = mfl = hext = None
+        hu = None
+        if self.magnetic:
+            H.launch(f"lbmff_magnetic_source_{d}d", dev, H.ptr(self.rho), H.ptr(self.mflags),
+                     *[H.ptr(t) for t in self.H_ext_mac], self.params, H.ptr(self._rhs), H.ptr(self._chi), *sz)
+            m = self._mcur
+            if self.magnetic_path == "faithful":
+                H.launch("lbmff_magnetic_sweeps_" + suf, dev, H.ptr(self._h[m]), H.ptr(self._h[1 - m]),
+                         H.ptr(self.mflags), H.ptr(self._rhs), H.ptr(self.psi), self.n_sweeps, float(self._tau),
+                         self.dx, self.dt, *sz)
+            else:
+                H.launch(f"lbmff_magnetic_sweeps_scalar_{d}d", dev, H.ptr(self._a[m]), H.ptr(self._a[1 - m]),
+                         H.ptr(self.mflags), H.ptr(self._rhs), H.ptr(self.psi), self.n_sweeps, self.dx, self.dt,
+                         *sz)
+            if self.n_sweeps & 1:
+                self._mcur = 1 - m
+            chi, psi, mfl, hext, hu = self._chi, self.psi, self.mflags, self.H_ext, self._H_uniform
+        H.launch(f"lbmff_hcz_capillary_fields_{d}d", dev, H.ptr(self.rho), H.ptr(self.flags),
+                 H.ptr(self.pressure), self.params, H.ptr(self._ws), *sz)
+        args = [H.ptr(self._f[cur]), H.ptr(self._g[cur]), H.ptr(self._f[nxt]), H.ptr(self._g[nxt]),
+                H.ptr(self.rho), H.ptr(self.flags), H.ptr(mfl), H.ptr(self._ws), H.ptr(chi), H.ptr(psi),
+                H.ptr(hext), ctypes.cast(hu, ctypes.c_void_p) if hu is not None else ctypes.c_void_p(0),
+                self.params]
+        if d == 2:
+            args.append(self._kbc_mode)
+        H.launch("lbmff_hcz_collide_stream_" + suf, dev, *args, H.ptr(self.vel), H.ptr(self.pressure),
+                 H.ptr(self.force), *sz)
+        self._cur = nxt
+        self.steps_done += 1
+
+    def step(self, n: int = 1):
+        """Advance n outer steps.  Asynchronous on torch's current stream."""
+        for _ in range(int(n)):
+            self._step_once()
+        return self
+
+    @property
+    def launches_per_step(self) -> int:
+        wet = 5 if self.dim == 3 else 3
+        return 1 + (1 + self.n_sweeps if self.magnetic else 0) + wet + 1 + 1
+
+    def total_mass(self) -> float:
+        """sum over ALL cells (walls included) of sum_q f: conserved to round-off."""
+        return float(self.f.double().sum().item())
+
+
+class SinglePhaseSolver:
+    """Single-phase BGK / KBC flow, D2Q9 or D3Q19: demo_2d_LBM.py / demo_2d_LBM_KBC.py loop in one kernel."""
+
+    def __init__(self, flags: torch.Tensor, *, tau: float, KBC_type: Optional[int] = None, dx=1.0, dt=1.0,
+                 force: Optional[torch.Tensor] = None):
+        self.flags = H.need_cuda(flags, "flags", torch.uint8)
+        self.device = self.flags.device
+        self.dim, self.B, _, self.D, self.Hh, self.W = H.dims(self.flags)
+        self.res = _res(self.flags)
+        self.Q = 9 if self.dim == 2 else 19
+        self.tau, self.dx, self.dt = float(tau), float(dx), float(dt)
+        if KBC_type is not None and self.dim == 3:
+            raise RuntimeError("the reference has no 3-D KBC/MRT collision (simulation_runner.py:107-108)")
+        self._kbc = -1 if KBC_type is None else (1 if KBCType.is_KBC(KBC_type) else 0)
+        self.force = H.need_cuda(force, "force") if force is not None else None
+        opts = dict(dtype=torch.float32, device=self.device)
+        self.rho = torch.zeros((self.B, 1, *self.res), **opts)
+        self.vel = torch.zeros((self.B, self.dim, *self.res), **opts)
+        self._f = [torch.zeros((self.B, self.Q, *self.res), **opts) for _ in range(2)]
+        self._cur = 0
+        self.steps_done = 0
+
+    @property
+    def f(self):
+        return self._f[self._cur]
+
+    def initialize(self, rho: torch.Tensor, vel: torch.Tensor):
+        """f = feq(rho, vel, force = 0) with self.tau (demo_2d_LBM.py:99)."""
+        self.rho.copy_(H.need_cuda(rho, "rho"))
+        self.vel.copy_(H.need_cuda(vel, "vel"))
+        col = (LBMCollision2d if self.dim == 2 else LBMCollision3d)(tau=self.tau, device=self.device)
+        self._cur = 0
+        self._f[0].copy_(col.get_feq_(dx=self.dx, dt=self.dt, rho=self.rho, vel=self.vel,
+                                      force=torch.zeros_like(self.vel)))
+        self.steps_done = 0
+        return self
+
+    def step(self, n: int = 1):
+        sz = H.sizes(self.dim, self.B, self.D, self.Hh, self.W)
+        for _ in range(int(n)):
+            cur, nxt = self._cur, 1 - self._cur
+            args = [H.ptr(self._f[cur]), H.ptr(self._f[nxt]), H.ptr(self.flags), H.ptr(self.force), H.ptr(self.rho),
+                    H.ptr(self.vel), self.tau]
+            if self.dim == 2:
+                args.append(self._kbc)
+            H.launch("lbmff_stream_collide_" + H.suffix(self.dim), self.device, *args, self.dx, self.dt, *sz)
+            self._cur = nxt
+            self.steps_done += 1
+        return self

@@ -60,9 +60,9 @@ def test_pointwise_and_stencils(name):
     assert_close(col.get_feq_(dx=dx, dt=dt, rho=G["rho"], vel=G["vel"], force=G["force"]), G["feq_force"], TOL,
                  "feq force")
     assert_close(col.get_geq_(dx=dx, dt=dt, rho=G["rho"], vel=G["vel"], density=G["density"],
-                              pressure=G["pressure"], force=None), G["geq"], TOL, "geq")
+                              pressure=G["pressure"], force=None), G["geq"], 4 * TOL, "geq")  # p - cs2*density cancels
     assert_close(col.get_geq_(dx=dx, dt=dt, rho=G["rho"], vel=G["vel"], density=G["density"],
-                              pressure=G["pressure"], force=None, feq=G["feq"]), G["geq"], TOL, "geq(feq)")
+                              pressure=G["pressure"], force=None, feq=G["feq"]), G["geq"], 4 * TOL, "geq(feq)")
     assert_close(type(col).get_grad(input_=G["rho"], dx=dx, flags=G["flags_io"]), G["grad_io"], TOL, "grad io")
     assert_close(type(col).get_grad(input_=G["rho"], dx=dx, flags=G["mflags"]), G["grad_open"], TOL, "grad open")
     assert_close(col.get_laplacian(input_=G["rho"], dx=dx, flags=G["flags"]), G["laplacian"], 4 * TOL, "laplacian")
