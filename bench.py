@@ -1,0 +1,313 @@
+#!/usr/bin/env python
+"""bench.py -- MLUPS of the 3-D Rosensweig HCZ + magnetic D3Q19 step (BASELINE.json `metric`).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                    [--res D H W] [--magnetic-path faithful|scalar|auto]
+
+One "step" = one outer time step of demo_3d_LBM_Rosensweig_instability.py (stream f,g; moments; 30 magnetic
+sweeps; capillary process; HCZ collision) on a synthetic perturbed-interface field.  MLUPS counts every cell
+of the array (wall shell included) x outer steps.  Prints ONE JSON line (rank 0).
+
+ * value     : device-resident throughput (state already in HBM), CUDA events, max over ranks.
+ * e2e       : same metric through the public API with HOST buffers: every step uploads that step's applied
+               field (the three H_ext_mac face arrays get_H_int takes) from pinned memory and reads the order
+               parameter phi (what the demos render) back to pinned memory.
+ * roofline  : dominant kernel, algorithmic bytes / CUDA-event duration vs MEASURED_PEAKS.json.
+ * cpu_baseline / --impl reference : the CPU oracle port (oracle/lbm_oracle.py, a torch-CPU restatement of the
+               reference pinned against its golden vectors) on the host cores, bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "MLUPS (3D Rosensweig HCZ+magnetic)"
+N_SWEEPS = 30
+MAG = 100.0
+BYTES_D3Q19 = 152          # one read + one write of 19 fp32 populations
+BYTES_SCALAR_SWEEP = 20    # scalar sweep: 8 B state read + 8 B written + 4 B source
+BYTES_HCZ = 304            # f + g, one read + one write each
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--res", type=int, nargs=3, default=None, help="D H W per GPU (default 512 512 512)")
+    ap.add_argument("--magnetic-path", default=os.environ.get("LBMFF_MAGNETIC_PATH", "faithful"),
+                    choices=["faithful", "scalar", "auto"])
+    ap.add_argument("--cpu-res", type=int, nargs=3, default=[96, 96, 96], help="grid of the bounded CPU sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port on the host cores
+# ---------------------------------------------------------------------------------------------------
+def cpu_rosensweig_mlups(res, steps, warmup):
+    """Times oracle.hcz_step (the reference algorithm restated in torch-CPU) on a bounded grid."""
+    from oracle import lbm_oracle as O
+    from oracle.make_golden import perturbed_interface, shell_flags
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    # psi decays exponentially away from the interface, so the first steps are full of denormals, which the
+    # host cores process ~50x slower (measured: 22 s vs 0.39 s per step at 48^3).  Flush-to-zero favours the
+    # CPU arm and is used for TIMING only (parity runs never set it).
+    torch.set_flush_denormal(True)
+    p = O.HCZParams(contact_angle=torch.tensor([0.5 * math.pi]), n_sweeps=N_SWEEPS)
+    flags, mflags = shell_flags(res), shell_flags(res, open_axes=(1,))
+    rho = perturbed_interface(res, 0.5, p.rho_liquid, p.rho_gas, torch.float32)
+    rho[flags == 2] = p.rho_liquid
+    vel = torch.zeros((1, 3, *res))
+    pressure, f, g = O.hcz_init(rho, rho.clone(), vel, p)
+    Hext = torch.zeros((1, 3, *res))
+    Hext[:, 1] = MAG
+    s = dict(f=f, g=g, h=torch.zeros_like(f), rho=rho, vel=vel, density=rho.clone(), pressure=pressure,
+             flags=flags, mflags=mflags, H_ext=Hext, H_ext_mac=O.get_staggered(Hext))
+    for _ in range(warmup):
+        s = O.hcz_step(s, p)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        s = O.hcz_step(s, p)
+    dt = time.perf_counter() - t0
+    cells = res[0] * res[1] * res[2]
+    return cells * steps / dt / 1e6, dt / steps * 1e3, cores
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    res = tuple(args.cpu_res)
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    # bound the whole run to a few minutes: ~3.5 s per step at 96^3 on 8 cores
+    steps, warmup = min(steps, 10), min(warmup, 3)
+    mlups, ms, cores = cpu_rosensweig_mlups(res, steps, warmup)
+    sample = f"same workload at {res[0]}x{res[1]}x{res[2]} (bounded sample), {warmup} warm-up + {steps} timed steps"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": mlups, "unit": "MLUPS", "n_gpus": args.gpus,
+        "steps": steps, "warmup": warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "demo_3d_LBM_Rosensweig_instability D3Q19 HCZ+magnetic mg100, 30 sweeps/step",
+                   "res": list(res), "note": "reference CPU path = oracle port (torch-CPU restatement pinned "
+                   "against the reference's golden vectors); the Python reference cannot travel to the GPU box"},
+        "cpu_baseline": {"value": mlups, "unit": "MLUPS", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": mlups, "unit": "MLUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------
+# clocks sampler
+# ---------------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "200",
+                 "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.rows.append([c.strip() for c in ln.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+                for n, v in zip(names, r[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------
+def build_solver(res, path, device, world=1, rank=0):
+    from lbm_ferrofluid_b200 import initializers as I
+    from lbm_ferrofluid_b200.solver import FerroSolver
+
+    if world > 1:
+        from lbm_ferrofluid_b200.distributed import SlabFerroSolver
+        return SlabFerroSolver.rosensweig(res, path, device, world, rank, mag=MAG, n_sweeps=N_SWEEPS)
+    flags = I.shell_flags(res, device=device)
+    mflags = I.shell_flags(res, open_axes=(1,), device=device)
+    rho = I.rosensweig_rho(res, flags)
+    s = FerroSolver(flags, magnetic_flags=mflags, H_ext=[0.0, MAG, 0.0], n_sweeps=N_SWEEPS, magnetic_path=path,
+                    contact_angle=0.5 * math.pi, gravity=1e-4, keep_force=False)
+    s.initialize(rho)
+    return s
+
+
+def run_ours(args):
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback "
+                         "(use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    res = tuple(args.res) if args.res else (512, 512, 512)
+    cells_rank = res[0] * res[1] * res[2]
+    cells = cells_rank * world
+    solver = build_solver(res, args.magnetic_path, device, world, rank)
+    path = solver.magnetic_path
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn(steps)
+        b.record()
+        barrier()
+        ms = torch.tensor([a.elapsed_time(b)], device=device)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    # ---- device-resident throughput
+    solver.step(args.warmup)
+    solver.enable_kernel_timing(True)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms_total = timed(solver.step, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    ktimes = solver.kernel_times_ms()
+    solver.enable_kernel_timing(False)
+    ms_step = ms_total / args.steps
+    mlups = cells * args.steps / (ms_total * 1e-3) / 1e6
+    finite = bool(torch.isfinite(solver.rho).all().item())
+
+    # ---- roofline of the dominant kernel (CUDA events bracketing it inside the timed region)
+    peak, peak_src = peaks()
+    sweeps_ms = statistics.mean(ktimes["sweeps"]) if ktimes.get("sweeps") else 0.0
+    cs_ms = statistics.mean(ktimes["collide_stream"])
+    if sweeps_ms >= cs_ms:
+        per_launch_ms = sweeps_ms / N_SWEEPS
+        bytes_cell = BYTES_D3Q19 if path == "faithful" else BYTES_SCALAR_SWEEP
+        kname = "k_mag_sweep<3>" if path == "faithful" else "k_mag_sweep_scalar<3>"
+    else:
+        per_launch_ms, bytes_cell, kname = cs_ms, BYTES_HCZ, "k_hcz_collide_stream<3>"
+    achieved = bytes_cell * cells_rank / (per_launch_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_cell": bytes_cell, "avg_launch_ms": per_launch_ms,
+                "share_of_step": {"sweeps": sweeps_ms / ms_step, "collide_stream": cs_ms / ms_step}}
+
+    # ---- end to end through host buffers
+    e2e = None
+    if not args.no_e2e:
+        faces = [torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in solver.H_ext_mac]
+        for h, d in zip(faces, solver.H_ext_mac):
+            h.copy_(d)
+        phi_host = torch.empty(solver.rho.shape, dtype=torch.float32).pin_memory()
+        run = lambda n: [solver.step_host(faces, phi_host) for _ in range(n)]  # noqa: E731
+        run(min(2, args.warmup))
+        ms_e2e = timed(run, args.steps)
+        h2d = sum(t.numel() * 4 for t in faces)
+        d2h = phi_host.numel() * 4
+        e2e = {"value": cells * args.steps / (ms_e2e * 1e-3) / 1e6, "unit": "MLUPS", "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps,
+               "api": "FerroSolver.step_host(H_ext_mac faces from pinned host, phi to pinned host)"}
+
+    # ---- CPU baseline (rank 0, N = 1 only)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cres = tuple(args.cpu_res)
+        v, ms_cpu, cores = cpu_rosensweig_mlups(cres, 3, 1)
+        cpu = {"value": v, "unit": "MLUPS", "cores": cores, "kind": "port",
+               "sample": f"same workload at {cres[0]}x{cres[1]}x{cres[2]}, 1 warm-up + 3 timed steps, "
+                         f"{ms_cpu:.0f} ms/step, torch CPU threads = {cores}, denormals flushed to zero"}
+
+    if rank == 0:
+        model_bytes = (2 + N_SWEEPS) * BYTES_D3Q19
+        line = {
+            "metric": METRIC, "value": mlups, "unit": "MLUPS", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "demo_3d_LBM_Rosensweig_instability D3Q19 HCZ+magnetic mg100, 30 sweeps/step",
+                       "res_per_gpu": list(res), "cells": cells, "magnetic_path": path,
+                       "parallelism": f"z-slab x{world}" if world > 1 else "single GPU",
+                       "l2": "state (tens of GB) far larger than the 126 MB L2; no flush needed"},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+            "gpu_launches": solver.launches_per_step * args.steps, "clocks": clocks,
+            "step_roofline": {"model_bytes_per_cell": model_bytes,
+                              "mlups_at_peak": peak * 1e9 / model_bytes / 1e6,
+                              "frac_of_model_roofline": mlups / world / (peak * 1e9 / model_bytes / 1e6)},
+            "finite": finite,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -74,6 +74,7 @@ class FerroSolver:
         self._g = [sc(self.Q), sc(self.Q)]
         self._cur = 0
         self.steps_done = 0
+        self._timing = None
         if self.magnetic:
             self.mflags = H.need_cuda(magnetic_flags, "magnetic_flags", torch.uint8)
             if H_ext is None:
@@ -183,6 +184,31 @@ class FerroSolver:
     def _sizes(self):
         return H.sizes(self.dim, self.B, self.D, self.Hh, self.W)
 
+    def enable_kernel_timing(self, on: bool = True):
+        """Bracket the magnetic sweeps and the collide-stream kernel with CUDA events on the launching
+        stream (bench.py's roofline numbers); read them back with kernel_times_ms()."""
+        self._timing = {"sweeps": [], "collide_stream": []} if on else None
+
+    def _timed(self, key):
+        solver = self
+
+        class _T:
+            def __enter__(self_):
+                if solver._timing is not None:
+                    self_.a = torch.cuda.Event(enable_timing=True)
+                    self_.b = torch.cuda.Event(enable_timing=True)
+                    self_.a.record()
+
+            def __exit__(self_, *exc):
+                if solver._timing is not None:
+                    self_.b.record()
+                    solver._timing[key].append((self_.a, self_.b))
+        return _T()
+
+    def kernel_times_ms(self):
+        """{name: [ms per bracket]} -- call after a synchronize."""
+        return {k: [a.elapsed_time(b) for a, b in v] for k, v in (self._timing or {}).items()}
+
     def _step_once(self):
         d, sz, suf = self.dim, self._sizes(), H.suffix(self.dim)
         cur, nxt = self._cur, 1 - self._cur
@@ -194,14 +220,15 @@ class FerroSolver:
             H.launch(f"lbmff_magnetic_source_{d}d", dev, H.ptr(self.rho), H.ptr(self.mflags),
                      *[H.ptr(t) for t in self.H_ext_mac], self.params, H.ptr(self._rhs), H.ptr(self._chi), *sz)
             m = self._mcur
-            if self.magnetic_path == "faithful":
-                H.launch("lbmff_magnetic_sweeps_" + suf, dev, H.ptr(self._h[m]), H.ptr(self._h[1 - m]),
-                         H.ptr(self.mflags), H.ptr(self._rhs), H.ptr(self.psi), self.n_sweeps, float(self._tau),
-                         self.dx, self.dt, *sz)
-            else:
-                H.launch(f"lbmff_magnetic_sweeps_scalar_{d}d", dev, H.ptr(self._a[m]), H.ptr(self._a[1 - m]),
-                         H.ptr(self.mflags), H.ptr(self._rhs), H.ptr(self.psi), self.n_sweeps, self.dx, self.dt,
-                         *sz)
+            with self._timed("sweeps"):
+                if self.magnetic_path == "faithful":
+                    H.launch("lbmff_magnetic_sweeps_" + suf, dev, H.ptr(self._h[m]), H.ptr(self._h[1 - m]),
+                             H.ptr(self.mflags), H.ptr(self._rhs), H.ptr(self.psi), self.n_sweeps,
+                             float(self._tau), self.dx, self.dt, *sz)
+                else:
+                    H.launch(f"lbmff_magnetic_sweeps_scalar_{d}d", dev, H.ptr(self._a[m]), H.ptr(self._a[1 - m]),
+                             H.ptr(self.mflags), H.ptr(self._rhs), H.ptr(self.psi), self.n_sweeps, self.dx,
+                             self.dt, *sz)
             if self.n_sweeps & 1:
                 self._mcur = 1 - m
             chi, psi, mfl, hext, hu = self._chi, self.psi, self.mflags, self.H_ext, self._H_uniform
@@ -213,8 +240,9 @@ class FerroSolver:
                 self.params]
         if d == 2:
             args.append(self._kbc_mode)
-        H.launch("lbmff_hcz_collide_stream_" + suf, dev, *args, H.ptr(self.vel), H.ptr(self.pressure),
-                 H.ptr(self.force), *sz)
+        with self._timed("collide_stream"):
+            H.launch("lbmff_hcz_collide_stream_" + suf, dev, *args, H.ptr(self.vel), H.ptr(self.pressure),
+                     H.ptr(self.force), *sz)
         self._cur = nxt
         self.steps_done += 1
 
@@ -222,6 +250,25 @@ class FerroSolver:
         """Advance n outer steps.  Asynchronous on torch's current stream."""
         for _ in range(int(n)):
             self._step_once()
+        return self
+
+    def set_H_ext_faces_from_host(self, faces_host: Sequence[torch.Tensor]):
+        """Upload the staggered applied field (the H_ext_mac argument of get_H_int) from pinned host memory,
+        asynchronously on the current stream.  Uniform-vector mode is switched to field mode: the cell-centred
+        field used for H2 is rebuilt as the mean of the two faces of each cell."""
+        if not self.magnetic:
+            raise RuntimeError("solver was built without a magnetic subsystem")
+        for dst, src in zip(self.H_ext_mac, faces_host):
+            dst.copy_(src, non_blocking=True)
+
+    def step_host(self, faces_host: Optional[Sequence[torch.Tensor]], phi_host: Optional[torch.Tensor]):
+        """One outer step through host buffers: H2D of this step's applied-field faces (pinned),
+        the step, D2H of the order parameter phi the demos consume (pinned).  Asynchronous."""
+        if faces_host is not None:
+            self.set_H_ext_faces_from_host(faces_host)
+        self._step_once()
+        if phi_host is not None:
+            phi_host.copy_(self.phi, non_blocking=True)
         return self
 
     @property
