@@ -171,20 +171,21 @@ int lbmff_get_H_int_d3q19(const float* phi, const uint8_t* flags, const float* H
  * (pre-stream), rho (shell values persist), pressure, vel, and the magnetic lattice.
  * ===================================================================================== */
 
-/* rho <- sum_q f_q(x - e_q) on non-OBSTACLE cells, in place (propagation + macro_compute). */
-int lbmff_hcz_moments_d2q9(const float* f, const uint8_t* flags, float* rho, int B, int H, int W,
-                           lbmff_stream_t stream);
-int lbmff_hcz_moments_d3q19(const float* f, const uint8_t* flags, float* rho, int B, int D, int H, int W,
-                            lbmff_stream_t stream);
+/* rho <- sum_q f_q(x - e_q) on non-OBSTACLE cells, in place (propagation + macro_compute); when chi_out is
+ * not NULL also chi = 0.33 (1 - H_eps(phi)) on every cell, phi from density(rho) (demo :162,
+ * LBM_magnetic_3d.py:162). */
+int lbmff_hcz_moments_d2q9(const float* f, const uint8_t* flags, float* rho, float* chi_out,
+                           const lbmff_fluid_params* p, int B, int H, int W, lbmff_stream_t stream);
+int lbmff_hcz_moments_d3q19(const float* f, const uint8_t* flags, float* rho, float* chi_out,
+                            const lbmff_fluid_params* p, int B, int D, int H, int W, lbmff_stream_t stream);
 
-/* Sweep-invariant magnetic source rhs (LBM_magnetic_3d.py:161-179) and chi, from rho via
- * density -> phi (demo :162) -> chi.  chi_out may be NULL. */
-int lbmff_magnetic_source_2d(const float* rho, const uint8_t* mflags, const float* Hx, const float* Hy,
-                             const lbmff_fluid_params* p, float* rhs_out, float* chi_out, int B, int H, int W,
+/* Sweep-invariant magnetic source rhs = div(chi_face H_face) dx / (1 + chi) on FLUID cells of mflags, else 0
+ * (LBM_magnetic_3d.py:161-179), from the cell-centred chi. */
+int lbmff_magnetic_source_2d(const float* chi, const uint8_t* mflags, const float* Hx, const float* Hy, double dx,
+                             float* rhs_out, int B, int H, int W, lbmff_stream_t stream);
+int lbmff_magnetic_source_3d(const float* chi, const uint8_t* mflags, const float* Hx, const float* Hy,
+                             const float* Hz, double dx, float* rhs_out, int B, int D, int H, int W,
                              lbmff_stream_t stream);
-int lbmff_magnetic_source_3d(const float* rho, const uint8_t* mflags, const float* Hx, const float* Hy,
-                             const float* Hz, const lbmff_fluid_params* p, float* rhs_out, float* chi_out, int B,
-                             int D, int H, int W, lbmff_stream_t stream);
 
 /* n_sweeps population-faithful sweeps (propagation + rebounce_obstacle + get_H_int collision per sweep,
  * one pass over h each).  Ping-pong hA -> hB -> hA ...: the result is in hA if n_sweeps is even, else hB.
@@ -226,15 +227,17 @@ int lbmff_hcz_capillary_fields_3d(float* rho, const uint8_t* flags, const float*
 /* propagation + rebounce_obstacle of f and g, capillary_process part 2 (forces, vel, pressure) and the
  * HCZ collision, in one pass: reads f_in/g_in (pulled), writes f_out/g_out.  chi/psi/mflags NULL = no
  * magnetic force.  H_ext: cell-centred [B][dim][...] or NULL with H_uniform[dim].  vel, pressure are
- * updated IN PLACE on FLUID cells; force_out may be NULL. */
+ * updated IN PLACE on FLUID cells; force_out may be NULL.  chi and psi get the get_grad shell rule folded in
+ * IN PLACE first (OBSTACLE shell cells of flags / mflags take the nearest interior value, the value
+ * get_grad would read there; those cells are never observed otherwise). */
 int lbmff_hcz_collide_stream_d2q9(const float* f_in, const float* g_in, float* f_out, float* g_out,
                                   const float* rho, const uint8_t* flags, const uint8_t* mflags, const float* ws,
-                                  const float* chi, const float* psi, const float* H_ext, const double* H_uniform,
+                                  float* chi, float* psi, const float* H_ext, const double* H_uniform,
                                   const lbmff_fluid_params* p, int kbc_on_g, float* vel, float* pressure,
                                   float* force_out, int B, int H, int W, lbmff_stream_t stream);
 int lbmff_hcz_collide_stream_d3q19(const float* f_in, const float* g_in, float* f_out, float* g_out,
                                    const float* rho, const uint8_t* flags, const uint8_t* mflags, const float* ws,
-                                   const float* chi, const float* psi, const float* H_ext, const double* H_uniform,
+                                   float* chi, float* psi, const float* H_ext, const double* H_uniform,
                                    const lbmff_fluid_params* p, float* vel, float* pressure, float* force_out,
                                    int B, int D, int H, int W, lbmff_stream_t stream);
 

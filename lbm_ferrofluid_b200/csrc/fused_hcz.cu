@@ -12,39 +12,49 @@
 #include "capi.cuh"
 #include "capillary.cuh"
 #include "collide.cuh"
+#include "hcz_fast.cuh"
 
 namespace lbmff {
 
+// Additive periodic-neighbour offsets: index(x - s e_q) = zo[...] + yo[...] + xo[...]
 template <int DIM>
-struct Nbr {  // periodic neighbour coordinates of a cell
-  int x[3], y[3], z[3];  // index 0: -1, 1: 0, 2: +1
-  __device__ __forceinline__ Nbr(const Cell& c, const Grid& g) {
-    x[0] = wrap(c.x - 1, g.W); x[1] = c.x; x[2] = wrap(c.x + 1, g.W);
-    y[0] = wrap(c.y - 1, g.H); y[1] = c.y; y[2] = wrap(c.y + 1, g.H);
-    z[0] = DIM == 3 ? wrap(c.z - 1, g.D) : 0; z[1] = c.z; z[2] = DIM == 3 ? wrap(c.z + 1, g.D) : 0;
+struct PullIndex {
+  long long zo[3], yo[3];
+  int xo[3];
+  __device__ __forceinline__ PullIndex(const Cell& c, const Grid& g) {
+    const long long HW = (long long)g.H * g.W;
+    xo[0] = wrap(c.x - 1, g.W); xo[1] = c.x; xo[2] = wrap(c.x + 1, g.W);
+    yo[0] = (long long)wrap(c.y - 1, g.H) * g.W; yo[1] = (long long)c.y * g.W; yo[2] = (long long)wrap(c.y + 1, g.H) * g.W;
+    zo[0] = DIM == 3 ? wrap(c.z - 1, g.D) * HW : 0; zo[1] = c.z * HW; zo[2] = DIM == 3 ? wrap(c.z + 1, g.D) * HW : 0;
   }
-  // linear index of x - s*e_q  (s = +1: pull source; s = -1: x + e_q)
-  __device__ __forceinline__ long long at(const Grid& g, int q, int s) const {
+  __device__ __forceinline__ long long at(int q, int s) const {
     using L = Lat<DIM>;
-    return lin(g, x[1 - s * L::ex(q)], y[1 - s * L::ey(q)], z[1 - s * L::ez(q)]);
+    return zo[1 - s * L::ez(q)] + yo[1 - s * L::ey(q)] + xo[1 - s * L::ex(q)];
   }
 };
 
+// rho = sum of the pulled f on non-OBSTACLE cells (old rho kept on OBSTACLE, LBM_macro_compute_3d.py:93-98) and,
+// for the magnetic subsystem, chi = k (1 - H_eps(phi(density(rho)))) on EVERY cell (demo :162, LBM_magnetic_3d.py:162)
 template <int DIM>
 __global__ void __launch_bounds__(kThreads) k_hcz_moments(const float* __restrict__ f,
                                                           const uint8_t* __restrict__ flags, float* __restrict__ rho,
-                                                          Grid g) {
+                                                          float* __restrict__ chi, Consts k, Grid g) {
   using L = Lat<DIM>;
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= g.N) return;
   const long long b = blockIdx.y;
-  if (flags[b * g.N + i] == LBMFF_OBSTACLE) return;  // old rho kept (LBM_macro_compute_3d.py:93-98)
-  const Nbr<DIM> nb(cell_of(i, g), g);
-  const float* fb = f + b * L::Q * g.N;
-  float s = 0.0f;
+  float s;
+  if (flags[b * g.N + i] == LBMFF_OBSTACLE) {
+    s = rho[b * g.N + i];
+  } else {
+    const PullIndex<DIM> nb(cell_of(i, g), g);
+    const float* fb = f + b * L::Q * g.N;
+    s = 0.0f;
 #pragma unroll
-  for (int q = 0; q < L::Q; ++q) s += __ldg(fb + q * g.N + nb.at(g, q, 1));
-  rho[b * g.N + i] = s;
+    for (int q = 0; q < L::Q; ++q) s += __ldg(fb + q * g.N + nb.at(q, 1));
+    rho[b * g.N + i] = s;
+  }
+  if (chi) chi[b * g.N + i] = susceptibility(phase_field(affine_density(s, k.aff), k.aff), k.sm);
 }
 
 struct AffineRho {
@@ -56,9 +66,12 @@ struct AffineRho {
   }
 };
 
-// ws = [lap | fai | prho], N floats each
+// ws = [lap | fai | prho], N floats each, every field with the get_grad shell rule folded into the data:
+// a shell cell holds what it contributes to a gradient stencil (OBSTACLE: nearest interior value; other
+// shell cells: their own value, which is 0 for lap and the replicate-padded interior value for fai / prho).
 template <int DIM>
 __global__ void __launch_bounds__(kThreads) k_hcz_fields(const float* __restrict__ rho,
+                                                         const uint8_t* __restrict__ flags,
                                                          const float* __restrict__ pressure, float* __restrict__ ws,
                                                          Consts k, Grid g) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -67,14 +80,30 @@ __global__ void __launch_bounds__(kThreads) k_hcz_fields(const float* __restrict
   const Cell c = cell_of(i, g);
   const float* r = rho + b * g.N;
   float* w = ws + b * 3 * g.N;
-  const bool shell = c.x == 0 || c.x == g.W - 1 || c.y == 0 || c.y == g.H - 1 ||
-                     (DIM == 3 && (c.z == 0 || c.z == g.D - 1));
-  w[i] = shell ? 0.0f : laplacian_at<DIM>(AffineRho{r, k.aff, g}, c.x, c.y, c.z, k.dx2);
-  const long long j = lin(g, interior(c.x, g.W), interior(c.y, g.H), DIM == 3 ? interior(c.z, g.D) : 0);
+  const int x = interior(c.x, g.W), y = interior(c.y, g.H), z = DIM == 3 ? interior(c.z, g.D) : 0;
+  const long long j = lin(g, x, y, z);
+  const bool shell = on_shell(c, g);
+  float lap = 0.0f;
+  if (!shell || flags[b * g.N + i] == LBMFF_OBSTACLE) lap = laplacian_at<DIM>(AffineRho{r, k.aff, g}, x, y, z, k.dx2);
+  w[i] = lap;
   const float rj = r[j];
   w[g.N + i] = eos_cs(rj, k.cs2, k.a_eos, 1) - rj * k.cs2;
   // density of the previous macro_compute at an interior cell = affine(rho) there (wetting touches the shell only)
   w[2 * g.N + i] = pressure[b * g.N + j] - k.cs2 * affine_density(rj, k.aff);
+}
+
+// psi on OBSTACLE shell cells of mflags <- nearest interior value (what get_grad(psi) reads there);
+// wall-cell psi is never observed otherwise.  Surface kernel: one thread per cell of the six faces.
+template <int DIM>
+__global__ void __launch_bounds__(kThreads) k_shell_rule(float* __restrict__ field,
+                                                         const uint8_t* __restrict__ flags, Grid g) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.N) return;
+  const long long b = blockIdx.y;
+  const Cell c = cell_of(i, g);
+  if (!on_shell(c, g) || flags[b * g.N + i] != LBMFF_OBSTACLE) return;
+  field[b * g.N + i] = field[b * g.N + lin(g, interior(c.x, g.W), interior(c.y, g.H),
+                                           DIM == 3 ? interior(c.z, g.D) : 0)];
 }
 
 struct HextUniform {
@@ -85,26 +114,28 @@ template <int DIM, bool MAGNETIC>
 __global__ void __launch_bounds__(kThreads, 2)
 k_hcz_collide_stream(const float* __restrict__ f_in, const float* __restrict__ g_in, float* __restrict__ f_out,
                      float* __restrict__ g_out, const float* __restrict__ rho_, const uint8_t* __restrict__ flags,
-                     const uint8_t* __restrict__ mflags, const float* __restrict__ ws,
-                     const float* __restrict__ chi, const float* __restrict__ psi, const float* __restrict__ Hext,
-                     HextUniform Hu, float* __restrict__ vel, float* __restrict__ pressure,
-                     float* __restrict__ force_out, Consts k, int kbc_on_g, KbcScalars K, Grid g) {
+                     const float* __restrict__ ws, const float* __restrict__ chi, const float* __restrict__ psi,
+                     const float* __restrict__ Hext, HextUniform Hu, float* __restrict__ vel,
+                     float* __restrict__ pressure, float* __restrict__ force_out, Consts k, int kbc_on_g,
+                     KbcScalars K, Grid g) {
   using L = Lat<DIM>;
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= g.N) return;
   const long long b = blockIdx.y;
   const Cell c = cell_of(i, g);
-  const Nbr<DIM> nb(c, g);
+  const PullIndex<DIM> nb(c, g);
   const float* fi = f_in + b * L::Q * g.N;
   const float* gi = g_in + b * L::Q * g.N;
   float* fo = f_out + b * L::Q * g.N;
   float* go = g_out + b * L::Q * g.N;
   const uint8_t fl = flags[b * g.N + i];
-  if (fl == LBMFF_OBSTACLE) {
-    // stream then full-way bounce: out_q(x) = in_opp(q)(x + e_q); walls never collide
+  if (fl != LBMFF_FLUID) {
+    // OBSTACLE: stream then full-way bounce, out_q(x) = in_opp(q)(x + e_q).  Other non-FLUID cells are only
+    // streamed (HCZ collides FLUID cells only, HCZ_3d.py:357-359).  Neither collides.
+    const bool obst = fl == LBMFF_OBSTACLE;
 #pragma unroll
     for (int q = 0; q < L::Q; ++q) {
-      const long long j = L::opp(q) * g.N + nb.at(g, q, -1);
+      const long long j = obst ? L::opp(q) * g.N + nb.at(q, -1) : q * g.N + nb.at(q, 1);
       fo[q * g.N + i] = __ldg(fi + j);
       go[q * g.N + i] = __ldg(gi + j);
     }
@@ -112,23 +143,17 @@ k_hcz_collide_stream(const float* __restrict__ f_in, const float* __restrict__ g
   }
   float gv[L::Q];
 #pragma unroll
-  for (int q = 0; q < L::Q; ++q) gv[q] = __ldg(gi + q * g.N + nb.at(g, q, 1));
-  if (fl != LBMFF_FLUID) {  // streamed only (HCZ collides FLUID cells only, HCZ_3d.py:357-359)
-#pragma unroll
-    for (int q = 0; q < L::Q; ++q) {
-      go[q * g.N + i] = gv[q];
-      fo[q * g.N + i] = __ldg(fi + q * g.N + nb.at(g, q, 1));
-    }
-    return;
-  }
-  // ---- capillary_process part 2 at a FLUID cell (HCZ_3d.py:217-261)
-  const uint8_t* flb = flags + b * g.N;
-  const float* w = ws + b * 3 * g.N;
+  for (int q = 0; q < L::Q; ++q) gv[q] = __ldg(gi + q * g.N + nb.at(q, 1));
+  // ---- capillary_process part 2 at a FLUID cell (HCZ_3d.py:217-261); all stencil inputs carry the
+  // get_grad shell rule in their data, so the 18-point stencils are plain constant-offset loads
   const int x = interior(c.x, g.W), y = interior(c.y, g.H), z = DIM == 3 ? interior(c.z, g.D) : 0;
+  const long long j0 = lin(g, x, y, z);
+  const long long HW = (long long)g.H * g.W;
+  const float* w = ws + b * 3 * g.N + j0;
   float glap[3], gfai[3], gprho[3];
-  grad_at<DIM>(ObstacleClampedField{w, flb, g}, x, y, z, k.dx, glap);
-  grad_at<DIM>(ObstacleClampedField{w + g.N, flb, g}, x, y, z, k.dx, gfai);
-  grad_at<DIM>(ObstacleClampedField{w + 2 * g.N, flb, g}, x, y, z, k.dx, gprho);
+  grad_at_fast<DIM>(CentredField{w, g.W, HW, x, y, z}, x, y, z, k.inv12dx, glap);
+  grad_at_fast<DIM>(CentredField{w + g.N, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gfai);
+  grad_at_fast<DIM>(CentredField{w + 2 * g.N, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gprho);
   const float rho = rho_[b * g.N + i];
   const float dn = affine_density(rho, k.aff);
   float F[DIM];
@@ -139,12 +164,12 @@ k_hcz_collide_stream(const float* __restrict__ f_in, const float* __restrict__ g
   }
   if (MAGNETIC) {
     float gchi[3], gpsi[3], H2 = 0.0f;
-    grad_at<DIM>(ObstacleClampedField{chi + b * g.N, flb, g}, x, y, z, k.dx, gchi);
-    grad_at<DIM>(ObstacleClampedField{psi + b * g.N, mflags + b * g.N, g}, x, y, z, k.dx, gpsi);
+    grad_at_fast<DIM>(CentredField{chi + b * g.N + j0, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gchi);
+    grad_at_fast<DIM>(CentredField{psi + b * g.N + j0, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gpsi);
 #pragma unroll
     for (int a = 0; a < DIM; ++a) {
       const float he = Hext ? __ldg(Hext + (b * DIM + a) * g.N + i) : Hu.v[a];
-      const float ht = he + (-gpsi[a]);  // H_ext + H_int, H_int = -grad(psi) (LBM_magnetic_3d.py:184)
+      const float ht = he - gpsi[a];  // H_ext + H_int, H_int = -grad(psi) (LBM_magnetic_3d.py:184)
       H2 += ht * ht;
     }
 #pragma unroll
@@ -154,29 +179,42 @@ k_hcz_collide_stream(const float* __restrict__ f_in, const float* __restrict__ g
 #pragma unroll
   for (int q = 0; q < L::Q; ++q) {
     s += gv[q];
-    if (L::ex(q) != 0) m[0] += gv[q] * (float)L::ex(q);
-    if (L::ey(q) != 0) m[1] += gv[q] * (float)L::ey(q);
-    if (DIM == 3 && L::ez(q) != 0) m[2] += gv[q] * (float)L::ez(q);
+    if (L::ex(q) == 1) m[0] += gv[q]; else if (L::ex(q) == -1) m[0] -= gv[q];
+    if (L::ey(q) == 1) m[1] += gv[q]; else if (L::ey(q) == -1) m[1] -= gv[q];
+    if (DIM == 3) { if (L::ez(q) == 1) m[2] += gv[q]; else if (L::ez(q) == -1) m[2] -= gv[q]; }
   }
   float u[DIM], dot = 0.f;
+  const float inv_dn = k.vel_scale / dn;  // 1 / (cs2 density)
 #pragma unroll
   for (int a = 0; a < DIM; ++a) {
-    u[a] = (m[a] * k.c + k.half_dt_RT * F[a]) / k.cs2 / dn;
+    u[a] = (m[a] * k.c + k.half_dt_RT * F[a]) * inv_dn;
     vel[(b * DIM + a) * g.N + i] = u[a];
     if (force_out) force_out[(b * DIM + a) * g.N + i] = F[a];
     dot += u[a] * gprho[a];
   }
   const float p = s - k.half_dt * dot;
   pressure[b * g.N + i] = p;
-  // ---- HCZ collision (HCZ_3d.py:283-361), f loaded only now to keep register pressure down
-  float fv[L::Q];
+  // ---- HCZ collision (HCZ_3d.py:283-361); f is pulled one population at a time to keep registers low
+  const HczCell<DIM> C = hcz_prepare<DIM>(rho, u, dn, p, F, gfai, gprho, k);
+  bool relaxed = false;
+  if constexpr (DIM == 2) {
+    if (kbc_on_g) {  // entropic KBC relaxation of g (HCZ_2d.py:244-256)
+      float geq[9], gk[9];
 #pragma unroll
-  for (int q = 0; q < L::Q; ++q) fv[q] = __ldg(fi + q * g.N + nb.at(g, q, 1));
-  hcz_collide_cell<DIM>(fv, gv, rho, u, dn, p, F, gfai, gprho, k, kbc_on_g, K);
+      for (int q = 0; q < 9; ++q) geq[q] = hcz_geq_q<2>(q, C);
+      kbc_relax(gv, geq, rho, u, k.c, kbc_on_g == 1 ? 1 : 0, K, gk);
+#pragma unroll
+      for (int q = 0; q < 9; ++q) gv[q] = gk[q];
+      relaxed = true;
+    }
+  }
 #pragma unroll
   for (int q = 0; q < L::Q; ++q) {
-    fo[q * g.N + i] = fv[q];
-    go[q * g.N + i] = gv[q];
+    float fq = __ldg(fi + q * g.N + nb.at(q, 1));
+    float gq = gv[q];
+    hcz_collide_q<DIM>(q, C, k, fq, gq, relaxed);
+    fo[q * g.N + i] = fq;
+    go[q * g.N + i] = gq;
   }
 }
 
@@ -192,18 +230,18 @@ __global__ void __launch_bounds__(kThreads) k_stream_collide(const float* __rest
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= g.N) return;
   const long long b = blockIdx.y;
-  const Nbr<DIM> nb(cell_of(i, g), g);
+  const PullIndex<DIM> nb(cell_of(i, g), g);
   const float* fi = f_in + b * L::Q * g.N;
   float* fo = f_out + b * L::Q * g.N;
   if (flags[b * g.N + i] == LBMFF_OBSTACLE) {
 #pragma unroll
-    for (int q = 0; q < L::Q; ++q) fo[q * g.N + i] = __ldg(fi + L::opp(q) * g.N + nb.at(g, q, -1));
+    for (int q = 0; q < L::Q; ++q) fo[q * g.N + i] = __ldg(fi + L::opp(q) * g.N + nb.at(q, -1));
     return;  // rho, vel keep their old values on OBSTACLE cells
   }
   float fv[L::Q], s = 0.f, m[3] = {0.f, 0.f, 0.f};
 #pragma unroll
   for (int q = 0; q < L::Q; ++q) {
-    fv[q] = __ldg(fi + q * g.N + nb.at(g, q, 1));
+    fv[q] = __ldg(fi + q * g.N + nb.at(q, 1));
     s += fv[q];
     if (L::ex(q) != 0) m[0] += fv[q] * (float)L::ex(q);
     if (L::ey(q) != 0) m[1] += fv[q] * (float)L::ey(q);
@@ -238,11 +276,11 @@ static Consts consts_of(const lbmff_fluid_params* p) {
 }
 
 template <int DIM>
-static int moments_impl(const float* f, const uint8_t* flags, float* rho, int B, int D, int H, int W,
-                        cudaStream_t st, const char* where) {
-  if (!(f && flags && rho)) return bad_arg(where, "null pointer");
+static int moments_impl(const float* f, const uint8_t* flags, float* rho, float* chi, const lbmff_fluid_params* p,
+                        int B, int D, int H, int W, cudaStream_t st, const char* where) {
+  if (!(f && flags && rho && p)) return bad_arg(where, "null pointer");
   const Grid g = make_grid(B, D, H, W);
-  k_hcz_moments<DIM><<<dim3(blocks_for(g.N), (unsigned)B), kThreads, 0, st>>>(f, flags, rho, g);
+  k_hcz_moments<DIM><<<dim3(blocks_for(g.N), (unsigned)B), kThreads, 0, st>>>(f, flags, rho, chi, consts_of(p), g);
   return check_launch(where);
 }
 
@@ -254,14 +292,14 @@ static int fields_impl(float* rho, const uint8_t* flags, const float* pressure, 
   const Grid g = make_grid(B, D, H, W);
   const Consts k = consts_of(p);
   launch_wetting<DIM>(rho, flags, k.cot, g, st);
-  k_hcz_fields<DIM><<<dim3(blocks_for(g.N), (unsigned)B), kThreads, 0, st>>>(rho, pressure, ws, k, g);
+  k_hcz_fields<DIM><<<dim3(blocks_for(g.N), (unsigned)B), kThreads, 0, st>>>(rho, flags, pressure, ws, k, g);
   return check_launch(where);
 }
 
 template <int DIM>
 static int collide_stream_impl(const float* f_in, const float* g_in, float* f_out, float* g_out, const float* rho,
-                               const uint8_t* flags, const uint8_t* mflags, const float* ws, const float* chi,
-                               const float* psi, const float* Hext, const double* Hu, const lbmff_fluid_params* p,
+                               const uint8_t* flags, const uint8_t* mflags, const float* ws, float* chi,
+                               float* psi, const float* Hext, const double* Hu, const lbmff_fluid_params* p,
                                int kbc_on_g, float* vel, float* pressure, float* force_out, int B, int D, int H,
                                int W, cudaStream_t st, const char* where) {
   if (!(f_in && g_in && f_out && g_out && rho && flags && ws && p && vel && pressure))
@@ -274,14 +312,17 @@ static int collide_stream_impl(const float* f_in, const float* g_in, float* f_ou
   HextUniform hu{{0.f, 0.f, 0.f}};
   if (Hu) for (int a = 0; a < DIM; ++a) hu.v[a] = (float)Hu[a];
   const dim3 grid(blocks_for(g.N), (unsigned)B);
-  if (magnetic)
-    k_hcz_collide_stream<DIM, true><<<grid, kThreads, 0, st>>>(f_in, g_in, f_out, g_out, rho, flags, mflags, ws, chi,
-                                                               psi, Hext, hu, vel, pressure, force_out, k, kbc_on_g,
+  if (magnetic) {
+    k_shell_rule<DIM><<<grid, kThreads, 0, st>>>(psi, mflags, g);
+    k_shell_rule<DIM><<<grid, kThreads, 0, st>>>(chi, flags, g);
+    k_hcz_collide_stream<DIM, true><<<grid, kThreads, 0, st>>>(f_in, g_in, f_out, g_out, rho, flags, ws, chi, psi,
+                                                               Hext, hu, vel, pressure, force_out, k, kbc_on_g,
                                                                make_kbc(p->tau_g), g);
-  else
-    k_hcz_collide_stream<DIM, false><<<grid, kThreads, 0, st>>>(f_in, g_in, f_out, g_out, rho, flags, mflags, ws,
-                                                                chi, psi, Hext, hu, vel, pressure, force_out, k,
-                                                                kbc_on_g, make_kbc(p->tau_g), g);
+  } else {
+    k_hcz_collide_stream<DIM, false><<<grid, kThreads, 0, st>>>(f_in, g_in, f_out, g_out, rho, flags, ws, chi, psi,
+                                                                Hext, hu, vel, pressure, force_out, k, kbc_on_g,
+                                                                make_kbc(p->tau_g), g);
+  }
   return check_launch(where);
 }
 
@@ -311,13 +352,13 @@ using namespace lbmff;
 
 extern "C" {
 
-int lbmff_hcz_moments_d2q9(const float* f, const uint8_t* flags, float* rho, int B, int H, int W,
-                           lbmff_stream_t stream) {
-  return moments_impl<2>(f, flags, rho, B, 1, H, W, (cudaStream_t)stream, __func__);
+int lbmff_hcz_moments_d2q9(const float* f, const uint8_t* flags, float* rho, float* chi_out,
+                           const lbmff_fluid_params* p, int B, int H, int W, lbmff_stream_t stream) {
+  return moments_impl<2>(f, flags, rho, chi_out, p, B, 1, H, W, (cudaStream_t)stream, __func__);
 }
-int lbmff_hcz_moments_d3q19(const float* f, const uint8_t* flags, float* rho, int B, int D, int H, int W,
-                            lbmff_stream_t stream) {
-  return moments_impl<3>(f, flags, rho, B, D, H, W, (cudaStream_t)stream, __func__);
+int lbmff_hcz_moments_d3q19(const float* f, const uint8_t* flags, float* rho, float* chi_out,
+                            const lbmff_fluid_params* p, int B, int D, int H, int W, lbmff_stream_t stream) {
+  return moments_impl<3>(f, flags, rho, chi_out, p, B, D, H, W, (cudaStream_t)stream, __func__);
 }
 int lbmff_hcz_capillary_fields_2d(float* rho, const uint8_t* flags, const float* pressure,
                                   const lbmff_fluid_params* p, float* ws, int B, int H, int W,
@@ -331,7 +372,7 @@ int lbmff_hcz_capillary_fields_3d(float* rho, const uint8_t* flags, const float*
 }
 int lbmff_hcz_collide_stream_d2q9(const float* f_in, const float* g_in, float* f_out, float* g_out,
                                   const float* rho, const uint8_t* flags, const uint8_t* mflags, const float* ws,
-                                  const float* chi, const float* psi, const float* H_ext, const double* H_uniform,
+                                  float* chi, float* psi, const float* H_ext, const double* H_uniform,
                                   const lbmff_fluid_params* p, int kbc_on_g, float* vel, float* pressure,
                                   float* force_out, int B, int H, int W, lbmff_stream_t stream) {
   return collide_stream_impl<2>(f_in, g_in, f_out, g_out, rho, flags, mflags, ws, chi, psi, H_ext, H_uniform, p,
@@ -339,7 +380,7 @@ int lbmff_hcz_collide_stream_d2q9(const float* f_in, const float* g_in, float* f
 }
 int lbmff_hcz_collide_stream_d3q19(const float* f_in, const float* g_in, float* f_out, float* g_out,
                                    const float* rho, const uint8_t* flags, const uint8_t* mflags, const float* ws,
-                                   const float* chi, const float* psi, const float* H_ext, const double* H_uniform,
+                                   float* chi, float* psi, const float* H_ext, const double* H_uniform,
                                    const lbmff_fluid_params* p, float* vel, float* pressure, float* force_out,
                                    int B, int D, int H, int W, lbmff_stream_t stream) {
   return collide_stream_impl<3>(f_in, g_in, f_out, g_out, rho, flags, mflags, ws, chi, psi, H_ext, H_uniform, p, 0,

@@ -13,35 +13,30 @@
 
 namespace lbmff {
 
-struct ChiOfRho {
-  const float* __restrict__ rho;
-  Affine A;
-  Smooth sm;
+struct ChiArray {
+  const float* __restrict__ chi;
   Grid g;
-  __device__ __forceinline__ float operator()(int x, int y, int z) const {
-    return susceptibility(phase_field(affine_density(__ldg(rho + lin(g, x, y, z)), A), A), sm);
-  }
+  __device__ __forceinline__ float operator()(int x, int y, int z) const { return __ldg(chi + lin(g, x, y, z)); }
 };
 
-// rhs (FLUID cells of mflags, else 0) and chi, from rho via density -> phi -> chi
+// rhs (FLUID cells of mflags, else 0) from the cell-centred susceptibility chi (raw, no shell rule)
 template <int DIM>
-__global__ void __launch_bounds__(kThreads) k_mag_source(const float* __restrict__ rho,
+__global__ void __launch_bounds__(kThreads) k_mag_source(const float* __restrict__ chi,
                                                          const uint8_t* __restrict__ mflags, HextFaces Hf,
-                                                         float* __restrict__ rhs, float* __restrict__ chi_out,
-                                                         Consts k, Grid g) {
+                                                         float* __restrict__ rhs, float dx, Grid g) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= g.N) return;
   const long long b = blockIdx.y;
-  const Cell c = cell_of(i, g);
-  ChiOfRho chi{rho + b * g.N, k.aff, k.sm, g};
-  HextFaces Hb = Hf;
-  Hb.x += b * (long long)g.D * g.H * (g.W + 1);
-  Hb.y += b * (long long)g.D * (g.H + 1) * g.W;
-  if (DIM == 3) Hb.z += b * (long long)(g.D + 1) * g.H * g.W;
   float r = 0.0f;
-  if (mflags[b * g.N + i] == LBMFF_FLUID) r = magnetic_rhs_at<DIM>(chi, Hb, c.x, c.y, c.z, g, k.dx);
+  if (mflags[b * g.N + i] == LBMFF_FLUID) {
+    const Cell c = cell_of(i, g);
+    HextFaces Hb = Hf;
+    Hb.x += b * (long long)g.D * g.H * (g.W + 1);
+    Hb.y += b * (long long)g.D * (g.H + 1) * g.W;
+    if (DIM == 3) Hb.z += b * (long long)(g.D + 1) * g.H * g.W;
+    r = magnetic_rhs_at<DIM>(ChiArray{chi + b * g.N, g}, Hb, c.x, c.y, c.z, g, dx);
+  }
   rhs[b * g.N + i] = r;
-  if (chi_out) chi_out[b * g.N + i] = chi(c.x, c.y, c.z);
 }
 
 // ---- population-faithful fused sweep ----------------------------------------------------------
@@ -235,16 +230,13 @@ static int sweeps_scalar_impl(float* aA, float* aB, const uint8_t* mflags, const
 }
 
 template <int DIM>
-static int source_impl(const float* rho, const uint8_t* mflags, const float* Hx, const float* Hy, const float* Hz,
-                       const lbmff_fluid_params* p, float* rhs, float* chi, int B, int D, int H, int W,
-                       cudaStream_t st, const char* where) {
-  if (!(rho && mflags && Hx && Hy && (DIM == 2 || Hz) && p && rhs)) return bad_arg(where, "null pointer");
+static int source_impl(const float* chi, const uint8_t* mflags, const float* Hx, const float* Hy, const float* Hz,
+                       double dx, float* rhs, int B, int D, int H, int W, cudaStream_t st, const char* where) {
+  if (!(chi && mflags && Hx && Hy && (DIM == 2 || Hz) && rhs)) return bad_arg(where, "null pointer");
   if (W < 3 || H < 3 || (DIM == 3 && D < 3)) return bad_arg(where, "every extent must be >= 3");
   const Grid g = make_grid(B, D, H, W);
-  const Consts k = make_consts(p->dx, p->dt, p->tau, p->tau_f, p->tau_g, p->density_liquid, p->density_gas,
-                               p->rho_liquid, p->rho_gas, p->kappa, p->gravity, p->cot_theta);
-  k_mag_source<DIM><<<dim3(blocks_for(g.N), (unsigned)B), kThreads, 0, st>>>(rho, mflags, HextFaces{Hx, Hy, Hz},
-                                                                             rhs, chi, k, g);
+  k_mag_source<DIM><<<dim3(blocks_for(g.N), (unsigned)B), kThreads, 0, st>>>(chi, mflags, HextFaces{Hx, Hy, Hz},
+                                                                             rhs, (float)dx, g);
   return check_launch(where);
 }
 
@@ -265,16 +257,14 @@ using namespace lbmff;
 
 extern "C" {
 
-int lbmff_magnetic_source_2d(const float* rho, const uint8_t* mflags, const float* Hx, const float* Hy,
-                             const lbmff_fluid_params* p, float* rhs_out, float* chi_out, int B, int H, int W,
-                             lbmff_stream_t stream) {
-  return source_impl<2>(rho, mflags, Hx, Hy, nullptr, p, rhs_out, chi_out, B, 1, H, W, (cudaStream_t)stream,
-                        __func__);
+int lbmff_magnetic_source_2d(const float* chi, const uint8_t* mflags, const float* Hx, const float* Hy, double dx,
+                             float* rhs_out, int B, int H, int W, lbmff_stream_t stream) {
+  return source_impl<2>(chi, mflags, Hx, Hy, nullptr, dx, rhs_out, B, 1, H, W, (cudaStream_t)stream, __func__);
 }
-int lbmff_magnetic_source_3d(const float* rho, const uint8_t* mflags, const float* Hx, const float* Hy,
-                             const float* Hz, const lbmff_fluid_params* p, float* rhs_out, float* chi_out, int B,
-                             int D, int H, int W, lbmff_stream_t stream) {
-  return source_impl<3>(rho, mflags, Hx, Hy, Hz, p, rhs_out, chi_out, B, D, H, W, (cudaStream_t)stream, __func__);
+int lbmff_magnetic_source_3d(const float* chi, const uint8_t* mflags, const float* Hx, const float* Hy,
+                             const float* Hz, double dx, float* rhs_out, int B, int D, int H, int W,
+                             lbmff_stream_t stream) {
+  return source_impl<3>(chi, mflags, Hx, Hy, Hz, dx, rhs_out, B, D, H, W, (cudaStream_t)stream, __func__);
 }
 int lbmff_magnetic_sweeps_d2q9(float* hA, float* hB, const uint8_t* mflags, const float* rhs, float* psi_out,
                                int n_sweeps, double tau, double dx, double dt, int B, int H, int W,

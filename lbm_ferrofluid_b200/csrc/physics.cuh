@@ -138,6 +138,25 @@ struct ObstacleClampedField {
   }
 };
 
+
+// Field sampled at constant offsets from a centre index whose 18 neighbours are all inside the array
+// (centre clamped to the interior): no wrap, no flag test, address = centre + immediate-like offsets.
+struct CentredField {
+  const float* __restrict__ p;  // already offset to the centre cell
+  int W;
+  long long HW;
+  int cx, cy, cz;               // centre coordinates, so grad_at / laplacian_at can pass absolute ones
+  __device__ __forceinline__ float operator()(int x, int y, int z) const {
+    return __ldg(p + (x - cx) + (long long)(y - cy) * W + (long long)(z - cz) * HW);
+  }
+};
+
+// The get_grad shell rule folded into the DATA: value a shell cell contributes to a gradient stencil.
+// OBSTACLE shell cells contribute the value of the nearest interior cell (LBM_collision_3d.py:217-218).
+__device__ __forceinline__ bool on_shell(const Cell& c, const Grid& g) {
+  return c.x == 0 || c.x == g.W - 1 || c.y == 0 || c.y == g.H - 1 || (g.D > 1 && (c.z == 0 || c.z == g.D - 1));
+}
+
 // Isotropic central gradient at an INTERIOR cell (LBM_collision_3d.py:224-275,
 // LBM_collision_2d.py:197-223): (k*axis + diagonals) / 12 / dx, k = 2 (3-D), 4 (2-D).
 template <int DIM, class Field>
@@ -164,6 +183,31 @@ __device__ __forceinline__ void grad_at(const Field& X, int x, int y, int z, flo
     const float pm = X(x + 1, y - 1, z), mp = X(x - 1, y + 1, z);
     out[0] = (k * (xp - xm) + (pp - mm + pm - mp)) / 12.0f / dx;
     out[1] = (k * (yp - ym) + (pp - mm + mp - pm)) / 12.0f / dx;
+  }
+}
+
+
+// Same stencil as grad_at with the two divisions replaced by one multiplication by inv12dx = 1/(12 dx)
+// (host-formed in double).  Used by the fused kernels; differs from grad_at by fp32 rounding only.
+template <int DIM, class Field>
+__device__ __forceinline__ void grad_at_fast(const Field& X, int x, int y, int z, float inv12dx, float* out) {
+  const float k = Lat<DIM>::grad_axis_w();
+  if (DIM == 3) {
+    const float xp = X(x + 1, y, z), xm = X(x - 1, y, z);
+    const float yp = X(x, y + 1, z), ym = X(x, y - 1, z);
+    const float zp = X(x, y, z + 1), zm = X(x, y, z - 1);
+    const float dxy = X(x + 1, y + 1, z) - X(x - 1, y - 1, z), sxy = X(x + 1, y - 1, z) - X(x - 1, y + 1, z);
+    const float dxz = X(x + 1, y, z + 1) - X(x - 1, y, z - 1), sxz = X(x + 1, y, z - 1) - X(x - 1, y, z + 1);
+    const float dyz = X(x, y + 1, z + 1) - X(x, y - 1, z - 1), syz = X(x, y + 1, z - 1) - X(x, y - 1, z + 1);
+    out[0] = (k * (xp - xm) + (dxz + sxz + dxy + sxy)) * inv12dx;
+    out[1] = (k * (yp - ym) + (dyz + syz + dxy - sxy)) * inv12dx;
+    out[2] = (k * (zp - zm) + (dyz - syz + dxz - sxz)) * inv12dx;
+  } else {
+    const float xp = X(x + 1, y, z), xm = X(x - 1, y, z);
+    const float yp = X(x, y + 1, z), ym = X(x, y - 1, z);
+    const float d = X(x + 1, y + 1, z) - X(x - 1, y - 1, z), s = X(x + 1, y - 1, z) - X(x - 1, y + 1, z);
+    out[0] = (k * (xp - xm) + (d + s)) * inv12dx;
+    out[1] = (k * (yp - ym) + (d - s)) * inv12dx;
   }
 }
 
@@ -205,6 +249,12 @@ struct Consts {
   float grav_y;      // -gravity                  LBM_collision_3d.py:124-131
   float cot;         // tan(pi/2 - contact_angle) HCZ_3d.py:97
   float mag_src;     // cs2 (0.5 - tau) dt        LBM_magnetic_3d.py:180
+  // combined constants of the fused (speed-ordered) collision, formed in double
+  float inv_cs2;     // 1 / cs2
+  float c_f;         // dt (1 - 0.5/tau_f) dt / cs2
+  float c_g;         // (1 - 0.5/tau_g) dt
+  float vel_scale;   // 1 / cs2 (velocity from g-moments)
+  float inv12dx;     // 1 / (12 dx)
 };
 
 inline Consts make_consts(double dx, double dt, double tau = 1.0, double tau_f = 1.0, double tau_g = 1.0,
@@ -225,6 +275,11 @@ inline Consts make_consts(double dx, double dt, double tau = 1.0, double tau_f =
   k.kelvin = (float)(-0.5 * (4 * 3.141592653589793 * 1e-7));
   k.grav_y = -(float)gravity; k.cot = (float)cot;
   k.mag_src = (float)(cs2 * (0.5 - tau) * dt);
+  k.inv_cs2 = (float)(1.0 / cs2);
+  k.c_f = (float)(dt * (1.0 - 0.5 / tau_f) * dt / cs2);
+  k.c_g = (float)((1.0 - 0.5 / tau_g) * dt);
+  k.vel_scale = (float)(1.0 / cs2);
+  k.inv12dx = (float)(1.0 / (12.0 * dx));
   return k;
 }
 

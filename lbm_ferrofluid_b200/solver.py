@@ -213,12 +213,13 @@ class FerroSolver:
         d, sz, suf = self.dim, self._sizes(), H.suffix(self.dim)
         cur, nxt = self._cur, 1 - self._cur
         dev = self.device
-        H.launch("lbmff_hcz_moments_" + suf, dev, H.ptr(self._f[cur]), H.ptr(self.flags), H.ptr(self.rho), *sz)
+        H.launch("lbmff_hcz_moments_" + suf, dev, H.ptr(self._f[cur]), H.ptr(self.flags), H.ptr(self.rho),
+                 H.ptr(self._chi if self.magnetic else None), self.params, *sz)
         chi = psi = mfl = hext = None
         hu = None
         if self.magnetic:
-            H.launch(f"lbmff_magnetic_source_{d}d", dev, H.ptr(self.rho), H.ptr(self.mflags),
-                     *[H.ptr(t) for t in self.H_ext_mac], self.params, H.ptr(self._rhs), H.ptr(self._chi), *sz)
+            H.launch(f"lbmff_magnetic_source_{d}d", dev, H.ptr(self._chi), H.ptr(self.mflags),
+                     *[H.ptr(t) for t in self.H_ext_mac], self.dx, H.ptr(self._rhs), *sz)
             m = self._mcur
             with self._timed("sweeps"):
                 if self.magnetic_path == "faithful":
