@@ -260,7 +260,7 @@ def run_ours(args):
         faces = [torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in solver.H_ext_mac]
         for h, d in zip(faces, solver.H_ext_mac):
             h.copy_(d)
-        phi_host = torch.empty(solver.rho.shape, dtype=torch.float32).pin_memory()
+        phi_host = torch.empty(solver.phi.shape, dtype=torch.float32).pin_memory()
         run = lambda n: [solver.step_host(faces, phi_host) for _ in range(n)]  # noqa: E731
         run(min(2, args.warmup))
         ms_e2e = timed(run, args.steps)

@@ -251,6 +251,62 @@ int lbmff_stream_collide_d3q19(const float* f_in, float* f_out, const uint8_t* f
                                float* rho, float* vel, double tau, double dx, double dt, int B, int D, int H, int W,
                                lbmff_stream_t stream);
 
+/* =====================================================================================
+ * SLAB TIER -- z-slab domain decomposition of the fused 3-D step (one process per GPU).
+ * No reference counterpart: the reference is single-device ("Parallelism").
+ * The local arrays hold D planes = halo planes + owned planes + halo planes of a globally periodic domain
+ * of Dg planes; local plane z is global plane (z + zoff) mod Dg.  Each call processes local planes
+ * [zb, zb + zn) only, so a step can be issued "boundary planes, start the halo exchange, interior planes".
+ * Position-dependent rules (outer shell, replicate clamps, wetting faces) use the global z, so a P-slab run
+ * performs bit-for-bit the per-cell arithmetic of the one-GPU run.  Halo planes are filled by the caller
+ * (lbm_ferrofluid_b200.distributed: NCCL point-to-point over NVLink); these entries never communicate.
+ * ===================================================================================== */
+typedef struct lbmff_slab {
+  int Dg;   /* global number of z planes */
+  int zoff; /* global z of local plane 0; negative for the lower halo of the first slab (wraps) */
+  int zb;   /* first local plane processed */
+  int zn;   /* number of local planes processed */
+} lbmff_slab;
+
+/* lbmff_hcz_moments_d3q19 on a plane range. */
+int lbmff_slab_hcz_moments_d3q19(const float* f, const uint8_t* flags, float* rho, float* chi_out,
+                                 const lbmff_fluid_params* p, const lbmff_slab* slab, int B, int D, int H, int W,
+                                 lbmff_stream_t stream);
+/* lbmff_magnetic_source_3d on a plane range (face arrays are slab-local: Hx [D][H][W+1], Hy [D][H+1][W],
+ * Hz [D+1][H][W]). */
+int lbmff_slab_magnetic_source_3d(const float* chi, const uint8_t* mflags, const float* Hx, const float* Hy,
+                                  const float* Hz, double dx, float* rhs_out, const lbmff_slab* slab, int B, int D,
+                                  int H, int W, lbmff_stream_t stream);
+/* ONE population-faithful sweep h_in -> h_out on a plane range; psi_out NULL = psi not stored. */
+int lbmff_slab_magnetic_sweep_d3q19(const float* h_in, float* h_out, const uint8_t* mflags, const float* rhs,
+                                    float* psi_out, double tau, double dx, double dt, const lbmff_slab* slab, int B,
+                                    int D, int H, int W, lbmff_stream_t stream);
+/* ONE tau == 1 scalar sweep (a_cur latest state, a_prev_out the one before, overwritten with the new state). */
+int lbmff_slab_magnetic_sweep_scalar_3d(const float* a_cur, float* a_prev_out, const uint8_t* mflags,
+                                        const float* rhs, float* psi_out, double dx, double dt,
+                                        const lbmff_slab* slab, int B, int D, int H, int W, lbmff_stream_t stream);
+/* get_grad shell rule folded into the data, in place: OBSTACLE shell cells take the nearest interior value
+ * (LBM_collision_3d.py:217-218). */
+int lbmff_slab_shell_rule_3d(float* field, const uint8_t* flags, const lbmff_slab* slab, int B, int D, int H, int W,
+                             lbmff_stream_t stream);
+/* Ordered wetting boundary on rho IN PLACE (HCZ_3d.py:84-211) for the shell cells of the plane range.
+ * stage 0: everything; 1: x faces only; 2: y faces, z faces, edges, corners (y faces read x-face cells of the
+ * planes above and below, so stage 1 must cover one more plane on each side than stage 2). */
+int lbmff_slab_hcz_wetting_3d(float* rho, const uint8_t* flags, const lbmff_fluid_params* p, int stage,
+                              const lbmff_slab* slab, int B, int D, int H, int W, lbmff_stream_t stream);
+/* ws = [lap(density) | fai | prho] on a plane range (second half of lbmff_hcz_capillary_fields_3d). */
+int lbmff_slab_hcz_fields_3d(const float* rho, const uint8_t* flags, const float* pressure,
+                             const lbmff_fluid_params* p, float* ws, const lbmff_slab* slab, int B, int D, int H,
+                             int W, lbmff_stream_t stream);
+/* lbmff_hcz_collide_stream_d3q19 on a plane range, uniform applied field; chi and psi must already carry the
+ * shell rule (lbmff_slab_shell_rule_3d) and valid halo planes. */
+int lbmff_slab_hcz_collide_stream_d3q19(const float* f_in, const float* g_in, float* f_out, float* g_out,
+                                        const float* rho, const uint8_t* flags, const uint8_t* mflags,
+                                        const float* ws, const float* chi, const float* psi,
+                                        const double* H_uniform, const lbmff_fluid_params* p, float* vel,
+                                        float* pressure, float* force_out, const lbmff_slab* slab, int B, int D,
+                                        int H, int W, lbmff_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -20,6 +20,11 @@ class FluidParams(ctypes.Structure):
         "gravity", "cot_theta")]
 
 
+class Slab(ctypes.Structure):
+    """Mirror of ``lbmff_slab`` (include/lbmff.h, slab tier)."""
+    _fields_ = [(n, ctypes.c_int) for n in ("Dg", "zoff", "zb", "zn")]
+
+
 _TYPE_MAP = [
     (re.compile(r"^const\s+lbmff_\w+_params\s*\*$"), None),  # filled per struct below
     (re.compile(r"^(const\s+)?(float|double|uint8_t|void)\s*\*$"), ctypes.c_void_p),
@@ -30,7 +35,7 @@ _TYPE_MAP = [
     (re.compile(r"^float$"), ctypes.c_float),
 ]
 
-_STRUCTS = {"lbmff_fluid_params": FluidParams}
+_STRUCTS = {"lbmff_fluid_params": FluidParams, "lbmff_slab": Slab}
 
 
 def register_struct(name, cls):

@@ -15,15 +15,34 @@
 
 namespace lbmff {
 
+// A Grid describes the LOCAL array a kernel works on.  On one GPU it is the whole domain.  Under z-slab
+// decomposition (multi-GPU, include/lbmff.h "slab tier") the local array holds D planes = owned planes plus
+// halo planes of a periodic global domain of Dg planes; local plane z is global plane (z + zoff) mod Dg.
+// Everything that depends on WHERE a cell sits in the domain (outer shell, replicate clamps, wetting faces)
+// uses the global z; addresses use the local z.  Fused kernels process cells [i0, i1) of the local array
+// (whole planes), so a step can be issued boundary planes first and interior planes while halos travel.
 struct Grid {
   int B, D, H, W;
-  long long N;  // cells per batch item = D*H*W
+  long long N;  // cells per batch item = D*H*W (also the channel stride)
+  int Dg;       // global number of z planes (== D on one GPU)
+  int zoff;     // global z of local plane 0, in (-Dg, Dg)
+  long long i0, i1;  // cell range processed by fused kernels, default [0, N)
 };
 
 __host__ __device__ inline Grid make_grid(int B, int D, int H, int W) {
   Grid g;
   g.B = B; g.D = D; g.H = H; g.W = W;
   g.N = (long long)D * H * W;
+  g.Dg = D; g.zoff = 0;
+  g.i0 = 0; g.i1 = g.N;
+  return g;
+}
+
+// Slab-local grid: planes [zb, zb + zn) of a local array of D planes are processed.
+inline Grid make_slab_grid(int B, int D, int H, int W, int Dg, int zoff, int zb, int zn) {
+  Grid g = make_grid(B, D, H, W);
+  g.Dg = Dg; g.zoff = zoff;
+  g.i0 = (long long)zb * H * W; g.i1 = (long long)(zb + zn) * H * W;
   return g;
 }
 
@@ -94,6 +113,35 @@ __device__ __forceinline__ int clampi(int v, int lo, int hi) { return v < lo ? l
 
 // clamp a coordinate into the interior [1, n-2] (identity for a size-1 axis)
 __device__ __forceinline__ int interior(int v, int n) { return n < 3 ? v : clampi(v, 1, n - 2); }
+
+// global z of local plane z
+__device__ __forceinline__ int global_z(const Grid& g, int z) {
+  int v = z + g.zoff;
+  return v < 0 ? v + g.Dg : (v >= g.Dg ? v - g.Dg : v);
+}
+// is local plane z one of the two outer z planes of the global domain?
+__device__ __forceinline__ bool z_on_shell(const Grid& g, int z) {
+  if (g.Dg <= 1) return false;
+  const int v = global_z(g, z);
+  return v == 0 || v == g.Dg - 1;
+}
+// local plane of the interior-clamped global z (moves by at most one plane; kept inside the local array)
+__device__ __forceinline__ int interior_z(const Grid& g, int z) {
+  if (g.Dg < 3) return z;
+  const int v = global_z(g, z);
+  return clampi(z + (clampi(v, 1, g.Dg - 2) - v), 0, g.D - 1);
+}
+// within one plane of the global z shell (tau == 1 scalar sweep: only such cells can have a wall neighbour)
+__device__ __forceinline__ bool near_z_shell(const Grid& g, int z) {
+  const int v = global_z(g, z);
+  return v <= 1 || v >= g.Dg - 2;
+}
+// local plane holding global plane gz, or -1 when this slab does not hold it
+__device__ __forceinline__ int local_z(const Grid& g, int gz) {
+  int l = gz - g.zoff;
+  if (l < 0) l += g.Dg; else if (l >= g.Dg) l -= g.Dg;
+  return l < g.D ? l : -1;
+}
 
 constexpr int kThreads = 256;
 

@@ -40,8 +40,8 @@ __global__ void __launch_bounds__(kThreads) k_hcz_moments(const float* __restric
                                                           const uint8_t* __restrict__ flags, float* __restrict__ rho,
                                                           float* __restrict__ chi, Consts k, Grid g) {
   using L = Lat<DIM>;
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= g.N) return;
+  const long long i = g.i0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.i1) return;
   const long long b = blockIdx.y;
   float s;
   if (flags[b * g.N + i] == LBMFF_OBSTACLE) {
@@ -74,13 +74,13 @@ __global__ void __launch_bounds__(kThreads) k_hcz_fields(const float* __restrict
                                                          const uint8_t* __restrict__ flags,
                                                          const float* __restrict__ pressure, float* __restrict__ ws,
                                                          Consts k, Grid g) {
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= g.N) return;
+  const long long i = g.i0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.i1) return;
   const long long b = blockIdx.y;
   const Cell c = cell_of(i, g);
   const float* r = rho + b * g.N;
   float* w = ws + b * 3 * g.N;
-  const int x = interior(c.x, g.W), y = interior(c.y, g.H), z = DIM == 3 ? interior(c.z, g.D) : 0;
+  const int x = interior(c.x, g.W), y = interior(c.y, g.H), z = DIM == 3 ? interior_z(g, c.z) : 0;
   const long long j = lin(g, x, y, z);
   const bool shell = on_shell(c, g);
   float lap = 0.0f;
@@ -97,13 +97,13 @@ __global__ void __launch_bounds__(kThreads) k_hcz_fields(const float* __restrict
 template <int DIM>
 __global__ void __launch_bounds__(kThreads) k_shell_rule(float* __restrict__ field,
                                                          const uint8_t* __restrict__ flags, Grid g) {
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= g.N) return;
+  const long long i = g.i0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.i1) return;
   const long long b = blockIdx.y;
   const Cell c = cell_of(i, g);
   if (!on_shell(c, g) || flags[b * g.N + i] != LBMFF_OBSTACLE) return;
   field[b * g.N + i] = field[b * g.N + lin(g, interior(c.x, g.W), interior(c.y, g.H),
-                                           DIM == 3 ? interior(c.z, g.D) : 0)];
+                                           DIM == 3 ? interior_z(g, c.z) : 0)];
 }
 
 struct HextUniform {
@@ -119,8 +119,8 @@ k_hcz_collide_stream(const float* __restrict__ f_in, const float* __restrict__ g
                      float* __restrict__ pressure, float* __restrict__ force_out, Consts k, int kbc_on_g,
                      KbcScalars K, Grid g) {
   using L = Lat<DIM>;
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= g.N) return;
+  const long long i = g.i0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.i1) return;
   const long long b = blockIdx.y;
   const Cell c = cell_of(i, g);
   const PullIndex<DIM> nb(c, g);
@@ -146,7 +146,7 @@ k_hcz_collide_stream(const float* __restrict__ f_in, const float* __restrict__ g
   for (int q = 0; q < L::Q; ++q) gv[q] = __ldg(gi + q * g.N + nb.at(q, 1));
   // ---- capillary_process part 2 at a FLUID cell (HCZ_3d.py:217-261); all stencil inputs carry the
   // get_grad shell rule in their data, so the 18-point stencils are plain constant-offset loads
-  const int x = interior(c.x, g.W), y = interior(c.y, g.H), z = DIM == 3 ? interior(c.z, g.D) : 0;
+  const int x = interior(c.x, g.W), y = interior(c.y, g.H), z = DIM == 3 ? interior_z(g, c.z) : 0;
   const long long j0 = lin(g, x, y, z);
   const long long HW = (long long)g.H * g.W;
   const float* w = ws + b * 3 * g.N + j0;
@@ -227,8 +227,8 @@ __global__ void __launch_bounds__(kThreads) k_stream_collide(const float* __rest
                                                              float* __restrict__ vel, int kbc, Consts k,
                                                              KbcScalars K, Grid g) {
   using L = Lat<DIM>;
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= g.N) return;
+  const long long i = g.i0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.i1) return;
   const long long b = blockIdx.y;
   const PullIndex<DIM> nb(cell_of(i, g), g);
   const float* fi = f_in + b * L::Q * g.N;
@@ -277,22 +277,29 @@ static Consts consts_of(const lbmff_fluid_params* p) {
 
 template <int DIM>
 static int moments_impl(const float* f, const uint8_t* flags, float* rho, float* chi, const lbmff_fluid_params* p,
-                        int B, int D, int H, int W, cudaStream_t st, const char* where) {
+                        const Grid& g, cudaStream_t st, const char* where) {
   if (!(f && flags && rho && p)) return bad_arg(where, "null pointer");
-  const Grid g = make_grid(B, D, H, W);
-  k_hcz_moments<DIM><<<dim3(blocks_for(g.N), (unsigned)B), kThreads, 0, st>>>(f, flags, rho, chi, consts_of(p), g);
+  k_hcz_moments<DIM><<<dim3(blocks_for(g.i1 - g.i0), (unsigned)g.B), kThreads, 0, st>>>(f, flags, rho, chi, consts_of(p), g);
   return check_launch(where);
 }
 
 template <int DIM>
 static int fields_impl(float* rho, const uint8_t* flags, const float* pressure, const lbmff_fluid_params* p,
-                       float* ws, int B, int D, int H, int W, cudaStream_t st, const char* where) {
-  if (!(rho && flags && pressure && p && ws)) return bad_arg(where, "null pointer");
-  if (W < 4 || H < 4 || (DIM == 3 && D < 4)) return bad_arg(where, "every extent must be >= 4");
-  const Grid g = make_grid(B, D, H, W);
+                       float* ws, const Grid& g, bool wetting, bool fields, int stage, cudaStream_t st,
+                       const char* where) {
+  if (!(rho && flags && p && (!fields || (pressure && ws)))) return bad_arg(where, "null pointer");
+  if (g.W < 4 || g.H < 4 || (DIM == 3 && g.D < 4)) return bad_arg(where, "every extent must be >= 4");
   const Consts k = consts_of(p);
-  launch_wetting<DIM>(rho, flags, k.cot, g, st);
-  k_hcz_fields<DIM><<<dim3(blocks_for(g.N), (unsigned)B), kThreads, 0, st>>>(rho, flags, pressure, ws, k, g);
+  if (wetting) launch_wetting<DIM>(rho, flags, k.cot, g, st, stage);
+  if (fields)
+    k_hcz_fields<DIM><<<dim3(blocks_for(g.i1 - g.i0), (unsigned)g.B), kThreads, 0, st>>>(rho, flags, pressure, ws, k, g);
+  return check_launch(where);
+}
+
+template <int DIM>
+static int shell_rule_impl(float* field, const uint8_t* flags, const Grid& g, cudaStream_t st, const char* where) {
+  if (!(field && flags)) return bad_arg(where, "null pointer");
+  k_shell_rule<DIM><<<dim3(blocks_for(g.i1 - g.i0), (unsigned)g.B), kThreads, 0, st>>>(field, flags, g);
   return check_launch(where);
 }
 
@@ -300,21 +307,22 @@ template <int DIM>
 static int collide_stream_impl(const float* f_in, const float* g_in, float* f_out, float* g_out, const float* rho,
                                const uint8_t* flags, const uint8_t* mflags, const float* ws, float* chi,
                                float* psi, const float* Hext, const double* Hu, const lbmff_fluid_params* p,
-                               int kbc_on_g, float* vel, float* pressure, float* force_out, int B, int D, int H,
-                               int W, cudaStream_t st, const char* where) {
+                               int kbc_on_g, float* vel, float* pressure, float* force_out, const Grid& g,
+                               bool fold_shell_rule, cudaStream_t st, const char* where) {
   if (!(f_in && g_in && f_out && g_out && rho && flags && ws && p && vel && pressure))
     return bad_arg(where, "null pointer");
   if (f_in == f_out || g_in == g_out) return bad_arg(where, "in and out population buffers must differ");
   const bool magnetic = chi != nullptr;
   if (magnetic && !(psi && mflags && (Hext || Hu))) return bad_arg(where, "magnetic inputs incomplete");
-  const Grid g = make_grid(B, D, H, W);
   const Consts k = consts_of(p);
   HextUniform hu{{0.f, 0.f, 0.f}};
   if (Hu) for (int a = 0; a < DIM; ++a) hu.v[a] = (float)Hu[a];
-  const dim3 grid(blocks_for(g.N), (unsigned)B);
+  const dim3 grid(blocks_for(g.i1 - g.i0), (unsigned)g.B);
   if (magnetic) {
-    k_shell_rule<DIM><<<grid, kThreads, 0, st>>>(psi, mflags, g);
-    k_shell_rule<DIM><<<grid, kThreads, 0, st>>>(chi, flags, g);
+    if (fold_shell_rule) {
+      k_shell_rule<DIM><<<grid, kThreads, 0, st>>>(psi, mflags, g);
+      k_shell_rule<DIM><<<grid, kThreads, 0, st>>>(chi, flags, g);
+    }
     k_hcz_collide_stream<DIM, true><<<grid, kThreads, 0, st>>>(f_in, g_in, f_out, g_out, rho, flags, ws, chi, psi,
                                                                Hext, hu, vel, pressure, force_out, k, kbc_on_g,
                                                                make_kbc(p->tau_g), g);
@@ -335,7 +343,7 @@ static int stream_collide_impl(const float* f_in, float* f_out, const uint8_t* f
   if (DIM == 3 && kbc >= 0) return bad_arg(where, "KBC collision exists for D2Q9 only");
   const Grid g = make_grid(B, D, H, W);
   const Consts k = make_consts(dx, dt, tau);
-  const dim3 grid(blocks_for(g.N), (unsigned)B);
+  const dim3 grid(blocks_for(g.i1 - g.i0), (unsigned)B);
   if constexpr (DIM == 2) {
     if (kbc >= 0) {
       k_stream_collide<2, 1><<<grid, kThreads, 0, st>>>(f_in, f_out, flags, force, rho, vel, kbc, k, make_kbc(tau), g);
@@ -354,21 +362,21 @@ extern "C" {
 
 int lbmff_hcz_moments_d2q9(const float* f, const uint8_t* flags, float* rho, float* chi_out,
                            const lbmff_fluid_params* p, int B, int H, int W, lbmff_stream_t stream) {
-  return moments_impl<2>(f, flags, rho, chi_out, p, B, 1, H, W, (cudaStream_t)stream, __func__);
+  return moments_impl<2>(f, flags, rho, chi_out, p, make_grid(B, 1, H, W), (cudaStream_t)stream, __func__);
 }
 int lbmff_hcz_moments_d3q19(const float* f, const uint8_t* flags, float* rho, float* chi_out,
                             const lbmff_fluid_params* p, int B, int D, int H, int W, lbmff_stream_t stream) {
-  return moments_impl<3>(f, flags, rho, chi_out, p, B, D, H, W, (cudaStream_t)stream, __func__);
+  return moments_impl<3>(f, flags, rho, chi_out, p, make_grid(B, D, H, W), (cudaStream_t)stream, __func__);
 }
 int lbmff_hcz_capillary_fields_2d(float* rho, const uint8_t* flags, const float* pressure,
                                   const lbmff_fluid_params* p, float* ws, int B, int H, int W,
                                   lbmff_stream_t stream) {
-  return fields_impl<2>(rho, flags, pressure, p, ws, B, 1, H, W, (cudaStream_t)stream, __func__);
+  return fields_impl<2>(rho, flags, pressure, p, ws, make_grid(B, 1, H, W), true, true, 0, (cudaStream_t)stream, __func__);
 }
 int lbmff_hcz_capillary_fields_3d(float* rho, const uint8_t* flags, const float* pressure,
                                   const lbmff_fluid_params* p, float* ws, int B, int D, int H, int W,
                                   lbmff_stream_t stream) {
-  return fields_impl<3>(rho, flags, pressure, p, ws, B, D, H, W, (cudaStream_t)stream, __func__);
+  return fields_impl<3>(rho, flags, pressure, p, ws, make_grid(B, D, H, W), true, true, 0, (cudaStream_t)stream, __func__);
 }
 int lbmff_hcz_collide_stream_d2q9(const float* f_in, const float* g_in, float* f_out, float* g_out,
                                   const float* rho, const uint8_t* flags, const uint8_t* mflags, const float* ws,
@@ -376,7 +384,8 @@ int lbmff_hcz_collide_stream_d2q9(const float* f_in, const float* g_in, float* f
                                   const lbmff_fluid_params* p, int kbc_on_g, float* vel, float* pressure,
                                   float* force_out, int B, int H, int W, lbmff_stream_t stream) {
   return collide_stream_impl<2>(f_in, g_in, f_out, g_out, rho, flags, mflags, ws, chi, psi, H_ext, H_uniform, p,
-                                kbc_on_g, vel, pressure, force_out, B, 1, H, W, (cudaStream_t)stream, __func__);
+                                kbc_on_g, vel, pressure, force_out, make_grid(B, 1, H, W), true,
+                                (cudaStream_t)stream, __func__);
 }
 int lbmff_hcz_collide_stream_d3q19(const float* f_in, const float* g_in, float* f_out, float* g_out,
                                    const float* rho, const uint8_t* flags, const uint8_t* mflags, const float* ws,
@@ -384,8 +393,57 @@ int lbmff_hcz_collide_stream_d3q19(const float* f_in, const float* g_in, float* 
                                    const lbmff_fluid_params* p, float* vel, float* pressure, float* force_out,
                                    int B, int D, int H, int W, lbmff_stream_t stream) {
   return collide_stream_impl<3>(f_in, g_in, f_out, g_out, rho, flags, mflags, ws, chi, psi, H_ext, H_uniform, p, 0,
-                                vel, pressure, force_out, B, D, H, W, (cudaStream_t)stream, __func__);
+                                vel, pressure, force_out, make_grid(B, D, H, W), true, (cudaStream_t)stream,
+                                __func__);
 }
+/* ---- slab tier (z-slab decomposition; D = local planes, halos included) ------------------------ */
+static int slab_grid(const lbmff_slab* s, int B, int D, int H, int W, Grid* g, const char* where) {
+  if (!s) return bad_arg(where, "null slab descriptor");
+  if (s->Dg < D || s->zoff <= -s->Dg || s->zoff >= s->Dg) return bad_arg(where, "slab: need D <= Dg and |zoff| < Dg");
+  if (s->zb < 0 || s->zn < 1 || s->zb + s->zn > D) return bad_arg(where, "slab: plane range outside the local array");
+  *g = make_slab_grid(B, D, H, W, s->Dg, s->zoff, s->zb, s->zn);
+  return 0;
+}
+#define LBMFF_SLAB_GRID                                              \
+  Grid g;                                                            \
+  if (int rc = slab_grid(slab, B, D, H, W, &g, __func__)) return rc
+
+int lbmff_slab_hcz_moments_d3q19(const float* f, const uint8_t* flags, float* rho, float* chi_out,
+                                 const lbmff_fluid_params* p, const lbmff_slab* slab, int B, int D, int H, int W,
+                                 lbmff_stream_t stream) {
+  LBMFF_SLAB_GRID;
+  return moments_impl<3>(f, flags, rho, chi_out, p, g, (cudaStream_t)stream, __func__);
+}
+int lbmff_slab_hcz_wetting_3d(float* rho, const uint8_t* flags, const lbmff_fluid_params* p, int stage,
+                              const lbmff_slab* slab, int B, int D, int H, int W, lbmff_stream_t stream) {
+  LBMFF_SLAB_GRID;
+  if (stage < 0 || stage > 2) return bad_arg(__func__, "stage must be 0, 1 or 2");
+  return fields_impl<3>(rho, flags, nullptr, p, nullptr, g, true, false, stage, (cudaStream_t)stream, __func__);
+}
+int lbmff_slab_hcz_fields_3d(const float* rho, const uint8_t* flags, const float* pressure,
+                             const lbmff_fluid_params* p, float* ws, const lbmff_slab* slab, int B, int D, int H,
+                             int W, lbmff_stream_t stream) {
+  LBMFF_SLAB_GRID;
+  return fields_impl<3>(const_cast<float*>(rho), flags, pressure, p, ws, g, false, true, 0, (cudaStream_t)stream,
+                        __func__);
+}
+int lbmff_slab_shell_rule_3d(float* field, const uint8_t* flags, const lbmff_slab* slab, int B, int D, int H, int W,
+                             lbmff_stream_t stream) {
+  LBMFF_SLAB_GRID;
+  return shell_rule_impl<3>(field, flags, g, (cudaStream_t)stream, __func__);
+}
+int lbmff_slab_hcz_collide_stream_d3q19(const float* f_in, const float* g_in, float* f_out, float* g_out,
+                                        const float* rho, const uint8_t* flags, const uint8_t* mflags,
+                                        const float* ws, const float* chi, const float* psi,
+                                        const double* H_uniform, const lbmff_fluid_params* p, float* vel,
+                                        float* pressure, float* force_out, const lbmff_slab* slab, int B, int D,
+                                        int H, int W, lbmff_stream_t stream) {
+  LBMFF_SLAB_GRID;
+  return collide_stream_impl<3>(f_in, g_in, f_out, g_out, rho, flags, mflags, ws, const_cast<float*>(chi),
+                                const_cast<float*>(psi), nullptr, H_uniform, p, 0, vel, pressure, force_out, g, false,
+                                (cudaStream_t)stream, __func__);
+}
+
 int lbmff_stream_collide_d2q9(const float* f_in, float* f_out, const uint8_t* flags, const float* force, float* rho,
                               float* vel, double tau, int kbc, double dx, double dt, int B, int H, int W,
                               lbmff_stream_t stream) {

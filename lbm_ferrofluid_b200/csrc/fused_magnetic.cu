@@ -24,8 +24,8 @@ template <int DIM>
 __global__ void __launch_bounds__(kThreads) k_mag_source(const float* __restrict__ chi,
                                                          const uint8_t* __restrict__ mflags, HextFaces Hf,
                                                          float* __restrict__ rhs, float dx, Grid g) {
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= g.N) return;
+  const long long i = g.i0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.i1) return;
   const long long b = blockIdx.y;
   float r = 0.0f;
   if (mflags[b * g.N + i] == LBMFF_FLUID) {
@@ -48,8 +48,8 @@ __global__ void __launch_bounds__(kThreads) k_mag_sweep(const float* __restrict_
                                                         const float* __restrict__ rhs, float* __restrict__ psi_out,
                                                         Consts k, Grid g) {
   using L = Lat<DIM>;
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= g.N) return;
+  const long long i = g.i0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.i1) return;
   const long long b = blockIdx.y;
   const float* in = hin + b * L::Q * g.N;
   float* out = hout + b * L::Q * g.N;
@@ -98,8 +98,8 @@ __global__ void __launch_bounds__(kThreads) k_mag_sweep_scalar(const float* __re
                                                                const float* __restrict__ rhs,
                                                                float* __restrict__ psi_out, Consts k, Grid g) {
   using L = Lat<DIM>;
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= g.N) return;
+  const long long i = g.i0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.i1) return;
   const long long b = blockIdx.y;
   const float* ca = cur + b * 2 * g.N;
   float* pa = prev_out + b * 2 * g.N;
@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(kThreads) k_mag_sweep_scalar(const float* __re
   }
   // walls lie on the outer shell only (checked by the host), so only shell-adjacent cells test flags
   const bool near_shell = c.x <= 1 || c.x >= g.W - 2 || c.y <= 1 || c.y >= g.H - 2 ||
-                          (DIM == 3 && (c.z <= 1 || c.z >= g.D - 2));
+                          (DIM == 3 && near_z_shell(g, c.z));
   unsigned wall_mask = 0;
   if (near_shell) {
 #pragma unroll
@@ -159,8 +159,8 @@ __global__ void __launch_bounds__(kThreads) k_mag_materialize(const float* __res
                                                               const uint8_t* __restrict__ mflags,
                                                               float* __restrict__ h, Consts k, Grid g) {
   using L = Lat<DIM>;
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= g.N) return;
+  const long long i = g.i0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.i1) return;
   const long long b = blockIdx.y;
   const float* ca = cur + b * 2 * g.N;
   const float* pa = prev + b * 2 * g.N;
@@ -190,18 +190,16 @@ __global__ void __launch_bounds__(kThreads) k_mag_materialize(const float* __res
 
 template <int DIM>
 static int sweeps_impl(float* hA, float* hB, const uint8_t* mflags, const float* rhs, float* psi_out, int n,
-                       double tau, double dx, double dt, int B, int D, int H, int W, cudaStream_t st,
-                       const char* where) {
-  if (!(hA && hB && hA != hB && mflags && rhs && psi_out)) return bad_arg(where, "null or aliased pointer");
+                       double tau, double dx, double dt, const Grid& g, cudaStream_t st, const char* where) {
+  if (!(hA && hB && hA != hB && mflags && rhs)) return bad_arg(where, "null or aliased pointer");
   if (n < 1) return bad_arg(where, "n_sweeps must be >= 1");
   if (!(tau > 0)) return bad_arg(where, "tau must be positive");
-  const Grid g = make_grid(B, D, H, W);
   const Consts k = make_consts(dx, dt, tau);
-  const dim3 grid(blocks_for(g.N), (unsigned)B);
+  const dim3 grid(blocks_for(g.i1 - g.i0), (unsigned)g.B);
   for (int s = 0; s < n; ++s) {
     const float* in = (s & 1) ? hB : hA;
     float* out = (s & 1) ? hA : hB;
-    if (s == n - 1)
+    if (s == n - 1 && psi_out)
       k_mag_sweep<DIM, true><<<grid, kThreads, 0, st>>>(in, out, mflags, rhs, psi_out, k, g);
     else
       k_mag_sweep<DIM, false><<<grid, kThreads, 0, st>>>(in, out, mflags, rhs, psi_out, k, g);
@@ -211,17 +209,15 @@ static int sweeps_impl(float* hA, float* hB, const uint8_t* mflags, const float*
 
 template <int DIM>
 static int sweeps_scalar_impl(float* aA, float* aB, const uint8_t* mflags, const float* rhs, float* psi_out, int n,
-                              double dx, double dt, int B, int D, int H, int W, cudaStream_t st,
-                              const char* where) {
-  if (!(aA && aB && aA != aB && mflags && rhs && psi_out)) return bad_arg(where, "null or aliased pointer");
+                              double dx, double dt, const Grid& g, cudaStream_t st, const char* where) {
+  if (!(aA && aB && aA != aB && mflags && rhs)) return bad_arg(where, "null or aliased pointer");
   if (n < 1) return bad_arg(where, "n_sweeps must be >= 1");
-  const Grid g = make_grid(B, D, H, W);
   const Consts k = make_consts(dx, dt, 1.0);
-  const dim3 grid(blocks_for(g.N), (unsigned)B);
+  const dim3 grid(blocks_for(g.i1 - g.i0), (unsigned)g.B);
   for (int s = 0; s < n; ++s) {
     const float* cur = (s & 1) ? aB : aA;
     float* prev = (s & 1) ? aA : aB;
-    if (s == n - 1)
+    if (s == n - 1 && psi_out)
       k_mag_sweep_scalar<DIM, true><<<grid, kThreads, 0, st>>>(cur, prev, mflags, rhs, psi_out, k, g);
     else
       k_mag_sweep_scalar<DIM, false><<<grid, kThreads, 0, st>>>(cur, prev, mflags, rhs, psi_out, k, g);
@@ -231,11 +227,10 @@ static int sweeps_scalar_impl(float* aA, float* aB, const uint8_t* mflags, const
 
 template <int DIM>
 static int source_impl(const float* chi, const uint8_t* mflags, const float* Hx, const float* Hy, const float* Hz,
-                       double dx, float* rhs, int B, int D, int H, int W, cudaStream_t st, const char* where) {
+                       double dx, float* rhs, const Grid& g, cudaStream_t st, const char* where) {
   if (!(chi && mflags && Hx && Hy && (DIM == 2 || Hz) && rhs)) return bad_arg(where, "null pointer");
-  if (W < 3 || H < 3 || (DIM == 3 && D < 3)) return bad_arg(where, "every extent must be >= 3");
-  const Grid g = make_grid(B, D, H, W);
-  k_mag_source<DIM><<<dim3(blocks_for(g.N), (unsigned)B), kThreads, 0, st>>>(chi, mflags, HextFaces{Hx, Hy, Hz},
+  if (g.W < 3 || g.H < 3 || (DIM == 3 && g.D < 3)) return bad_arg(where, "every extent must be >= 3");
+  k_mag_source<DIM><<<dim3(blocks_for(g.i1 - g.i0), (unsigned)g.B), kThreads, 0, st>>>(chi, mflags, HextFaces{Hx, Hy, Hz},
                                                                              rhs, (float)dx, g);
   return check_launch(where);
 }
@@ -246,7 +241,7 @@ static int materialize_impl(const float* cur, const float* prev, const float* ps
                             cudaStream_t st, const char* where) {
   if (!(cur && prev && psi && rhs && mflags && h)) return bad_arg(where, "null pointer");
   const Grid g = make_grid(B, D, H, W);
-  k_mag_materialize<DIM><<<dim3(blocks_for(g.N), (unsigned)B), kThreads, 0, st>>>(cur, prev, psi, rhs, mflags, h,
+  k_mag_materialize<DIM><<<dim3(blocks_for(g.i1 - g.i0), (unsigned)B), kThreads, 0, st>>>(cur, prev, psi, rhs, mflags, h,
                                                                                   make_consts(dx, dt, 1.0), g);
   return check_launch(where);
 }
@@ -259,37 +254,75 @@ extern "C" {
 
 int lbmff_magnetic_source_2d(const float* chi, const uint8_t* mflags, const float* Hx, const float* Hy, double dx,
                              float* rhs_out, int B, int H, int W, lbmff_stream_t stream) {
-  return source_impl<2>(chi, mflags, Hx, Hy, nullptr, dx, rhs_out, B, 1, H, W, (cudaStream_t)stream, __func__);
+  return source_impl<2>(chi, mflags, Hx, Hy, nullptr, dx, rhs_out, make_grid(B, 1, H, W), (cudaStream_t)stream,
+                        __func__);
 }
 int lbmff_magnetic_source_3d(const float* chi, const uint8_t* mflags, const float* Hx, const float* Hy,
                              const float* Hz, double dx, float* rhs_out, int B, int D, int H, int W,
                              lbmff_stream_t stream) {
-  return source_impl<3>(chi, mflags, Hx, Hy, Hz, dx, rhs_out, B, D, H, W, (cudaStream_t)stream, __func__);
+  return source_impl<3>(chi, mflags, Hx, Hy, Hz, dx, rhs_out, make_grid(B, D, H, W), (cudaStream_t)stream,
+                        __func__);
 }
 int lbmff_magnetic_sweeps_d2q9(float* hA, float* hB, const uint8_t* mflags, const float* rhs, float* psi_out,
                                int n_sweeps, double tau, double dx, double dt, int B, int H, int W,
                                lbmff_stream_t stream) {
-  return sweeps_impl<2>(hA, hB, mflags, rhs, psi_out, n_sweeps, tau, dx, dt, B, 1, H, W, (cudaStream_t)stream,
-                        __func__);
+  if (!psi_out) return bad_arg(__func__, "null psi_out");
+  return sweeps_impl<2>(hA, hB, mflags, rhs, psi_out, n_sweeps, tau, dx, dt, make_grid(B, 1, H, W),
+                        (cudaStream_t)stream, __func__);
 }
 int lbmff_magnetic_sweeps_d3q19(float* hA, float* hB, const uint8_t* mflags, const float* rhs, float* psi_out,
                                 int n_sweeps, double tau, double dx, double dt, int B, int D, int H, int W,
                                 lbmff_stream_t stream) {
-  return sweeps_impl<3>(hA, hB, mflags, rhs, psi_out, n_sweeps, tau, dx, dt, B, D, H, W, (cudaStream_t)stream,
-                        __func__);
+  if (!psi_out) return bad_arg(__func__, "null psi_out");
+  return sweeps_impl<3>(hA, hB, mflags, rhs, psi_out, n_sweeps, tau, dx, dt, make_grid(B, D, H, W),
+                        (cudaStream_t)stream, __func__);
 }
 int lbmff_magnetic_sweeps_scalar_2d(float* aA, float* aB, const uint8_t* mflags, const float* rhs, float* psi_out,
                                     int n_sweeps, double dx, double dt, int B, int H, int W,
                                     lbmff_stream_t stream) {
-  return sweeps_scalar_impl<2>(aA, aB, mflags, rhs, psi_out, n_sweeps, dx, dt, B, 1, H, W, (cudaStream_t)stream,
-                               __func__);
+  if (!psi_out) return bad_arg(__func__, "null psi_out");
+  return sweeps_scalar_impl<2>(aA, aB, mflags, rhs, psi_out, n_sweeps, dx, dt, make_grid(B, 1, H, W),
+                               (cudaStream_t)stream, __func__);
 }
 int lbmff_magnetic_sweeps_scalar_3d(float* aA, float* aB, const uint8_t* mflags, const float* rhs, float* psi_out,
                                     int n_sweeps, double dx, double dt, int B, int D, int H, int W,
                                     lbmff_stream_t stream) {
-  return sweeps_scalar_impl<3>(aA, aB, mflags, rhs, psi_out, n_sweeps, dx, dt, B, D, H, W, (cudaStream_t)stream,
-                               __func__);
+  if (!psi_out) return bad_arg(__func__, "null psi_out");
+  return sweeps_scalar_impl<3>(aA, aB, mflags, rhs, psi_out, n_sweeps, dx, dt, make_grid(B, D, H, W),
+                               (cudaStream_t)stream, __func__);
 }
+/* ---- slab tier: one sweep over local planes [zb, zb + zn); psi_out may be NULL ---------------------- */
+static int slab_grid_m(const lbmff_slab* s, int B, int D, int H, int W, Grid* g, const char* where) {
+  if (!s) return bad_arg(where, "null slab descriptor");
+  if (s->Dg < D || s->zoff <= -s->Dg || s->zoff >= s->Dg) return bad_arg(where, "slab: need D <= Dg and |zoff| < Dg");
+  if (s->zb < 0 || s->zn < 1 || s->zb + s->zn > D) return bad_arg(where, "slab: plane range outside the local array");
+  *g = make_slab_grid(B, D, H, W, s->Dg, s->zoff, s->zb, s->zn);
+  return 0;
+}
+int lbmff_slab_magnetic_source_3d(const float* chi, const uint8_t* mflags, const float* Hx, const float* Hy,
+                                  const float* Hz, double dx, float* rhs_out, const lbmff_slab* slab, int B, int D,
+                                  int H, int W, lbmff_stream_t stream) {
+  Grid g;
+  if (int rc = slab_grid_m(slab, B, D, H, W, &g, __func__)) return rc;
+  return source_impl<3>(chi, mflags, Hx, Hy, Hz, dx, rhs_out, g, (cudaStream_t)stream, __func__);
+}
+int lbmff_slab_magnetic_sweep_d3q19(const float* h_in, float* h_out, const uint8_t* mflags, const float* rhs,
+                                    float* psi_out, double tau, double dx, double dt, const lbmff_slab* slab, int B,
+                                    int D, int H, int W, lbmff_stream_t stream) {
+  Grid g;
+  if (int rc = slab_grid_m(slab, B, D, H, W, &g, __func__)) return rc;
+  return sweeps_impl<3>(const_cast<float*>(h_in), h_out, mflags, rhs, psi_out, 1, tau, dx, dt, g,
+                        (cudaStream_t)stream, __func__);
+}
+int lbmff_slab_magnetic_sweep_scalar_3d(const float* a_cur, float* a_prev_out, const uint8_t* mflags,
+                                        const float* rhs, float* psi_out, double dx, double dt,
+                                        const lbmff_slab* slab, int B, int D, int H, int W, lbmff_stream_t stream) {
+  Grid g;
+  if (int rc = slab_grid_m(slab, B, D, H, W, &g, __func__)) return rc;
+  return sweeps_scalar_impl<3>(const_cast<float*>(a_cur), a_prev_out, mflags, rhs, psi_out, 1, dx, dt, g,
+                               (cudaStream_t)stream, __func__);
+}
+
 int lbmff_magnetic_materialize_h_2d(const float* a_cur, const float* a_prev, const float* psi, const float* rhs,
                                     const uint8_t* mflags, float* h_out, double dx, double dt, int B, int H, int W,
                                     lbmff_stream_t stream) {

@@ -29,7 +29,10 @@ __device__ __forceinline__ float magnetic_rhs_at(const Chi& chi, const HextFaces
   float div = (fxh * __ldg(Hf.x + ix + 1) - fxl * __ldg(Hf.x + ix)) +
               (fyh * __ldg(Hf.y + iy + g.W) - fyl * __ldg(Hf.y + iy));
   if (DIM == 3) {
-    const int zl = clampi(z, 1, g.D - 1), zh = clampi(z + 1, 1, g.D - 1);
+    // replicate clamp on the GLOBAL face index, addresses local (slab decomposition: common.cuh Grid)
+    const int gz = global_z(g, z);
+    const int zl = clampi(z + (clampi(gz, 1, g.Dg - 1) - gz), 1, g.D - 1);
+    const int zh = clampi(z + (clampi(gz + 1, 1, g.Dg - 1) - gz), 1, g.D - 1);
     const float fzl = (chi(x, y, zl) + chi(x, y, zl - 1)) * 0.5f, fzh = (chi(x, y, zh) + chi(x, y, zh - 1)) * 0.5f;
     const long long iz = ((long long)z * g.H + y) * g.W + x;
     div = div + (fzh * __ldg(Hf.z + iz + (long long)g.H * g.W) - fzl * __ldg(Hf.z + iz));

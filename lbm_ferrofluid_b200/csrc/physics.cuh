@@ -130,9 +130,9 @@ struct ObstacleClampedField {
   __device__ __forceinline__ float operator()(int x, int y, int z) const {
     long long i = lin(g, x, y, z);
     // the interior clamp is the identity off the shell, so only shell cells need their flag read
-    const bool shell = x == 0 || x == g.W - 1 || y == 0 || y == g.H - 1 || (g.D > 1 && (z == 0 || z == g.D - 1));
+    const bool shell = x == 0 || x == g.W - 1 || y == 0 || y == g.H - 1 || z_on_shell(g, z);
     if (shell && flags[i] == LBMFF_OBSTACLE) {
-      i = lin(g, interior(x, g.W), interior(y, g.H), interior(z, g.D));
+      i = lin(g, interior(x, g.W), interior(y, g.H), interior_z(g, z));
     }
     return __ldg(p + i);
   }
@@ -154,7 +154,7 @@ struct CentredField {
 // The get_grad shell rule folded into the DATA: value a shell cell contributes to a gradient stencil.
 // OBSTACLE shell cells contribute the value of the nearest interior cell (LBM_collision_3d.py:217-218).
 __device__ __forceinline__ bool on_shell(const Cell& c, const Grid& g) {
-  return c.x == 0 || c.x == g.W - 1 || c.y == 0 || c.y == g.H - 1 || (g.D > 1 && (c.z == 0 || c.z == g.D - 1));
+  return c.x == 0 || c.x == g.W - 1 || c.y == 0 || c.y == g.H - 1 || z_on_shell(g, c.z);
 }
 
 // Isotropic central gradient at an INTERIOR cell (LBM_collision_3d.py:224-275,

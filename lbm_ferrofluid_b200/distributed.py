@@ -1,0 +1,503 @@
+"""z-slab domain decomposition of the fused 3-D step: one process per GPU, NCCL point-to-point halo
+exchange over NVLink, boundary planes first so the exchange overlaps the interior compute.
+
+The reference is single-device ("Parallelism": none), so there is no reference
+interface here; the contract is: a P-slab run equals the one-GPU FerroSolver run BIT FOR BIT on every owned
+cell.  That holds by construction -- the slab entries of the C ABI (include/lbmff.h, "slab tier") run the
+same kernels with the same per-cell arithmetic, position-dependent rules use the global z, and halo planes
+are copies of the neighbour's owned planes.
+
+Layout of one slab (z is the slowest spatial axis, so one z plane of one channel is a contiguous H*W block):
+
+    local plane   0 .. halo-1 | halo .. halo+Dl-1 | halo+Dl .. Dl+2*halo-1
+                  lower halo  |      owned        |      upper halo
+    global plane  (z + zoff) mod Dg,   zoff = rank*Dl - halo          (the global domain is periodic in z,
+                  so rank 0 and rank P-1 are neighbours too: LBM_propagation_3d.py:31-37)
+
+``SlabFerroSolver.step`` is written as a generator of halo requests so that the same code runs under
+``torch.distributed`` (DistExchanger: NCCL on GPUs, gloo in the CPU tests) and as P "virtual ranks" inside
+one process on one GPU (LoopbackExchanger: the bit-for-bit test).
+"""
+from __future__ import annotations
+
+import ctypes
+import math
+from dataclasses import dataclass
+from typing import Callable, List, Optional, Sequence
+
+import torch
+
+from . import _host as H
+from ._lib import Slab
+from .types import CellType
+
+FLUID, OBSTACLE = int(CellType.FLUID), int(CellType.OBSTACLE)
+HALO = 2  # rho needs two planes (kappa rho grad(lap(rho))); everything else one
+
+
+# ---------------------------------------------------------------------------------------------------
+# layout
+# ---------------------------------------------------------------------------------------------------
+@dataclass(frozen=True)
+class SlabLayout:
+    """Which planes of the global [Dg, H, W] domain one rank holds."""
+    Dg: int
+    world: int
+    rank: int
+    halo: int = HALO
+
+    def __post_init__(self):
+        if self.world < 2:
+            raise ValueError("slab decomposition needs world >= 2 (use FerroSolver on one GPU)")
+        if self.Dg % self.world:
+            raise ValueError(f"global depth {self.Dg} is not divisible by world size {self.world}")
+        if self.Dl < 2 * self.halo:
+            raise ValueError(f"{self.Dl} owned planes per rank < 2*halo = {2 * self.halo}")
+
+    @property
+    def Dl(self) -> int:
+        return self.Dg // self.world
+
+    @property
+    def D(self) -> int:
+        return self.Dl + 2 * self.halo
+
+    @property
+    def z0(self) -> int:
+        """global z of the first owned plane"""
+        return self.rank * self.Dl
+
+    @property
+    def zoff(self) -> int:
+        return self.z0 - self.halo
+
+    @property
+    def own(self) -> slice:
+        return slice(self.halo, self.halo + self.Dl)
+
+    @property
+    def up(self) -> int:
+        return (self.rank + 1) % self.world
+
+    @property
+    def down(self) -> int:
+        return (self.rank - 1) % self.world
+
+    def global_planes(self) -> torch.Tensor:
+        return (torch.arange(self.D) + self.zoff) % self.Dg
+
+    def take(self, t: torch.Tensor) -> torch.Tensor:
+        """Local array (halos filled) of a global [B, C, Dg, H, W] tensor."""
+        return t.index_select(2, self.global_planes().to(t.device)).contiguous()
+
+    def owned(self, t: torch.Tensor) -> torch.Tensor:
+        return t[:, :, self.own]
+
+    def slab(self, zb: int, zn: int) -> Slab:
+        return Slab(Dg=self.Dg, zoff=self.zoff, zb=zb, zn=zn)
+
+    # plane ranges (zb, zn) used by the step
+    def planes_owned(self):
+        return self.halo, self.Dl
+
+    def planes_depth(self, d: int):
+        """owned planes plus d halo planes on each side"""
+        return self.halo - d, self.Dl + 2 * d
+
+
+def slab_shell_flags(layout: SlabLayout, H_: int, W: int, open_axes: Sequence[int] = (), device="cuda"):
+    """shell_flags (initializers.py) of the global domain, restricted to one slab -- built without ever
+    materialising the global array."""
+    gz = layout.global_planes().to(device)
+    wall_z = ((gz == 0) | (gz == layout.Dg - 1)).reshape(-1, 1, 1)
+    y = torch.arange(H_, device=device).reshape(1, -1, 1)
+    x = torch.arange(W, device=device).reshape(1, 1, -1)
+    wall = torch.zeros((layout.D, H_, W), dtype=torch.bool, device=device)
+    if 2 not in open_axes:
+        wall |= wall_z
+    if 1 not in open_axes:
+        wall |= (y == 0) | (y == H_ - 1)
+    if 0 not in open_axes:
+        wall |= (x == 0) | (x == W - 1)
+    fl = torch.where(wall, OBSTACLE, FLUID).to(torch.uint8)
+    return fl.reshape(1, 1, layout.D, H_, W).contiguous()
+
+
+# ---------------------------------------------------------------------------------------------------
+# halo exchange
+# ---------------------------------------------------------------------------------------------------
+def _send_slices(layout: SlabLayout, depth: int):
+    """(to_up, to_down, from_down, from_up) plane slices for a halo of `depth` planes."""
+    h, Dl = layout.halo, layout.Dl
+    return (slice(h + Dl - depth, h + Dl),   # my top owned planes -> upper neighbour's lower halo
+            slice(h, h + depth),             # my bottom owned planes -> lower neighbour's upper halo
+            slice(h - depth, h),             # my lower halo  <- lower neighbour's top owned planes
+            slice(h + Dl, h + Dl + depth))   # my upper halo  <- upper neighbour's bottom owned planes
+
+
+class _Pending:
+    def __init__(self, finish: Callable[[], None]):
+        self.finish = finish
+
+
+class DistExchanger:
+    """Ring halo exchange with torch.distributed point-to-point ops (NCCL: one grouped send/recv pair per
+    neighbour over NVLink; gloo on CPU).  All tensors of one call travel in ONE message per direction.
+    On CUDA the exchange runs on its own high-priority stream: ``start`` makes that stream wait for the work
+    queued so far (the boundary planes), the caller then queues the interior planes on its stream, and
+    ``finish`` makes the caller's stream wait for the halos."""
+
+    def __init__(self, layout: SlabLayout, device, group=None):
+        import torch.distributed as dist
+
+        self.dist = dist
+        self.layout = layout
+        self.device = torch.device(device)
+        self.group = group
+        self._bufs = {}
+        self.stream = torch.cuda.Stream(device=self.device, priority=-1) if self.device.type == "cuda" else None
+        self.calls = 0
+        self.bytes_per_direction = 0
+
+    def _buffers(self, key, n):
+        b = self._bufs.get(key)
+        if b is None or b[0].numel() != n:
+            b = [torch.empty(n, dtype=torch.float32, device=self.device) for _ in range(4)]
+            self._bufs[key] = b
+        return b
+
+    def _run(self, tensors: Sequence[torch.Tensor], depth: int):
+        lay, dist = self.layout, self.dist
+        to_up, to_down, from_down, from_up = _send_slices(lay, depth)
+        sizes = [t[:, :, to_up].numel() for t in tensors]
+        n = sum(sizes)
+        key = (tuple(t.data_ptr() for t in tensors), depth)
+        s_up, s_down, r_down, r_up = self._buffers(key, n)
+        o = 0
+        for t, sz in zip(tensors, sizes):
+            s_up[o:o + sz].view_as(t[:, :, to_up]).copy_(t[:, :, to_up])
+            s_down[o:o + sz].view_as(t[:, :, to_down]).copy_(t[:, :, to_down])
+            o += sz
+        ops = [dist.P2POp(dist.isend, s_up, lay.up, self.group), dist.P2POp(dist.isend, s_down, lay.down, self.group),
+               dist.P2POp(dist.irecv, r_down, lay.down, self.group), dist.P2POp(dist.irecv, r_up, lay.up, self.group)]
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+        o = 0
+        for t, sz in zip(tensors, sizes):
+            t[:, :, from_down].copy_(r_down[o:o + sz].view_as(t[:, :, from_down]))
+            t[:, :, from_up].copy_(r_up[o:o + sz].view_as(t[:, :, from_up]))
+            o += sz
+        self.calls += 1
+        self.bytes_per_direction += 4 * n
+
+    def start(self, tensors, depth) -> _Pending:
+        if self.stream is None:
+            self._run(tensors, depth)
+            return _Pending(lambda: None)
+        cur = torch.cuda.current_stream(self.device)
+        self.stream.wait_stream(cur)
+        with torch.cuda.stream(self.stream):
+            self._run(tensors, depth)
+        return _Pending(lambda: cur.wait_stream(self.stream))
+
+    def exchange(self, tensors, depth):
+        self.start(tensors, depth).finish()
+
+
+def loopback_exchange(layouts: Sequence[SlabLayout], tensor_sets: Sequence[Sequence[torch.Tensor]], depth: int):
+    """Halo exchange between P virtual ranks living in one process (tensor_sets[r] = rank r's tensors)."""
+    P = len(layouts)
+    for r in range(P):
+        lay = layouts[r]
+        to_up, to_down, from_down, from_up = _send_slices(lay, depth)
+        for mine, below, above in zip(tensor_sets[r], tensor_sets[lay.down], tensor_sets[lay.up]):
+            mine[:, :, from_down].copy_(below[:, :, to_up])
+            mine[:, :, from_up].copy_(above[:, :, to_down])
+
+
+@dataclass
+class HaloRequest:
+    """Yielded by SlabFerroSolver._step_gen: fill `depth` halo planes of `tensors`; `overlap` (optional)
+    queues work that does not touch those halos and may run while they travel."""
+    tensors: List[torch.Tensor]
+    depth: int
+    overlap: Optional[Callable[[], None]] = None
+
+
+# ---------------------------------------------------------------------------------------------------
+# the slab solver
+# ---------------------------------------------------------------------------------------------------
+class SlabFerroSolver:
+    """One z-slab of FerroSolver's 3-D HCZ (+ magnetic) step.  Same constructor vocabulary as FerroSolver;
+    ``flags`` / ``magnetic_flags`` are the slab-LOCAL arrays [1, 1, D, H, W] (halo planes included, e.g. from
+    slab_shell_flags or SlabLayout.take), H_ext is a uniform vector (all the reference's demos use one:
+    demo_3d_LBM_Rosensweig_instability.py:147-148)."""
+
+    def __init__(self, layout: SlabLayout, flags: torch.Tensor, *, exchanger=None, density_liquid=0.2508,
+                 density_gas=0.02381, rho_liquid=0.2508, rho_gas=0.02381, kappa=0.01, tau_f=0.68, tau_g=0.68,
+                 tau=1.0, contact_angle=0.5 * math.pi, gravity=1e-4, dx=1.0, dt=1.0,
+                 magnetic_flags: Optional[torch.Tensor] = None, H_ext=None, n_sweeps: int = 30,
+                 magnetic_path: str = "faithful", keep_force: bool = False):
+        self.layout = layout
+        self.flags = H.need_cuda(flags, "flags", torch.uint8)
+        self.device = self.flags.device
+        dim, self.B, _, self.D, self.Hh, self.W = H.dims(self.flags)
+        if dim != 3 or self.D != layout.D:
+            raise RuntimeError(f"flags must be the slab-local [B,1,{layout.D},H,W] array")
+        if layout.Dl < 4:
+            raise RuntimeError("need at least 4 owned planes per slab")
+        self.dim, self.Q = 3, 19
+        self.res = (self.D, self.Hh, self.W)
+        self.dx, self.dt = float(dx), float(dt)
+        self._density_liquid, self._density_gas = density_liquid, density_gas
+        self._rho_liquid, self._rho_gas = rho_liquid, rho_gas
+        self._kappa, self._tau_f, self._tau_g, self._tau = kappa, tau_f, tau_g, tau
+        self.gravity = float(gravity)
+        self.cot = H.cot_of_contact_angle(contact_angle)
+        self.n_sweeps = int(n_sweeps)
+        self.params = H.fluid_params(self, self.dx, self.dt, cot=self.cot, gravity=self.gravity)
+        self.exchanger = exchanger
+        opts = dict(dtype=torch.float32, device=self.device)
+        sc = lambda c: torch.zeros((self.B, c, *self.res), **opts)  # noqa: E731
+        self.rho, self.pressure, self.vel = sc(1), sc(1), sc(3)
+        self.force = sc(3) if keep_force else None
+        self._ws = sc(3)
+        self._f, self._g = [sc(19), sc(19)], [sc(19), sc(19)]
+        self._cur = 0
+        self.steps_done = 0
+        self._timing = None
+        self.magnetic = magnetic_flags is not None
+        if self.magnetic:
+            self.mflags = H.need_cuda(magnetic_flags, "magnetic_flags", torch.uint8)
+            if H_ext is None or torch.is_tensor(H_ext):
+                raise NotImplementedError("slab mode takes a uniform applied field (3 floats)")
+            vec = [float(v) for v in H_ext]
+            self._H_uniform = (ctypes.c_double * 3)(*vec)
+            D, Hh, W = self.res
+            self.H_ext_mac = [torch.full((self.B, 1, D, Hh, W + 1), vec[0], **opts),
+                              torch.full((self.B, 1, D, Hh + 1, W), vec[1], **opts),
+                              torch.full((self.B, 1, D + 1, Hh, W), vec[2], **opts)]
+            if magnetic_path == "auto":
+                magnetic_path = "scalar" if float(tau) == 1.0 else "faithful"
+            if magnetic_path not in ("scalar", "faithful"):
+                raise ValueError("magnetic_path must be 'auto', 'faithful' or 'scalar'")
+            if magnetic_path == "scalar" and float(tau) != 1.0:
+                raise RuntimeError("magnetic_path='scalar' needs tau == 1")
+            self.magnetic_path = magnetic_path
+            self.psi, self._rhs, self._chi = sc(1), sc(1), sc(1)
+            self._h = [sc(19), sc(19)] if magnetic_path == "faithful" else [sc(2), sc(2)]
+            self._mcur = 0
+        else:
+            self.magnetic_path, self.mflags = None, None
+
+    # ---- state (slab-local views; *_owned drop the halo planes) -----------------------------------
+    @property
+    def f(self):
+        return self._f[self._cur]
+
+    @property
+    def g(self):
+        return self._g[self._cur]
+
+    @property
+    def h(self):
+        return self._h[self._mcur] if self.magnetic and self.magnetic_path == "faithful" else None
+
+    def owned(self, name: str) -> torch.Tensor:
+        return self.layout.owned(getattr(self, name)).contiguous()
+
+    def initialize(self, rho: torch.Tensor):
+        """rho: slab-local [B,1,D,H,W] with valid halo planes.  p = EOS(rho), f = feq(rho, 0), g = geq,
+        h = 0 (demo_3d_LBM_Rosensweig_instability.py:128-145) -- pointwise, so halos come out valid too."""
+        from .collision import LBMCollision3d
+        from .macro_compute import LBMMacroCompute3d
+
+        rho = H.need_cuda(rho, "rho")
+        self.rho.copy_(rho)
+        self.vel.zero_()
+        kw = dict(density_liquid=self._density_liquid, density_gas=self._density_gas, rho_liquid=self._rho_liquid,
+                  rho_gas=self._rho_gas, device=self.device)
+        macro, col = LBMMacroCompute3d(**kw), LBMCollision3d(tau=1.0, **kw)
+        self.pressure.copy_(macro.get_pressure(dx=self.dx, dt=self.dt, density=rho))
+        zero = torch.zeros_like(self.vel)
+        f0 = col.get_feq_(dx=self.dx, dt=self.dt, rho=rho, vel=self.vel, force=zero)
+        g0 = col.get_geq_(dx=self.dx, dt=self.dt, rho=self.rho, vel=self.vel, density=rho, pressure=self.pressure,
+                          force=zero, feq=f0)
+        self._cur = 0
+        self._f[0].copy_(f0)
+        self._g[0].copy_(g0)
+        del f0, g0
+        if self.magnetic:
+            for t in self._h:
+                t.zero_()
+            self.psi.zero_()
+            self._mcur = 0
+        self.steps_done = 0
+        return self
+
+    # ---- timing hooks (same contract as FerroSolver) ----------------------------------------------
+    def enable_kernel_timing(self, on: bool = True):
+        self._timing = {"sweeps": [], "collide_stream": []} if on else None
+
+    def kernel_times_ms(self):
+        return {k: [a.elapsed_time(b) for a, b in v] for k, v in (self._timing or {}).items()}
+
+    def _mark(self):
+        if self._timing is None:
+            return None
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        return e
+
+    # ---- launches ---------------------------------------------------------------------------------
+    def _launch(self, name, *args, planes):
+        zb, zn = planes
+        if zn <= 0:
+            return
+        slab = self.layout.slab(zb, zn)
+        H.launch(name, self.device, *args, ctypes.byref(slab), self.B, self.D, self.Hh, self.W)
+
+    def _split(self):
+        """(interior planes, [boundary plane ranges]) of the owned block"""
+        h, Dl = self.layout.halo, self.layout.Dl
+        return (h + 1, Dl - 2), [(h, 1), (h + Dl - 1, 1)]
+
+    def _step_gen(self):
+        L, p = self.layout, H.ptr
+        own, d1 = L.planes_owned(), L.planes_depth(1)
+        interior, edges = self._split()
+        cur, nxt = self._cur, 1 - self._cur
+        f, g = self._f[cur], self._g[cur]
+        chi = self._chi if self.magnetic else None
+
+        def moments(planes):
+            self._launch("lbmff_slab_hcz_moments_d3q19", p(f), p(self.flags), p(self.rho), p(chi), self.params,
+                         planes=planes)
+
+        # f, g halos travel while the interior moments are taken
+        yield HaloRequest([f, g], 1, overlap=lambda: moments(interior))
+        for e in edges:
+            moments(e)
+        yield HaloRequest([self.rho, self.pressure] + ([chi] if self.magnetic else []), L.halo)
+        if self.magnetic:
+            self._launch("lbmff_slab_magnetic_source_3d", p(chi), p(self.mflags), *[p(t) for t in self.H_ext_mac],
+                         self.dx, p(self._rhs), planes=own)
+            t0 = self._mark()
+            sweep = ("lbmff_slab_magnetic_sweep_d3q19" if self.magnetic_path == "faithful"
+                     else "lbmff_slab_magnetic_sweep_scalar_3d")
+            for s in range(self.n_sweeps):
+                m = self._mcur
+                src, dst = self._h[m], self._h[1 - m]
+                psi = p(self.psi if s == self.n_sweeps - 1 else None)
+                tail = (float(self._tau), self.dx, self.dt) if self.magnetic_path == "faithful" else (self.dx, self.dt)
+
+                def run(planes, src=src, dst=dst, psi=psi, tail=tail):
+                    self._launch(sweep, p(src), p(dst), p(self.mflags), p(self._rhs), psi, *tail, planes=planes)
+
+                for e in edges:
+                    run(e)
+                self._mcur = 1 - m
+                yield HaloRequest([dst], 1, overlap=lambda run=run: run(interior))
+            t1 = self._mark()
+            if self._timing is not None:
+                self._timing["sweeps"].append((t0, t1))
+            self._launch("lbmff_slab_shell_rule_3d", p(self.psi), p(self.mflags), planes=own)
+            self._launch("lbmff_slab_shell_rule_3d", p(chi), p(self.flags), planes=d1)
+        # ordered wetting boundary: x faces one plane beyond the owned block (the y faces read them)
+        self._launch("lbmff_slab_hcz_wetting_3d", p(self.rho), p(self.flags), self.params, 1, planes=d1)
+        self._launch("lbmff_slab_hcz_wetting_3d", p(self.rho), p(self.flags), self.params, 2, planes=own)
+        yield HaloRequest([self.rho], L.halo)
+        self._launch("lbmff_slab_hcz_fields_3d", p(self.rho), p(self.flags), p(self.pressure), self.params,
+                     p(self._ws), planes=d1)
+        hu = ctypes.cast(self._H_uniform, ctypes.c_void_p) if self.magnetic else ctypes.c_void_p(0)
+
+        def collide(planes):
+            self._launch("lbmff_slab_hcz_collide_stream_d3q19", p(f), p(g), p(self._f[nxt]), p(self._g[nxt]),
+                         p(self.rho), p(self.flags), p(self.mflags), p(self._ws), p(chi),
+                         p(self.psi if self.magnetic else None), hu, self.params, p(self.vel), p(self.pressure),
+                         p(self.force), planes=planes)
+
+        t0 = self._mark()
+        if self.magnetic:   # psi halos travel while the interior planes collide
+            yield HaloRequest([self.psi], 1, overlap=lambda: collide(interior))
+        else:
+            collide(interior)
+        for e in edges:
+            collide(e)
+        t1 = self._mark()
+        if self._timing is not None:
+            self._timing["collide_stream"].append((t0, t1))
+        self._cur = nxt
+        self.steps_done += 1
+
+    def step(self, n: int = 1):
+        """Advance n outer steps (asynchronous on torch's current stream; halos via self.exchanger)."""
+        if self.exchanger is None:
+            raise RuntimeError("SlabFerroSolver.step needs an exchanger (DistExchanger); virtual ranks use "
+                               "step_virtual_ranks")
+        for _ in range(int(n)):
+            for req in self._step_gen():
+                pending = self.exchanger.start(req.tensors, req.depth)
+                if req.overlap is not None:
+                    req.overlap()
+                pending.finish()
+        return self
+
+    @property
+    def phi(self):
+        """Order parameter of the owned planes (demo_3d...Rosensweig...py:162)."""
+        dg, dl, rg, rl = self._density_gas, self._density_liquid, self._rho_gas, self._rho_liquid
+        density = dg + (dl - dg) * ((self.layout.owned(self.rho) - rg) / (rl - rg))
+        return -(2.0 * (density - dg) / (dl - dg) - 1.0)
+
+    def step_host(self, faces_host, phi_host):
+        """One outer step through host buffers (same contract as FerroSolver.step_host): upload this slab's
+        applied-field faces from pinned memory, step, download phi of the owned planes."""
+        if faces_host is not None:
+            for dst, src in zip(self.H_ext_mac, faces_host):
+                dst.copy_(src, non_blocking=True)
+        self.step(1)
+        if phi_host is not None:
+            phi_host.copy_(self.phi, non_blocking=True)
+        return self
+
+    @property
+    def launches_per_step(self) -> int:
+        return 3 + 5 + 1 + 3 + ((1 + 3 * self.n_sweeps + 2) if self.magnetic else 0)
+
+    def total_mass(self) -> float:
+        return float(self.layout.owned(self.f).double().sum().item())
+
+    # ---- benchmark constructor --------------------------------------------------------------------
+    @classmethod
+    def rosensweig(cls, res_per_rank, path, device, world, rank, mag=100.0, n_sweeps=30):
+        """Weak-scaling Rosensweig case: every rank owns res_per_rank = (Dl, H, W); global depth world*Dl."""
+        from . import initializers as I
+
+        Dl, Hh, W = res_per_rank
+        lay = SlabLayout(Dl * world, world, rank)
+        flags = slab_shell_flags(lay, Hh, W, device=device)
+        mflags = slab_shell_flags(lay, Hh, W, open_axes=(1,), device=device)
+        rho = I.rosensweig_rho((lay.D, Hh, W), flags, global_depth=lay.Dg, z_offset=lay.zoff)
+        s = cls(lay, flags, exchanger=DistExchanger(lay, device), magnetic_flags=mflags, H_ext=[0.0, mag, 0.0],
+                n_sweeps=n_sweeps, magnetic_path=path, contact_angle=0.5 * math.pi, gravity=1e-4)
+        return s.initialize(rho)
+
+
+def step_virtual_ranks(solvers: Sequence[SlabFerroSolver], n: int = 1):
+    """Advance P slab solvers living in ONE process (one GPU) in lockstep, halos by device copies.
+    This is the bit-for-bit test vehicle of the decomposition."""
+    layouts = [s.layout for s in solvers]
+    for _ in range(int(n)):
+        gens = [s._step_gen() for s in solvers]
+        while True:
+            reqs = [next(g, None) for g in gens]
+            if all(r is None for r in reqs):
+                break
+            if any(r is None for r in reqs):
+                raise RuntimeError("virtual ranks fell out of lockstep")
+            loopback_exchange(layouts, [r.tensors for r in reqs], reqs[0].depth)
+            for r in reqs:
+                if r.overlap is not None:
+                    r.overlap()
+    return solvers
