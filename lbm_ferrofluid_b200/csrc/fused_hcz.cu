@@ -57,12 +57,18 @@ __global__ void __launch_bounds__(kThreads) k_hcz_moments(const float* __restric
   if (chi) chi[b * g.N + i] = susceptibility(phase_field(affine_density(s, k.aff), k.aff), k.sm);
 }
 
-struct AffineRho {
-  const float* __restrict__ rho;
+// density = affine(rho) sampled at constant offsets from an interior centre cell; the division by
+// (rho_liquid - rho_gas) is a multiplication by the host-formed reciprocal (differs from affine_density by
+// one rounding; held to the fp32-floor parity bar like the rest of the fused step).
+struct CentredDensity {
+  const float* __restrict__ p;  // rho, offset to the centre cell
+  int W;
+  long long HW;
+  int cx, cy, cz;
   Affine A;
-  Grid g;
   __device__ __forceinline__ float operator()(int x, int y, int z) const {
-    return affine_density(__ldg(rho + lin(g, x, y, z)), A);
+    const float r = __ldg(p + (x - cx) + (long long)(y - cy) * W + (long long)(z - cz) * HW);
+    return A.dg + A.ddiff * ((r - A.rg) * A.inv_rdiff);
   }
 };
 
@@ -84,7 +90,8 @@ __global__ void __launch_bounds__(kThreads) k_hcz_fields(const float* __restrict
   const long long j = lin(g, x, y, z);
   const bool shell = on_shell(c, g);
   float lap = 0.0f;
-  if (!shell || flags[b * g.N + i] == LBMFF_OBSTACLE) lap = laplacian_at<DIM>(AffineRho{r, k.aff, g}, x, y, z, k.dx2);
+  if (!shell || flags[b * g.N + i] == LBMFF_OBSTACLE)
+    lap = laplacian_at<DIM>(CentredDensity{r + j, g.W, (long long)g.H * g.W, x, y, z, k.aff}, x, y, z, k.dx2);
   w[i] = lap;
   const float rj = r[j];
   w[g.N + i] = eos_cs(rj, k.cs2, k.a_eos, 1) - rj * k.cs2;
@@ -93,17 +100,56 @@ __global__ void __launch_bounds__(kThreads) k_hcz_fields(const float* __restrict
 }
 
 // psi on OBSTACLE shell cells of mflags <- nearest interior value (what get_grad(psi) reads there);
-// wall-cell psi is never observed otherwise.  Surface kernel: one thread per cell of the six faces.
+// wall-cell psi is never observed otherwise.  Surface kernels: k_shell_rule_rim visits the x / y rim of every
+// plane of the range (planes on the global z shell are skipped), k_shell_rule_plane one whole z-shell plane.
 template <int DIM>
-__global__ void __launch_bounds__(kThreads) k_shell_rule(float* __restrict__ field,
-                                                         const uint8_t* __restrict__ flags, Grid g) {
-  const long long i = g.i0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= g.i1) return;
+__device__ __forceinline__ void shell_rule_cell(float* __restrict__ field, const uint8_t* __restrict__ flags,
+                                                int x, int y, int z, const Grid& g) {
+  const long long i = lin(g, x, y, z);
+  if (flags[i] != LBMFF_OBSTACLE) return;
+  field[i] = field[lin(g, interior(x, g.W), interior(y, g.H), DIM == 3 ? interior_z(g, z) : 0)];
+}
+
+template <int DIM>
+__global__ void __launch_bounds__(kThreads) k_shell_rule_rim(float* __restrict__ field,
+                                                             const uint8_t* __restrict__ flags, int zlo, int zn,
+                                                             Grid g) {
+  const int rim = 2 * g.W + 2 * (g.H - 2);
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long long)zn * rim) return;
+  const int z = zlo + (int)(t / rim), k = (int)(t % rim);
+  if (DIM == 3 && z_on_shell(g, z)) return;
+  int x, y;
+  if (k < g.W) { x = k; y = 0; }
+  else if (k < 2 * g.W) { x = k - g.W; y = g.H - 1; }
+  else { y = 1 + (k - 2 * g.W) / 2; x = ((k - 2 * g.W) & 1) ? g.W - 1 : 0; }
   const long long b = blockIdx.y;
-  const Cell c = cell_of(i, g);
-  if (!on_shell(c, g) || flags[b * g.N + i] != LBMFF_OBSTACLE) return;
-  field[b * g.N + i] = field[b * g.N + lin(g, interior(c.x, g.W), interior(c.y, g.H),
-                                           DIM == 3 ? interior_z(g, c.z) : 0)];
+  shell_rule_cell<DIM>(field + b * g.N, flags + b * g.N, x, y, z, g);
+}
+
+template <int DIM>
+__global__ void __launch_bounds__(kThreads) k_shell_rule_plane(float* __restrict__ field,
+                                                               const uint8_t* __restrict__ flags, int z, Grid g) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long long)g.H * g.W) return;
+  const long long b = blockIdx.y;
+  shell_rule_cell<DIM>(field + b * g.N, flags + b * g.N, (int)(t % g.W), (int)(t / g.W), z, g);
+}
+
+template <int DIM>
+static void launch_shell_rule(float* field, const uint8_t* flags, const Grid& g, cudaStream_t st) {
+  const long long HW = (long long)g.H * g.W;
+  const int zlo = (int)(g.i0 / HW), zn = (int)((g.i1 - g.i0) / HW);
+  const long long rim = 2LL * g.W + 2LL * (g.H - 2);
+  k_shell_rule_rim<DIM><<<dim3(blocks_for(zn * rim), (unsigned)g.B), kThreads, 0, st>>>(field, flags, zlo, zn, g);
+  if (DIM == 3 && g.Dg > 1) {
+    for (int side = 0; side < 2; ++side) {   // local plane of global plane 0 / Dg-1, when this range holds it
+      int l = (side ? g.Dg - 1 : 0) - g.zoff;
+      l = l < 0 ? l + g.Dg : (l >= g.Dg ? l - g.Dg : l);
+      if (l >= zlo && l < zlo + zn)
+        k_shell_rule_plane<DIM><<<dim3(blocks_for(HW), (unsigned)g.B), kThreads, 0, st>>>(field, flags, l, g);
+    }
+  }
 }
 
 struct HextUniform {
@@ -141,9 +187,15 @@ k_hcz_collide_stream(const float* __restrict__ f_in, const float* __restrict__ g
     }
     return;
   }
-  float gv[L::Q];
+  // all 2Q population loads are issued first: they are the only HBM-latency loads of the kernel (the stencil
+  // fields below mostly hit L1/L2), and at 512 threads/SM this keeps ~78 KB per SM in flight
+  float gv[L::Q], fv[L::Q];
 #pragma unroll
-  for (int q = 0; q < L::Q; ++q) gv[q] = __ldg(gi + q * g.N + nb.at(q, 1));
+  for (int q = 0; q < L::Q; ++q) {
+    const long long j = q * g.N + nb.at(q, 1);
+    gv[q] = __ldg(gi + j);
+    fv[q] = __ldg(fi + j);
+  }
   // ---- capillary_process part 2 at a FLUID cell (HCZ_3d.py:217-261); all stencil inputs carry the
   // get_grad shell rule in their data, so the 18-point stencils are plain constant-offset loads
   const int x = interior(c.x, g.W), y = interior(c.y, g.H), z = DIM == 3 ? interior_z(g, c.z) : 0;
@@ -194,7 +246,7 @@ k_hcz_collide_stream(const float* __restrict__ f_in, const float* __restrict__ g
   }
   const float p = s - k.half_dt * dot;
   pressure[b * g.N + i] = p;
-  // ---- HCZ collision (HCZ_3d.py:283-361); f is pulled one population at a time to keep registers low
+  // ---- HCZ collision (HCZ_3d.py:283-361)
   const HczCell<DIM> C = hcz_prepare<DIM>(rho, u, dn, p, F, gfai, gprho, k);
   bool relaxed = false;
   if constexpr (DIM == 2) {
@@ -210,7 +262,7 @@ k_hcz_collide_stream(const float* __restrict__ f_in, const float* __restrict__ g
   }
 #pragma unroll
   for (int q = 0; q < L::Q; ++q) {
-    float fq = __ldg(fi + q * g.N + nb.at(q, 1));
+    float fq = fv[q];
     float gq = gv[q];
     hcz_collide_q<DIM>(q, C, k, fq, gq, relaxed);
     fo[q * g.N + i] = fq;
@@ -299,7 +351,7 @@ static int fields_impl(float* rho, const uint8_t* flags, const float* pressure, 
 template <int DIM>
 static int shell_rule_impl(float* field, const uint8_t* flags, const Grid& g, cudaStream_t st, const char* where) {
   if (!(field && flags)) return bad_arg(where, "null pointer");
-  k_shell_rule<DIM><<<dim3(blocks_for(g.i1 - g.i0), (unsigned)g.B), kThreads, 0, st>>>(field, flags, g);
+  launch_shell_rule<DIM>(field, flags, g, st);
   return check_launch(where);
 }
 
@@ -320,8 +372,8 @@ static int collide_stream_impl(const float* f_in, const float* g_in, float* f_ou
   const dim3 grid(blocks_for(g.i1 - g.i0), (unsigned)g.B);
   if (magnetic) {
     if (fold_shell_rule) {
-      k_shell_rule<DIM><<<grid, kThreads, 0, st>>>(psi, mflags, g);
-      k_shell_rule<DIM><<<grid, kThreads, 0, st>>>(chi, flags, g);
+      launch_shell_rule<DIM>(psi, mflags, g, st);
+      launch_shell_rule<DIM>(chi, flags, g, st);
     }
     k_hcz_collide_stream<DIM, true><<<grid, kThreads, 0, st>>>(f_in, g_in, f_out, g_out, rho, flags, ws, chi, psi,
                                                                Hext, hu, vel, pressure, force_out, k, kbc_on_g,

@@ -26,6 +26,7 @@ struct Affine {
   float ddiff;  // density_liquid - density_gas
   float rg;     // rho_gas
   float rdiff;  // rho_liquid - rho_gas
+  float inv_rdiff;  // 1 / (rho_liquid - rho_gas), formed in double (fused kernels only)
 };
 __device__ __forceinline__ float affine_density(float rho, const Affine& A) {
   return A.dg + A.ddiff * ((rho - A.rg) / A.rdiff);
@@ -265,6 +266,7 @@ inline Consts make_consts(double dx, double dt, double tau = 1.0, double tau_f =
   k.dx = (float)dx; k.dt = (float)dt; k.c = (float)c; k.cs2 = (float)cs2;
   k.a_eos = (float)(12.0 * cs2); k.dx2 = (float)(dx * dx);
   k.aff.dg = (float)dg; k.aff.ddiff = (float)(dl - dg); k.aff.rg = (float)rg; k.aff.rdiff = (float)(rl - rg);
+  k.aff.inv_rdiff = (float)(1.0 / (rl - rg));
   const double eps = 0.1 * dx;
   k.sm.eps = (float)eps; k.sm.half_inv = (float)(0.5 / eps); k.sm.pi_inv = (float)(3.141592653589793 / eps);
   k.kappa = (float)kappa; k.tau = (float)tau; k.tau_f = (float)tau_f; k.tau_g = (float)tau_g;
