@@ -27,6 +27,7 @@ struct Grid {
   int Dg;       // global number of z planes (== D on one GPU)
   int zoff;     // global z of local plane 0, in (-Dg, Dg)
   long long i0, i1;  // cell range processed by fused kernels, default [0, N)
+  int zb, zn;        // the same range in planes: [zb, zb + zn)
 };
 
 __host__ __device__ inline Grid make_grid(int B, int D, int H, int W) {
@@ -35,6 +36,7 @@ __host__ __device__ inline Grid make_grid(int B, int D, int H, int W) {
   g.N = (long long)D * H * W;
   g.Dg = D; g.zoff = 0;
   g.i0 = 0; g.i1 = g.N;
+  g.zb = 0; g.zn = D;
   return g;
 }
 
@@ -43,6 +45,7 @@ inline Grid make_slab_grid(int B, int D, int H, int W, int Dg, int zoff, int zb,
   Grid g = make_grid(B, D, H, W);
   g.Dg = Dg; g.zoff = zoff;
   g.i0 = (long long)zb * H * W; g.i1 = (long long)(zb + zn) * H * W;
+  g.zb = zb; g.zn = zn;
   return g;
 }
 
@@ -143,7 +146,76 @@ __device__ __forceinline__ int local_z(const Grid& g, int gz) {
   return l < g.D ? l : -1;
 }
 
+// ---- 32-bit neighbour addressing -----------------------------------------------------------------------
+// Cells per batch item fit in an int (checked on the host: N < 2^31), so a neighbour is "my cell index plus a
+// signed 32-bit delta" and a population value is base_q[cell], base_q = lattice + q * N formed once per q in
+// 64 bits (uniform across the grid).  The periodic wrap lives in the six per-axis deltas; a pulled or pushed
+// population then costs one or two integer adds instead of a 64-bit multiply-add chain per load.
+struct Nbr {
+  int xm, xp, ym, yp, zm, zp;  // index deltas to x-1, x+1, y-1, y+1, z-1, z+1 (periodic in the local array)
+  template <class C>
+  __device__ __forceinline__ Nbr(const C& c, const Grid& g) {
+    const int HW = g.H * g.W;
+    xm = c.x == 0 ? g.W - 1 : -1;
+    xp = c.x == g.W - 1 ? 1 - g.W : 1;
+    ym = c.y == 0 ? (g.H - 1) * g.W : -g.W;
+    yp = c.y == g.H - 1 ? -(g.H - 1) * g.W : g.W;
+    zm = g.D > 1 ? (c.z == 0 ? (g.D - 1) * HW : -HW) : 0;
+    zp = g.D > 1 ? (c.z == g.D - 1 ? -(g.D - 1) * HW : HW) : 0;
+  }
+  // delta to the cell at x - s*e_q (s = +1: pull source, s = -1: the cell population q moves to)
+  template <int DIM>
+  __device__ __forceinline__ int at(int q, int s) const {
+    using L = Lat<DIM>;
+    const int ex = s * L::ex(q), ey = s * L::ey(q), ez = s * L::ez(q);
+    return (ex == 1 ? xm : (ex == -1 ? xp : 0)) + (ey == 1 ? ym : (ey == -1 ? yp : 0)) +
+           (DIM == 3 ? (ez == 1 ? zm : (ez == -1 ? zp : 0)) : 0);
+  }
+};
+
+// Read-only global load the compiler may neither drop nor merge with a later conditional reload of the same
+// variable: the fused kernels issue the common-path (FLUID) loads before the cell's flag byte has arrived.
+__device__ __forceinline__ float ld_spec(const float* p) {
+  float v;
+  asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
+}
+
 constexpr int kThreads = 256;
+
+// ---- division-free launch geometry of the fused kernels ---------------------------------------------------
+// threadIdx.x/blockIdx.x run along x, threadIdx.y/blockIdx.y along y, blockIdx.z over the planes (batch items
+// are separate launches with offset pointers, so no address carries a batch term): the cell
+// coordinates come straight from the hardware indices -- no integer division (there is no divide unit: the two
+// divisions of cell_of cost ~90 of the ~700 instructions of the sweep kernel).  Rows narrower than 256 cells
+// pack several rows into one block.
+struct PlaneLaunch {
+  dim3 grid, block;
+};
+inline PlaneLaunch plane_launch(const Grid& g) {
+  int bx = ((g.W + 31) / 32) * 32;
+  if (bx > kThreads) bx = kThreads;
+  int by = kThreads / bx;
+  if (by > g.H) by = g.H;
+  if (by < 1) by = 1;
+  PlaneLaunch L;
+  L.block = dim3((unsigned)bx, (unsigned)by, 1);
+  L.grid = dim3((unsigned)((g.W + bx - 1) / bx), (unsigned)((g.H + by - 1) / by), (unsigned)g.zn);
+  return L;
+}
+struct PlaneCell {
+  int x, y, z, i;  // i = cell index inside one batch item (N < 2^31, checked on the host)
+  bool live;
+};
+__device__ __forceinline__ PlaneCell plane_cell(const Grid& g) {
+  PlaneCell c;
+  c.x = blockIdx.x * blockDim.x + threadIdx.x;
+  c.y = blockIdx.y * blockDim.y + threadIdx.y;
+  c.z = g.zb + blockIdx.z;
+  c.live = c.x < g.W && c.y < g.H;
+  c.i = (c.z * g.H + c.y) * g.W + c.x;
+  return c;
+}
 
 inline unsigned blocks_for(long long n, int threads = kThreads) {
   return (unsigned)((n + threads - 1) / threads);

@@ -44,49 +44,66 @@ __global__ void __launch_bounds__(kThreads) k_mag_source(const float* __restrict
 // ---- population-faithful fused sweep ----------------------------------------------------------
 // OBSTACLE cell x: out_q(x) = in_opp(q)(x + e_q)   (stream, then bounce; walls never collide)
 // other cells:     h_q = in_q(x - e_q); psi = sum_{q>=1} h_q / (1 - w0); out_q = collide(h_q, psi, rhs)
-template <int DIM, bool WRITE_PSI>
+// Element index of population q at cell i (+ delta): 32-bit unsigned when the whole lattice has fewer than
+// 2^32 elements (every named configuration: 19 * 512^3 = 2.55e9), so an address is one IMAD.WIDE.U32.
+template <bool IDX32>
+struct PopIndex;
+template <>
+struct PopIndex<true> {
+  unsigned N;
+  __device__ __forceinline__ explicit PopIndex(const Grid& g) : N((unsigned)g.N) {}
+  __device__ __forceinline__ unsigned operator()(int q, int cell) const { return (unsigned)q * N + (unsigned)cell; }
+};
+template <>
+struct PopIndex<false> {
+  long long N;
+  __device__ __forceinline__ explicit PopIndex(const Grid& g) : N(g.N) {}
+  __device__ __forceinline__ long long operator()(int q, int cell) const { return q * N + cell; }
+};
+
+// HINT: 0 default caching, 1 streaming stores (st.global.cs)
+template <int DIM, bool WRITE_PSI, int HINT = 0, bool IDX32 = true>
 __global__ void __launch_bounds__(kThreads) k_mag_sweep(const float* __restrict__ hin, float* __restrict__ hout,
                                                         const uint8_t* __restrict__ mflags,
                                                         const float* __restrict__ rhs, float* __restrict__ psi_out,
                                                         Consts k, Grid g) {
   using L = Lat<DIM>;
-  const long long i = g.i0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= g.i1) return;
-  const long long b = blockIdx.y;
-  const float* in = hin + b * L::Q * g.N;
-  float* out = hout + b * L::Q * g.N;
-  const Cell c = cell_of(i, g);
-  const int xm = wrap(c.x - 1, g.W), xp = wrap(c.x + 1, g.W);
-  const int ym = wrap(c.y - 1, g.H), yp = wrap(c.y + 1, g.H);
-  const int zm = DIM == 3 ? wrap(c.z - 1, g.D) : 0, zp = DIM == 3 ? wrap(c.z + 1, g.D) : 0;
-  const bool obst = mflags[b * g.N + i] == LBMFF_OBSTACLE;
+  const PlaneCell c = plane_cell(g);
+  if (!c.live) return;
+  const int i = c.i;
+  const float* in = hin;
+  float* out = hout;
+  const Nbr nb(c, g);
+  const PopIndex<IDX32> at(g);
+  // The 19 pulls are issued BEFORE the flag byte is known (a load that waits for the flag costs a second full
+  // memory round trip per thread).  A wall cell needs out_q(x) = in_opp(q)(x + e_q), which is exactly the value
+  // pulled for population opp(q): bounce-back is a permutation of the same 19 loads.
   float hv[L::Q];
-  if (!obst) {
 #pragma unroll
-    for (int q = 0; q < L::Q; ++q) {
-      const int sx = L::ex(q) == 1 ? xm : (L::ex(q) == -1 ? xp : c.x);
-      const int sy = L::ey(q) == 1 ? ym : (L::ey(q) == -1 ? yp : c.y);
-      const int sz = L::ez(q) == 1 ? zm : (L::ez(q) == -1 ? zp : c.z);
-      hv[q] = __ldg(in + q * g.N + lin(g, sx, sy, sz));
-    }
-  } else {  // walls are rare: divergence only in warps that touch one
+  for (int q = 0; q < L::Q; ++q) hv[q] = ld_spec(in + at(q, i + nb.at<DIM>(q, 1)));
+  const bool obst = mflags[i] == LBMFF_OBSTACLE;
+  const float r = __ldg(rhs + i);
+  if (obst) {  // divergence only in warps that touch a wall
 #pragma unroll
-    for (int q = 0; q < L::Q; ++q) {
-      const int sx = L::ex(q) == 1 ? xp : (L::ex(q) == -1 ? xm : c.x);
-      const int sy = L::ey(q) == 1 ? yp : (L::ey(q) == -1 ? ym : c.y);
-      const int sz = L::ez(q) == 1 ? zp : (L::ez(q) == -1 ? zm : c.z);
-      hv[q] = __ldg(in + L::opp(q) * g.N + lin(g, sx, sy, sz));
+    for (int q = 1; q < L::Q; ++q) {
+      if (q < L::opp(q)) {
+        const float t = hv[q];
+        hv[q] = hv[L::opp(q)];
+        hv[L::opp(q)] = t;
+      }
     }
   }
   const float psi = psi_of<DIM>(hv);
-  if (WRITE_PSI) psi_out[b * g.N + i] = psi;
+  if (WRITE_PSI) psi_out[i] = psi;
   if (!obst) {
-    const float r = rhs[b * g.N + i];
 #pragma unroll
     for (int q = 0; q < L::Q; ++q) hv[q] = mag_collide_q<DIM>(q, hv[q], psi, r, k);
   }
 #pragma unroll
-  for (int q = 0; q < L::Q; ++q) out[q * g.N + i] = hv[q];
+  for (int q = 0; q < L::Q; ++q) {
+    if (HINT >= 1) __stcs(out + at(q, i), hv[q]);
+    else out[at(q, i)] = hv[q];
+  }
 }
 
 // ---- population-faithful sweep, four cells per thread -------------------------------------------------
@@ -299,6 +316,25 @@ __global__ void __launch_bounds__(kThreads) k_mag_materialize(const float* __res
   }
 }
 
+template <int DIM>
+static void launch_sweep(bool wp, int hint, bool idx32, const PlaneLaunch& pl, cudaStream_t st, const float* in,
+                         float* out, const uint8_t* mflags, const float* rhs, float* psi_out, const Consts& k,
+                         const Grid& g) {
+#define LBMFF_SW(WP, HI, IX)                                                                                \
+  k_mag_sweep<DIM, WP, HI, IX><<<pl.grid, pl.block, 0, st>>>(in + b * Lat<DIM>::Q * g.N, out + b * Lat<DIM>::Q * g.N, \
+                                                             mflags + b * g.N, rhs + b * g.N,                    \
+                                                             psi_out ? psi_out + b * g.N : nullptr, k, g)
+  for (long long b = 0; b < g.B; ++b) {
+    if (idx32) {
+      if (hint) { if (wp) LBMFF_SW(true, 1, true); else LBMFF_SW(false, 1, true); }
+      else { if (wp) LBMFF_SW(true, 0, true); else LBMFF_SW(false, 0, true); }
+    } else {
+      if (wp) LBMFF_SW(true, 0, false); else LBMFF_SW(false, 0, false);
+    }
+  }
+#undef LBMFF_SW
+}
+
 // LBMFF_SWEEP_VARIANT = 1 (one cell per thread, default: 3.80 ms per 512^3 sweep) | 4 (four cells per thread: 3.87 ms)
 static int sweep_variant() {
   static const int v = [] {
@@ -314,12 +350,14 @@ static int sweeps_impl(float* hA, float* hB, const uint8_t* mflags, const float*
   if (!(hA && hB && hA != hB && mflags && rhs)) return bad_arg(where, "null or aliased pointer");
   if (n < 1) return bad_arg(where, "n_sweeps must be >= 1");
   if (!(tau > 0)) return bad_arg(where, "tau must be positive");
+  if (g.N > 0x7fffffffLL) return bad_arg(where, "more than 2^31-1 cells per batch item");
   const Consts k = make_consts(dx, dt, tau);
   const dim3 grid(blocks_for(g.i1 - g.i0), (unsigned)g.B);
   // four cells per thread needs 16-byte aligned rows and plane ranges
   const bool vec4 = sweep_variant() == 4 && g.W % 4 == 0 && g.i0 % 4 == 0 && g.i1 % 4 == 0 &&
                     ((uintptr_t)hA | (uintptr_t)hB | (uintptr_t)rhs | (uintptr_t)psi_out | (uintptr_t)mflags) % 16 == 0;
   const dim3 grid4(blocks_for((g.i1 - g.i0) / 4), (unsigned)g.B);
+  const PlaneLaunch pl = plane_launch(g);
   for (int s = 0; s < n; ++s) {
     const float* in = (s & 1) ? hB : hA;
     float* out = (s & 1) ? hA : hB;
@@ -328,8 +366,8 @@ static int sweeps_impl(float* hA, float* hB, const uint8_t* mflags, const float*
       if (wp) k_mag_sweep_v4<DIM, true><<<grid4, kThreads, 0, st>>>(in, out, mflags, rhs, psi_out, k, g);
       else k_mag_sweep_v4<DIM, false><<<grid4, kThreads, 0, st>>>(in, out, mflags, rhs, psi_out, k, g);
     } else {
-      if (wp) k_mag_sweep<DIM, true><<<grid, kThreads, 0, st>>>(in, out, mflags, rhs, psi_out, k, g);
-      else k_mag_sweep<DIM, false><<<grid, kThreads, 0, st>>>(in, out, mflags, rhs, psi_out, k, g);
+      launch_sweep<DIM>(wp, sweep_variant() == 2 ? 1 : 0, (long long)Lat<DIM>::Q * g.N < 0xffffffffLL, pl, st, in, out,
+                        mflags, rhs, psi_out, k, g);
     }
   }
   return check_launch(where);
