@@ -173,6 +173,23 @@ struct Nbr {
   }
 };
 
+// Element index of population q at cell i (+ delta): 32-bit unsigned when the whole lattice has fewer than
+// 2^32 elements (every named configuration: 19 * 512^3 = 2.55e9), so an address is one IMAD.WIDE.U32.
+template <bool IDX32>
+struct PopIndex;
+template <>
+struct PopIndex<true> {
+  unsigned N;
+  __device__ __forceinline__ explicit PopIndex(const Grid& g) : N((unsigned)g.N) {}
+  __device__ __forceinline__ unsigned operator()(int q, int cell) const { return (unsigned)q * N + (unsigned)cell; }
+};
+template <>
+struct PopIndex<false> {
+  long long N;
+  __device__ __forceinline__ explicit PopIndex(const Grid& g) : N(g.N) {}
+  __device__ __forceinline__ long long operator()(int q, int cell) const { return q * N + cell; }
+};
+
 // Read-only global load the compiler may neither drop nor merge with a later conditional reload of the same
 // variable: the fused kernels issue the common-path (FLUID) loads before the cell's flag byte has arrived.
 __device__ __forceinline__ float ld_spec(const float* p) {

@@ -35,26 +35,30 @@ struct PullIndex {
 
 // rho = sum of the pulled f on non-OBSTACLE cells (old rho kept on OBSTACLE, LBM_macro_compute_3d.py:93-98) and,
 // for the magnetic subsystem, chi = k (1 - H_eps(phi(density(rho)))) on EVERY cell (demo :162, LBM_magnetic_3d.py:162)
-template <int DIM>
+// Launch geometry / addressing: common.cuh (plane_launch, Nbr, PopIndex); pulls are issued before the flag.
+template <int DIM, bool IDX32>
 __global__ void __launch_bounds__(kThreads) k_hcz_moments(const float* __restrict__ f,
                                                           const uint8_t* __restrict__ flags, float* __restrict__ rho,
                                                           float* __restrict__ chi, Consts k, Grid g) {
   using L = Lat<DIM>;
-  const long long i = g.i0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= g.i1) return;
-  const long long b = blockIdx.y;
+  const PlaneCell c = plane_cell(g);
+  if (!c.live) return;
+  const int i = c.i;
+  const Nbr nb(c, g);
+  const PopIndex<IDX32> at(g);
+  float fv[L::Q];
+#pragma unroll
+  for (int q = 0; q < L::Q; ++q) fv[q] = ld_spec(f + at(q, i + nb.at<DIM>(q, 1)));
   float s;
-  if (flags[b * g.N + i] == LBMFF_OBSTACLE) {
-    s = rho[b * g.N + i];
+  if (flags[i] == LBMFF_OBSTACLE) {
+    s = rho[i];
   } else {
-    const PullIndex<DIM> nb(cell_of(i, g), g);
-    const float* fb = f + b * L::Q * g.N;
     s = 0.0f;
 #pragma unroll
-    for (int q = 0; q < L::Q; ++q) s += __ldg(fb + q * g.N + nb.at(q, 1));
-    rho[b * g.N + i] = s;
+    for (int q = 0; q < L::Q; ++q) s += fv[q];
+    rho[i] = s;
   }
-  if (chi) chi[b * g.N + i] = susceptibility(phase_field(affine_density(s, k.aff), k.aff), k.sm);
+  if (chi) chi[i] = susceptibility(phase_field(affine_density(s, k.aff), k.aff), k.sm);
 }
 
 // density = affine(rho) sampled at constant offsets from an interior centre cell; the division by
@@ -62,12 +66,11 @@ __global__ void __launch_bounds__(kThreads) k_hcz_moments(const float* __restric
 // one rounding; held to the fp32-floor parity bar like the rest of the fused step).
 struct CentredDensity {
   const float* __restrict__ p;  // rho, offset to the centre cell
-  int W;
-  long long HW;
+  int W, HW;
   int cx, cy, cz;
   Affine A;
   __device__ __forceinline__ float operator()(int x, int y, int z) const {
-    const float r = __ldg(p + (x - cx) + (long long)(y - cy) * W + (long long)(z - cz) * HW);
+    const float r = __ldg(p + ((x - cx) + (y - cy) * W + (z - cz) * HW));
     return A.dg + A.ddiff * ((r - A.rg) * A.inv_rdiff);
   }
 };
@@ -80,23 +83,21 @@ __global__ void __launch_bounds__(kThreads) k_hcz_fields(const float* __restrict
                                                          const uint8_t* __restrict__ flags,
                                                          const float* __restrict__ pressure, float* __restrict__ ws,
                                                          Consts k, Grid g) {
-  const long long i = g.i0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= g.i1) return;
-  const long long b = blockIdx.y;
-  const Cell c = cell_of(i, g);
-  const float* r = rho + b * g.N;
-  float* w = ws + b * 3 * g.N;
+  const PlaneCell c = plane_cell(g);
+  if (!c.live) return;
+  const int i = c.i;
   const int x = interior(c.x, g.W), y = interior(c.y, g.H), z = DIM == 3 ? interior_z(g, c.z) : 0;
-  const long long j = lin(g, x, y, z);
-  const bool shell = on_shell(c, g);
+  const int HW = g.H * g.W;
+  const int j = i + (x - c.x) + (y - c.y) * g.W + (z - c.z) * HW;   // nearest interior cell
+  const bool shell = j != i;
   float lap = 0.0f;
-  if (!shell || flags[b * g.N + i] == LBMFF_OBSTACLE)
-    lap = laplacian_at<DIM>(CentredDensity{r + j, g.W, (long long)g.H * g.W, x, y, z, k.aff}, x, y, z, k.dx2);
-  w[i] = lap;
-  const float rj = r[j];
-  w[g.N + i] = eos_cs(rj, k.cs2, k.a_eos, 1) - rj * k.cs2;
+  if (!shell || flags[i] == LBMFF_OBSTACLE)
+    lap = laplacian_at<DIM>(CentredDensity{rho + j, g.W, HW, x, y, z, k.aff}, x, y, z, k.dx2);
+  ws[i] = lap;
+  const float rj = rho[j];
+  ws[g.N + i] = eos_cs(rj, k.cs2, k.a_eos, 1) - rj * k.cs2;
   // density of the previous macro_compute at an interior cell = affine(rho) there (wetting touches the shell only)
-  w[2 * g.N + i] = pressure[b * g.N + j] - k.cs2 * affine_density(rj, k.aff);
+  ws[2 * g.N + i] = pressure[j] - k.cs2 * affine_density(rj, k.aff);
 }
 
 // psi on OBSTACLE shell cells of mflags <- nearest interior value (what get_grad(psi) reads there);
@@ -156,57 +157,62 @@ struct HextUniform {
   float v[3];
 };
 
-template <int DIM, bool MAGNETIC>
+// 32-bit constant-offset sampler around an interior centre cell (see CentredField in physics.cuh)
+struct Centred32 {
+  const float* __restrict__ p;  // already offset to the centre cell
+  int W, HW;
+  int cx, cy, cz;
+  __device__ __forceinline__ float operator()(int x, int y, int z) const {
+    return __ldg(p + ((x - cx) + (y - cy) * W + (z - cz) * HW));
+  }
+};
+
+template <int DIM, bool MAGNETIC, bool IDX32>
 __global__ void __launch_bounds__(kThreads, 2)
-k_hcz_collide_stream(const float* __restrict__ f_in, const float* __restrict__ g_in, float* __restrict__ f_out,
-                     float* __restrict__ g_out, const float* __restrict__ rho_, const uint8_t* __restrict__ flags,
+k_hcz_collide_stream(const float* __restrict__ fi, const float* __restrict__ gi, float* __restrict__ fo,
+                     float* __restrict__ go, const float* __restrict__ rho_, const uint8_t* __restrict__ flags,
                      const float* __restrict__ ws, const float* __restrict__ chi, const float* __restrict__ psi,
                      const float* __restrict__ Hext, HextUniform Hu, float* __restrict__ vel,
                      float* __restrict__ pressure, float* __restrict__ force_out, Consts k, int kbc_on_g,
                      KbcScalars K, Grid g) {
   using L = Lat<DIM>;
-  const long long i = g.i0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= g.i1) return;
-  const long long b = blockIdx.y;
-  const Cell c = cell_of(i, g);
-  const PullIndex<DIM> nb(c, g);
-  const float* fi = f_in + b * L::Q * g.N;
-  const float* gi = g_in + b * L::Q * g.N;
-  float* fo = f_out + b * L::Q * g.N;
-  float* go = g_out + b * L::Q * g.N;
-  const uint8_t fl = flags[b * g.N + i];
-  if (fl != LBMFF_FLUID) {
-    // OBSTACLE: stream then full-way bounce, out_q(x) = in_opp(q)(x + e_q).  Other non-FLUID cells are only
-    // streamed (HCZ collides FLUID cells only, HCZ_3d.py:357-359).  Neither collides.
-    const bool obst = fl == LBMFF_OBSTACLE;
-#pragma unroll
-    for (int q = 0; q < L::Q; ++q) {
-      const long long j = obst ? L::opp(q) * g.N + nb.at(q, -1) : q * g.N + nb.at(q, 1);
-      fo[q * g.N + i] = __ldg(fi + j);
-      go[q * g.N + i] = __ldg(gi + j);
-    }
-    return;
-  }
-  // all 2Q population loads are issued first: they are the only HBM-latency loads of the kernel (the stencil
-  // fields below mostly hit L1/L2), and at 512 threads/SM this keeps ~78 KB per SM in flight
+  const PlaneCell c = plane_cell(g);
+  if (!c.live) return;
+  const int i = c.i;
+  const Nbr nb(c, g);
+  const PopIndex<IDX32> at(g);
+  // All 2Q pulls are issued first, before the flag byte is known: they are the only HBM-latency loads of the
+  // kernel (the stencil fields below mostly hit L1/L2); at 512 threads/SM this keeps ~78 KB per SM in flight.
   float gv[L::Q], fv[L::Q];
 #pragma unroll
   for (int q = 0; q < L::Q; ++q) {
-    const long long j = q * g.N + nb.at(q, 1);
-    gv[q] = __ldg(gi + j);
-    fv[q] = __ldg(fi + j);
+    const auto j = at(q, i + nb.at<DIM>(q, 1));
+    gv[q] = ld_spec(gi + j);
+    fv[q] = ld_spec(fi + j);
+  }
+  const uint8_t fl = flags[i];
+  if (fl != LBMFF_FLUID) {
+    // OBSTACLE: stream then full-way bounce, out_q(x) = in_opp(q)(x + e_q) -- the value pulled for opp(q).
+    // Other non-FLUID cells are only streamed (HCZ collides FLUID cells only, HCZ_3d.py:357-359).
+    const bool obst = fl == LBMFF_OBSTACLE;
+#pragma unroll
+    for (int q = 0; q < L::Q; ++q) {
+      fo[at(q, i)] = obst ? fv[L::opp(q)] : fv[q];
+      go[at(q, i)] = obst ? gv[L::opp(q)] : gv[q];
+    }
+    return;
   }
   // ---- capillary_process part 2 at a FLUID cell (HCZ_3d.py:217-261); all stencil inputs carry the
   // get_grad shell rule in their data, so the 18-point stencils are plain constant-offset loads
   const int x = interior(c.x, g.W), y = interior(c.y, g.H), z = DIM == 3 ? interior_z(g, c.z) : 0;
-  const long long j0 = lin(g, x, y, z);
-  const long long HW = (long long)g.H * g.W;
-  const float* w = ws + b * 3 * g.N + j0;
+  const int HW = g.H * g.W;
+  const int j0 = i + (x - c.x) + (y - c.y) * g.W + (z - c.z) * HW;
+  const float* w = ws + j0;
   float glap[3], gfai[3], gprho[3];
-  grad_at_fast<DIM>(CentredField{w, g.W, HW, x, y, z}, x, y, z, k.inv12dx, glap);
-  grad_at_fast<DIM>(CentredField{w + g.N, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gfai);
-  grad_at_fast<DIM>(CentredField{w + 2 * g.N, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gprho);
-  const float rho = rho_[b * g.N + i];
+  grad_at_fast<DIM>(Centred32{w, g.W, HW, x, y, z}, x, y, z, k.inv12dx, glap);
+  grad_at_fast<DIM>(Centred32{w + g.N, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gfai);
+  grad_at_fast<DIM>(Centred32{w + 2 * g.N, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gprho);
+  const float rho = rho_[i];
   const float dn = affine_density(rho, k.aff);
   float F[DIM];
 #pragma unroll
@@ -216,11 +222,11 @@ k_hcz_collide_stream(const float* __restrict__ f_in, const float* __restrict__ g
   }
   if (MAGNETIC) {
     float gchi[3], gpsi[3], H2 = 0.0f;
-    grad_at_fast<DIM>(CentredField{chi + b * g.N + j0, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gchi);
-    grad_at_fast<DIM>(CentredField{psi + b * g.N + j0, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gpsi);
+    grad_at_fast<DIM>(Centred32{chi + j0, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gchi);
+    grad_at_fast<DIM>(Centred32{psi + j0, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gpsi);
 #pragma unroll
     for (int a = 0; a < DIM; ++a) {
-      const float he = Hext ? __ldg(Hext + (b * DIM + a) * g.N + i) : Hu.v[a];
+      const float he = Hext ? __ldg(Hext + a * g.N + i) : Hu.v[a];
       const float ht = he - gpsi[a];  // H_ext + H_int, H_int = -grad(psi) (LBM_magnetic_3d.py:184)
       H2 += ht * ht;
     }
@@ -240,12 +246,12 @@ k_hcz_collide_stream(const float* __restrict__ f_in, const float* __restrict__ g
 #pragma unroll
   for (int a = 0; a < DIM; ++a) {
     u[a] = (m[a] * k.c + k.half_dt_RT * F[a]) * inv_dn;
-    vel[(b * DIM + a) * g.N + i] = u[a];
-    if (force_out) force_out[(b * DIM + a) * g.N + i] = F[a];
+    vel[a * g.N + i] = u[a];
+    if (force_out) force_out[a * g.N + i] = F[a];
     dot += u[a] * gprho[a];
   }
   const float p = s - k.half_dt * dot;
-  pressure[b * g.N + i] = p;
+  pressure[i] = p;
   // ---- HCZ collision (HCZ_3d.py:283-361)
   const HczCell<DIM> C = hcz_prepare<DIM>(rho, u, dn, p, F, gfai, gprho, k);
   bool relaxed = false;
@@ -265,8 +271,8 @@ k_hcz_collide_stream(const float* __restrict__ f_in, const float* __restrict__ g
     float fq = fv[q];
     float gq = gv[q];
     hcz_collide_q<DIM>(q, C, k, fq, gq, relaxed);
-    fo[q * g.N + i] = fq;
-    go[q * g.N + i] = gq;
+    fo[at(q, i)] = fq;
+    go[at(q, i)] = gq;
   }
 }
 
@@ -331,7 +337,18 @@ template <int DIM>
 static int moments_impl(const float* f, const uint8_t* flags, float* rho, float* chi, const lbmff_fluid_params* p,
                         const Grid& g, cudaStream_t st, const char* where) {
   if (!(f && flags && rho && p)) return bad_arg(where, "null pointer");
-  k_hcz_moments<DIM><<<dim3(blocks_for(g.i1 - g.i0), (unsigned)g.B), kThreads, 0, st>>>(f, flags, rho, chi, consts_of(p), g);
+  if (g.N > 0x7fffffffLL) return bad_arg(where, "more than 2^31-1 cells per batch item");
+  const PlaneLaunch pl = plane_launch(g);
+  const Consts k = consts_of(p);
+  const long long Q = Lat<DIM>::Q;
+  for (long long b = 0; b < g.B; ++b) {
+    if (Q * g.N < 0xffffffffLL)
+      k_hcz_moments<DIM, true><<<pl.grid, pl.block, 0, st>>>(f + b * Q * g.N, flags + b * g.N, rho + b * g.N,
+                                                             chi ? chi + b * g.N : nullptr, k, g);
+    else
+      k_hcz_moments<DIM, false><<<pl.grid, pl.block, 0, st>>>(f + b * Q * g.N, flags + b * g.N, rho + b * g.N,
+                                                              chi ? chi + b * g.N : nullptr, k, g);
+  }
   return check_launch(where);
 }
 
@@ -343,8 +360,13 @@ static int fields_impl(float* rho, const uint8_t* flags, const float* pressure, 
   if (g.W < 4 || g.H < 4 || (DIM == 3 && g.D < 4)) return bad_arg(where, "every extent must be >= 4");
   const Consts k = consts_of(p);
   if (wetting) launch_wetting<DIM>(rho, flags, k.cot, g, st, stage);
-  if (fields)
-    k_hcz_fields<DIM><<<dim3(blocks_for(g.i1 - g.i0), (unsigned)g.B), kThreads, 0, st>>>(rho, flags, pressure, ws, k, g);
+  if (fields) {
+    if (g.N > 0x7fffffffLL / 3) return bad_arg(where, "more than (2^31-1)/3 cells per batch item");
+    const PlaneLaunch pl = plane_launch(g);
+    for (long long b = 0; b < g.B; ++b)
+      k_hcz_fields<DIM><<<pl.grid, pl.block, 0, st>>>(rho + b * g.N, flags + b * g.N, pressure + b * g.N,
+                                                      ws + b * 3 * g.N, k, g);
+  }
   return check_launch(where);
 }
 
@@ -369,19 +391,24 @@ static int collide_stream_impl(const float* f_in, const float* g_in, float* f_ou
   const Consts k = consts_of(p);
   HextUniform hu{{0.f, 0.f, 0.f}};
   if (Hu) for (int a = 0; a < DIM; ++a) hu.v[a] = (float)Hu[a];
-  const dim3 grid(blocks_for(g.i1 - g.i0), (unsigned)g.B);
-  if (magnetic) {
-    if (fold_shell_rule) {
-      launch_shell_rule<DIM>(psi, mflags, g, st);
-      launch_shell_rule<DIM>(chi, flags, g, st);
-    }
-    k_hcz_collide_stream<DIM, true><<<grid, kThreads, 0, st>>>(f_in, g_in, f_out, g_out, rho, flags, ws, chi, psi,
-                                                               Hext, hu, vel, pressure, force_out, k, kbc_on_g,
-                                                               make_kbc(p->tau_g), g);
-  } else {
-    k_hcz_collide_stream<DIM, false><<<grid, kThreads, 0, st>>>(f_in, g_in, f_out, g_out, rho, flags, ws, chi, psi,
-                                                                Hext, hu, vel, pressure, force_out, k, kbc_on_g,
-                                                                make_kbc(p->tau_g), g);
+  if (g.N > 0x7fffffffLL / 3) return bad_arg(where, "more than (2^31-1)/3 cells per batch item");
+  if (magnetic && fold_shell_rule) {
+    launch_shell_rule<DIM>(psi, mflags, g, st);
+    launch_shell_rule<DIM>(chi, flags, g, st);
+  }
+  const PlaneLaunch pl = plane_launch(g);
+  const long long Q = Lat<DIM>::Q, N = g.N;
+  const KbcScalars K = make_kbc(p->tau_g);
+  for (long long b = 0; b < g.B; ++b) {
+#define LBMFF_CS(MAG, IX)                                                                                         \
+  k_hcz_collide_stream<DIM, MAG, IX><<<pl.grid, pl.block, 0, st>>>(                                               \
+      f_in + b * Q * N, g_in + b * Q * N, f_out + b * Q * N, g_out + b * Q * N, rho + b * N, flags + b * N,       \
+      ws + b * 3 * N, MAG ? chi + b * N : nullptr, MAG ? psi + b * N : nullptr, Hext ? Hext + b * DIM * N : nullptr, \
+      hu, vel + b * DIM * N, pressure + b * N, force_out ? force_out + b * DIM * N : nullptr, k, kbc_on_g, K, g)
+    const bool ix = Q * N < 0xffffffffLL;
+    if (magnetic) { if (ix) LBMFF_CS(true, true); else LBMFF_CS(true, false); }
+    else { if (ix) LBMFF_CS(false, true); else LBMFF_CS(false, false); }
+#undef LBMFF_CS
   }
   return check_launch(where);
 }

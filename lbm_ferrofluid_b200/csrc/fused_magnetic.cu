@@ -17,8 +17,8 @@ namespace lbmff {
 
 struct ChiArray {
   const float* __restrict__ chi;
-  Grid g;
-  __device__ __forceinline__ float operator()(int x, int y, int z) const { return __ldg(chi + lin(g, x, y, z)); }
+  int W, HW;
+  __device__ __forceinline__ float operator()(int x, int y, int z) const { return __ldg(chi + (z * HW + y * W + x)); }
 };
 
 // rhs (FLUID cells of mflags, else 0) from the cell-centred susceptibility chi (raw, no shell rule)
@@ -26,41 +26,17 @@ template <int DIM>
 __global__ void __launch_bounds__(kThreads) k_mag_source(const float* __restrict__ chi,
                                                          const uint8_t* __restrict__ mflags, HextFaces Hf,
                                                          float* __restrict__ rhs, float dx, Grid g) {
-  const long long i = g.i0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= g.i1) return;
-  const long long b = blockIdx.y;
+  const PlaneCell c = plane_cell(g);
+  if (!c.live) return;
   float r = 0.0f;
-  if (mflags[b * g.N + i] == LBMFF_FLUID) {
-    const Cell c = cell_of(i, g);
-    HextFaces Hb = Hf;
-    Hb.x += b * (long long)g.D * g.H * (g.W + 1);
-    Hb.y += b * (long long)g.D * (g.H + 1) * g.W;
-    if (DIM == 3) Hb.z += b * (long long)(g.D + 1) * g.H * g.W;
-    r = magnetic_rhs_at<DIM>(ChiArray{chi + b * g.N, g}, Hb, c.x, c.y, c.z, g, dx);
-  }
-  rhs[b * g.N + i] = r;
+  if (mflags[c.i] == LBMFF_FLUID)
+    r = magnetic_rhs_at<DIM>(ChiArray{chi, g.W, g.H * g.W}, Hf, c.x, c.y, c.z, g, dx);
+  rhs[c.i] = r;
 }
 
 // ---- population-faithful fused sweep ----------------------------------------------------------
 // OBSTACLE cell x: out_q(x) = in_opp(q)(x + e_q)   (stream, then bounce; walls never collide)
 // other cells:     h_q = in_q(x - e_q); psi = sum_{q>=1} h_q / (1 - w0); out_q = collide(h_q, psi, rhs)
-// Element index of population q at cell i (+ delta): 32-bit unsigned when the whole lattice has fewer than
-// 2^32 elements (every named configuration: 19 * 512^3 = 2.55e9), so an address is one IMAD.WIDE.U32.
-template <bool IDX32>
-struct PopIndex;
-template <>
-struct PopIndex<true> {
-  unsigned N;
-  __device__ __forceinline__ explicit PopIndex(const Grid& g) : N((unsigned)g.N) {}
-  __device__ __forceinline__ unsigned operator()(int q, int cell) const { return (unsigned)q * N + (unsigned)cell; }
-};
-template <>
-struct PopIndex<false> {
-  long long N;
-  __device__ __forceinline__ explicit PopIndex(const Grid& g) : N(g.N) {}
-  __device__ __forceinline__ long long operator()(int q, int cell) const { return q * N + cell; }
-};
-
 // HINT: 0 default caching, 1 streaming stores (st.global.cs)
 template <int DIM, bool WRITE_PSI, int HINT = 0, bool IDX32 = true>
 __global__ void __launch_bounds__(kThreads) k_mag_sweep(const float* __restrict__ hin, float* __restrict__ hout,
@@ -221,60 +197,47 @@ __global__ void __launch_bounds__(kThreads) k_mag_sweep_v4(const float* __restri
 // that comes back from a wall cell is this cell's own outgoing value of two sweeps ago (full-way bounce-back
 // = one sweep of delay), i.e. prev at the SAME cell, read by the same thread before it overwrites it.
 template <int DIM, bool WRITE_PSI>
-__global__ void __launch_bounds__(kThreads) k_mag_sweep_scalar(const float* __restrict__ cur, float* prev_out,
-                                                               const uint8_t* __restrict__ mflags,
+__global__ void __launch_bounds__(kThreads) k_mag_sweep_scalar(const float* __restrict__ ca, float* pa,
+                                                               const uint8_t* __restrict__ fl,
                                                                const float* __restrict__ rhs,
                                                                float* __restrict__ psi_out, Consts k, Grid g) {
   using L = Lat<DIM>;
-  const long long i = g.i0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= g.i1) return;
-  const long long b = blockIdx.y;
-  const float* ca = cur + b * 2 * g.N;
-  float* pa = prev_out + b * 2 * g.N;
-  const uint8_t* fl = mflags + b * g.N;
-  if (fl[i] == LBMFF_OBSTACLE) return;  // wall state is implicit (never observed: get_grad masks it)
-  const Cell c = cell_of(i, g);
-  const int xm = wrap(c.x - 1, g.W), xp = wrap(c.x + 1, g.W);
-  const int ym = wrap(c.y - 1, g.H), yp = wrap(c.y + 1, g.H);
-  const int zm = DIM == 3 ? wrap(c.z - 1, g.D) : 0, zp = DIM == 3 ? wrap(c.z + 1, g.D) : 0;
+  const PlaneCell c = plane_cell(g);
+  if (!c.live) return;
+  const int i = c.i, N = (int)g.N;
+  const Nbr nb(c, g);
+  // the 18 neighbour values are requested before any flag is looked at
   float hv[L::Q];
   hv[0] = 0.0f;
-  bool need_prev = false;
-  long long src[L::Q];
-#pragma unroll
-  for (int q = 1; q < L::Q; ++q) {
-    const int sx = L::ex(q) == 1 ? xm : (L::ex(q) == -1 ? xp : c.x);
-    const int sy = L::ey(q) == 1 ? ym : (L::ey(q) == -1 ? yp : c.y);
-    const int sz = L::ez(q) == 1 ? zm : (L::ez(q) == -1 ? zp : c.z);
-    src[q] = lin(g, sx, sy, sz);
-  }
-  // walls lie on the outer shell only (checked by the host), so only shell-adjacent cells test flags
-  const bool near_shell = c.x <= 1 || c.x >= g.W - 2 || c.y <= 1 || c.y >= g.H - 2 ||
-                          (DIM == 3 && near_z_shell(g, c.z));
-  unsigned wall_mask = 0;
-  if (near_shell) {
-#pragma unroll
-    for (int q = 1; q < L::Q; ++q)
-      if (fl[src[q]] == LBMFF_OBSTACLE) wall_mask |= 1u << q;
-    need_prev = wall_mask != 0;
-  }
-  float p_axis = 0.f, p_diag = 0.f;
-  if (need_prev) {
-    p_axis = pa[i];
-    p_diag = pa[g.N + i];
-  }
 #pragma unroll
   for (int q = 1; q < L::Q; ++q) {
     const bool axis = (L::ex(q) != 0) + (L::ey(q) != 0) + (L::ez(q) != 0) == 1;
-    const float v = __ldg(ca + (axis ? 0 : g.N) + src[q]);
-    hv[q] = (wall_mask >> q) & 1u ? (axis ? p_axis : p_diag) : v;
+    hv[q] = ld_spec(ca + (axis ? 0 : N) + (i + nb.at<DIM>(q, 1)));
+  }
+  const float r = __ldg(rhs + i);
+  if (fl[i] == LBMFF_OBSTACLE) return;  // wall state is implicit (never observed: get_grad masks it)
+  // walls lie on the outer shell only (checked by the host), so only shell-adjacent cells test flags
+  const bool near_shell = c.x <= 1 || c.x >= g.W - 2 || c.y <= 1 || c.y >= g.H - 2 ||
+                          (DIM == 3 && near_z_shell(g, c.z));
+  if (near_shell) {
+    unsigned wall_mask = 0;
+#pragma unroll
+    for (int q = 1; q < L::Q; ++q)
+      if (fl[i + nb.at<DIM>(q, 1)] == LBMFF_OBSTACLE) wall_mask |= 1u << q;
+    if (wall_mask) {
+      const float p_axis = pa[i], p_diag = pa[N + i];
+#pragma unroll
+      for (int q = 1; q < L::Q; ++q) {
+        const bool axis = (L::ex(q) != 0) + (L::ey(q) != 0) + (L::ez(q) != 0) == 1;
+        if ((wall_mask >> q) & 1u) hv[q] = axis ? p_axis : p_diag;
+      }
+    }
   }
   const float psi = psi_of<DIM>(hv);
-  if (WRITE_PSI) psi_out[b * g.N + i] = psi;
-  const float r = rhs[b * g.N + i];
+  if (WRITE_PSI) psi_out[i] = psi;
   // representative populations of the two weight classes: q = 1 (axis), q = 5 (diagonal) in both lattices
   pa[i] = mag_collide_q<DIM>(1, 0.0f, psi, r, k);
-  pa[g.N + i] = mag_collide_q<DIM>(5, 0.0f, psi, r, k);
+  pa[N + i] = mag_collide_q<DIM>(5, 0.0f, psi, r, k);
 }
 
 // Rebuild the population-faithful h from the scalar state (for API users that ask for h).
@@ -378,15 +341,21 @@ static int sweeps_scalar_impl(float* aA, float* aB, const uint8_t* mflags, const
                               double dx, double dt, const Grid& g, cudaStream_t st, const char* where) {
   if (!(aA && aB && aA != aB && mflags && rhs)) return bad_arg(where, "null or aliased pointer");
   if (n < 1) return bad_arg(where, "n_sweeps must be >= 1");
+  if (g.N > 0x7fffffffLL / 2) return bad_arg(where, "more than (2^31-1)/2 cells per batch item");
   const Consts k = make_consts(dx, dt, 1.0);
-  const dim3 grid(blocks_for(g.i1 - g.i0), (unsigned)g.B);
+  const PlaneLaunch pl = plane_launch(g);
   for (int s = 0; s < n; ++s) {
     const float* cur = (s & 1) ? aB : aA;
     float* prev = (s & 1) ? aA : aB;
-    if (s == n - 1 && psi_out)
-      k_mag_sweep_scalar<DIM, true><<<grid, kThreads, 0, st>>>(cur, prev, mflags, rhs, psi_out, k, g);
-    else
-      k_mag_sweep_scalar<DIM, false><<<grid, kThreads, 0, st>>>(cur, prev, mflags, rhs, psi_out, k, g);
+    for (long long b = 0; b < g.B; ++b) {
+      if (s == n - 1 && psi_out)
+        k_mag_sweep_scalar<DIM, true><<<pl.grid, pl.block, 0, st>>>(cur + b * 2 * g.N, prev + b * 2 * g.N,
+                                                                    mflags + b * g.N, rhs + b * g.N,
+                                                                    psi_out + b * g.N, k, g);
+      else
+        k_mag_sweep_scalar<DIM, false><<<pl.grid, pl.block, 0, st>>>(cur + b * 2 * g.N, prev + b * 2 * g.N,
+                                                                     mflags + b * g.N, rhs + b * g.N, nullptr, k, g);
+    }
   }
   return check_launch(where);
 }
@@ -396,8 +365,13 @@ static int source_impl(const float* chi, const uint8_t* mflags, const float* Hx,
                        double dx, float* rhs, const Grid& g, cudaStream_t st, const char* where) {
   if (!(chi && mflags && Hx && Hy && (DIM == 2 || Hz) && rhs)) return bad_arg(where, "null pointer");
   if (g.W < 3 || g.H < 3 || (DIM == 3 && g.D < 3)) return bad_arg(where, "every extent must be >= 3");
-  k_mag_source<DIM><<<dim3(blocks_for(g.i1 - g.i0), (unsigned)g.B), kThreads, 0, st>>>(chi, mflags, HextFaces{Hx, Hy, Hz},
-                                                                             rhs, (float)dx, g);
+  if ((g.D + 1LL) * (g.H + 1LL) * (g.W + 1LL) > 0x7fffffffLL) return bad_arg(where, "grid too large for 32-bit cell indices");
+  const PlaneLaunch pl = plane_launch(g);
+  const long long D = g.D, H = g.H, W = g.W;
+  for (long long b = 0; b < g.B; ++b) {
+    const HextFaces Hf{Hx + b * D * H * (W + 1), Hy + b * D * (H + 1) * W, DIM == 3 ? Hz + b * (D + 1) * H * W : nullptr};
+    k_mag_source<DIM><<<pl.grid, pl.block, 0, st>>>(chi + b * g.N, mflags + b * g.N, Hf, rhs + b * g.N, (float)dx, g);
+  }
   return check_launch(where);
 }
 

@@ -24,8 +24,9 @@ __device__ __forceinline__ float magnetic_rhs_at(const Chi& chi, const HextFaces
   const int yl = clampi(y, 1, g.H - 1), yh = clampi(y + 1, 1, g.H - 1);
   const float fxl = (chi(xl, y, z) + chi(xl - 1, y, z)) * 0.5f, fxh = (chi(xh, y, z) + chi(xh - 1, y, z)) * 0.5f;
   const float fyl = (chi(x, yl, z) + chi(x, yl - 1, z)) * 0.5f, fyh = (chi(x, yh, z) + chi(x, yh - 1, z)) * 0.5f;
-  const long long ix = ((long long)z * g.H + y) * (g.W + 1) + x;
-  const long long iy = ((long long)z * (g.H + 1) + y) * g.W + x;
+  // 32-bit face indices: (D+1)(H+1)(W+1) < 2^31 is checked on the host
+  const int ix = (z * g.H + y) * (g.W + 1) + x;
+  const int iy = (z * (g.H + 1) + y) * g.W + x;
   float div = (fxh * __ldg(Hf.x + ix + 1) - fxl * __ldg(Hf.x + ix)) +
               (fyh * __ldg(Hf.y + iy + g.W) - fyl * __ldg(Hf.y + iy));
   if (DIM == 3) {
@@ -34,8 +35,8 @@ __device__ __forceinline__ float magnetic_rhs_at(const Chi& chi, const HextFaces
     const int zl = clampi(z + (clampi(gz, 1, g.Dg - 1) - gz), 1, g.D - 1);
     const int zh = clampi(z + (clampi(gz + 1, 1, g.Dg - 1) - gz), 1, g.D - 1);
     const float fzl = (chi(x, y, zl) + chi(x, y, zl - 1)) * 0.5f, fzh = (chi(x, y, zh) + chi(x, y, zh - 1)) * 0.5f;
-    const long long iz = ((long long)z * g.H + y) * g.W + x;
-    div = div + (fzh * __ldg(Hf.z + iz + (long long)g.H * g.W) - fzl * __ldg(Hf.z + iz));
+    const int iz = (z * g.H + y) * g.W + x;
+    div = div + (fzh * __ldg(Hf.z + iz + g.H * g.W) - fzl * __ldg(Hf.z + iz));
   }
   return div * dx / (1.0f + c0);
 }
