@@ -91,7 +91,10 @@ __global__ void __launch_bounds__(kThreads) k_hcz_fields(const float* __restrict
   const int j = i + (x - c.x) + (y - c.y) * g.W + (z - c.z) * HW;   // nearest interior cell
   const bool shell = j != i;
   float lap = 0.0f;
-  if (!shell || flags[i] == LBMFF_OBSTACLE)
+  // (slab decomposition: a halo plane that is a global z-shell plane clamps onto the outermost local plane,
+  //  whose stencil would leave the array; its lap is never consumed, so it is not evaluated)
+  const bool inside = DIM == 2 || (z >= 1 && z <= g.D - 2);
+  if (inside && (!shell || flags[i] == LBMFF_OBSTACLE))
     lap = laplacian_at<DIM>(CentredDensity{rho + j, g.W, HW, x, y, z, k.aff}, x, y, z, k.dx2);
   ws[i] = lap;
   const float rj = rho[j];

@@ -463,7 +463,8 @@ class SlabFerroSolver:
 
     @property
     def launches_per_step(self) -> int:
-        return 3 + 5 + 1 + 3 + ((1 + 3 * self.n_sweeps + 2) if self.magnetic else 0)
+        # moments x3, wetting 5, fields, collide x3, source, sweeps x3 each, shell rule (rim + z-shell planes) x2
+        return 3 + 5 + 1 + 3 + ((1 + 3 * self.n_sweeps + 4) if self.magnetic else 0)
 
     def total_mass(self) -> float:
         return float(self.layout.owned(self.f).double().sum().item())

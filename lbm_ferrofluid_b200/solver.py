@@ -275,7 +275,8 @@ class FerroSolver:
     @property
     def launches_per_step(self) -> int:
         wet = 5 if self.dim == 3 else 3
-        return 1 + (1 + self.n_sweeps if self.magnetic else 0) + wet + 1 + 1
+        shell = (6 if self.dim == 3 else 2) if self.magnetic else 0   # rim (+ two z-shell planes) for psi and chi
+        return 1 + (1 + self.n_sweeps if self.magnetic else 0) + wet + 1 + shell + 1
 
     def total_mass(self) -> float:
         """sum over ALL cells (walls included) of sum_q f: conserved to round-off."""
