@@ -240,6 +240,124 @@ __global__ void __launch_bounds__(kThreads) k_mag_sweep_scalar(const float* __re
   pa[N + i] = mag_collide_q<DIM>(5, 0.0f, psi, r, k);
 }
 
+// ---- tau == 1 scalar sweep, shared-memory tiled, marching along z (3-D) --------------------------------------
+// One block owns a 32 x 8 column of cells and walks zc planes upwards.  Each plane of the two state arrays is
+// staged once (with its one-cell x/y rim: 34 x 10 values) into a ring of four shared-memory slots, so a value is
+// fetched from L2 1.33 times instead of 9 times, and the 18 neighbour values of a cell are shared-memory reads.
+// Arithmetic and summation order are those of k_mag_sweep_scalar / k_mag_sweep: bit-identical psi.
+constexpr int kTX = 32, kTY = 8, kRing = 4;
+constexpr int kTileW = kTX + 2, kTileH = kTY + 2;
+
+template <bool WRITE_PSI>
+__global__ void __launch_bounds__(kTX* kTY) k_mag_sweep_scalar_tiled(const float* __restrict__ ca, float* pa,
+                                                                      const uint8_t* __restrict__ fl,
+                                                                      const float* __restrict__ rhs,
+                                                                      float* __restrict__ psi_out, Consts k, Grid g,
+                                                                      int zc) {
+  using L = Lat<3>;
+  __shared__ float sA[kRing][kTileH][kTileW];  // axis-class value
+  __shared__ float sD[kRing][kTileH][kTileW];  // diagonal-class value
+  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * kTX + tx;
+  const int x0 = blockIdx.x * kTX, y0 = blockIdx.y * kTY;
+  const int zs = g.zb + blockIdx.z * zc;
+  const int ze = min(zs + zc, g.zb + g.zn);
+  const int HW = g.H * g.W, N = (int)g.N;
+  // the (up to) two rim-tile elements this thread stages per plane: in-plane offsets, periodic in x and y
+  int off[2];
+  int sy[2], sx[2];
+#pragma unroll
+  for (int t = 0; t < 2; ++t) {
+    const int e = tid + t * kTX * kTY;
+    sy[t] = e / kTileW; sx[t] = e - sy[t] * kTileW;
+    int gx = x0 - 1 + sx[t], gy = y0 - 1 + sy[t];
+    gx = gx < 0 ? gx + g.W : gx; gy = gy < 0 ? gy + g.H : gy;
+    while (gx >= g.W) gx -= g.W;
+    while (gy >= g.H) gy -= g.H;
+    off[t] = e < kTileW * kTileH ? gy * g.W + gx : -1;
+  }
+  // software pipeline: plane z+2 is fetched into registers while plane z is computed, and put into its ring
+  // slot at the top of the next iteration -- no iteration waits for a global load it has just issued
+  float ra[2], rd[2];
+  auto fetch = [&](int z) {  // local plane z (periodic in the local array) -> registers
+    const int zz = z < 0 ? z + g.D : (z >= g.D ? z - g.D : z);
+#pragma unroll
+    for (int t = 0; t < 2; ++t)
+      if (off[t] >= 0) {
+        const int j = zz * HW + off[t];
+        ra[t] = __ldg(ca + j);
+        rd[t] = __ldg(ca + N + j);
+      }
+  };
+  auto put = [&](int z) {  // registers -> ring slot of plane z
+    const int slot = (z - zs + 1) & (kRing - 1);
+#pragma unroll
+    for (int t = 0; t < 2; ++t)
+      if (off[t] >= 0) {
+        sA[slot][sy[t]][sx[t]] = ra[t];
+        sD[slot][sy[t]][sx[t]] = rd[t];
+      }
+  };
+  fetch(zs - 1); put(zs - 1);
+  fetch(zs); put(zs);
+  fetch(zs + 1);
+  const int x = x0 + tx, y = y0 + ty;
+  const bool live = x < g.W && y < g.H;
+  const Nbr nb0(PlaneCell{live ? x : 0, live ? y : 0, 0, 0, true}, g);  // x / y deltas do not depend on z
+  // the cell's own source and flag are prefetched one plane ahead as well
+  const int i0 = live ? zs * HW + y * g.W + x : 0;
+  float r_next = __ldg(rhs + i0);
+  uint8_t f_next = fl[i0];
+  for (int z = zs; z < ze; ++z) {
+    put(z + 1);
+    if (z + 1 < ze) fetch(z + 2);
+    const float r = r_next;
+    const uint8_t fcell = f_next;
+    if (live && z + 1 < ze) {
+      r_next = __ldg(rhs + (z + 1) * HW + y * g.W + x);
+      f_next = fl[(z + 1) * HW + y * g.W + x];
+    }
+    __syncthreads();
+    if (live) {
+      const int i = z * HW + y * g.W + x;
+      if (fcell != LBMFF_OBSTACLE) {
+        const int s0 = (z - zs) & (kRing - 1), s1 = (z - zs + 1) & (kRing - 1), s2 = (z - zs + 2) & (kRing - 1);
+        const int sl[3] = {s0, s1, s2};  // planes z-1, z, z+1
+        float hv[L::Q];
+        hv[0] = 0.0f;
+#pragma unroll
+        for (int q = 1; q < L::Q; ++q) {
+          const bool axis = (L::ex(q) != 0) + (L::ey(q) != 0) + (L::ez(q) != 0) == 1;
+          const int px = tx + 1 - L::ex(q), py = ty + 1 - L::ey(q), ps = sl[1 - L::ez(q)];
+          hv[q] = axis ? sA[ps][py][px] : sD[ps][py][px];
+        }
+        // walls lie on the outer shell only (checked by the host), so only shell-adjacent cells test flags
+        const bool near_shell = x <= 1 || x >= g.W - 2 || y <= 1 || y >= g.H - 2 || near_z_shell(g, z);
+        if (near_shell) {
+          Nbr nb = nb0;
+          nb.zm = z == 0 ? (g.D - 1) * HW : -HW;
+          nb.zp = z == g.D - 1 ? -(g.D - 1) * HW : HW;
+          unsigned wall_mask = 0;
+#pragma unroll
+          for (int q = 1; q < L::Q; ++q)
+            if (fl[i + nb.at<3>(q, 1)] == LBMFF_OBSTACLE) wall_mask |= 1u << q;
+          if (wall_mask) {
+            const float p_axis = pa[i], p_diag = pa[N + i];
+#pragma unroll
+            for (int q = 1; q < L::Q; ++q) {
+              const bool axis = (L::ex(q) != 0) + (L::ey(q) != 0) + (L::ez(q) != 0) == 1;
+              if ((wall_mask >> q) & 1u) hv[q] = axis ? p_axis : p_diag;
+            }
+          }
+        }
+        const float psi = psi_of<3>(hv);
+        if (WRITE_PSI) psi_out[i] = psi;
+        pa[i] = mag_collide_q<3>(1, 0.0f, psi, r, k);
+        pa[N + i] = mag_collide_q<3>(5, 0.0f, psi, r, k);
+      }
+    }
+  }
+}
+
 // Rebuild the population-faithful h from the scalar state (for API users that ask for h).
 // cur = state after the last sweep, prev = one sweep earlier, psi = psi of the last sweep.
 template <int DIM>
@@ -307,6 +425,15 @@ static int sweep_variant() {
   return v;
 }
 
+// LBMFF_SCALAR_VARIANT = 1 (shared-memory tiled, default) | 0 (one thread per cell, L1/L2 served)
+static int scalar_variant() {
+  static const int v = [] {
+    const char* e = getenv("LBMFF_SCALAR_VARIANT");
+    return e ? atoi(e) : 1;
+  }();
+  return v;
+}
+
 template <int DIM>
 static int sweeps_impl(float* hA, float* hB, const uint8_t* mflags, const float* rhs, float* psi_out, int n,
                        double tau, double dx, double dt, const Grid& g, cudaStream_t st, const char* where) {
@@ -348,6 +475,19 @@ static int sweeps_scalar_impl(float* aA, float* aB, const uint8_t* mflags, const
     const float* cur = (s & 1) ? aB : aA;
     float* prev = (s & 1) ? aA : aB;
     for (long long b = 0; b < g.B; ++b) {
+      if (DIM == 3 && scalar_variant() == 1 && g.W >= 4 && g.H >= 4) {
+        const int zc = g.zn < 32 ? g.zn : 32;
+        const dim3 tg((g.W + kTX - 1) / kTX, (g.H + kTY - 1) / kTY, (g.zn + zc - 1) / zc);
+        if (s == n - 1 && psi_out)
+          k_mag_sweep_scalar_tiled<true><<<tg, dim3(kTX, kTY), 0, st>>>(cur + b * 2 * g.N, prev + b * 2 * g.N,
+                                                                        mflags + b * g.N, rhs + b * g.N,
+                                                                        psi_out + b * g.N, k, g, zc);
+        else
+          k_mag_sweep_scalar_tiled<false><<<tg, dim3(kTX, kTY), 0, st>>>(cur + b * 2 * g.N, prev + b * 2 * g.N,
+                                                                         mflags + b * g.N, rhs + b * g.N, nullptr,
+                                                                         k, g, zc);
+        continue;
+      }
       if (s == n - 1 && psi_out)
         k_mag_sweep_scalar<DIM, true><<<pl.grid, pl.block, 0, st>>>(cur + b * 2 * g.N, prev + b * 2 * g.N,
                                                                     mflags + b * g.N, rhs + b * g.N,
