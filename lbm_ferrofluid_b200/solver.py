@@ -209,15 +209,25 @@ class FerroSolver:
         """{name: [ms per bracket]} -- call after a synchronize."""
         return {k: [a.elapsed_time(b) for a, b in v] for k, v in (self._timing or {}).items()}
 
-    def _step_once(self):
+    def _step_once(self, before_source=None, after_rho_final=None):
+        """One outer step.  Hooks (used by step_host to overlap host copies): ``before_source`` runs just before
+        the first kernel that reads the applied-field faces, ``after_rho_final`` right after the wetting boundary,
+        when rho (hence phi) has its end-of-step value."""
         d, sz, suf = self.dim, self._sizes(), H.suffix(self.dim)
         cur, nxt = self._cur, 1 - self._cur
         dev = self.device
         H.launch("lbmff_hcz_moments_" + suf, dev, H.ptr(self._f[cur]), H.ptr(self.flags), H.ptr(self.rho),
                  H.ptr(self._chi if self.magnetic else None), self.params, *sz)
+        # capillary_process part 1 does not depend on the magnetic subsystem: issue it first
+        H.launch(f"lbmff_hcz_capillary_fields_{d}d", dev, H.ptr(self.rho), H.ptr(self.flags),
+                 H.ptr(self.pressure), self.params, H.ptr(self._ws), *sz)
+        if after_rho_final is not None:
+            after_rho_final()
         chi = psi = mfl = hext = None
         hu = None
         if self.magnetic:
+            if before_source is not None:
+                before_source()
             H.launch(f"lbmff_magnetic_source_{d}d", dev, H.ptr(self._chi), H.ptr(self.mflags),
                      *[H.ptr(t) for t in self.H_ext_mac], self.dx, H.ptr(self._rhs), *sz)
             m = self._mcur
@@ -233,8 +243,6 @@ class FerroSolver:
             if self.n_sweeps & 1:
                 self._mcur = 1 - m
             chi, psi, mfl, hext, hu = self._chi, self.psi, self.mflags, self.H_ext, self._H_uniform
-        H.launch(f"lbmff_hcz_capillary_fields_{d}d", dev, H.ptr(self.rho), H.ptr(self.flags),
-                 H.ptr(self.pressure), self.params, H.ptr(self._ws), *sz)
         args = [H.ptr(self._f[cur]), H.ptr(self._g[cur]), H.ptr(self._f[nxt]), H.ptr(self._g[nxt]),
                 H.ptr(self.rho), H.ptr(self.flags), H.ptr(mfl), H.ptr(self._ws), H.ptr(chi), H.ptr(psi),
                 H.ptr(hext), ctypes.cast(hu, ctypes.c_void_p) if hu is not None else ctypes.c_void_p(0),
@@ -263,14 +271,50 @@ class FerroSolver:
             dst.copy_(src, non_blocking=True)
 
     def step_host(self, faces_host: Optional[Sequence[torch.Tensor]], phi_host: Optional[torch.Tensor]):
-        """One outer step through host buffers: H2D of this step's applied-field faces (pinned),
-        the step, D2H of the order parameter phi the demos consume (pinned).  Asynchronous."""
+        """One outer step through host buffers: H2D of this step's applied-field faces (pinned), the step, D2H of
+        the order parameter phi the demos consume (pinned).  Asynchronous.  The copies ride a second stream: the
+        upload overlaps the moments / wetting / capillary-field kernels (which do not read the faces), the
+        download of phi starts as soon as rho is final and overlaps the magnetic sweeps and the collision."""
+        if faces_host is not None and not self.magnetic:
+            raise RuntimeError("solver was built without a magnetic subsystem")
+        cur = torch.cuda.current_stream(self.device)
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        cs = self._copy_stream
+        up = None
         if faces_host is not None:
-            self.set_H_ext_faces_from_host(faces_host)
-        self._step_once()
-        if phi_host is not None:
-            phi_host.copy_(self.phi, non_blocking=True)
+            cs.wait_stream(cur)          # the previous step's source kernel has read the old faces
+            with torch.cuda.stream(cs):
+                for dst, src in zip(self.H_ext_mac, faces_host):
+                    dst.copy_(src, non_blocking=True)
+                up = torch.cuda.Event()
+                up.record(cs)
+        phi_done = [None]
+
+        def download():
+            if phi_host is None:
+                return
+            ev = torch.cuda.Event()
+            ev.record(cur)
+            with torch.cuda.stream(cs):
+                cs.wait_event(ev)
+                phi = self.phi
+                phi_done[0] = torch.cuda.Event()
+                phi_done[0].record(cs)       # rho may be overwritten once phi has been formed
+                phi_host.copy_(phi, non_blocking=True)
+                phi.record_stream(cs)
+
+        self._step_once(before_source=(lambda: cur.wait_event(up)) if up is not None else None,
+                        after_rho_final=download)
+        if phi_done[0] is not None:
+            cur.wait_event(phi_done[0])
+        self._host_copy_pending = True
         return self
+
+    def wait_host_copies(self):
+        """Make the current stream wait for the host copies queued by step_host."""
+        if getattr(self, "_copy_stream", None) is not None:
+            torch.cuda.current_stream(self.device).wait_stream(self._copy_stream)
 
     @property
     def launches_per_step(self) -> int:
