@@ -234,3 +234,39 @@ def test_mass_conserved_and_finite_at_full_demo_size():
     assert abs(s.total_mass() - m0) / m0 < 1.5e-7 * 25
     for t in (s.f, s.g, s.vel, s.pressure, s.psi):
         assert torch.isfinite(t).all()
+
+
+@pytest.mark.parametrize("path", ["faithful", "scalar"])
+def test_batch_items_are_independent(path):
+    """B = 2 (the reference's latent batch axis, demo_3d...py:51): each batch item of a fused run equals the
+    B = 1 run of that item bit for bit (batch items are separate launches with offset pointers)."""
+    from lbm_ferrofluid_b200 import initializers as I
+    from lbm_ferrofluid_b200.solver import FerroSolver
+
+    res = (14, 12, 36)
+    dev = torch.device("cuda")
+    fl1 = I.shell_flags(res, device=dev)
+    mf1 = I.shell_flags(res, open_axes=(1,), device=dev)
+    rhos = [I.rosensweig_rho(res, fl1, noise=1e-3, seed=s, frac=fr) for s, fr in ((1, 0.5), (2, 0.4))]
+    kw = dict(H_ext=[0.0, 100.0, 0.0], n_sweeps=5, magnetic_path=path)
+    singles = [FerroSolver(fl1, magnetic_flags=mf1, **kw).initialize(r).step(3) for r in rhos]
+    both = FerroSolver(torch.cat([fl1, fl1]), magnetic_flags=torch.cat([mf1, mf1]), **kw)
+    both.initialize(torch.cat(rhos)).step(3)
+    for b, one in enumerate(singles):
+        for name in ("f", "g", "rho", "vel", "pressure", "psi"):
+            assert torch.equal(getattr(both, name)[b:b + 1], getattr(one, name)), f"batch item {b}: {name}"
+
+
+def test_step_host_matches_step_and_fills_host_buffers():
+    """step_host (host faces in, phi out, copies on a second stream) advances the same state as step()."""
+    G = load_golden("traj_ros3d")
+    a = make_solver(G, "faithful").step(3)
+    b = make_solver(G, "faithful")
+    faces = [t.cpu().pin_memory() for t in b.H_ext_mac]
+    phi_host = torch.empty(b.rho.shape, dtype=torch.float32).pin_memory()
+    for _ in range(3):
+        b.step_host(faces, phi_host)
+    b.wait_host_copies()
+    torch.cuda.synchronize()
+    assert torch.equal(a.f, b.f) and torch.equal(a.g, b.g) and torch.equal(a.psi, b.psi)
+    assert torch.equal(phi_host, b.phi.cpu())
