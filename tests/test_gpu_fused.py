@@ -270,3 +270,41 @@ def test_step_host_matches_step_and_fills_host_buffers():
     torch.cuda.synchronize()
     assert torch.equal(a.f, b.f) and torch.equal(a.g, b.g) and torch.equal(a.psi, b.psi)
     assert torch.equal(phi_host, b.phi.cpu())
+
+
+def test_interior_obstacles_and_tau_not_one_vs_oracle():
+    """Generic path of the fused step: a solid block INSIDE the domain (both flag arrays), magnetic tau = 0.8
+    (the population-faithful sweep really relaxes), contact angle 0.6 pi -- against the CPU oracle, fp32-floor bar.
+    Exercises bounce-back-as-permutation at interior walls and the get_grad shell rule off the outer shell."""
+    from lbm_ferrofluid_b200.solver import FerroSolver
+    from oracle.make_golden import perturbed_interface, shell_flags
+
+    res, steps = (22, 20, 26), 3
+    flags = shell_flags(res)
+    flags[0, 0, 8:12, 5:9, 10:15] = 2
+    mflags = shell_flags(res, open_axes=(1,))
+    mflags[0, 0, 8:12, 5:9, 10:15] = 2
+
+    def run(dtype):
+        p = O.HCZParams(contact_angle=torch.tensor([0.6 * math.pi]).to(dtype), n_sweeps=7, tau_h=0.8)
+        rho = perturbed_interface(res, 0.5, p.rho_liquid, p.rho_gas, torch.float32, False)
+        rho[flags == 2] = p.rho_liquid
+        rho0 = rho.clone()
+        rho = rho.to(dtype)
+        vel = torch.zeros((1, 3, *res), dtype=dtype)
+        pressure, f, g = O.hcz_init(rho, rho.clone(), vel, p)
+        Hext = torch.zeros((1, 3, *res), dtype=dtype)
+        Hext[:, 1] = 60.0
+        s = dict(f=f, g=g, h=torch.zeros_like(f), rho=rho.clone(), vel=vel, density=rho.clone(), pressure=pressure,
+                 flags=flags, mflags=mflags, H_ext=Hext, H_ext_mac=O.get_staggered(Hext))
+        for _ in range(steps):
+            s = O.hcz_step(s, p)
+        return s, rho0
+
+    s32, rho0 = run(torch.float32)
+    s64, _ = run(torch.float64)
+    sol = FerroSolver(flags.cuda(), contact_angle=torch.tensor([0.6 * math.pi]), magnetic_flags=mflags.cuda(),
+                      H_ext=[0.0, 60.0, 0.0], n_sweeps=7, tau=0.8, magnetic_path="auto")
+    assert sol.magnetic_path == "faithful"
+    sol.initialize(rho0.cuda()).step(steps)
+    check(sol, s32, ["f", "g", "rho", "density", "pressure", "vel", "psi", "h"], s64)
