@@ -308,3 +308,25 @@ def test_interior_obstacles_and_tau_not_one_vs_oracle():
     assert sol.magnetic_path == "faithful"
     sol.initialize(rho0.cuda()).step(steps)
     check(sol, s32, ["f", "g", "rho", "density", "pressure", "vel", "psi", "h"], s64)
+
+
+def test_kbc_zero_over_zero_quirk_is_reproduced():
+    """The reference's KBC stabiliser gamma = 1/beta - (2 - 1/beta) <ds|dh> / <dh|dh> is 0/0 = NaN wherever the
+    pulled populations already equal their equilibrium (LBM_collision_MRT_2d.py:213-222); on the 4096^2 KBC demo
+    that happens in 172 cells at step 1.  The fused kernel must produce NaN in exactly the same cells."""
+    from lbm_ferrofluid_b200.solver import SinglePhaseSolver
+
+    n, tau = 24, 0.8
+    vel = torch.zeros((1, 2, n, n))
+    vel[:, 0] = 0.1
+    vel[:, 1, :, n // 2:] = 0.02          # two uniform regions: NaN inside them, finite along their borders
+    rho = torch.full((1, 1, n, n), 0.265)
+    flags = torch.ones((1, 1, n, n), dtype=torch.uint8)
+    f = O.get_feq(1.0, 1.0, rho, vel, torch.zeros_like(vel), tau)
+    f_ref, _, _ = O.single_phase_step(f, rho, vel, flags, torch.zeros_like(vel), 1.0, 1.0, tau, O.KBC_A)
+    s = SinglePhaseSolver(flags.cuda(), tau=tau, KBC_type=O.KBC_A).initialize(rho.cuda(), vel.cuda()).step(1)
+    bad_ref, bad = ~torch.isfinite(f_ref), ~torch.isfinite(s.f.cpu())
+    assert bad_ref.any() and not bad_ref.all()
+    assert torch.equal(bad, bad_ref)
+    ok = ~bad_ref
+    assert (s.f.cpu()[ok] - f_ref[ok]).abs().max() <= 2e-6 * f_ref[ok].abs().max()

@@ -64,7 +64,47 @@ def streams(res):
     print(f"19 one-population copies: ms={ms:.4f} GB/s={152 * N / ms / 1e6:.1f}", flush=True)
 
 
+def single2d(n, steps=50):
+    """demo_2d_LBM(_KBC) at n x n: SinglePhaseSolver BGK and KBC, MLUPS and GB/s at 72 B/cell."""
+    from lbm_ferrofluid_b200.solver import SinglePhaseSolver
+    from lbm_ferrofluid_b200.types import KBCType
+    dev = torch.device("cuda")
+    flags = torch.ones((1, 1, n, n), dtype=torch.uint8, device=dev)
+    tau = 0.5 + 3 * 0.2 * n / 3000
+    vel = I.double_shear_layer((n, n), device=dev)
+    rho = torch.full((1, 1, n, n), 0.265, device=dev)
+    for name, kbc in (("BGK", None), ("KBC", int(KBCType.KBC_A))):
+        s = SinglePhaseSolver(flags, tau=tau, KBC_type=kbc).initialize(rho, vel)
+        ms = timed(lambda: s.step(steps), reps=3) / steps
+        print(f"D2Q9 {name} {n}^2: {ms:.4f} ms/step {n * n / ms / 1e3:.0f} MLUPS {72 * n * n / ms / 1e6:.0f} GB/s "
+              f"finite={bool(torch.isfinite(s.f).all())}", flush=True)
+
+
+def ros2d(n, steps=10):
+    """demo_2d_LBM_Rosensweig_instability at n x n (HCZ + magnetic + KBC on g), both magnetic paths."""
+    import math
+    from lbm_ferrofluid_b200.solver import FerroSolver
+    from lbm_ferrofluid_b200.types import KBCType
+    dev = torch.device("cuda")
+    res = (n, n)
+    flags = I.shell_flags(res, device=dev)
+    mflags = I.shell_flags(res, open_axes=(1,), device=dev)
+    rho = I.rosensweig_rho(res, flags, frac=0.45)
+    for path in ("faithful", "scalar"):
+        s = FerroSolver(flags, magnetic_flags=mflags, H_ext=[0.0, 100.0], tau_f=0.7, tau_g=0.8,
+                        contact_angle=0.75 * math.pi, KBC_type=int(KBCType.KBC_A), magnetic_path=path)
+        s.initialize(rho)
+        ms = timed(lambda: s.step(steps), reps=3) / steps
+        print(f"2-D Rosensweig {path} {n}^2: {ms:.4f} ms/step {n * n / ms / 1e3:.0f} MLUPS "
+              f"({32 * 72 * n * n / ms / 1e6:.0f} GB/s of the 2304 B/cell model) finite={bool(torch.isfinite(s.rho).all())}",
+              flush=True)
+
+
 if __name__ == "__main__":
+    if sys.argv[1] == "single2d":
+        single2d(int(sys.argv[2]))
+    if sys.argv[1] == "ros2d":
+        ros2d(int(sys.argv[2]))
     if sys.argv[1] == "streams":
         streams(tuple(int(v) for v in sys.argv[2:5]))
     if sys.argv[1] == "sweep":
