@@ -209,9 +209,10 @@ constexpr int kThreads = 256;
 struct PlaneLaunch {
   dim3 grid, block;
 };
-inline PlaneLaunch plane_launch(const Grid& g) {
+// max_bx < 256 gives a 2-D block (e.g. 64 x 4): stencil kernels then share their y neighbours inside a block.
+inline PlaneLaunch plane_launch(const Grid& g, int max_bx = kThreads) {
   int bx = ((g.W + 31) / 32) * 32;
-  if (bx > kThreads) bx = kThreads;
+  if (bx > max_bx) bx = max_bx;
   int by = kThreads / bx;
   if (by > g.H) by = g.H;
   if (by < 1) by = 1;

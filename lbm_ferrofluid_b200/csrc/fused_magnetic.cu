@@ -506,7 +506,7 @@ static int source_impl(const float* chi, const uint8_t* mflags, const float* Hx,
   if (!(chi && mflags && Hx && Hy && (DIM == 2 || Hz) && rhs)) return bad_arg(where, "null pointer");
   if (g.W < 3 || g.H < 3 || (DIM == 3 && g.D < 3)) return bad_arg(where, "every extent must be >= 3");
   if ((g.D + 1LL) * (g.H + 1LL) * (g.W + 1LL) > 0x7fffffffLL) return bad_arg(where, "grid too large for 32-bit cell indices");
-  const PlaneLaunch pl = plane_launch(g);
+  const PlaneLaunch pl = plane_launch(g, 64);
   const long long D = g.D, H = g.H, W = g.W;
   for (long long b = 0; b < g.B; ++b) {
     const HextFaces Hf{Hx + b * D * H * (W + 1), Hy + b * D * (H + 1) * W, DIM == 3 ? Hz + b * (D + 1) * H * W : nullptr};
