@@ -38,8 +38,8 @@ __global__ void __launch_bounds__(kThreads) k_mag_source(const float* __restrict
 // OBSTACLE cell x: out_q(x) = in_opp(q)(x + e_q)   (stream, then bounce; walls never collide)
 // other cells:     h_q = in_q(x - e_q); psi = sum_{q>=1} h_q / (1 - w0); out_q = collide(h_q, psi, rhs)
 // HINT: 0 default caching, 1 streaming stores (st.global.cs)
-template <int DIM, bool WRITE_PSI, int HINT = 0, bool IDX32 = true>
-__global__ void __launch_bounds__(kThreads) k_mag_sweep(const float* __restrict__ hin, float* __restrict__ hout,
+template <int DIM, bool WRITE_PSI, int HINT = 0, bool IDX32 = true, int MB = 1>
+__global__ void __launch_bounds__(kThreads, MB) k_mag_sweep(const float* __restrict__ hin, float* __restrict__ hout,
                                                         const uint8_t* __restrict__ mflags,
                                                         const float* __restrict__ rhs, float* __restrict__ psi_out,
                                                         Consts k, Grid g) {
@@ -405,7 +405,21 @@ static void launch_sweep(bool wp, int hint, bool idx32, const PlaneLaunch& pl, c
   k_mag_sweep<DIM, WP, HI, IX><<<pl.grid, pl.block, 0, st>>>(in + b * Lat<DIM>::Q * g.N, out + b * Lat<DIM>::Q * g.N, \
                                                              mflags + b * g.N, rhs + b * g.N,                    \
                                                              psi_out ? psi_out + b * g.N : nullptr, k, g)
+  // minimum resident blocks per SM (register cap): 5 -> 48 registers, 1280 threads/SM: 3.17 ms per 512^3 sweep
+  // (6.43 TB/s); uncapped (64 registers, 4 blocks) 3.29 ms; 6 -> 40 registers with spills 3.38 ms; 8 -> 4.84 ms
+  static const int mb = [] { const char* e = getenv("LBMFF_SWEEP_MB"); return e ? atoi(e) : 5; }();
   for (long long b = 0; b < g.B; ++b) {
+    if (idx32 && !hint && mb >= 5) {
+#define LBMFF_SWMB(WP, M)                                                                                          \
+  k_mag_sweep<DIM, WP, 0, true, M><<<pl.grid, pl.block, 0, st>>>(in + b * Lat<DIM>::Q * g.N, out + b * Lat<DIM>::Q * g.N, \
+                                                                 mflags + b * g.N, rhs + b * g.N,                 \
+                                                                 psi_out ? psi_out + b * g.N : nullptr, k, g)
+      if (mb == 5) { if (wp) LBMFF_SWMB(true, 5); else LBMFF_SWMB(false, 5); }
+      else if (mb == 6) { if (wp) LBMFF_SWMB(true, 6); else LBMFF_SWMB(false, 6); }
+      else { if (wp) LBMFF_SWMB(true, 8); else LBMFF_SWMB(false, 8); }
+#undef LBMFF_SWMB
+      continue;
+    }
     if (idx32) {
       if (hint) { if (wp) LBMFF_SW(true, 1, true); else LBMFF_SW(false, 1, true); }
       else { if (wp) LBMFF_SW(true, 0, true); else LBMFF_SW(false, 0, true); }
