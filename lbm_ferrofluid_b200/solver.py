@@ -230,6 +230,9 @@ class FerroSolver:
                 before_source()
             H.launch(f"lbmff_magnetic_source_{d}d", dev, H.ptr(self._chi), H.ptr(self.mflags),
                      *[H.ptr(t) for t in self.H_ext_mac], self.dx, H.ptr(self._rhs), *sz)
+            if before_source is not None:   # the faces are free again: the next upload may start under the sweeps
+                self._faces_read = torch.cuda.Event()
+                self._faces_read.record()
             m = self._mcur
             with self._timed("sweeps"):
                 if self.magnetic_path == "faithful":
@@ -273,22 +276,30 @@ class FerroSolver:
     def step_host(self, faces_host: Optional[Sequence[torch.Tensor]], phi_host: Optional[torch.Tensor]):
         """One outer step through host buffers: H2D of this step's applied-field faces (pinned), the step, D2H of
         the order parameter phi the demos consume (pinned).  Asynchronous.  The copies ride a second stream: the
-        upload overlaps the moments / wetting / capillary-field kernels (which do not read the faces), the
-        download of phi starts as soon as rho is final and overlaps the magnetic sweeps and the collision."""
+        upload waits only for the previous step's last reader of the faces and so runs under that step's
+        magnetic sweeps (the host enqueues steps faster than the device executes them), the download of phi starts
+        as soon as rho is final and overlaps the sweeps and the collision of its own step."""
         if faces_host is not None and not self.magnetic:
             raise RuntimeError("solver was built without a magnetic subsystem")
         cur = torch.cuda.current_stream(self.device)
         if getattr(self, "_copy_stream", None) is None:
-            self._copy_stream = torch.cuda.Stream(device=self.device)
-        cs = self._copy_stream
+            self._copy_stream = torch.cuda.Stream(device=self.device)      # downloads
+            self._up_stream = torch.cuda.Stream(device=self.device)        # uploads (other copy engine)
+            self._faces_read = None
+        cs, us = self._copy_stream, self._up_stream
         up = None
         if faces_host is not None:
-            cs.wait_stream(cur)          # the previous step's source kernel has read the old faces
-            with torch.cuda.stream(cs):
+            # WAR on the face arrays: wait only for the previous step's source kernel (their last reader), not for
+            # the whole previous step -- the upload then runs under the previous step's magnetic sweeps
+            if self._faces_read is not None:
+                us.wait_event(self._faces_read)
+            else:
+                us.wait_stream(cur)
+            with torch.cuda.stream(us):
                 for dst, src in zip(self.H_ext_mac, faces_host):
                     dst.copy_(src, non_blocking=True)
                 up = torch.cuda.Event()
-                up.record(cs)
+                up.record(us)
         phi_done = [None]
 
         def download():
@@ -315,6 +326,7 @@ class FerroSolver:
         """Make the current stream wait for the host copies queued by step_host."""
         if getattr(self, "_copy_stream", None) is not None:
             torch.cuda.current_stream(self.device).wait_stream(self._copy_stream)
+            torch.cuda.current_stream(self.device).wait_stream(self._up_stream)
 
     @property
     def launches_per_step(self) -> int:
