@@ -266,6 +266,8 @@ class SlabFerroSolver:
         self._cur = 0
         self.steps_done = 0
         self._timing = None
+        self._hook_before_source = self._hook_after_source = self._hook_after_rho_final = None
+        self._down_stream = self._up_stream = self._faces_read = None
         self.magnetic = magnetic_flags is not None
         if self.magnetic:
             self.mflags = H.need_cuda(magnetic_flags, "magnetic_flags", torch.uint8)
@@ -380,8 +382,12 @@ class SlabFerroSolver:
             moments(e)
         yield HaloRequest([self.rho, self.pressure] + ([chi] if self.magnetic else []), L.halo)
         if self.magnetic:
+            if self._hook_before_source is not None:
+                self._hook_before_source()
             self._launch("lbmff_slab_magnetic_source_3d", p(chi), p(self.mflags), *[p(t) for t in self.H_ext_mac],
                          self.dx, p(self._rhs), planes=own)
+            if self._hook_after_source is not None:
+                self._hook_after_source()
             t0 = self._mark()
             sweep = ("lbmff_slab_magnetic_sweep_d3q19" if self.magnetic_path == "faithful"
                      else "lbmff_slab_magnetic_sweep_scalar_3d")
@@ -406,6 +412,8 @@ class SlabFerroSolver:
         # ordered wetting boundary: x faces one plane beyond the owned block (the y faces read them)
         self._launch("lbmff_slab_hcz_wetting_3d", p(self.rho), p(self.flags), self.params, 1, planes=d1)
         self._launch("lbmff_slab_hcz_wetting_3d", p(self.rho), p(self.flags), self.params, 2, planes=own)
+        if self._hook_after_rho_final is not None:   # owned planes of rho have their end-of-step value
+            self._hook_after_rho_final()
         yield HaloRequest([self.rho], L.halo)
         self._launch("lbmff_slab_hcz_fields_3d", p(self.rho), p(self.flags), p(self.pressure), self.params,
                      p(self._ws), planes=d1)
@@ -451,15 +459,61 @@ class SlabFerroSolver:
         return -(2.0 * (density - dg) / (dl - dg) - 1.0)
 
     def step_host(self, faces_host, phi_host):
-        """One outer step through host buffers (same contract as FerroSolver.step_host): upload this slab's
-        applied-field faces from pinned memory, step, download phi of the owned planes."""
+        """One outer step through host buffers (same contract and copy/compute overlap as FerroSolver.step_host):
+        this slab's applied-field faces come from pinned memory on an upload stream that waits only for the previous
+        step's source kernel, phi of the owned planes goes to pinned memory on a download stream as soon as rho is
+        final, both under the magnetic sweeps."""
+        cur = torch.cuda.current_stream(self.device)
+        if self._down_stream is None:
+            self._down_stream = torch.cuda.Stream(device=self.device)
+            self._up_stream = torch.cuda.Stream(device=self.device)
+        ds, us = self._down_stream, self._up_stream
+        up = None
         if faces_host is not None:
-            for dst, src in zip(self.H_ext_mac, faces_host):
-                dst.copy_(src, non_blocking=True)
-        self.step(1)
-        if phi_host is not None:
-            phi_host.copy_(self.phi, non_blocking=True)
+            if self._faces_read is not None:
+                us.wait_event(self._faces_read)
+            else:
+                us.wait_stream(cur)
+            with torch.cuda.stream(us):
+                for dst, src in zip(self.H_ext_mac, faces_host):
+                    dst.copy_(src, non_blocking=True)
+                up = torch.cuda.Event()
+                up.record(us)
+        phi_done = [None]
+
+        def after_source():
+            self._faces_read = torch.cuda.Event()
+            self._faces_read.record(cur)
+
+        def download():
+            if phi_host is None:
+                return
+            ev = torch.cuda.Event()
+            ev.record(cur)
+            with torch.cuda.stream(ds):
+                ds.wait_event(ev)
+                phi = self.phi
+                phi_done[0] = torch.cuda.Event()
+                phi_done[0].record(ds)
+                phi_host.copy_(phi, non_blocking=True)
+                phi.record_stream(ds)
+
+        self._hook_before_source = (lambda: cur.wait_event(up)) if up is not None else None
+        self._hook_after_source = after_source
+        self._hook_after_rho_final = download
+        try:
+            self.step(1)
+        finally:
+            self._hook_before_source = self._hook_after_source = self._hook_after_rho_final = None
+        if phi_done[0] is not None:
+            cur.wait_event(phi_done[0])
         return self
+
+    def wait_host_copies(self):
+        if self._down_stream is not None:
+            cur = torch.cuda.current_stream(self.device)
+            cur.wait_stream(self._down_stream)
+            cur.wait_stream(self._up_stream)
 
     @property
     def launches_per_step(self) -> int:
