@@ -430,6 +430,246 @@ static void launch_sweep(bool wp, int hint, bool idx32, const PlaneLaunch& pl, c
 #undef LBMFF_SW
 }
 
+// ---- TWO population-faithful sweeps in one pass over h (temporal blocking, 3-D) -----------------------------------
+// A block owns a 32 x 8 column of cells and marches upwards in z.  Per plane it (A) runs sweep 1 on the column
+// extended by a one-cell rim (34 x 10 cells, one thread each) straight from global memory and parks the 19
+// post-sweep-1 populations of that plane in a four-slot shared-memory ring, then (B) runs sweep 2 for the 32 x 8
+// cells of the plane below from the ring and stores the result.  h is read 1.33x and written once per TWO sweeps
+// (about 180 B per cell instead of 304 B); the rim is recomputed by the neighbouring block with identical
+// arithmetic, so the result is bit-identical to two k_mag_sweep launches.  The 19 pulls of the next plane are in
+// flight in registers while (B) runs.
+constexpr int kPX = 32, kPY = 8, kPW = kPX + 2, kPH = kPY + 2, kPCells = kPW * kPH, kPThreads = 352, kPRing = 4;
+constexpr size_t kPairSmem = (size_t)kPRing * 19 * kPCells * sizeof(float);
+
+template <bool WRITE_PSI, bool IDX32>
+__global__ void __launch_bounds__(kPThreads, 2)
+k_mag_sweep_pair(const float* __restrict__ in, float* __restrict__ out, const uint8_t* __restrict__ fl,
+                 const float* __restrict__ rhs, float* __restrict__ psi_out, Consts k, Grid g, int zc) {
+  using L = Lat<3>;
+  extern __shared__ float s1[];   // [ring][q][kPH][kPW]
+  const int tid = threadIdx.x;
+  const int x0 = blockIdx.x * kPX, y0 = blockIdx.y * kPY;
+  const int zs = g.zb + blockIdx.z * zc;
+  const int ze = min(zs + zc, g.zb + g.zn);   // sweep-2 output planes [zs, ze)
+  const int HW = g.H * g.W;
+  const PopIndex<IDX32> at(g);
+  // ---- role A: one cell of the rim-extended tile (periodic in x, y)
+  const bool a_on = tid < kPCells;
+  const int ay = a_on ? tid / kPW : 0, ax = a_on ? tid - ay * kPW : 0;
+  int gx = x0 - 1 + ax, gy = y0 - 1 + ay;
+  gx = gx < 0 ? gx + g.W : gx; gy = gy < 0 ? gy + g.H : gy;
+  while (gx >= g.W) gx -= g.W;
+  while (gy >= g.H) gy -= g.H;
+  const int a_xy = gy * g.W + gx;
+  Nbr nba(PlaneCell{gx, gy, 0, 0, true}, g);
+  // ---- role B: one output cell of the tile
+  const bool b_on = tid < kPX * kPY;
+  const int bx = tid & (kPX - 1), by = tid / kPX;
+  const int ox = x0 + bx, oy = y0 + by;
+  const bool b_live = b_on && ox < g.W && oy < g.H;
+  const int b_xy = b_live ? oy * g.W + ox : 0;
+
+  float P[L::Q];      // pulls of the plane role A works on next (in flight while role B runs)
+  float p_rhs = 0.f;
+  uint8_t p_fl = LBMFF_FLUID;
+  auto fetch = [&](int z) {   // z: any integer plane index, periodic in the local array
+    if (!a_on) return;
+    const int zz = z < 0 ? z + g.D : (z >= g.D ? z - g.D : z);
+    nba.zm = zz == 0 ? (g.D - 1) * HW : -HW;
+    nba.zp = zz == g.D - 1 ? -(g.D - 1) * HW : HW;
+    const int i = zz * HW + a_xy;
+#pragma unroll
+    for (int q = 0; q < L::Q; ++q) P[q] = ld_spec(in + at(q, i + nba.at<3>(q, 1)));
+    p_rhs = __ldg(rhs + i);
+    p_fl = fl[i];
+  };
+  auto sweep1_to_ring = [&](int z) {   // consume P: h1 of plane z -> ring slot
+    if (!a_on) return;
+    if (p_fl == LBMFF_OBSTACLE) {
+#pragma unroll
+      for (int q = 1; q < L::Q; ++q)
+        if (q < L::opp(q)) { const float t = P[q]; P[q] = P[L::opp(q)]; P[L::opp(q)] = t; }
+    } else {
+      const float psi = psi_of<3>(P);
+#pragma unroll
+      for (int q = 0; q < L::Q; ++q) P[q] = mag_collide_q<3>(q, P[q], psi, p_rhs, k);
+    }
+    float* slot = s1 + ((z - zs + 1) & (kPRing - 1)) * (L::Q * kPCells) + ay * kPW + ax;
+#pragma unroll
+    for (int q = 0; q < L::Q; ++q) slot[q * kPCells] = P[q];
+  };
+
+  fetch(zs - 1);
+  sweep1_to_ring(zs - 1);
+  fetch(zs);
+  sweep1_to_ring(zs);
+  fetch(zs + 1);
+  // own flag / source of the first output plane
+  float b_rhs = b_live ? __ldg(rhs + zs * HW + b_xy) : 0.f;
+  uint8_t b_fl = b_live ? fl[zs * HW + b_xy] : (uint8_t)LBMFF_FLUID;
+  for (int z = zs; z < ze; ++z) {
+    sweep1_to_ring(z + 1);
+    if (z + 1 < ze) fetch(z + 2);
+    const float r = b_rhs;
+    const uint8_t f0 = b_fl;
+    if (b_live && z + 1 < ze) {
+      b_rhs = __ldg(rhs + (z + 1) * HW + b_xy);
+      b_fl = fl[(z + 1) * HW + b_xy];
+    }
+    __syncthreads();
+    if (b_live) {
+      const int i = z * HW + b_xy;
+      const float* ring[3] = {s1 + ((z - zs) & (kPRing - 1)) * (L::Q * kPCells),
+                              s1 + ((z - zs + 1) & (kPRing - 1)) * (L::Q * kPCells),
+                              s1 + ((z - zs + 2) & (kPRing - 1)) * (L::Q * kPCells)};   // planes z-1, z, z+1
+      float hv[L::Q];
+#pragma unroll
+      for (int q = 0; q < L::Q; ++q)
+        hv[q] = ring[1 - L::ez(q)][q * kPCells + (by + 1 - L::ey(q)) * kPW + (bx + 1 - L::ex(q))];
+      const bool obst = f0 == LBMFF_OBSTACLE;
+      if (obst) {
+#pragma unroll
+        for (int q = 1; q < L::Q; ++q)
+          if (q < L::opp(q)) { const float t = hv[q]; hv[q] = hv[L::opp(q)]; hv[L::opp(q)] = t; }
+      }
+      const float psi = psi_of<3>(hv);
+      if (WRITE_PSI) psi_out[i] = psi;
+      if (!obst) {
+#pragma unroll
+        for (int q = 0; q < L::Q; ++q) hv[q] = mag_collide_q<3>(q, hv[q], psi, r, k);
+      }
+#pragma unroll
+      for (int q = 0; q < L::Q; ++q) out[at(q, i)] = hv[q];
+    }
+  }
+}
+
+// ---- the same two-sweep pass, warp-specialised ---------------------------------------------------------------------
+// Producer warps (352 threads, one per cell of the 34 x 10 extended tile) run sweep 1 plane after plane into the
+// ring; consumer warps (256 threads, one per output cell) run sweep 2 out of it.  The two groups are coupled only by
+// one full/empty named barrier pair per ring slot (bar.arrive / bar.sync), so producers run up to three planes ahead
+// and neither group ever waits for the other's memory latency at a block-wide barrier.
+constexpr int kWsProd = 352, kWsCons = kPX * kPY, kWsThreads = kWsProd + kWsCons;
+
+__device__ __forceinline__ void named_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void named_arrive(int id, int n) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory");
+}
+
+template <bool WRITE_PSI, bool IDX32>
+__global__ void __launch_bounds__(kWsThreads, 2)
+k_mag_sweep_pair_ws(const float* __restrict__ in, float* __restrict__ out, const uint8_t* __restrict__ fl,
+                    const float* __restrict__ rhs, float* __restrict__ psi_out, Consts k, Grid g, int zc) {
+  using L = Lat<3>;
+  extern __shared__ float s1[];   // [ring][q][kPH][kPW]
+  const int x0 = blockIdx.x * kPX, y0 = blockIdx.y * kPY;
+  const int zs = g.zb + blockIdx.z * zc;
+  const int ze = min(zs + zc, g.zb + g.zn);   // sweep-2 output planes [zs, ze)
+  const int HW = g.H * g.W;
+  const PopIndex<IDX32> at(g);
+  // barrier ids: 1 + slot = "slot full", 1 + kPRing + slot = "slot empty"
+  if (threadIdx.x >= kWsCons) {
+    // ================= producers: sweep 1 on the extended tile =================
+    const int tid = threadIdx.x - kWsCons;
+    const bool on = tid < kPCells;
+    const int ay = on ? tid / kPW : 0, ax = on ? tid - ay * kPW : 0;
+    int gx = x0 - 1 + ax, gy = y0 - 1 + ay;
+    gx = gx < 0 ? gx + g.W : gx; gy = gy < 0 ? gy + g.H : gy;
+    while (gx >= g.W) gx -= g.W;
+    while (gy >= g.H) gy -= g.H;
+    const int a_xy = gy * g.W + gx;
+    Nbr nba(PlaneCell{gx, gy, 0, 0, true}, g);
+    float P[L::Q];
+    float p_rhs = 0.f;
+    uint8_t p_fl = LBMFF_FLUID;
+    auto fetch = [&](int z) {
+      const int zz = z < 0 ? z + g.D : (z >= g.D ? z - g.D : z);
+      nba.zm = zz == 0 ? (g.D - 1) * HW : -HW;
+      nba.zp = zz == g.D - 1 ? -(g.D - 1) * HW : HW;
+      const int i = zz * HW + a_xy;
+#pragma unroll
+      for (int q = 0; q < L::Q; ++q) P[q] = ld_spec(in + at(q, i + nba.at<3>(q, 1)));
+      p_rhs = __ldg(rhs + i);
+      p_fl = fl[i];
+    };
+    if (on) fetch(zs - 1);
+    for (int pz = zs - 1, it = 0; pz <= ze; ++pz, ++it) {
+      const int slot = (pz - zs + 1) & (kPRing - 1);
+      if (it >= kPRing) named_sync(1 + kPRing + slot, kWsThreads);   // consumers are done with plane pz - 4
+      if (on) {
+        if (p_fl == LBMFF_OBSTACLE) {
+#pragma unroll
+          for (int q = 1; q < L::Q; ++q)
+            if (q < L::opp(q)) { const float t = P[q]; P[q] = P[L::opp(q)]; P[L::opp(q)] = t; }
+        } else {
+          const float psi = psi_of<3>(P);
+#pragma unroll
+          for (int q = 0; q < L::Q; ++q) P[q] = mag_collide_q<3>(q, P[q], psi, p_rhs, k);
+        }
+        float* dst = s1 + slot * (L::Q * kPCells) + ay * kPW + ax;
+#pragma unroll
+        for (int q = 0; q < L::Q; ++q) dst[q * kPCells] = P[q];
+        if (pz < ze) fetch(pz + 1);
+      }
+      __threadfence_block();
+      named_arrive(1 + slot, kWsThreads);
+    }
+  } else {
+    // ================= consumers: sweep 2 on the tile =================
+    const int tid = threadIdx.x;
+    const int bx = tid & (kPX - 1), by = tid / kPX;
+    const int ox = x0 + bx, oy = y0 + by;
+    const bool live = ox < g.W && oy < g.H;
+    const int b_xy = live ? oy * g.W + ox : 0;
+    float b_rhs = live ? __ldg(rhs + zs * HW + b_xy) : 0.f;
+    uint8_t b_fl = live ? fl[zs * HW + b_xy] : (uint8_t)LBMFF_FLUID;
+    named_sync(1 + 0, kWsThreads);   // plane zs - 1 (slot 0)
+    named_sync(1 + 1, kWsThreads);   // plane zs     (slot 1)
+    for (int z = zs; z < ze; ++z) {
+      const int s0 = (z - zs) & (kPRing - 1), s1i = (z - zs + 1) & (kPRing - 1), s2 = (z - zs + 2) & (kPRing - 1);
+      const float r = b_rhs;
+      const uint8_t f0 = b_fl;
+      if (live && z + 1 < ze) {
+        b_rhs = __ldg(rhs + (z + 1) * HW + b_xy);
+        b_fl = fl[(z + 1) * HW + b_xy];
+      }
+      named_sync(1 + s2, kWsThreads);   // plane z + 1
+      if (live) {
+        const int i = z * HW + b_xy;
+        const float* ring[3] = {s1 + s0 * (L::Q * kPCells), s1 + s1i * (L::Q * kPCells), s1 + s2 * (L::Q * kPCells)};
+        float hv[L::Q];
+#pragma unroll
+        for (int q = 0; q < L::Q; ++q)
+          hv[q] = ring[1 - L::ez(q)][q * kPCells + (by + 1 - L::ey(q)) * kPW + (bx + 1 - L::ex(q))];
+        const bool obst = f0 == LBMFF_OBSTACLE;
+        if (obst) {
+#pragma unroll
+          for (int q = 1; q < L::Q; ++q)
+            if (q < L::opp(q)) { const float t = hv[q]; hv[q] = hv[L::opp(q)]; hv[L::opp(q)] = t; }
+        }
+        const float psi = psi_of<3>(hv);
+        if (WRITE_PSI) psi_out[i] = psi;
+        if (!obst) {
+#pragma unroll
+          for (int q = 0; q < L::Q; ++q) hv[q] = mag_collide_q<3>(q, hv[q], psi, r, k);
+        }
+#pragma unroll
+        for (int q = 0; q < L::Q; ++q) out[at(q, i)] = hv[q];
+      }
+      named_arrive(1 + kPRing + s0, kWsThreads);   // plane z - 1 is free
+    }
+  }
+}
+
+// LBMFF_SWEEP_PAIR = 1: issue the population-faithful sweeps two at a time (k_mag_sweep_pair) | 0: one per launch
+static int pair_variant() {
+  static const int v = [] {
+    const char* e = getenv("LBMFF_SWEEP_PAIR");
+    return e ? atoi(e) : 0;
+  }();
+  return v;
+}
+
 // LBMFF_SWEEP_VARIANT = 1 (one cell per thread, default: 3.80 ms per 512^3 sweep) | 4 (four cells per thread: 3.87 ms)
 static int sweep_variant() {
   static const int v = [] {
@@ -462,10 +702,54 @@ static int sweeps_impl(float* hA, float* hB, const uint8_t* mflags, const float*
                     ((uintptr_t)hA | (uintptr_t)hB | (uintptr_t)rhs | (uintptr_t)psi_out | (uintptr_t)mflags) % 16 == 0;
   const dim3 grid4(blocks_for((g.i1 - g.i0) / 4), (unsigned)g.B);
   const PlaneLaunch pl = plane_launch(g);
-  for (int s = 0; s < n; ++s) {
+  // Temporal blocking: sweeps are issued two at a time where that keeps the documented buffer parity (the result
+  // must land in hA for even n, hB for odd n, and every launch flips the buffer): n - 2*np singles, np pairs,
+  // with (n - np) of the same parity as n, i.e. np even.
+  int np = 0;
+  if (DIM == 3 && pair_variant() && g.W >= 8 && g.H >= 8 && g.zn >= 4) {
+    np = (n / 2) & ~1;
+    static bool attr_set = false;
+    if (!attr_set) {
+      cudaFuncSetAttribute(k_mag_sweep_pair<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmem);
+      cudaFuncSetAttribute(k_mag_sweep_pair<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmem);
+      cudaFuncSetAttribute(k_mag_sweep_pair<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmem);
+      cudaFuncSetAttribute(k_mag_sweep_pair<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmem);
+      cudaFuncSetAttribute(k_mag_sweep_pair_ws<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmem);
+      cudaFuncSetAttribute(k_mag_sweep_pair_ws<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmem);
+      attr_set = true;
+    }
+  }
+  const int launches = n - np;
+  int done = 0;   // sweeps completed
+  for (int s = 0; s < launches; ++s) {
     const float* in = (s & 1) ? hB : hA;
     float* out = (s & 1) ? hA : hB;
-    const bool wp = s == n - 1 && psi_out;
+    const bool pair = s < np;
+    done += pair ? 2 : 1;
+    const bool wp = done == n && psi_out;
+    if (pair) {
+      const int zc = g.zn < 32 ? g.zn : 32;
+      const dim3 tg((g.W + kPX - 1) / kPX, (g.H + kPY - 1) / kPY, (g.zn + zc - 1) / zc);
+      const bool ix = (long long)Lat<DIM>::Q * g.N < 0xffffffffLL;
+      for (long long b = 0; b < g.B; ++b) {
+        const float* i_ = in + b * 19 * g.N;
+        float* o_ = out + b * 19 * g.N;
+        const uint8_t* f_ = mflags + b * g.N;
+        const float* r_ = rhs + b * g.N;
+        float* p_ = psi_out ? psi_out + b * g.N : nullptr;
+        if (ix && pair_variant() == 2) {
+          if (wp) k_mag_sweep_pair_ws<true, true><<<tg, kWsThreads, kPairSmem, st>>>(i_, o_, f_, r_, p_, k, g, zc);
+          else k_mag_sweep_pair_ws<false, true><<<tg, kWsThreads, kPairSmem, st>>>(i_, o_, f_, r_, p_, k, g, zc);
+        } else if (ix) {
+          if (wp) k_mag_sweep_pair<true, true><<<tg, kPThreads, kPairSmem, st>>>(i_, o_, f_, r_, p_, k, g, zc);
+          else k_mag_sweep_pair<false, true><<<tg, kPThreads, kPairSmem, st>>>(i_, o_, f_, r_, p_, k, g, zc);
+        } else {
+          if (wp) k_mag_sweep_pair<true, false><<<tg, kPThreads, kPairSmem, st>>>(i_, o_, f_, r_, p_, k, g, zc);
+          else k_mag_sweep_pair<false, false><<<tg, kPThreads, kPairSmem, st>>>(i_, o_, f_, r_, p_, k, g, zc);
+        }
+      }
+      continue;
+    }
     if (vec4) {
       if (wp) k_mag_sweep_v4<DIM, true><<<grid4, kThreads, 0, st>>>(in, out, mflags, rhs, psi_out, k, g);
       else k_mag_sweep_v4<DIM, false><<<grid4, kThreads, 0, st>>>(in, out, mflags, rhs, psi_out, k, g);
