@@ -281,125 +281,6 @@ k_hcz_collide_stream(const float* __restrict__ fi, const float* __restrict__ gi,
   }
 }
 
-// Phased 3-D variant: g is pulled, collided and stored before f is pulled, so only Q populations are live at a
-// time and three blocks fit on an SM (24 warps instead of 16) -- measured against the all-pulls-first kernel.
-template <int DIM, bool MAGNETIC, bool IDX32>
-__global__ void __launch_bounds__(kThreads, 3)
-k_hcz_collide_stream_phased(const float* __restrict__ fi, const float* __restrict__ gi, float* __restrict__ fo,
-                     float* __restrict__ go, const float* __restrict__ rho_, const uint8_t* __restrict__ flags,
-                     const float* __restrict__ ws, const float* __restrict__ chi, const float* __restrict__ psi,
-                     const float* __restrict__ Hext, HextUniform Hu, float* __restrict__ vel,
-                     float* __restrict__ pressure, float* __restrict__ force_out, Consts k, int kbc_on_g,
-                     KbcScalars K, Grid g) {
-  using L = Lat<DIM>;
-  const PlaneCell c = plane_cell(g);
-  if (!c.live) return;
-  const int i = c.i;
-  const Nbr nb(c, g);
-  const PopIndex<IDX32> at(g);
-  // All 2Q pulls are issued first, before the flag byte is known: they are the only HBM-latency loads of the
-  // kernel (the stencil fields below mostly hit L1/L2); at 512 threads/SM this keeps ~78 KB per SM in flight.
-  float gv[L::Q];
-#pragma unroll
-  for (int q = 0; q < L::Q; ++q) gv[q] = ld_spec(gi + at(q, i + nb.at<DIM>(q, 1)));
-  const uint8_t fl = flags[i];
-  if (fl != LBMFF_FLUID) {
-    float fv[L::Q];
-#pragma unroll
-    for (int q = 0; q < L::Q; ++q) fv[q] = __ldg(fi + at(q, i + nb.at<DIM>(q, 1)));
-    // OBSTACLE: stream then full-way bounce, out_q(x) = in_opp(q)(x + e_q) -- the value pulled for opp(q).
-    // Other non-FLUID cells are only streamed (HCZ collides FLUID cells only, HCZ_3d.py:357-359).
-    const bool obst = fl == LBMFF_OBSTACLE;
-#pragma unroll
-    for (int q = 0; q < L::Q; ++q) {
-      fo[at(q, i)] = obst ? fv[L::opp(q)] : fv[q];
-      go[at(q, i)] = obst ? gv[L::opp(q)] : gv[q];
-    }
-    return;
-  }
-  // ---- capillary_process part 2 at a FLUID cell (HCZ_3d.py:217-261); all stencil inputs carry the
-  // get_grad shell rule in their data, so the 18-point stencils are plain constant-offset loads
-  const int x = interior(c.x, g.W), y = interior(c.y, g.H), z = DIM == 3 ? interior_z(g, c.z) : 0;
-  const int HW = g.H * g.W;
-  const int j0 = i + (x - c.x) + (y - c.y) * g.W + (z - c.z) * HW;
-  const float* w = ws + j0;
-  float glap[3], gfai[3], gprho[3];
-  grad_at_fast<DIM>(Centred32{w, g.W, HW, x, y, z}, x, y, z, k.inv12dx, glap);
-  grad_at_fast<DIM>(Centred32{w + g.N, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gfai);
-  grad_at_fast<DIM>(Centred32{w + 2 * g.N, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gprho);
-  const float rho = rho_[i];
-  const float dn = affine_density(rho, k.aff);
-  float F[DIM];
-#pragma unroll
-  for (int a = 0; a < DIM; ++a) {
-    F[a] = k.kappa * dn * glap[a];
-    if (a == 1) F[a] += k.grav_y * dn;
-  }
-  if (MAGNETIC) {
-    float gchi[3], gpsi[3], H2 = 0.0f;
-    grad_at_fast<DIM>(Centred32{chi + j0, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gchi);
-    grad_at_fast<DIM>(Centred32{psi + j0, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gpsi);
-#pragma unroll
-    for (int a = 0; a < DIM; ++a) {
-      const float he = Hext ? __ldg(Hext + a * g.N + i) : Hu.v[a];
-      const float ht = he - gpsi[a];  // H_ext + H_int, H_int = -grad(psi) (LBM_magnetic_3d.py:184)
-      H2 += ht * ht;
-    }
-#pragma unroll
-    for (int a = 0; a < DIM; ++a) F[a] += k.kelvin * H2 * gchi[a];
-  }
-  float s = 0.f, m[3] = {0.f, 0.f, 0.f};
-#pragma unroll
-  for (int q = 0; q < L::Q; ++q) {
-    s += gv[q];
-    if (L::ex(q) == 1) m[0] += gv[q]; else if (L::ex(q) == -1) m[0] -= gv[q];
-    if (L::ey(q) == 1) m[1] += gv[q]; else if (L::ey(q) == -1) m[1] -= gv[q];
-    if (DIM == 3) { if (L::ez(q) == 1) m[2] += gv[q]; else if (L::ez(q) == -1) m[2] -= gv[q]; }
-  }
-  float u[DIM], dot = 0.f;
-  const float inv_dn = k.vel_scale / dn;  // 1 / (cs2 density)
-#pragma unroll
-  for (int a = 0; a < DIM; ++a) {
-    u[a] = (m[a] * k.c + k.half_dt_RT * F[a]) * inv_dn;
-    vel[a * g.N + i] = u[a];
-    if (force_out) force_out[a * g.N + i] = F[a];
-    dot += u[a] * gprho[a];
-  }
-  const float p = s - k.half_dt * dot;
-  pressure[i] = p;
-  // ---- HCZ collision (HCZ_3d.py:283-361)
-  const HczCell<DIM> C = hcz_prepare<DIM>(rho, u, dn, p, F, gfai, gprho, k);
-  bool relaxed = false;
-  if constexpr (DIM == 2) {
-    if (kbc_on_g) {  // entropic KBC relaxation of g (HCZ_2d.py:244-256)
-      float geq[9], gk[9];
-#pragma unroll
-      for (int q = 0; q < 9; ++q) geq[q] = hcz_geq_q<2>(q, C);
-      kbc_relax(gv, geq, rho, u, k.c, kbc_on_g == 1 ? 1 : 0, K, gk);
-#pragma unroll
-      for (int q = 0; q < 9; ++q) gv[q] = gk[q];
-      relaxed = true;
-    }
-  }
-#pragma unroll
-  for (int q = 0; q < L::Q; ++q) {
-    float fq = 0.0f;
-    float gq = gv[q];
-    hcz_collide_q<DIM>(q, C, k, fq, gq, relaxed);
-    go[at(q, i)] = gq;
-  }
-  float fv[L::Q];
-#pragma unroll
-  for (int q = 0; q < L::Q; ++q) fv[q] = ld_spec(fi + at(q, i + nb.at<DIM>(q, 1)));
-#pragma unroll
-  for (int q = 0; q < L::Q; ++q) {
-    float fq = fv[q];
-    float gq = 0.0f;
-    hcz_collide_q<DIM>(q, C, k, fq, gq, relaxed);
-    fo[at(q, i)] = fq;
-  }
-}
-
 // ---- single-phase: stream + macro + bounce + BGK/KBC (demo_2d_LBM.py:101-121) -------------------
 template <int DIM, int MODE, bool IDX32>  // MODE 0: BGK, 1: KBC (D2Q9)
 __global__ void __launch_bounds__(kThreads) k_stream_collide(const float* __restrict__ fi, float* __restrict__ fo,
@@ -501,23 +382,6 @@ static int shell_rule_impl(float* field, const uint8_t* flags, const Grid& g, cu
   return check_launch(where);
 }
 
-// LBMFF_COLLIDE_VARIANT = 0 (all 2Q pulls first, 2 blocks/SM) | 1 (phased g then f, 3 blocks/SM; 3-D)
-static int collide_variant() {
-  static const int v = [] {
-    const char* e = getenv("LBMFF_COLLIDE_VARIANT");
-    return e ? atoi(e) : 0;
-  }();
-  return v;
-}
-
-static int collide_block_x() {
-  static const int v = [] {
-    const char* e = getenv("LBMFF_COLLIDE_BX");
-    return e ? atoi(e) : 64;   // 64 x 4 blocks: 14.3 ms vs 15.2 ms for 256 x 1 at 512^3 (y neighbours shared in L1)
-  }();
-  return v;
-}
-
 template <int DIM>
 static int collide_stream_impl(const float* f_in, const float* g_in, float* f_out, float* g_out, const float* rho,
                                const uint8_t* flags, const uint8_t* mflags, const float* ws, float* chi,
@@ -537,12 +401,12 @@ static int collide_stream_impl(const float* f_in, const float* g_in, float* f_ou
     launch_shell_rule<DIM>(psi, mflags, g, st);
     launch_shell_rule<DIM>(chi, flags, g, st);
   }
-  const PlaneLaunch pl = plane_launch(g, collide_block_x());
+  const PlaneLaunch pl = plane_launch(g, 64)  /* 64 x 4 blocks share y neighbours in L1: 14.3 ms vs 15.2 ms for 256 x 1 at 512^3 */;
   const long long Q = Lat<DIM>::Q, N = g.N;
   const KbcScalars K = make_kbc(p->tau_g);
   for (long long b = 0; b < g.B; ++b) {
 #define LBMFF_CS(MAG, IX)                                                                                         \
-  (DIM == 3 && collide_variant() == 1 ? k_hcz_collide_stream_phased<DIM, MAG, IX> : k_hcz_collide_stream<DIM, MAG, IX>)<<<pl.grid, pl.block, 0, st>>>( \
+  k_hcz_collide_stream<DIM, MAG, IX><<<pl.grid, pl.block, 0, st>>>(                                               \
       f_in + b * Q * N, g_in + b * Q * N, f_out + b * Q * N, g_out + b * Q * N, rho + b * N, flags + b * N,       \
       ws + b * 3 * N, MAG ? chi + b * N : nullptr, MAG ? psi + b * N : nullptr, Hext ? Hext + b * DIM * N : nullptr, \
       hu, vel + b * DIM * N, pressure + b * N, force_out ? force_out + b * DIM * N : nullptr, k, kbc_on_g, K, g)

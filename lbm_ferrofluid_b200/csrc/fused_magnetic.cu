@@ -37,9 +37,10 @@ __global__ void __launch_bounds__(kThreads) k_mag_source(const float* __restrict
 // ---- population-faithful fused sweep ----------------------------------------------------------
 // OBSTACLE cell x: out_q(x) = in_opp(q)(x + e_q)   (stream, then bounce; walls never collide)
 // other cells:     h_q = in_q(x - e_q); psi = sum_{q>=1} h_q / (1 - w0); out_q = collide(h_q, psi, rhs)
-// HINT: 0 default caching, 1 streaming stores (st.global.cs)
-template <int DIM, bool WRITE_PSI, int HINT = 0, bool IDX32 = true, int MB = 1>
-__global__ void __launch_bounds__(kThreads, MB) k_mag_sweep(const float* __restrict__ hin, float* __restrict__ hout,
+// Register cap: five resident blocks per SM in 3-D (48 registers, 1280 threads/SM) measured fastest -- 3.17 ms per
+// 512^3 sweep against 3.29 ms uncapped (64 registers) and 3.38 ms at six blocks (40 registers, spills).
+template <int DIM, bool WRITE_PSI, bool IDX32>
+__global__ void __launch_bounds__(kThreads, DIM == 3 ? 5 : 1) k_mag_sweep(const float* __restrict__ hin, float* __restrict__ hout,
                                                         const uint8_t* __restrict__ mflags,
                                                         const float* __restrict__ rhs, float* __restrict__ psi_out,
                                                         Consts k, Grid g) {
@@ -76,119 +77,7 @@ __global__ void __launch_bounds__(kThreads, MB) k_mag_sweep(const float* __restr
     for (int q = 0; q < L::Q; ++q) hv[q] = mag_collide_q<DIM>(q, hv[q], psi, r, k);
   }
 #pragma unroll
-  for (int q = 0; q < L::Q; ++q) {
-    if (HINT >= 1) __stcs(out + at(q, i), hv[q]);
-    else out[at(q, i)] = hv[q];
-  }
-}
-
-// ---- population-faithful sweep, four cells per thread -------------------------------------------------
-// Same arithmetic per cell as k_mag_sweep (bit-identical results); W % 4 == 0.  A thread owns cells
-// x0..x0+3 of one row: populations with e_x = 0 are one aligned 128-bit load, those with e_x = +-1 one aligned
-// 128-bit load plus the neighbouring lane's edge value (warp shuffle; the lane at a warp or row end loads
-// it), every store is an aligned 128-bit store.  A quarter of the address arithmetic per cell and 16 B
-// requests on every stream.  OBSTACLE cells (the x shell of every row, whole z-shell planes) are redone by
-// the one-cell routine after the vector store.
-template <int DIM>
-__device__ __forceinline__ void mag_sweep_cell(const float* __restrict__ in, float* __restrict__ out,
-                                               const uint8_t* __restrict__ fl, const float* __restrict__ rhs,
-                                               float* __restrict__ psi_out, bool write_psi, long long i,
-                                               const Consts& k, const Grid& g) {
-  using L = Lat<DIM>;
-  const Cell c = cell_of(i, g);
-  const int xm = wrap(c.x - 1, g.W), xp = wrap(c.x + 1, g.W);
-  const int ym = wrap(c.y - 1, g.H), yp = wrap(c.y + 1, g.H);
-  const int zm = DIM == 3 ? wrap(c.z - 1, g.D) : 0, zp = DIM == 3 ? wrap(c.z + 1, g.D) : 0;
-  const bool obst = fl[i] == LBMFF_OBSTACLE;
-  float hv[L::Q];
-#pragma unroll
-  for (int q = 0; q < L::Q; ++q) {
-    const int s = obst ? -1 : 1;
-    const int sx = L::ex(q) * s == 1 ? xm : (L::ex(q) * s == -1 ? xp : c.x);
-    const int sy = L::ey(q) * s == 1 ? ym : (L::ey(q) * s == -1 ? yp : c.y);
-    const int sz = L::ez(q) * s == 1 ? zm : (L::ez(q) * s == -1 ? zp : c.z);
-    hv[q] = __ldg(in + (obst ? L::opp(q) : q) * g.N + lin(g, sx, sy, sz));
-  }
-  const float psi = psi_of<DIM>(hv);
-  if (write_psi) psi_out[i] = psi;
-  if (!obst) {
-    const float r = rhs[i];
-#pragma unroll
-    for (int q = 0; q < L::Q; ++q) hv[q] = mag_collide_q<DIM>(q, hv[q], psi, r, k);
-  }
-#pragma unroll
-  for (int q = 0; q < L::Q; ++q) out[q * g.N + i] = hv[q];
-}
-
-template <int DIM, bool WRITE_PSI>
-__global__ void __launch_bounds__(kThreads) k_mag_sweep_v4(const float* __restrict__ hin, float* __restrict__ hout,
-                                                           const uint8_t* __restrict__ mflags,
-                                                           const float* __restrict__ rhs,
-                                                           float* __restrict__ psi_out, Consts k, Grid g) {
-  using L = Lat<DIM>;
-  const long long i = g.i0 + 4 * ((long long)blockIdx.x * blockDim.x + threadIdx.x);
-  const bool live = i < g.i1;
-  const long long b = blockIdx.y;
-  const float* in = hin + b * L::Q * g.N;
-  float* out = hout + b * L::Q * g.N;
-  const uint8_t* fl = mflags + b * g.N;
-  const long long ic = live ? i : g.i0;   // idle lanes shadow a valid cell so the shuffles stay full-warp
-  const Cell c = cell_of(ic, g);
-  const int lane = threadIdx.x & 31;
-  const long long HW = (long long)g.H * g.W;
-  const long long yo[3] = {(long long)wrap(c.y - 1, g.H) * g.W, (long long)c.y * g.W,
-                           (long long)wrap(c.y + 1, g.H) * g.W};
-  const long long zo[3] = {DIM == 3 ? wrap(c.z - 1, g.D) * HW : 0, c.z * HW, DIM == 3 ? wrap(c.z + 1, g.D) * HW : 0};
-  const bool row_start = c.x == 0, row_end = c.x + 4 == g.W;
-  const int xl = row_start ? g.W - 1 : c.x - 1, xr = row_end ? 0 : c.x + 4;
-  float4 hv[L::Q];
-#pragma unroll
-  for (int q = 0; q < L::Q; ++q) {
-    const float* row = in + q * g.N + zo[1 - L::ez(q)] + yo[1 - L::ey(q)];
-    const float4 a = __ldg(reinterpret_cast<const float4*>(row + c.x));
-    if (L::ex(q) == 0) {
-      hv[q] = a;
-    } else if (L::ex(q) == 1) {   // cell x pulls from x - 1
-      float left = __shfl_up_sync(0xffffffffu, a.w, 1);
-      if (lane == 0 || row_start) left = __ldg(row + xl);
-      hv[q] = make_float4(left, a.x, a.y, a.z);
-    } else {                       // cell x pulls from x + 1
-      float right = __shfl_down_sync(0xffffffffu, a.x, 1);
-      if (lane == 31 || row_end) right = __ldg(row + xr);
-      hv[q] = make_float4(a.y, a.z, a.w, right);
-    }
-  }
-  if (!live) return;
-  float4 psi;
-  {
-    float4 s = hv[1];
-#pragma unroll
-    for (int q = 2; q < L::Q; ++q) {
-      s.x = __fadd_rn(s.x, hv[q].x); s.y = __fadd_rn(s.y, hv[q].y);
-      s.z = __fadd_rn(s.z, hv[q].z); s.w = __fadd_rn(s.w, hv[q].w);
-    }
-    const float d = 1.0f - L::w(0);
-    psi = make_float4(s.x / d, s.y / d, s.z / d, s.w / d);
-  }
-  if (WRITE_PSI) *reinterpret_cast<float4*>(psi_out + b * g.N + i) = psi;
-  const float4 r = __ldg(reinterpret_cast<const float4*>(rhs + b * g.N + i));
-#pragma unroll
-  for (int q = 0; q < L::Q; ++q) {
-    float4 o;
-    o.x = mag_collide_q<DIM>(q, hv[q].x, psi.x, r.x, k);
-    o.y = mag_collide_q<DIM>(q, hv[q].y, psi.y, r.y, k);
-    o.z = mag_collide_q<DIM>(q, hv[q].z, psi.z, r.z, k);
-    o.w = mag_collide_q<DIM>(q, hv[q].w, psi.w, r.w, k);
-    *reinterpret_cast<float4*>(out + q * g.N + i) = o;
-  }
-  const uchar4 f4 = *reinterpret_cast<const uchar4*>(fl + i);
-  if (f4.x == LBMFF_OBSTACLE || f4.y == LBMFF_OBSTACLE || f4.z == LBMFF_OBSTACLE || f4.w == LBMFF_OBSTACLE) {
-    const uint8_t fv[4] = {f4.x, f4.y, f4.z, f4.w};
-#pragma unroll
-    for (int t = 0; t < 4; ++t)
-      if (fv[t] == LBMFF_OBSTACLE)
-        mag_sweep_cell<DIM>(in, out, fl, rhs + b * g.N, psi_out + b * g.N, WRITE_PSI, i + t, k, g);
-  }
+  for (int q = 0; q < L::Q; ++q) out[at(q, i)] = hv[q];
 }
 
 // ---- tau == 1 scalar sweep ---------------------------------------------------------------------
@@ -398,294 +287,18 @@ __global__ void __launch_bounds__(kThreads) k_mag_materialize(const float* __res
 }
 
 template <int DIM>
-static void launch_sweep(bool wp, int hint, bool idx32, const PlaneLaunch& pl, cudaStream_t st, const float* in,
-                         float* out, const uint8_t* mflags, const float* rhs, float* psi_out, const Consts& k,
-                         const Grid& g) {
-#define LBMFF_SW(WP, HI, IX)                                                                                \
-  k_mag_sweep<DIM, WP, HI, IX><<<pl.grid, pl.block, 0, st>>>(in + b * Lat<DIM>::Q * g.N, out + b * Lat<DIM>::Q * g.N, \
-                                                             mflags + b * g.N, rhs + b * g.N,                    \
-                                                             psi_out ? psi_out + b * g.N : nullptr, k, g)
-  // minimum resident blocks per SM (register cap): 5 -> 48 registers, 1280 threads/SM: 3.17 ms per 512^3 sweep
-  // (6.43 TB/s); uncapped (64 registers, 4 blocks) 3.29 ms; 6 -> 40 registers with spills 3.38 ms; 8 -> 4.84 ms
-  static const int mb = [] { const char* e = getenv("LBMFF_SWEEP_MB"); return e ? atoi(e) : 5; }();
+static void launch_sweep(bool wp, const PlaneLaunch& pl, cudaStream_t st, const float* in, float* out,
+                         const uint8_t* mflags, const float* rhs, float* psi_out, const Consts& k, const Grid& g) {
+  const long long Q = Lat<DIM>::Q;
+  const bool idx32 = Q * g.N < 0xffffffffLL;
+#define LBMFF_SW(WP, IX)                                                                                    \
+  k_mag_sweep<DIM, WP, IX><<<pl.grid, pl.block, 0, st>>>(in + b * Q * g.N, out + b * Q * g.N, mflags + b * g.N, \
+                                                         rhs + b * g.N, psi_out ? psi_out + b * g.N : nullptr, k, g)
   for (long long b = 0; b < g.B; ++b) {
-    if (idx32 && !hint && mb >= 5) {
-#define LBMFF_SWMB(WP, M)                                                                                          \
-  k_mag_sweep<DIM, WP, 0, true, M><<<pl.grid, pl.block, 0, st>>>(in + b * Lat<DIM>::Q * g.N, out + b * Lat<DIM>::Q * g.N, \
-                                                                 mflags + b * g.N, rhs + b * g.N,                 \
-                                                                 psi_out ? psi_out + b * g.N : nullptr, k, g)
-      if (mb == 5) { if (wp) LBMFF_SWMB(true, 5); else LBMFF_SWMB(false, 5); }
-      else if (mb == 6) { if (wp) LBMFF_SWMB(true, 6); else LBMFF_SWMB(false, 6); }
-      else { if (wp) LBMFF_SWMB(true, 8); else LBMFF_SWMB(false, 8); }
-#undef LBMFF_SWMB
-      continue;
-    }
-    if (idx32) {
-      if (hint) { if (wp) LBMFF_SW(true, 1, true); else LBMFF_SW(false, 1, true); }
-      else { if (wp) LBMFF_SW(true, 0, true); else LBMFF_SW(false, 0, true); }
-    } else {
-      if (wp) LBMFF_SW(true, 0, false); else LBMFF_SW(false, 0, false);
-    }
+    if (idx32) { if (wp) LBMFF_SW(true, true); else LBMFF_SW(false, true); }
+    else { if (wp) LBMFF_SW(true, false); else LBMFF_SW(false, false); }
   }
 #undef LBMFF_SW
-}
-
-// ---- TWO population-faithful sweeps in one pass over h (temporal blocking, 3-D) -----------------------------------
-// A block owns a 32 x 8 column of cells and marches upwards in z.  Per plane it (A) runs sweep 1 on the column
-// extended by a one-cell rim (34 x 10 cells, one thread each) straight from global memory and parks the 19
-// post-sweep-1 populations of that plane in a four-slot shared-memory ring, then (B) runs sweep 2 for the 32 x 8
-// cells of the plane below from the ring and stores the result.  h is read 1.33x and written once per TWO sweeps
-// (about 180 B per cell instead of 304 B); the rim is recomputed by the neighbouring block with identical
-// arithmetic, so the result is bit-identical to two k_mag_sweep launches.  The 19 pulls of the next plane are in
-// flight in registers while (B) runs.
-constexpr int kPX = 32, kPY = 8, kPW = kPX + 2, kPH = kPY + 2, kPCells = kPW * kPH, kPThreads = 352, kPRing = 4;
-constexpr size_t kPairSmem = (size_t)kPRing * 19 * kPCells * sizeof(float);
-
-template <bool WRITE_PSI, bool IDX32>
-__global__ void __launch_bounds__(kPThreads, 2)
-k_mag_sweep_pair(const float* __restrict__ in, float* __restrict__ out, const uint8_t* __restrict__ fl,
-                 const float* __restrict__ rhs, float* __restrict__ psi_out, Consts k, Grid g, int zc) {
-  using L = Lat<3>;
-  extern __shared__ float s1[];   // [ring][q][kPH][kPW]
-  const int tid = threadIdx.x;
-  const int x0 = blockIdx.x * kPX, y0 = blockIdx.y * kPY;
-  const int zs = g.zb + blockIdx.z * zc;
-  const int ze = min(zs + zc, g.zb + g.zn);   // sweep-2 output planes [zs, ze)
-  const int HW = g.H * g.W;
-  const PopIndex<IDX32> at(g);
-  // ---- role A: one cell of the rim-extended tile (periodic in x, y)
-  const bool a_on = tid < kPCells;
-  const int ay = a_on ? tid / kPW : 0, ax = a_on ? tid - ay * kPW : 0;
-  int gx = x0 - 1 + ax, gy = y0 - 1 + ay;
-  gx = gx < 0 ? gx + g.W : gx; gy = gy < 0 ? gy + g.H : gy;
-  while (gx >= g.W) gx -= g.W;
-  while (gy >= g.H) gy -= g.H;
-  const int a_xy = gy * g.W + gx;
-  Nbr nba(PlaneCell{gx, gy, 0, 0, true}, g);
-  // ---- role B: one output cell of the tile
-  const bool b_on = tid < kPX * kPY;
-  const int bx = tid & (kPX - 1), by = tid / kPX;
-  const int ox = x0 + bx, oy = y0 + by;
-  const bool b_live = b_on && ox < g.W && oy < g.H;
-  const int b_xy = b_live ? oy * g.W + ox : 0;
-
-  float P[L::Q];      // pulls of the plane role A works on next (in flight while role B runs)
-  float p_rhs = 0.f;
-  uint8_t p_fl = LBMFF_FLUID;
-  auto fetch = [&](int z) {   // z: any integer plane index, periodic in the local array
-    if (!a_on) return;
-    const int zz = z < 0 ? z + g.D : (z >= g.D ? z - g.D : z);
-    nba.zm = zz == 0 ? (g.D - 1) * HW : -HW;
-    nba.zp = zz == g.D - 1 ? -(g.D - 1) * HW : HW;
-    const int i = zz * HW + a_xy;
-#pragma unroll
-    for (int q = 0; q < L::Q; ++q) P[q] = ld_spec(in + at(q, i + nba.at<3>(q, 1)));
-    p_rhs = __ldg(rhs + i);
-    p_fl = fl[i];
-  };
-  auto sweep1_to_ring = [&](int z) {   // consume P: h1 of plane z -> ring slot
-    if (!a_on) return;
-    if (p_fl == LBMFF_OBSTACLE) {
-#pragma unroll
-      for (int q = 1; q < L::Q; ++q)
-        if (q < L::opp(q)) { const float t = P[q]; P[q] = P[L::opp(q)]; P[L::opp(q)] = t; }
-    } else {
-      const float psi = psi_of<3>(P);
-#pragma unroll
-      for (int q = 0; q < L::Q; ++q) P[q] = mag_collide_q<3>(q, P[q], psi, p_rhs, k);
-    }
-    float* slot = s1 + ((z - zs + 1) & (kPRing - 1)) * (L::Q * kPCells) + ay * kPW + ax;
-#pragma unroll
-    for (int q = 0; q < L::Q; ++q) slot[q * kPCells] = P[q];
-  };
-
-  fetch(zs - 1);
-  sweep1_to_ring(zs - 1);
-  fetch(zs);
-  sweep1_to_ring(zs);
-  fetch(zs + 1);
-  // own flag / source of the first output plane
-  float b_rhs = b_live ? __ldg(rhs + zs * HW + b_xy) : 0.f;
-  uint8_t b_fl = b_live ? fl[zs * HW + b_xy] : (uint8_t)LBMFF_FLUID;
-  for (int z = zs; z < ze; ++z) {
-    sweep1_to_ring(z + 1);
-    if (z + 1 < ze) fetch(z + 2);
-    const float r = b_rhs;
-    const uint8_t f0 = b_fl;
-    if (b_live && z + 1 < ze) {
-      b_rhs = __ldg(rhs + (z + 1) * HW + b_xy);
-      b_fl = fl[(z + 1) * HW + b_xy];
-    }
-    __syncthreads();
-    if (b_live) {
-      const int i = z * HW + b_xy;
-      const float* ring[3] = {s1 + ((z - zs) & (kPRing - 1)) * (L::Q * kPCells),
-                              s1 + ((z - zs + 1) & (kPRing - 1)) * (L::Q * kPCells),
-                              s1 + ((z - zs + 2) & (kPRing - 1)) * (L::Q * kPCells)};   // planes z-1, z, z+1
-      float hv[L::Q];
-#pragma unroll
-      for (int q = 0; q < L::Q; ++q)
-        hv[q] = ring[1 - L::ez(q)][q * kPCells + (by + 1 - L::ey(q)) * kPW + (bx + 1 - L::ex(q))];
-      const bool obst = f0 == LBMFF_OBSTACLE;
-      if (obst) {
-#pragma unroll
-        for (int q = 1; q < L::Q; ++q)
-          if (q < L::opp(q)) { const float t = hv[q]; hv[q] = hv[L::opp(q)]; hv[L::opp(q)] = t; }
-      }
-      const float psi = psi_of<3>(hv);
-      if (WRITE_PSI) psi_out[i] = psi;
-      if (!obst) {
-#pragma unroll
-        for (int q = 0; q < L::Q; ++q) hv[q] = mag_collide_q<3>(q, hv[q], psi, r, k);
-      }
-#pragma unroll
-      for (int q = 0; q < L::Q; ++q) out[at(q, i)] = hv[q];
-    }
-  }
-}
-
-// ---- the same two-sweep pass, warp-specialised ---------------------------------------------------------------------
-// Producer warps (352 threads, one per cell of the 34 x 10 extended tile) run sweep 1 plane after plane into the
-// ring; consumer warps (256 threads, one per output cell) run sweep 2 out of it.  The two groups are coupled only by
-// one full/empty named barrier pair per ring slot (bar.arrive / bar.sync), so producers run up to three planes ahead
-// and neither group ever waits for the other's memory latency at a block-wide barrier.
-constexpr int kWsProd = 352, kWsCons = kPX * kPY, kWsThreads = kWsProd + kWsCons;
-
-__device__ __forceinline__ void named_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
-__device__ __forceinline__ void named_arrive(int id, int n) {
-  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory");
-}
-
-template <bool WRITE_PSI, bool IDX32>
-__global__ void __launch_bounds__(kWsThreads, 2)
-k_mag_sweep_pair_ws(const float* __restrict__ in, float* __restrict__ out, const uint8_t* __restrict__ fl,
-                    const float* __restrict__ rhs, float* __restrict__ psi_out, Consts k, Grid g, int zc) {
-  using L = Lat<3>;
-  extern __shared__ float s1[];   // [ring][q][kPH][kPW]
-  const int x0 = blockIdx.x * kPX, y0 = blockIdx.y * kPY;
-  const int zs = g.zb + blockIdx.z * zc;
-  const int ze = min(zs + zc, g.zb + g.zn);   // sweep-2 output planes [zs, ze)
-  const int HW = g.H * g.W;
-  const PopIndex<IDX32> at(g);
-  // barrier ids: 1 + slot = "slot full", 1 + kPRing + slot = "slot empty"
-  if (threadIdx.x >= kWsCons) {
-    // ================= producers: sweep 1 on the extended tile =================
-    const int tid = threadIdx.x - kWsCons;
-    const bool on = tid < kPCells;
-    const int ay = on ? tid / kPW : 0, ax = on ? tid - ay * kPW : 0;
-    int gx = x0 - 1 + ax, gy = y0 - 1 + ay;
-    gx = gx < 0 ? gx + g.W : gx; gy = gy < 0 ? gy + g.H : gy;
-    while (gx >= g.W) gx -= g.W;
-    while (gy >= g.H) gy -= g.H;
-    const int a_xy = gy * g.W + gx;
-    Nbr nba(PlaneCell{gx, gy, 0, 0, true}, g);
-    float P[L::Q];
-    float p_rhs = 0.f;
-    uint8_t p_fl = LBMFF_FLUID;
-    auto fetch = [&](int z) {
-      const int zz = z < 0 ? z + g.D : (z >= g.D ? z - g.D : z);
-      nba.zm = zz == 0 ? (g.D - 1) * HW : -HW;
-      nba.zp = zz == g.D - 1 ? -(g.D - 1) * HW : HW;
-      const int i = zz * HW + a_xy;
-#pragma unroll
-      for (int q = 0; q < L::Q; ++q) P[q] = ld_spec(in + at(q, i + nba.at<3>(q, 1)));
-      p_rhs = __ldg(rhs + i);
-      p_fl = fl[i];
-    };
-    if (on) fetch(zs - 1);
-    for (int pz = zs - 1, it = 0; pz <= ze; ++pz, ++it) {
-      const int slot = (pz - zs + 1) & (kPRing - 1);
-      if (it >= kPRing) named_sync(1 + kPRing + slot, kWsThreads);   // consumers are done with plane pz - 4
-      if (on) {
-        if (p_fl == LBMFF_OBSTACLE) {
-#pragma unroll
-          for (int q = 1; q < L::Q; ++q)
-            if (q < L::opp(q)) { const float t = P[q]; P[q] = P[L::opp(q)]; P[L::opp(q)] = t; }
-        } else {
-          const float psi = psi_of<3>(P);
-#pragma unroll
-          for (int q = 0; q < L::Q; ++q) P[q] = mag_collide_q<3>(q, P[q], psi, p_rhs, k);
-        }
-        float* dst = s1 + slot * (L::Q * kPCells) + ay * kPW + ax;
-#pragma unroll
-        for (int q = 0; q < L::Q; ++q) dst[q * kPCells] = P[q];
-        if (pz < ze) fetch(pz + 1);
-      }
-      __threadfence_block();
-      named_arrive(1 + slot, kWsThreads);
-    }
-  } else {
-    // ================= consumers: sweep 2 on the tile =================
-    const int tid = threadIdx.x;
-    const int bx = tid & (kPX - 1), by = tid / kPX;
-    const int ox = x0 + bx, oy = y0 + by;
-    const bool live = ox < g.W && oy < g.H;
-    const int b_xy = live ? oy * g.W + ox : 0;
-    float b_rhs = live ? __ldg(rhs + zs * HW + b_xy) : 0.f;
-    uint8_t b_fl = live ? fl[zs * HW + b_xy] : (uint8_t)LBMFF_FLUID;
-    named_sync(1 + 0, kWsThreads);   // plane zs - 1 (slot 0)
-    named_sync(1 + 1, kWsThreads);   // plane zs     (slot 1)
-    for (int z = zs; z < ze; ++z) {
-      const int s0 = (z - zs) & (kPRing - 1), s1i = (z - zs + 1) & (kPRing - 1), s2 = (z - zs + 2) & (kPRing - 1);
-      const float r = b_rhs;
-      const uint8_t f0 = b_fl;
-      if (live && z + 1 < ze) {
-        b_rhs = __ldg(rhs + (z + 1) * HW + b_xy);
-        b_fl = fl[(z + 1) * HW + b_xy];
-      }
-      named_sync(1 + s2, kWsThreads);   // plane z + 1
-      if (live) {
-        const int i = z * HW + b_xy;
-        const float* ring[3] = {s1 + s0 * (L::Q * kPCells), s1 + s1i * (L::Q * kPCells), s1 + s2 * (L::Q * kPCells)};
-        float hv[L::Q];
-#pragma unroll
-        for (int q = 0; q < L::Q; ++q)
-          hv[q] = ring[1 - L::ez(q)][q * kPCells + (by + 1 - L::ey(q)) * kPW + (bx + 1 - L::ex(q))];
-        const bool obst = f0 == LBMFF_OBSTACLE;
-        if (obst) {
-#pragma unroll
-          for (int q = 1; q < L::Q; ++q)
-            if (q < L::opp(q)) { const float t = hv[q]; hv[q] = hv[L::opp(q)]; hv[L::opp(q)] = t; }
-        }
-        const float psi = psi_of<3>(hv);
-        if (WRITE_PSI) psi_out[i] = psi;
-        if (!obst) {
-#pragma unroll
-          for (int q = 0; q < L::Q; ++q) hv[q] = mag_collide_q<3>(q, hv[q], psi, r, k);
-        }
-#pragma unroll
-        for (int q = 0; q < L::Q; ++q) out[at(q, i)] = hv[q];
-      }
-      named_arrive(1 + kPRing + s0, kWsThreads);   // plane z - 1 is free
-    }
-  }
-}
-
-// LBMFF_SWEEP_PAIR = 1: issue the population-faithful sweeps two at a time (k_mag_sweep_pair) | 0: one per launch
-static int pair_variant() {
-  static const int v = [] {
-    const char* e = getenv("LBMFF_SWEEP_PAIR");
-    return e ? atoi(e) : 0;
-  }();
-  return v;
-}
-
-// LBMFF_SWEEP_VARIANT = 1 (one cell per thread, default: 3.80 ms per 512^3 sweep) | 4 (four cells per thread: 3.87 ms)
-static int sweep_variant() {
-  static const int v = [] {
-    const char* e = getenv("LBMFF_SWEEP_VARIANT");
-    return e ? atoi(e) : 1;
-  }();
-  return v;
-}
-
-// LBMFF_SCALAR_VARIANT = 1 (shared-memory tiled, default) | 0 (one thread per cell, L1/L2 served)
-static int scalar_variant() {
-  static const int v = [] {
-    const char* e = getenv("LBMFF_SCALAR_VARIANT");
-    return e ? atoi(e) : 1;
-  }();
-  return v;
 }
 
 template <int DIM>
@@ -696,67 +309,11 @@ static int sweeps_impl(float* hA, float* hB, const uint8_t* mflags, const float*
   if (!(tau > 0)) return bad_arg(where, "tau must be positive");
   if (g.N > 0x7fffffffLL) return bad_arg(where, "more than 2^31-1 cells per batch item");
   const Consts k = make_consts(dx, dt, tau);
-  const dim3 grid(blocks_for(g.i1 - g.i0), (unsigned)g.B);
-  // four cells per thread needs 16-byte aligned rows and plane ranges
-  const bool vec4 = sweep_variant() == 4 && g.W % 4 == 0 && g.i0 % 4 == 0 && g.i1 % 4 == 0 &&
-                    ((uintptr_t)hA | (uintptr_t)hB | (uintptr_t)rhs | (uintptr_t)psi_out | (uintptr_t)mflags) % 16 == 0;
-  const dim3 grid4(blocks_for((g.i1 - g.i0) / 4), (unsigned)g.B);
   const PlaneLaunch pl = plane_launch(g);
-  // Temporal blocking: sweeps are issued two at a time where that keeps the documented buffer parity (the result
-  // must land in hA for even n, hB for odd n, and every launch flips the buffer): n - 2*np singles, np pairs,
-  // with (n - np) of the same parity as n, i.e. np even.
-  int np = 0;
-  if (DIM == 3 && pair_variant() && g.W >= 8 && g.H >= 8 && g.zn >= 4) {
-    np = (n / 2) & ~1;
-    static bool attr_set = false;
-    if (!attr_set) {
-      cudaFuncSetAttribute(k_mag_sweep_pair<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmem);
-      cudaFuncSetAttribute(k_mag_sweep_pair<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmem);
-      cudaFuncSetAttribute(k_mag_sweep_pair<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmem);
-      cudaFuncSetAttribute(k_mag_sweep_pair<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmem);
-      cudaFuncSetAttribute(k_mag_sweep_pair_ws<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmem);
-      cudaFuncSetAttribute(k_mag_sweep_pair_ws<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmem);
-      attr_set = true;
-    }
-  }
-  const int launches = n - np;
-  int done = 0;   // sweeps completed
-  for (int s = 0; s < launches; ++s) {
+  for (int s = 0; s < n; ++s) {
     const float* in = (s & 1) ? hB : hA;
     float* out = (s & 1) ? hA : hB;
-    const bool pair = s < np;
-    done += pair ? 2 : 1;
-    const bool wp = done == n && psi_out;
-    if (pair) {
-      const int zc = g.zn < 32 ? g.zn : 32;
-      const dim3 tg((g.W + kPX - 1) / kPX, (g.H + kPY - 1) / kPY, (g.zn + zc - 1) / zc);
-      const bool ix = (long long)Lat<DIM>::Q * g.N < 0xffffffffLL;
-      for (long long b = 0; b < g.B; ++b) {
-        const float* i_ = in + b * 19 * g.N;
-        float* o_ = out + b * 19 * g.N;
-        const uint8_t* f_ = mflags + b * g.N;
-        const float* r_ = rhs + b * g.N;
-        float* p_ = psi_out ? psi_out + b * g.N : nullptr;
-        if (ix && pair_variant() == 2) {
-          if (wp) k_mag_sweep_pair_ws<true, true><<<tg, kWsThreads, kPairSmem, st>>>(i_, o_, f_, r_, p_, k, g, zc);
-          else k_mag_sweep_pair_ws<false, true><<<tg, kWsThreads, kPairSmem, st>>>(i_, o_, f_, r_, p_, k, g, zc);
-        } else if (ix) {
-          if (wp) k_mag_sweep_pair<true, true><<<tg, kPThreads, kPairSmem, st>>>(i_, o_, f_, r_, p_, k, g, zc);
-          else k_mag_sweep_pair<false, true><<<tg, kPThreads, kPairSmem, st>>>(i_, o_, f_, r_, p_, k, g, zc);
-        } else {
-          if (wp) k_mag_sweep_pair<true, false><<<tg, kPThreads, kPairSmem, st>>>(i_, o_, f_, r_, p_, k, g, zc);
-          else k_mag_sweep_pair<false, false><<<tg, kPThreads, kPairSmem, st>>>(i_, o_, f_, r_, p_, k, g, zc);
-        }
-      }
-      continue;
-    }
-    if (vec4) {
-      if (wp) k_mag_sweep_v4<DIM, true><<<grid4, kThreads, 0, st>>>(in, out, mflags, rhs, psi_out, k, g);
-      else k_mag_sweep_v4<DIM, false><<<grid4, kThreads, 0, st>>>(in, out, mflags, rhs, psi_out, k, g);
-    } else {
-      launch_sweep<DIM>(wp, sweep_variant() == 2 ? 1 : 0, (long long)Lat<DIM>::Q * g.N < 0xffffffffLL, pl, st, in, out,
-                        mflags, rhs, psi_out, k, g);
-    }
+    launch_sweep<DIM>(s == n - 1 && psi_out, pl, st, in, out, mflags, rhs, psi_out, k, g);
   }
   return check_launch(where);
 }
@@ -773,7 +330,7 @@ static int sweeps_scalar_impl(float* aA, float* aB, const uint8_t* mflags, const
     const float* cur = (s & 1) ? aB : aA;
     float* prev = (s & 1) ? aA : aB;
     for (long long b = 0; b < g.B; ++b) {
-      if (DIM == 3 && scalar_variant() == 1 && g.W >= 4 && g.H >= 4) {
+      if (DIM == 3 && g.W >= 4 && g.H >= 4) {  // tiled kernel: 1.09 ms per 512^3 sweep; one thread per cell: 2.50 ms
         const int zc = g.zn < 32 ? g.zn : 32;
         const dim3 tg((g.W + kTX - 1) / kTX, (g.H + kTY - 1) / kTY, (g.zn + zc - 1) / zc);
         if (s == n - 1 && psi_out)
