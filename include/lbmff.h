@@ -307,6 +307,31 @@ int lbmff_slab_hcz_collide_stream_d3q19(const float* f_in, const float* g_in, fl
                                         float* pressure, float* force_out, const lbmff_slab* slab, int B, int D,
                                         int H, int W, lbmff_stream_t stream);
 
+/* ---- converged magnetic potential (opt-in; NOT a drop-in: the reference never converges) ----------------
+ * The reference relaxes the Poisson lattice with a fixed 30 warm-started sweeps per outer step
+ * (demo_3d_LBM_Rosensweig_instability.py:163-173; LBM_magnetic_3d.py:125-188).  These entries solve for the FIXED
+ * POINT of those sweeps at tau == 1 instead:  L psi = b  with the wall-aware D2Q9 / D3Q19 weighted graph Laplacian
+ * (full-way bounce-back = mirror), by Jacobi-preconditioned conjugate gradients entirely on the device (dot
+ * products reduced in double in a fixed order: deterministic; no host synchronisation).  psi is defined up to a
+ * constant -- only its gradient is used (H_int = -grad psi, LBM_magnetic_3d.py:183-186).  If sum(b) != 0 the
+ * sweeps' stationary state gains a constant c per sweep; the entry solves for that state (b is replaced by
+ * b - c (1 + omega), omega = wall-weight fraction of the cell; csrc/poisson_cg.cu) and reports c.
+ *   rhs      [B][N]  sweep-invariant source of lbmff_magnetic_source_*            (in)
+ *   psi      [B][N]  warm start in, solution out (OBSTACLE cells of mflags untouched)
+ *   work     [B][4][N] floats, scratch [B][lbmff_poisson_cg_scratch_doubles(D,H,W)] doubles    (device workspace)
+ *   max_iters, tol   stop when |r| <= tol * |b - c(1+omega)| or after max_iters iterations (always launched; the
+ *                    kernels of a finished solve return at once)
+ *   res_hist [B][max_iters + 1] floats or NULL: |r| after each iteration (entry 0 = warm start)
+ *   info     [B][5] doubles or NULL: iterations done, converged (0/1), |r|^2, |b - c(1+omega)|^2, c
+ * tau must be 1.0 (for tau != 1 the fixed point is not a compact stencil): anything else is rejected. */
+int lbmff_poisson_cg_scratch_doubles(int D, int H, int W);
+int lbmff_poisson_cg_2d(const float* rhs, const uint8_t* mflags, float* psi, float* work, double* scratch,
+                        int max_iters, double tol, double tau, double dx, double dt, float* res_hist, double* info,
+                        int B, int H, int W, lbmff_stream_t stream);
+int lbmff_poisson_cg_3d(const float* rhs, const uint8_t* mflags, float* psi, float* work, double* scratch,
+                        int max_iters, double tol, double tau, double dx, double dt, float* res_hist, double* info,
+                        int B, int D, int H, int W, lbmff_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -35,14 +35,17 @@ class FerroSolver:
     cell-centred field [B,dim,...] (then its staggered faces are built with get_staggered, as the demos
     do) or a uniform vector of ``dim`` floats; ``gravity`` the scalar given to set_gravity.
     ``magnetic_path``: "faithful" (population lattice h, any tau), "scalar" (tau == 1 collapse, walls on
-    the shell only; bit-identical psi) or "auto" (scalar when valid).
+    the shell only; bit-identical psi) or "auto" (scalar when valid).  "converged" is NOT the reference's
+    algorithm: instead of n_sweeps relaxation sweeps it solves for their fixed point with conjugate gradients
+    (poisson.PoissonCG; tau == 1 only) to relative residual ``cg_tol`` in at most ``cg_max_iters`` iterations,
+    warm-started from the previous step.
     """
 
     def __init__(self, flags: torch.Tensor, *, density_liquid=0.2508, density_gas=0.02381, rho_liquid=0.2508,
                  rho_gas=0.02381, kappa=0.01, tau_f=0.68, tau_g=0.68, tau=1.0, contact_angle=0.5 * math.pi,
                  gravity=1e-4, dx=1.0, dt=1.0, magnetic_flags: Optional[torch.Tensor] = None,
                  H_ext=None, n_sweeps: int = 30, KBC_type: Optional[int] = None, magnetic_path: str = "auto",
-                 keep_force: bool = True):
+                 keep_force: bool = True, cg_tol: float = 1e-4, cg_max_iters: int = 60):
         self.flags = H.need_cuda(flags, "flags", torch.uint8)
         self.device = self.flags.device
         self.dim, self.B, _, self.D, self.Hh, self.W = H.dims(self.flags)
@@ -101,14 +104,20 @@ class FerroSolver:
             if magnetic_path == "scalar" and not scalar_ok:
                 raise RuntimeError("magnetic_path='scalar' needs tau == 1 and every OBSTACLE cell of "
                                    "magnetic_flags on the outer shell")
-            if magnetic_path not in ("scalar", "faithful"):
-                raise ValueError("magnetic_path must be 'auto', 'faithful' or 'scalar'")
+            if magnetic_path == "converged" and float(tau) != 1.0:
+                raise RuntimeError("magnetic_path='converged' solves the fixed point of the tau == 1 sweeps only")
+            if magnetic_path not in ("scalar", "faithful", "converged"):
+                raise ValueError("magnetic_path must be 'auto', 'faithful', 'scalar' or 'converged'")
             self.magnetic_path = magnetic_path
             self.psi, self._rhs, self._chi = sc(1), sc(1), sc(1)
             if magnetic_path == "faithful":
                 self._h = [sc(self.Q), sc(self.Q)]
-            else:
+            elif magnetic_path == "scalar":
                 self._a = [sc(2), sc(2)]
+            else:
+                from .poisson import PoissonCG
+                self._h = self._a = ()
+                self.cg = PoissonCG(self.mflags, dx=self.dx, dt=self.dt, tol=cg_tol, max_iters=cg_max_iters)
             self._mcur = 0
         else:
             self.magnetic_path = None
@@ -142,6 +151,8 @@ class FerroSolver:
             return None
         if self.magnetic_path == "faithful":
             return self._h[self._mcur]
+        if self.magnetic_path == "converged":
+            raise RuntimeError("magnetic_path='converged' keeps no lattice populations (psi is solved for directly)")
         out = torch.empty((self.B, self.Q, *self.res), dtype=torch.float32, device=self.device)
         H.launch(f"lbmff_magnetic_materialize_h_{self.dim}d", self.device, H.ptr(self._a[self._mcur]),
                  H.ptr(self._a[1 - self._mcur]), H.ptr(self.psi), H.ptr(self._rhs), H.ptr(self.mflags), H.ptr(out),
@@ -235,7 +246,9 @@ class FerroSolver:
                 self._faces_read.record()
             m = self._mcur
             with self._timed("sweeps"):
-                if self.magnetic_path == "faithful":
+                if self.magnetic_path == "converged":
+                    self.cg.solve(self._rhs, self.psi)
+                elif self.magnetic_path == "faithful":
                     H.launch("lbmff_magnetic_sweeps_" + suf, dev, H.ptr(self._h[m]), H.ptr(self._h[1 - m]),
                              H.ptr(self.mflags), H.ptr(self._rhs), H.ptr(self.psi), self.n_sweeps,
                              float(self._tau), self.dx, self.dt, *sz)
@@ -243,7 +256,7 @@ class FerroSolver:
                     H.launch(f"lbmff_magnetic_sweeps_scalar_{d}d", dev, H.ptr(self._a[m]), H.ptr(self._a[1 - m]),
                              H.ptr(self.mflags), H.ptr(self._rhs), H.ptr(self.psi), self.n_sweeps, self.dx,
                              self.dt, *sz)
-            if self.n_sweeps & 1:
+            if self.n_sweeps & 1 and self.magnetic_path != "converged":
                 self._mcur = 1 - m
             chi, psi, mfl, hext, hu = self._chi, self.psi, self.mflags, self.H_ext, self._H_uniform
         args = [H.ptr(self._f[cur]), H.ptr(self._g[cur]), H.ptr(self._f[nxt]), H.ptr(self._g[nxt]),
@@ -332,7 +345,11 @@ class FerroSolver:
     def launches_per_step(self) -> int:
         wet = 5 if self.dim == 3 else 3
         shell = (6 if self.dim == 3 else 2) if self.magnetic else 0   # rim (+ two z-shell planes) for psi and chi
-        return 1 + (1 + self.n_sweeps if self.magnetic else 0) + wet + 1 + shell + 1
+        if self.magnetic_path == "converged":
+            mag = 1 + self.cg.launches_per_solve
+        else:
+            mag = 1 + self.n_sweeps if self.magnetic else 0
+        return 1 + mag + wet + 1 + shell + 1
 
     def total_mass(self) -> float:
         """sum over ALL cells (walls included) of sum_q f: conserved to round-off."""

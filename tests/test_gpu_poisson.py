@@ -1,0 +1,143 @@
+"""Converged magnetic potential: lbmff_poisson_cg_* / PoissonCG / FerroSolver("converged").
+
+The reference has no converged solver, so there is no golden: the checker is the reference's OWN sweep.  A solution
+psi* is correct iff it is a fixed point (modulo the additive constant the sweeps themselves drift by) of one
+propagation -> rebounce_obstacle -> psi_of_h sweep, which the CPU oracle executes in fp64
+(oracle/lbm_oracle.py, pinned against the reference's goldens), and iff the parity-tested GPU sweeps run long enough
+arrive at the same potential."""
+import math
+
+import pytest
+import torch
+
+from tests.util import one_oracle_sweep as _one_oracle_sweep, poisson_b_and_drift, poisson_case as _case
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("res", [(40, 36), (18, 20, 22)])
+def test_cg_solution_is_a_fixed_point_of_the_reference_sweep(res):
+    from lbm_ferrofluid_b200.poisson import PoissonCG
+
+    mflags, rhs, dim = _case(res)
+    cg = PoissonCG(mflags.cuda(), tol=1e-6, max_iters=1500, keep_history=True)
+    psi = torch.zeros((1, 1, *res), device="cuda")
+    cg.solve(rhs.cuda(), psi)
+    info = cg.info()[0]
+    assert info["converged"], info
+    assert info["iters"] < 400, info                  # Jacobi-PCG on n ~ 40: O(n) iterations, not O(n^2) sweeps
+    hist = cg.history()[0]
+    assert len(hist) == info["iters"] + 1 and hist[-1] <= 1e-6 * info["rhs_norm"] * 1.001
+    fluid = (mflags != 2)
+    _, _, c = poisson_b_and_drift(rhs, mflags)        # fp64, by rolls: what every sweep adds in the stationary state
+    assert abs(info["drift"] - c.item()) <= 1e-5 * abs(c.item()) + 1e-12
+    after = _one_oracle_sweep(psi.cpu(), rhs, mflags, drift=c.item())
+    d = (after - psi.cpu().double())[fluid]
+    scale = (psi.cpu().double()[fluid] - psi.cpu().double()[fluid].mean()).abs().max()
+    assert scale > 1e-3
+    assert (d - c.item()).abs().max().item() <= 2e-5 * scale.item(), ((d - c.item()).abs().max().item(), scale.item())
+
+
+@pytest.mark.parametrize("res", [(32, 28), (16, 14, 18)])
+def test_cg_equals_the_sweeps_run_to_convergence(res):
+    from lbm_ferrofluid_b200 import _host as H
+    from lbm_ferrofluid_b200.poisson import PoissonCG
+
+    mflags, rhs, dim = _case(res, seed=1)
+    mf, r = mflags.cuda(), rhs.cuda()
+    Q = 9 if dim == 2 else 19
+    hA = torch.zeros((1, Q, *res), device="cuda")
+    hB = torch.zeros_like(hA)
+    psi_sw = torch.zeros((1, 1, *res), device="cuda")
+    H.launch("lbmff_magnetic_sweeps_" + H.suffix(dim), mf.device, H.ptr(hA), H.ptr(hB), H.ptr(mf), H.ptr(r),
+             H.ptr(psi_sw), 6000, 1.0, 1.0, 1.0, *H.sizes(dim, 1, res[0] if dim == 3 else 1, res[-2], res[-1]))
+    psi = torch.zeros_like(psi_sw)
+    PoissonCG(mf, tol=1e-6, max_iters=1000).solve(r, psi)
+    fluid = (mf != 2)
+    a = psi_sw[fluid].double()
+    b = psi[fluid].double()
+    a, b = a - a.mean(), b - b.mean()
+    assert (a - b).norm().item() <= 1e-4 * a.norm().item(), (a - b).norm().item() / a.norm().item()
+
+
+def test_cg_is_deterministic_warm_start_is_free_and_batches_are_independent():
+    from lbm_ferrofluid_b200.poisson import PoissonCG
+
+    res = (20, 18, 16)
+    m0, r0, _ = _case(res, seed=2)
+    m1, r1, _ = _case(res, seed=3, interior_wall=False)
+    mf, r = torch.cat([m0, m1]).cuda(), torch.cat([r0, r1]).cuda()
+    cg = PoissonCG(mf, tol=1e-5, max_iters=300)
+    p1, p2 = torch.zeros_like(r), torch.zeros_like(r)
+    cg.solve(r, p1)
+    i1 = cg.info()
+    cg.solve(r, p2)
+    assert torch.equal(p1, p2) and all(i["converged"] for i in i1)
+    single = PoissonCG(m1.cuda(), tol=1e-5, max_iters=300)
+    q = torch.zeros((1, 1, *res), device="cuda")
+    single.solve(r1.cuda(), q)
+    assert torch.equal(q[0], p1[1])
+    before = p1.clone()
+    cg.solve(r, p1)                                   # already converged: zero iterations, psi untouched
+    assert [i["iters"] for i in cg.info()] == [0, 0] and torch.equal(before, p1)
+
+
+def test_cg_argument_errors():
+    from lbm_ferrofluid_b200 import _host as H
+    from lbm_ferrofluid_b200.poisson import PoissonCG
+    from lbm_ferrofluid_b200.solver import FerroSolver
+
+    m, r, _ = _case((12, 12, 12))
+    cg = PoissonCG(m.cuda(), max_iters=5)
+    psi = torch.zeros_like(r).cuda()
+    with pytest.raises(RuntimeError, match="tau == 1"):
+        H.launch("lbmff_poisson_cg_3d", psi.device, H.ptr(r.cuda()), H.ptr(cg.mflags), H.ptr(psi), H.ptr(cg._work),
+                 H.ptr(cg._scratch), 5, 1e-4, 0.8, 1.0, 1.0, H.ptr(None), H.ptr(None), 1, 12, 12, 12)
+    with pytest.raises(RuntimeError, match="null pointer"):
+        H.launch("lbmff_poisson_cg_3d", psi.device, H.ptr(None), H.ptr(cg.mflags), H.ptr(psi), H.ptr(cg._work),
+                 H.ptr(cg._scratch), 5, 1e-4, 1.0, 1.0, 1.0, H.ptr(None), H.ptr(None), 1, 12, 12, 12)
+    with pytest.raises(RuntimeError, match="sized for"):
+        cg.solve(r.cuda(), psi, max_iters=6)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        cg.solve(r, psi)
+    with pytest.raises(RuntimeError, match="tau == 1"):
+        FerroSolver(m.cuda(), magnetic_flags=m.cuda(), H_ext=[0.0, 1.0, 0.0], tau=0.9, magnetic_path="converged")
+
+
+def test_converged_path_matches_many_sweeps_in_the_full_step():
+    """FerroSolver("converged") against the reference algorithm with its sweep count raised until the potential is
+    converged every step (n_sweeps = 1500 at 20 x 24 x 20): same physics, so the trajectories agree to the
+    tolerance of the two iterative solves -- while n_sweeps = 30 (the demo's value) visibly has not converged."""
+    from lbm_ferrofluid_b200.solver import FerroSolver
+    from oracle.make_golden import perturbed_interface, shell_flags
+
+    res, steps = (20, 24, 20), 4
+    flags = shell_flags(res)
+    mflags = shell_flags(res, open_axes=(1,))
+    rho0 = perturbed_interface(res, 0.5, 0.2508, 0.02381, torch.float32, False)
+
+    def run(path, n):
+        s = FerroSolver(flags.cuda(), magnetic_flags=mflags.cuda(), H_ext=[0.0, 60.0, 0.0], n_sweeps=n,
+                        magnetic_path=path, cg_tol=1e-6, cg_max_iters=300)
+        s.initialize(rho0.cuda()).step(steps)
+        return s
+
+    ref, cg, demo = run("scalar", 1500), run("converged", 30), run("scalar", 30)
+    assert all(i["converged"] for i in cg.cg.info())
+    fluid = (mflags != 2).cuda()
+
+    def centred(s):
+        p = s.psi[fluid].double()
+        return p - p.mean()
+
+    e_cg = ((centred(cg) - centred(ref)).norm() / centred(ref).norm()).item()
+    e_demo = ((centred(demo) - centred(ref)).norm() / centred(ref).norm()).item()
+    assert e_cg <= 2e-4, e_cg
+    assert e_demo > 20 * e_cg, (e_demo, e_cg)
+    for k in ("rho", "pressure", "vel"):
+        a, b = getattr(cg, k).double(), getattr(ref, k).double()
+        assert torch.isfinite(a).all()
+        assert ((a - b).norm() / b.norm()).item() <= (5e-3 if k == "vel" else 1e-4), k
+    assert abs(cg.total_mass() - ref.total_mass()) <= 1e-5 * abs(ref.total_mass())
+    assert cg.launches_per_step == 1 + (1 + 4 + 5 * 300) + 5 + 1 + 6 + 1
+    assert math.isfinite(cg.total_mass())

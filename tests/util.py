@@ -83,3 +83,78 @@ def oracle_hcz_trajectory(G, dtype=torch.float32, steps=None):
     for _ in range(int(G["steps"]) if steps is None else steps):
         s = O.hcz_step(s, p)
     return s
+
+
+# ---------------------------------------------------------------------------------------------------
+# Converged magnetic potential (lbmff_poisson_cg_*): the checker is the reference's own sweep.
+# ---------------------------------------------------------------------------------------------------
+def poisson_case(res, seed=0, interior_wall=True):
+    from oracle.make_golden import shell_flags
+
+    g = torch.Generator().manual_seed(seed)
+    dim = len(res)
+    mflags = shell_flags(res, open_axes=(1,))       # periodic along y, walls on the other faces
+    if interior_wall:
+        sl = (0, 0) + tuple(slice(n // 3, n // 3 + 3) for n in res)
+        mflags[sl] = 2
+    rhs = torch.randn((1, 1, *res), generator=g, dtype=torch.float32) * 0.05
+    # a smooth dipole-like part on top of the noise: the physical source is smooth
+    ax = [torch.linspace(-1, 1, n) for n in res]
+    grid = torch.meshgrid(*ax, indexing="ij")
+    rhs[0, 0] += 0.5 * torch.exp(-8 * sum(x * x for x in grid)) * grid[-2]
+    rhs[mflags != 1] = 0.0                           # lbmff_magnetic_source_* writes 0 off FLUID cells
+    return mflags, rhs, dim
+
+
+def poisson_b_and_drift(rhs, mflags, dx=1.0, dt=1.0):
+    """fp64, by rolls: b = sum_q w_q S(fluid neighbour, else the cell itself) / (1 - w0), the wall-weight fraction
+    omega = sum_{q: wall neighbour} w_q / (1 - w0), and the constant c = sum b / sum (1 + omega) that every sweep of
+    the stationary state adds to psi (wall-returned populations are one sweep older, hence the 1 + omega)."""
+    O = _O()
+    rhs = rhs.double()
+    lat = O.lattice_for(rhs)
+    w = O._wt(lat, rhs)
+    S = dt * rhs * ((dx / dt) ** 2 / 3.0 * (0.5 - 1.0) * dt)
+    fluid = mflags != 2
+    b = torch.zeros_like(S)
+    omega = torch.zeros_like(S)
+    axes = list(range(lat.dim))
+    for q in range(1, lat.Q):
+        roll = dict(shifts=[lat.e[q][a] for a in axes], dims=[-1 - a for a in axes])
+        nb_fluid = torch.roll(fluid, **roll)
+        b += w[:, q:q + 1] * torch.where(nb_fluid, torch.roll(S, **roll), S)
+        omega += w[:, q:q + 1] * (~nb_fluid).double()
+    inv = 1.0 / (1.0 - w[:, 0:1])
+    b, omega = torch.where(fluid, b * inv, 0 * b), torch.where(fluid, omega * inv, 0 * b)
+    c = b.flatten(1).sum(1) / (fluid.double() * (1.0 + omega)).flatten(1).sum(1)
+    return b, omega, c
+
+
+def one_oracle_sweep(psi, rhs, mflags, dx=1.0, dt=1.0, drift=0.0):
+    """fp64: post-collision populations of the stationary state built from psi, then ONE sweep of the reference
+    (propagation, rebounce_obstacle, psi = sum h / (1 - w0)); returns psi after the sweep.  ``drift`` is the
+    constant the stationary state gains per sweep: what a wall holds left its cell one sweep earlier."""
+    psi, rhs = psi.double(), rhs.double()
+    lat = _O().lattice_for(torch.empty((1, 1) + tuple(psi.shape[2:])))
+    w = _O()._wt(lat, psi)
+    cs2 = (dx / dt) ** 2 / 3.0
+    S = dt * rhs * (cs2 * (0.5 - 1.0) * dt)
+    A = psi + S
+    fluid = mflags != 2
+    h = torch.where(fluid, w * A, torch.zeros_like(w * A))
+    h[:, 0:1] = torch.where(fluid, h[:, 0:1] - psi, torch.zeros_like(psi))
+    # a wall cell s holds, in slot q, what the fluid cell s + e_q sent into it one sweep ago (already swapped by
+    # rebounce_obstacle): w_q A(s + e_q); it streams back to s + e_q in this sweep
+    for q in range(1, lat.Q):
+        axes = list(range(lat.dim))
+        src = torch.roll(torch.where(fluid, A - drift, torch.zeros_like(A)), shifts=[-lat.e[q][a] for a in axes],
+                         dims=[-1 - a for a in axes])
+        h[:, q:q + 1] = torch.where(fluid, h[:, q:q + 1], w[:, q:q + 1] * src)
+    # the sweep: stream, bounce; the bounce of THIS sweep only matters for the next one
+    hs = _O().propagation(h)
+    return _O().psi_of_h(_O().rebounce_obstacle(hs, mflags))
+
+
+def _O():
+    from oracle import lbm_oracle
+    return lbm_oracle

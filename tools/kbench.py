@@ -100,7 +100,44 @@ def ros2d(n, steps=10):
               flush=True)
 
 
+def cg(res, steps=6, tol=1e-4):
+    """3-D Rosensweig with magnetic_path="converged": iterations of the cold and the warm-started solves, ms per CG
+    iteration (5 launches) against one population-faithful sweep, and the whole step against the 30-sweep step."""
+    import math
+    from lbm_ferrofluid_b200.poisson import PoissonCG
+    from lbm_ferrofluid_b200.solver import FerroSolver
+    dev = torch.device("cuda")
+    flags = I.shell_flags(res, device=dev)
+    mflags = I.shell_flags(res, open_axes=(1,), device=dev)
+    rho = I.rosensweig_rho(res, flags)
+    N = res[0] * res[1] * res[2]
+    mk = lambda path, **kw: FerroSolver(flags, magnetic_flags=mflags, H_ext=[0.0, 100.0, 0.0], magnetic_path=path,  # noqa
+                                        contact_angle=0.5 * math.pi, gravity=1e-4, keep_force=False, **kw).initialize(rho)
+    s = mk("converged", cg_tol=tol, cg_max_iters=3000)
+    its = []
+    for _ in range(steps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); s.step(); b.record()
+        torch.cuda.synchronize()
+        i = s.cg.info()[0]
+        its.append((i["iters"], i["converged"], round(a.elapsed_time(b), 2)))
+    print(f"cg res={res} tol={tol}: (iters, converged, ms) per step = {its}", flush=True)
+    # cost of one iteration: a solve that cannot converge (tol = 0) with a fixed iteration count
+    rhs = s._rhs.clone()
+    fixed = PoissonCG(mflags, tol=0.0, max_iters=50)
+    psi = torch.zeros_like(rhs)
+    ms = timed(lambda: fixed.solve(rhs, psi), reps=3) / 50
+    print(f"cg iteration: {ms:.3f} ms = {N / ms / 1e6:.1f} GLUPS-iter, {56 * N / ms / 1e6:.0f} GB/s of a 56 B/cell model",
+          flush=True)
+    del s, fixed
+    t = mk("scalar")
+    ms30 = timed(lambda: t.step(), reps=3)
+    print(f"30-sweep scalar step: {ms30:.2f} ms", flush=True)
+
+
 if __name__ == "__main__":
+    if sys.argv[1] == "cg":
+        cg(tuple(int(v) for v in sys.argv[2:5]), tol=float(sys.argv[5]) if len(sys.argv) > 5 else 1e-4)
     if sys.argv[1] == "single2d":
         single2d(int(sys.argv[2]))
     if sys.argv[1] == "ros2d":
