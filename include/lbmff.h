@@ -318,9 +318,11 @@ int lbmff_slab_hcz_collide_stream_d3q19(const float* f_in, const float* g_in, fl
  * b - c (1 + omega), omega = wall-weight fraction of the cell; csrc/poisson_cg.cu) and reports c.
  *   rhs      [B][N]  sweep-invariant source of lbmff_magnetic_source_*            (in)
  *   psi      [B][N]  warm start in, solution out (OBSTACLE cells of mflags untouched)
- *   work     [B][4][N] floats, scratch [B][lbmff_poisson_cg_scratch_doubles(D,H,W)] doubles    (device workspace)
- *   max_iters, tol   stop when |r| <= tol * |b - c(1+omega)| or after max_iters iterations (always launched; the
- *                    kernels of a finished solve return at once)
+ *   work     [B][5][N] floats, scratch [B][lbmff_poisson_cg_scratch_doubles(D,H,W)] doubles    (device workspace)
+ *   max_iters, tol   stop when |r| <= tol * |b - c(1+omega)| or after max_iters iterations.  The iterations run as
+ *                    a CUDA-graph WHILE node whose condition the reduction kernel sets on the device: one graph
+ *                    launch per batch item, nothing is launched after convergence, no host synchronisation
+ *                    (LBMFF_CG_NO_GRAPH=1 in the environment launches max_iters iterations one by one instead)
  *   res_hist [B][max_iters + 1] floats or NULL: |r| after each iteration (entry 0 = warm start)
  *   info     [B][5] doubles or NULL: iterations done, converged (0/1), |r|^2, |b - c(1+omega)|^2, c
  * tau must be 1.0 (for tau != 1 the fixed point is not a compact stencil): anything else is rejected. */

@@ -18,12 +18,16 @@
 // the oracle's sweeps).  That compatible system is solved by Jacobi-preconditioned conjugate gradients.  Stencil kernels on the division-free plane geometry
 // (common.cuh); every dot product / residual norm is a warp-shuffle reduction to one partial per block followed by a
 // fixed-order single-block finish in double precision, so the iteration is deterministic and never leaves the device:
-// alpha, beta and the residual history live in device memory.
+// alpha, beta and the residual history live in device memory, and the iteration itself is a CUDA-graph WHILE node
+// whose condition the reduction kernel sets (cudaGraphSetConditional): one graph launch per solve, no launches
+// after convergence, no host synchronisation.
 //
 // This path has NO counterpart in the reference and changes results (a converged potential instead of 30 sweeps):
 // it is opt-in (FerroSolver(magnetic_path="converged")) and validated against the sweeps run to convergence.
 #include "capi.cuh"
 #include "magnetic.cuh"
+
+#include <stdlib.h>
 
 namespace lbmff {
 
@@ -32,6 +36,8 @@ struct CgScalars {
   double iters, done, rr, bb, mean;  // the five doubles `info` exposes (include/lbmff.h); mean = drift c
   double rz, pAp, alpha, beta;
 };
+
+constexpr unsigned kWallSelf = 1u;  // bit 0 of a wall mask: the cell itself is a wall; bit q: neighbour x - e_q is
 
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
@@ -65,9 +71,11 @@ __device__ __forceinline__ void block_partials(const double (&v)[NV], double* __
 // fixed-order finish of the 3 partial arrays by ONE block, then the scalar update selected by `what`
 //   0: drift c = v0 / v1 (v0 = sum b, v1 = sum (1 + omega))    1: rz = v0, rr = v1, bb = |b - c(1+omega)|^2 = v2 (start)
 //   2: pAp = v0 -> alpha                                          3: rz_new = v0, rr = v1 -> beta, history, stop test
+// USE_GRAPH: what == 3 also decides whether the WHILE node runs its body again.
+template <bool USE_GRAPH>
 __global__ void __launch_bounds__(1024) k_cg_finish(const double* __restrict__ partials, int nblocks, int what,
                                                     CgScalars* __restrict__ sc, float* __restrict__ hist,
-                                                    double tol2) {
+                                                    double tol2, int max_iters, cudaGraphConditionalHandle handle) {
   __shared__ double sm[3][32];
   double a = 0.0, b = 0.0, c = 0.0;
   for (int i = threadIdx.x; i < nblocks; i += blockDim.x) {
@@ -98,49 +106,92 @@ __global__ void __launch_bounds__(1024) k_cg_finish(const double* __restrict__ p
     sc->pAp = a;
     sc->alpha = a > 0.0 ? sc->rz / a : 0.0;
   } else {
-    if (sc->done != 0.0) return;
-    sc->rr = b;
-    sc->beta = sc->rz > 0.0 ? a / sc->rz : 0.0;
-    sc->rz = a;
-    sc->iters += 1.0;
-    if (hist) hist[(int)sc->iters] = (float)sqrt(b);
-    if (b <= tol2 * sc->bb) sc->done = 1.0;
+    if (sc->done == 0.0) {
+      sc->rr = b;
+      sc->beta = sc->rz > 0.0 ? a / sc->rz : 0.0;
+      sc->rz = a;
+      sc->iters += 1.0;
+      if (hist) hist[(int)sc->iters] = (float)sqrt(b);
+      if (b <= tol2 * sc->bb) sc->done = 1.0;
+    }
+    if (USE_GRAPH) cudaGraphSetConditional(handle, (sc->done == 0.0 && (int)sc->iters < max_iters) ? 1u : 0u);
   }
 }
 
-// weights of the wall-aware stencil at a non-wall cell: sum over fluid neighbours of w_q v(nbr), and their weight sum
+// diagonal of L from a wall mask: (sum of the weights of the non-wall neighbours) / (1 - w0)
 template <int DIM>
-__device__ __forceinline__ void nbr_sums(const float* __restrict__ v, const uint8_t* __restrict__ fl, int i,
-                                         const Nbr& nb, float& sum_wv, float& sum_w) {
+__device__ __forceinline__ float diag_of(unsigned m) {
   using L = Lat<DIM>;
-  sum_wv = 0.f; sum_w = 0.f;
+  if (m == 0) return 1.0f;
+  float sw = 0.f;
 #pragma unroll
-  for (int q = 1; q < L::Q; ++q) {
-    const int j = i + nb.at<DIM>(q, 1);
-    const float x = __ldg(v + j);
-    if (fl[j] != LBMFF_OBSTACLE) { sum_wv += L::w(q) * x; sum_w += L::w(q); }
-  }
+  for (int q = 1; q < L::Q; ++q)
+    if (!((m >> q) & 1u)) sw += L::w(q);
+  return sw / (1.0f - L::w(0));
 }
 
-// b = 1/(1-w0) sum_q w_q S(nbr or self), S = dt*rhs*mag_src; partials: sum b, sum (1 + omega) (fluid cells)
+// sum over the non-wall neighbours of w_q v(x - e_q); mask == 0 (no wall around) takes the flag-free path
+template <int DIM>
+__device__ __forceinline__ float nbr_sum(const float* __restrict__ v, int i, const Nbr& nb, unsigned m) {
+  using L = Lat<DIM>;
+  float s_axis = 0.f, s_diag = 0.f;
+  if (m == 0) {
+#pragma unroll
+    for (int q = 1; q < L::Q; ++q) {
+      const bool axis = (L::ex(q) != 0) + (L::ey(q) != 0) + (L::ez(q) != 0) == 1;
+      const float x = __ldg(v + i + nb.at<DIM>(q, 1));
+      if (axis) s_axis += x; else s_diag += x;
+    }
+  } else {
+#pragma unroll
+    for (int q = 1; q < L::Q; ++q) {
+      const bool axis = (L::ex(q) != 0) + (L::ey(q) != 0) + (L::ez(q) != 0) == 1;
+      const float x = ((m >> q) & 1u) ? 0.f : __ldg(v + i + nb.at<DIM>(q, 1));
+      if (axis) s_axis += x; else s_diag += x;
+    }
+  }
+  return L::w(1) * s_axis + L::w(5) * s_diag;  // q = 1 / q = 5: the axis / diagonal weight of both lattices
+}
+
+// the z planes a block walks: blockIdx.z, blockIdx.z + gridDim.z, ...
+#define LBMFF_CG_PLANES(c)                                               \
+  for (int zz_ = blockIdx.z; zz_ < g.zn; zz_ += gridDim.z)               \
+    if (PlaneCell c = plane_cell_at(g, g.zb + zz_); c.live)
+
+__device__ __forceinline__ PlaneCell plane_cell_at(const Grid& g, int z) {
+  PlaneCell c;
+  c.x = blockIdx.x * blockDim.x + threadIdx.x;
+  c.y = blockIdx.y * blockDim.y + threadIdx.y;
+  c.z = z;
+  c.live = c.x < g.W && c.y < g.H;
+  c.i = (c.z * g.H + c.y) * g.W + c.x;
+  return c;
+}
+
+// wall mask, b = 1/(1-w0) sum_q w_q S(nbr or self) with S = dt*rhs*mag_src; partials: sum b, sum (1 + omega)
 template <int DIM>
 __global__ void __launch_bounds__(kThreads) k_cg_rhs(const float* __restrict__ rhs, const uint8_t* __restrict__ fl,
-                                                     float* __restrict__ b, double* __restrict__ partials,
-                                                     int nblocks, Consts k, Grid g) {
+                                                     float* __restrict__ b, unsigned* __restrict__ mask,
+                                                     double* __restrict__ partials, int nblocks, Consts k, Grid g) {
   using L = Lat<DIM>;
-  const PlaneCell c = plane_cell(g);
   double acc[3] = {0.0, 0.0, 0.0};
-  if (c.live) {
+  LBMFF_CG_PLANES(c) {
     float out = 0.f;
+    unsigned m = kWallSelf;
     if (fl[c.i] != LBMFF_OBSTACLE) {
       const Nbr nb(c, g);
-      float swv, sw;
-      nbr_sums<DIM>(rhs, fl, c.i, nb, swv, sw);
-      const float wall_w = (1.0f - L::w(0)) - sw;
-      out = (k.dt * k.mag_src) * (swv + wall_w * __ldg(rhs + c.i)) / (1.0f - L::w(0));
-      acc[0] = out; acc[1] = 1.0 + (double)(wall_w / (1.0f - L::w(0)));
+      m = 0;
+#pragma unroll
+      for (int q = 1; q < L::Q; ++q)
+        if (fl[c.i + nb.at<DIM>(q, 1)] == LBMFF_OBSTACLE) m |= 1u << q;
+      const float diag = diag_of<DIM>(m);
+      const float swv = nbr_sum<DIM>(rhs, c.i, nb, m) / (1.0f - L::w(0));
+      out = (k.dt * k.mag_src) * (swv + (1.0f - diag) * __ldg(rhs + c.i));
+      acc[0] += out;
+      acc[1] += 2.0 - (double)diag;  // 1 + omega, omega = 1 - diag
     }
     b[c.i] = out;
+    mask[c.i] = m;
   }
   block_partials<3>(acc, partials, nblocks);
 }
@@ -148,25 +199,23 @@ __global__ void __launch_bounds__(kThreads) k_cg_rhs(const float* __restrict__ r
 // r = (b - c(1+omega)) - L psi on fluid cells; z = r / diag; p = z; partials: r.z, r.r, |b - c(1+omega)|^2
 template <int DIM>
 __global__ void __launch_bounds__(kThreads) k_cg_start(const float* __restrict__ b, const float* __restrict__ psi,
-                                                       const uint8_t* __restrict__ fl, float* __restrict__ r,
+                                                       const unsigned* __restrict__ mask, float* __restrict__ r,
                                                        float* __restrict__ p, double* __restrict__ partials,
                                                        int nblocks, const CgScalars* __restrict__ sc, Grid g) {
   using L = Lat<DIM>;
-  const PlaneCell c = plane_cell(g);
   double acc[3] = {0.0, 0.0, 0.0};
-  if (c.live) {
+  const float drift = (float)sc->mean;
+  LBMFF_CG_PLANES(c) {
     float rv = 0.f, zv = 0.f;
-    if (fl[c.i] != LBMFF_OBSTACLE) {
+    const unsigned m = mask[c.i];
+    if (!(m & kWallSelf)) {
       const Nbr nb(c, g);
-      float swv, sw;
-      nbr_sums<DIM>(psi, fl, c.i, nb, swv, sw);
-      const float inv = 1.0f / (1.0f - L::w(0));
-      const float Lpsi = (sw * __ldg(psi + c.i) - swv) * inv;
-      const float diag = sw * inv;
-      const float bz = b[c.i] - (float)sc->mean * (2.0f - diag);  // 1 + omega = 2 - diag
+      const float diag = diag_of<DIM>(m);
+      const float Lpsi = diag * __ldg(psi + c.i) - nbr_sum<DIM>(psi, c.i, nb, m) / (1.0f - L::w(0));
+      const float bz = b[c.i] - drift * (2.0f - diag);
       rv = bz - Lpsi;
       zv = diag > 0.f ? rv / diag : 0.f;
-      acc[0] = (double)rv * zv; acc[1] = (double)rv * rv; acc[2] = (double)bz * bz;
+      acc[0] += (double)rv * zv; acc[1] += (double)rv * rv; acc[2] += (double)bz * bz;
     }
     r[c.i] = rv; p[c.i] = zv;
   }
@@ -175,22 +224,20 @@ __global__ void __launch_bounds__(kThreads) k_cg_start(const float* __restrict__
 
 // Ap = L p; partial: p.Ap
 template <int DIM>
-__global__ void __launch_bounds__(kThreads) k_cg_apply(const float* __restrict__ p, const uint8_t* __restrict__ fl,
+__global__ void __launch_bounds__(kThreads) k_cg_apply(const float* __restrict__ p, const unsigned* __restrict__ mask,
                                                        float* __restrict__ Ap, double* __restrict__ partials,
                                                        int nblocks, const CgScalars* __restrict__ sc, Grid g) {
   using L = Lat<DIM>;
   if (sc->done != 0.0) return;
-  const PlaneCell c = plane_cell(g);
   double acc[3] = {0.0, 0.0, 0.0};
-  if (c.live) {
+  LBMFF_CG_PLANES(c) {
     float out = 0.f;
-    if (fl[c.i] != LBMFF_OBSTACLE) {
+    const unsigned m = mask[c.i];
+    if (!(m & kWallSelf)) {
       const Nbr nb(c, g);
-      float swv, sw;
-      nbr_sums<DIM>(p, fl, c.i, nb, swv, sw);
       const float pc = __ldg(p + c.i);
-      out = (sw * pc - swv) / (1.0f - L::w(0));
-      acc[0] = (double)pc * out;
+      out = diag_of<DIM>(m) * pc - nbr_sum<DIM>(p, c.i, nb, m) / (1.0f - L::w(0));
+      acc[0] += (double)pc * out;
     }
     Ap[c.i] = out;
   }
@@ -201,43 +248,126 @@ __global__ void __launch_bounds__(kThreads) k_cg_apply(const float* __restrict__
 template <int DIM>
 __global__ void __launch_bounds__(kThreads) k_cg_update(float* __restrict__ psi, float* __restrict__ r,
                                                         const float* __restrict__ p, float* __restrict__ Ap,
-                                                        const uint8_t* __restrict__ fl, double* __restrict__ partials,
-                                                        int nblocks, const CgScalars* __restrict__ sc, Grid g) {
-  using L = Lat<DIM>;
+                                                        const unsigned* __restrict__ mask,
+                                                        double* __restrict__ partials, int nblocks,
+                                                        const CgScalars* __restrict__ sc, Grid g) {
   if (sc->done != 0.0) return;
-  const PlaneCell c = plane_cell(g);
   double acc[3] = {0.0, 0.0, 0.0};
-  if (c.live && fl[c.i] != LBMFF_OBSTACLE) {
-    const float alpha = (float)sc->alpha;
+  const float alpha = (float)sc->alpha;
+  LBMFF_CG_PLANES(c) {
+    const unsigned m = mask[c.i];
+    if (m & kWallSelf) continue;
     psi[c.i] += alpha * p[c.i];
     const float rv = r[c.i] - alpha * Ap[c.i];
     r[c.i] = rv;
-    const Nbr nb(c, g);
-    float sw = 0.f;
-#pragma unroll
-    for (int q = 1; q < L::Q; ++q)
-      if (fl[c.i + nb.at<DIM>(q, 1)] != LBMFF_OBSTACLE) sw += L::w(q);
-    const float diag = sw / (1.0f - L::w(0));
+    const float diag = diag_of<DIM>(m);
     const float zv = diag > 0.f ? rv / diag : 0.f;
     Ap[c.i] = zv;
-    acc[0] = (double)rv * zv; acc[1] = (double)rv * rv;
+    acc[0] += (double)rv * zv; acc[1] += (double)rv * rv;
   }
   block_partials<3>(acc, partials, nblocks);
 }
 
 // p = z + beta p
 __global__ void __launch_bounds__(kThreads) k_cg_direction(float* __restrict__ p, const float* __restrict__ z,
-                                                           const uint8_t* __restrict__ fl,
+                                                           const unsigned* __restrict__ mask,
                                                            const CgScalars* __restrict__ sc, Grid g) {
   if (sc->done != 0.0) return;
-  const PlaneCell c = plane_cell(g);
-  if (c.live && fl[c.i] != LBMFF_OBSTACLE) p[c.i] = z[c.i] + (float)sc->beta * p[c.i];
+  const float beta = (float)sc->beta;
+  LBMFF_CG_PLANES(c) {
+    if (!(mask[c.i] & kWallSelf)) p[c.i] = z[c.i] + beta * p[c.i];
+  }
 }
 
-
 // ---- host side ---------------------------------------------------------------------------------------------
+// blocks walk z: at most kZGroups plane groups, so a reduction leaves <= a few thousand partials per array
+constexpr int kZGroups = 8;
+static PlaneLaunch cg_launch(const Grid& g) {
+  PlaneLaunch pl = plane_launch(g, 64);
+  if (pl.grid.z > (unsigned)kZGroups) pl.grid.z = kZGroups;
+  return pl;
+}
 static int cg_blocks(const PlaneLaunch& pl) { return (int)(pl.grid.x * pl.grid.y * pl.grid.z); }
 static long long cg_scratch_doubles(const PlaneLaunch& pl) { return 3LL * cg_blocks(pl) + 16; }
+
+struct CgBuffers {
+  float *b, *r, *p, *Ap, *psi;
+  unsigned* mask;
+  CgScalars* sc;
+  double* part;
+  float* hist;
+};
+
+// One CG iteration = 5 kernels.  With `graph` they become the body of a WHILE conditional node: k_cg_finish<true>
+// (what = 3) re-arms the loop while the solve is neither converged nor at max_iters.
+template <int DIM>
+static cudaError_t iterate_plain(const CgBuffers& B, const PlaneLaunch& pl, int nb, int max_iters, double tol2,
+                                 const Grid& g, cudaStream_t st) {
+  for (int it = 0; it < max_iters; ++it) {
+    k_cg_apply<DIM><<<pl.grid, pl.block, 0, st>>>(B.p, B.mask, B.Ap, B.part, nb, B.sc, g);
+    k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, nb, 2, B.sc, nullptr, 0.0, max_iters, 0);
+    k_cg_update<DIM><<<pl.grid, pl.block, 0, st>>>(B.psi, B.r, B.p, B.Ap, B.mask, B.part, nb, B.sc, g);
+    k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, nb, 3, B.sc, B.hist, tol2, max_iters, 0);
+    k_cg_direction<<<pl.grid, pl.block, 0, st>>>(B.p, B.Ap, B.mask, B.sc, g);
+  }
+  return cudaGetLastError();
+}
+
+template <int DIM>
+static cudaError_t iterate_graph(const CgBuffers& B, const PlaneLaunch& pl, int nb, int max_iters, double tol2,
+                                 const Grid& g, cudaStream_t st) {
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  cudaError_t e = cudaGraphCreate(&graph, 0);
+  if (e != cudaSuccess) return e;
+  auto fail = [&](cudaError_t err) {
+    if (exec) cudaGraphExecDestroy(exec);
+    if (graph) cudaGraphDestroy(graph);
+    return err;
+  };
+  cudaGraphConditionalHandle handle;
+  if ((e = cudaGraphConditionalHandleCreate(&handle, graph, 1, cudaGraphCondAssignDefault)) != cudaSuccess) return fail(e);
+  cudaGraphNodeParams np = {};
+  np.type = cudaGraphNodeTypeConditional;
+  np.conditional.handle = handle;
+  np.conditional.type = cudaGraphCondTypeWhile;
+  np.conditional.size = 1;
+  cudaGraphNode_t loop;
+  if ((e = cudaGraphAddNode(&loop, graph, nullptr, 0, &np)) != cudaSuccess) return fail(e);
+  cudaGraph_t body = np.conditional.phGraph_out[0];
+
+  cudaGraphNode_t prev = nullptr;
+  auto add = [&](void* fn, dim3 grid, dim3 block, void** args) {
+    cudaKernelNodeParams kp = {};
+    kp.func = fn; kp.gridDim = grid; kp.blockDim = block; kp.sharedMemBytes = 0; kp.kernelParams = args;
+    cudaGraphNode_t n;
+    const cudaError_t err = cudaGraphAddKernelNode(&n, body, prev ? &prev : nullptr, prev ? 1 : 0, &kp);
+    prev = n;
+    return err;
+  };
+  // argument storage must outlive the AddKernelNode calls only (values are copied into the node)
+  int nbv = nb, what2 = 2, what3 = 3, mi = max_iters;
+  double zero = 0.0, t2 = tol2;
+  float* nohist = nullptr;
+  Grid gv = g;
+  CgBuffers b = B;
+  void* a_apply[] = {&b.p, &b.mask, &b.Ap, &b.part, &nbv, &b.sc, &gv};
+  void* a_fin2[] = {&b.part, &nbv, &what2, &b.sc, &nohist, &zero, &mi, &handle};
+  void* a_update[] = {&b.psi, &b.r, &b.p, &b.Ap, &b.mask, &b.part, &nbv, &b.sc, &gv};
+  void* a_fin3[] = {&b.part, &nbv, &what3, &b.sc, &b.hist, &t2, &mi, &handle};
+  void* a_dir[] = {&b.p, &b.Ap, &b.mask, &b.sc, &gv};
+  if ((e = add((void*)k_cg_apply<DIM>, pl.grid, pl.block, a_apply)) != cudaSuccess) return fail(e);
+  if ((e = add((void*)k_cg_finish<true>, dim3(1), dim3(1024), a_fin2)) != cudaSuccess) return fail(e);
+  if ((e = add((void*)k_cg_update<DIM>, pl.grid, pl.block, a_update)) != cudaSuccess) return fail(e);
+  if ((e = add((void*)k_cg_finish<true>, dim3(1), dim3(1024), a_fin3)) != cudaSuccess) return fail(e);
+  if ((e = add((void*)k_cg_direction, pl.grid, pl.block, a_dir)) != cudaSuccess) return fail(e);
+  if ((e = cudaGraphInstantiate(&exec, graph, 0)) != cudaSuccess) return fail(e);
+  if ((e = cudaGraphLaunch(exec, st)) != cudaSuccess) return fail(e);
+  // an in-flight launch keeps what it needs; the handles can go now
+  cudaGraphExecDestroy(exec);
+  cudaGraphDestroy(graph);
+  return cudaSuccess;
+}
 
 template <int DIM>
 static int poisson_cg_impl(const float* rhs, const uint8_t* mflags, float* psi, float* work, double* scratch,
@@ -249,32 +379,37 @@ static int poisson_cg_impl(const float* rhs, const uint8_t* mflags, float* psi, 
   if (tau != 1.0) return bad_arg(where, "the converged solve is the fixed point of the tau == 1 sweeps only");
   if (g.N > 0x7fffffffLL) return bad_arg(where, "more than 2^31-1 cells per batch item");
   const Consts k = make_consts(dx, dt, tau);
-  const PlaneLaunch pl = plane_launch(g, 64);
+  const PlaneLaunch pl = cg_launch(g);
   const int nb = cg_blocks(pl);
   const long long stride = cg_scratch_doubles(pl);
+  const char* env = getenv("LBMFF_CG_NO_GRAPH");
+  const bool use_graph = !(env && env[0] == '1');
   for (long long b = 0; b < g.B; ++b) {
     const float* rb = rhs + b * g.N;
     const uint8_t* fl = mflags + b * g.N;
-    float* x = psi + b * g.N;
-    float* bv = work + (4 * b + 0) * g.N;
-    float* r = work + (4 * b + 1) * g.N;
-    float* pv = work + (4 * b + 2) * g.N;
-    float* Ap = work + (4 * b + 3) * g.N;
-    CgScalars* sc = reinterpret_cast<CgScalars*>(scratch + b * stride);
-    double* part = scratch + b * stride + 16;
-    float* hist = res_hist ? res_hist + b * (max_iters + 1LL) : nullptr;
-    k_cg_rhs<DIM><<<pl.grid, pl.block, 0, st>>>(rb, fl, bv, part, nb, k, g);
-    k_cg_finish<<<1, 1024, 0, st>>>(part, nb, 0, sc, nullptr, 0.0);
-    k_cg_start<DIM><<<pl.grid, pl.block, 0, st>>>(bv, x, fl, r, pv, part, nb, sc, g);
-    k_cg_finish<<<1, 1024, 0, st>>>(part, nb, 1, sc, hist, tol * tol);
-    for (int it = 0; it < max_iters; ++it) {
-      k_cg_apply<DIM><<<pl.grid, pl.block, 0, st>>>(pv, fl, Ap, part, nb, sc, g);
-      k_cg_finish<<<1, 1024, 0, st>>>(part, nb, 2, sc, nullptr, 0.0);
-      k_cg_update<DIM><<<pl.grid, pl.block, 0, st>>>(x, r, pv, Ap, fl, part, nb, sc, g);
-      k_cg_finish<<<1, 1024, 0, st>>>(part, nb, 3, sc, hist, tol * tol);
-      k_cg_direction<<<pl.grid, pl.block, 0, st>>>(pv, Ap, fl, sc, g);
+    CgBuffers B;
+    B.psi = psi + b * g.N;
+    B.b = work + (5 * b + 0) * g.N;
+    B.r = work + (5 * b + 1) * g.N;
+    B.p = work + (5 * b + 2) * g.N;
+    B.Ap = work + (5 * b + 3) * g.N;
+    B.mask = reinterpret_cast<unsigned*>(work + (5 * b + 4) * g.N);
+    B.sc = reinterpret_cast<CgScalars*>(scratch + b * stride);
+    B.part = scratch + b * stride + 16;
+    B.hist = res_hist ? res_hist + b * (max_iters + 1LL) : nullptr;
+    k_cg_rhs<DIM><<<pl.grid, pl.block, 0, st>>>(rb, fl, B.b, B.mask, B.part, nb, k, g);
+    k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, nb, 0, B.sc, nullptr, 0.0, max_iters, 0);
+    k_cg_start<DIM><<<pl.grid, pl.block, 0, st>>>(B.b, B.psi, B.mask, B.r, B.p, B.part, nb, B.sc, g);
+    k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, nb, 1, B.sc, B.hist, tol * tol, max_iters, 0);
+    if (max_iters > 0) {
+      const cudaError_t e = use_graph ? iterate_graph<DIM>(B, pl, nb, max_iters, tol * tol, g, st)
+                                      : iterate_plain<DIM>(B, pl, nb, max_iters, tol * tol, g, st);
+      if (e != cudaSuccess) {
+        set_last_error(where, e);
+        return (int)e;
+      }
     }
-    if (info) cudaMemcpyAsync(info + 5 * b, sc, 5 * sizeof(double), cudaMemcpyDeviceToDevice, st);
+    if (info) cudaMemcpyAsync(info + 5 * b, B.sc, 5 * sizeof(double), cudaMemcpyDeviceToDevice, st);
   }
   return check_launch(where);
 }
@@ -287,7 +422,7 @@ extern "C" {
 
 int lbmff_poisson_cg_scratch_doubles(int D, int H, int W) {
   if (D < 1 || H < 1 || W < 1) return -1;
-  const long long n = cg_scratch_doubles(plane_launch(make_grid(1, D, H, W), 64));
+  const long long n = cg_scratch_doubles(cg_launch(make_grid(1, D, H, W)));
   return n > 0x7fffffffLL ? -1 : (int)n;
 }
 

@@ -28,7 +28,7 @@ class PoissonCG:
         if n <= 0:
             raise RuntimeError("lbmff_poisson_cg_scratch_doubles: bad extents")
         N = self.D * self.Hh * self.W
-        self._work = torch.empty((self.B, 4, N), dtype=torch.float32, device=self.device)
+        self._work = torch.empty((self.B, 5, N), dtype=torch.float32, device=self.device)
         self._scratch = torch.zeros((self.B, n), dtype=torch.float64, device=self.device)
         self._info = torch.zeros((self.B, 5), dtype=torch.float64, device=self.device)
         self._hist = (torch.zeros((self.B, self.max_iters + 1), dtype=torch.float32, device=self.device)
@@ -36,7 +36,7 @@ class PoissonCG:
 
     @property
     def launches_per_solve(self) -> int:
-        return self.B * (4 + 5 * self.max_iters)
+        return self.B * (4 + 1)   # rhs, start, two reductions + ONE graph launch (the iterations are a device-side WHILE loop)
 
     def solve(self, rhs: torch.Tensor, psi: torch.Tensor, max_iters: Optional[int] = None):
         """psi (warm start) is updated in place to the solution of the sweeps' fixed-point equation."""
