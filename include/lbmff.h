@@ -311,7 +311,7 @@ int lbmff_slab_hcz_collide_stream_d3q19(const float* f_in, const float* g_in, fl
  * The reference relaxes the Poisson lattice with a fixed 30 warm-started sweeps per outer step
  * (demo_3d_LBM_Rosensweig_instability.py:163-173; LBM_magnetic_3d.py:125-188).  These entries solve for the FIXED
  * POINT of those sweeps at tau == 1 instead:  L psi = b  with the wall-aware D2Q9 / D3Q19 weighted graph Laplacian
- * (full-way bounce-back = mirror), by Jacobi-preconditioned conjugate gradients entirely on the device (dot
+ * (full-way bounce-back = mirror), by conjugate gradients entirely on the device (dot
  * products reduced in double in a fixed order: deterministic; no host synchronisation).  psi is defined up to a
  * constant -- only its gradient is used (H_int = -grad psi, LBM_magnetic_3d.py:183-186).  If sum(b) != 0 the
  * sweeps' stationary state gains a constant c per sweep; the entry solves for that state (b is replaced by
@@ -333,6 +333,22 @@ int lbmff_poisson_cg_2d(const float* rhs, const uint8_t* mflags, float* psi, flo
 int lbmff_poisson_cg_3d(const float* rhs, const uint8_t* mflags, float* psi, float* work, double* scratch,
                         int max_iters, double tol, double tau, double dx, double dt, float* res_hist, double* info,
                         int B, int D, int H, int W, lbmff_stream_t stream);
+
+/* ---- iso-surface of the order parameter on the device (replaces the host round trip
+ *      mcubes.marching_cubes((-phi * s).cpu().numpy()[0, 0], 0) of src/LBM/utils/io.py:50-63).
+ * u [D][H][W] fp32 (device).  Marching cubes with a case table derived at load time (csrc/iso_surface.cu; PyMCubes is
+ * not vendored by the reference), triangle soup out: triangles [F][3 vertices][3] in array-index coordinates
+ * (axis 0, axis 1, axis 2), the order PyMCubes returns.  Two passes, deterministic triangle order, no atomics:
+ *   count: block_offsets [lbmff_iso_surface_blocks(D,H,W)] ints receive the exclusive scan of the per-block triangle
+ *          counts, *total (device int) the number of triangles F;
+ *   emit : writes min(F, capacity) triangles.  flip = 0: counter-clockwise normal towards increasing u.
+ * lbmff_mc_case_table is host-only (no GPU): ntri [256], edges [256][24] cube-edge ids (-1 padded), for tests. */
+int lbmff_mc_case_table(int* ntri, int* edges);
+int lbmff_iso_surface_blocks(int D, int H, int W);
+int lbmff_iso_surface_count_3d(const float* u, double iso, int* block_offsets, int* total, int D, int H, int W,
+                               lbmff_stream_t stream);
+int lbmff_iso_surface_emit_3d(const float* u, double iso, int flip, const int* block_offsets, float* triangles,
+                              int capacity, int D, int H, int W, lbmff_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -27,7 +27,7 @@ class Slab(ctypes.Structure):
 
 _TYPE_MAP = [
     (re.compile(r"^const\s+lbmff_\w+_params\s*\*$"), None),  # filled per struct below
-    (re.compile(r"^(const\s+)?(float|double|uint8_t|void)\s*\*$"), ctypes.c_void_p),
+    (re.compile(r"^(const\s+)?(float|double|uint8_t|void|int)\s*\*$"), ctypes.c_void_p),
     (re.compile(r"^lbmff_stream_t$"), ctypes.c_void_p),
     (re.compile(r"^int$"), ctypes.c_int),
     (re.compile(r"^long long$"), ctypes.c_longlong),

@@ -15,7 +15,8 @@
 // a stationary state that gains a constant c per sweep, psi_n = psi* + n c; a population returned by a wall is one
 // sweep older than one received from a neighbour, so psi* solves  L psi* = b - c (1 + omega),  omega(x) =
 // sum_{q: wall nbr} w_q / (1-w0),  with c = sum b / sum (1 + omega) (tests/test_poisson_math.py checks this against
-// the oracle's sweeps).  That compatible system is solved by Jacobi-preconditioned conjugate gradients.  Stencil kernels on the division-free plane geometry
+// the oracle's sweeps).  That compatible system is solved by conjugate gradients (no preconditioner: the diagonal of
+// L is 1 on every cell without a wall neighbour).  Stencil kernels on the division-free plane geometry
 // (common.cuh); every dot product / residual norm is a warp-shuffle reduction to one partial per block followed by a
 // fixed-order single-block finish in double precision, so the iteration is deterministic and never leaves the device:
 // alpha, beta and the residual history live in device memory, and the iteration itself is a CUDA-graph WHILE node
@@ -135,22 +136,30 @@ template <int DIM>
 __device__ __forceinline__ float nbr_sum(const float* __restrict__ v, int i, const Nbr& nb, unsigned m) {
   using L = Lat<DIM>;
   float s_axis = 0.f, s_diag = 0.f;
-  if (m == 0) {
 #pragma unroll
-    for (int q = 1; q < L::Q; ++q) {
-      const bool axis = (L::ex(q) != 0) + (L::ey(q) != 0) + (L::ez(q) != 0) == 1;
-      const float x = __ldg(v + i + nb.at<DIM>(q, 1));
-      if (axis) s_axis += x; else s_diag += x;
-    }
-  } else {
-#pragma unroll
-    for (int q = 1; q < L::Q; ++q) {
-      const bool axis = (L::ex(q) != 0) + (L::ey(q) != 0) + (L::ez(q) != 0) == 1;
-      const float x = ((m >> q) & 1u) ? 0.f : __ldg(v + i + nb.at<DIM>(q, 1));
-      if (axis) s_axis += x; else s_diag += x;
-    }
+  for (int q = 1; q < L::Q; ++q) {
+    const bool axis = (L::ex(q) != 0) + (L::ey(q) != 0) + (L::ez(q) != 0) == 1;
+    const float x = (m != 0 && ((m >> q) & 1u)) ? 0.f : __ldg(v + i + nb.at<DIM>(q, 1));
+    if (axis) s_axis += x; else s_diag += x;
   }
   return L::w(1) * s_axis + L::w(5) * s_diag;  // q = 1 / q = 5: the axis / diagonal weight of both lattices
+}
+
+// (L v)(x) (1 - w0) = sum over the non-wall neighbours of w_q (v(x) - v(x - e_q)).  The DIFFERENCES are formed
+// first: neighbouring values of a smooth field are within a factor 2, so each subtraction is exact, and the
+// rounding error of L v scales with |grad v| instead of |v| -- without this the fp32 residual stagnates near
+// 1e-4 |b| at 512^3 (diag * v - sum w v loses log2(n^2) bits to cancellation).
+template <int DIM>
+__device__ __forceinline__ float laplace(const float* __restrict__ v, float vc, int i, const Nbr& nb, unsigned m) {
+  using L = Lat<DIM>;
+  float s_axis = 0.f, s_diag = 0.f;
+#pragma unroll
+  for (int q = 1; q < L::Q; ++q) {
+    const bool axis = (L::ex(q) != 0) + (L::ey(q) != 0) + (L::ez(q) != 0) == 1;
+    const float d = (m != 0 && ((m >> q) & 1u)) ? 0.f : vc - __ldg(v + i + nb.at<DIM>(q, 1));
+    if (axis) s_axis += d; else s_diag += d;
+  }
+  return (L::w(1) * s_axis + L::w(5) * s_diag) / (1.0f - L::w(0));
 }
 
 // the z planes a block walks: blockIdx.z, blockIdx.z + gridDim.z, ...
@@ -196,7 +205,7 @@ __global__ void __launch_bounds__(kThreads) k_cg_rhs(const float* __restrict__ r
   block_partials<3>(acc, partials, nblocks);
 }
 
-// r = (b - c(1+omega)) - L psi on fluid cells; z = r / diag; p = z; partials: r.z, r.r, |b - c(1+omega)|^2
+// r = (b - c(1+omega)) - L psi on fluid cells, 0 on walls; p = r; partials: r.r (twice), |b - c(1+omega)|^2
 template <int DIM>
 __global__ void __launch_bounds__(kThreads) k_cg_start(const float* __restrict__ b, const float* __restrict__ psi,
                                                        const unsigned* __restrict__ mask, float* __restrict__ r,
@@ -206,18 +215,17 @@ __global__ void __launch_bounds__(kThreads) k_cg_start(const float* __restrict__
   double acc[3] = {0.0, 0.0, 0.0};
   const float drift = (float)sc->mean;
   LBMFF_CG_PLANES(c) {
-    float rv = 0.f, zv = 0.f;
+    float rv = 0.f;
     const unsigned m = mask[c.i];
     if (!(m & kWallSelf)) {
       const Nbr nb(c, g);
       const float diag = diag_of<DIM>(m);
-      const float Lpsi = diag * __ldg(psi + c.i) - nbr_sum<DIM>(psi, c.i, nb, m) / (1.0f - L::w(0));
+      const float Lpsi = laplace<DIM>(psi, __ldg(psi + c.i), c.i, nb, m);
       const float bz = b[c.i] - drift * (2.0f - diag);
       rv = bz - Lpsi;
-      zv = diag > 0.f ? rv / diag : 0.f;
-      acc[0] += (double)rv * zv; acc[1] += (double)rv * rv; acc[2] += (double)bz * bz;
+      acc[0] += (double)rv * rv; acc[1] += (double)rv * rv; acc[2] += (double)bz * bz;
     }
-    r[c.i] = rv; p[c.i] = zv;
+    r[c.i] = rv; p[c.i] = rv;
   }
   block_partials<3>(acc, partials, nblocks);
 }
@@ -236,7 +244,7 @@ __global__ void __launch_bounds__(kThreads) k_cg_apply(const float* __restrict__
     if (!(m & kWallSelf)) {
       const Nbr nb(c, g);
       const float pc = __ldg(p + c.i);
-      out = diag_of<DIM>(m) * pc - nbr_sum<DIM>(p, c.i, nb, m) / (1.0f - L::w(0));
+      out = laplace<DIM>(p, pc, c.i, nb, m);
       acc[0] += (double)pc * out;
     }
     Ap[c.i] = out;
@@ -244,38 +252,56 @@ __global__ void __launch_bounds__(kThreads) k_cg_apply(const float* __restrict__
   block_partials<3>(acc, partials, nblocks);
 }
 
-// psi += alpha p; r -= alpha Ap; z = r / diag (stored in Ap); partials: r.z, r.r
-template <int DIM>
+// The two vector updates are flat streaming kernels (no stencil, no flags: r, p and Ap are kept at exactly 0 on wall
+// cells, so psi is untouched there), float4 when the item is 16-byte aligned, grid-stride over `nblocks` blocks.
+// psi += alpha p; r -= alpha Ap; partials: r.r (twice: the unpreconditioned r.z is r.r)
+template <bool VEC4>
 __global__ void __launch_bounds__(kThreads) k_cg_update(float* __restrict__ psi, float* __restrict__ r,
-                                                        const float* __restrict__ p, float* __restrict__ Ap,
-                                                        const unsigned* __restrict__ mask,
-                                                        double* __restrict__ partials, int nblocks,
-                                                        const CgScalars* __restrict__ sc, Grid g) {
+                                                        const float* __restrict__ p, const float* __restrict__ Ap,
+                                                        long long n, double* __restrict__ partials, int nblocks,
+                                                        const CgScalars* __restrict__ sc) {
   if (sc->done != 0.0) return;
   double acc[3] = {0.0, 0.0, 0.0};
   const float alpha = (float)sc->alpha;
-  LBMFF_CG_PLANES(c) {
-    const unsigned m = mask[c.i];
-    if (m & kWallSelf) continue;
-    psi[c.i] += alpha * p[c.i];
-    const float rv = r[c.i] - alpha * Ap[c.i];
-    r[c.i] = rv;
-    const float diag = diag_of<DIM>(m);
-    const float zv = diag > 0.f ? rv / diag : 0.f;
-    Ap[c.i] = zv;
-    acc[0] += (double)rv * zv; acc[1] += (double)rv * rv;
+  const long long stride = (long long)gridDim.x * blockDim.x, t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (VEC4) {
+    for (long long i = t0; i < n / 4; i += stride) {
+      float4 x = reinterpret_cast<float4*>(psi)[i], rv = reinterpret_cast<float4*>(r)[i];
+      const float4 pv = reinterpret_cast<const float4*>(p)[i], av = reinterpret_cast<const float4*>(Ap)[i];
+      x.x += alpha * pv.x; x.y += alpha * pv.y; x.z += alpha * pv.z; x.w += alpha * pv.w;
+      rv.x -= alpha * av.x; rv.y -= alpha * av.y; rv.z -= alpha * av.z; rv.w -= alpha * av.w;
+      reinterpret_cast<float4*>(psi)[i] = x;
+      reinterpret_cast<float4*>(r)[i] = rv;
+      acc[0] += (double)rv.x * rv.x + (double)rv.y * rv.y + (double)rv.z * rv.z + (double)rv.w * rv.w;
+    }
+  } else {
+    for (long long i = t0; i < n; i += stride) {
+      psi[i] += alpha * p[i];
+      const float rv = r[i] - alpha * Ap[i];
+      r[i] = rv;
+      acc[0] += (double)rv * rv;
+    }
   }
+  acc[1] = acc[0];
   block_partials<3>(acc, partials, nblocks);
 }
 
-// p = z + beta p
-__global__ void __launch_bounds__(kThreads) k_cg_direction(float* __restrict__ p, const float* __restrict__ z,
-                                                           const unsigned* __restrict__ mask,
-                                                           const CgScalars* __restrict__ sc, Grid g) {
+// p = r + beta p
+template <bool VEC4>
+__global__ void __launch_bounds__(kThreads) k_cg_direction(float* __restrict__ p, const float* __restrict__ r,
+                                                           long long n, const CgScalars* __restrict__ sc) {
   if (sc->done != 0.0) return;
   const float beta = (float)sc->beta;
-  LBMFF_CG_PLANES(c) {
-    if (!(mask[c.i] & kWallSelf)) p[c.i] = z[c.i] + beta * p[c.i];
+  const long long stride = (long long)gridDim.x * blockDim.x, t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (VEC4) {
+    for (long long i = t0; i < n / 4; i += stride) {
+      float4 pv = reinterpret_cast<float4*>(p)[i];
+      const float4 rv = reinterpret_cast<const float4*>(r)[i];
+      pv.x = rv.x + beta * pv.x; pv.y = rv.y + beta * pv.y; pv.z = rv.z + beta * pv.z; pv.w = rv.w + beta * pv.w;
+      reinterpret_cast<float4*>(p)[i] = pv;
+    }
+  } else {
+    for (long long i = t0; i < n; i += stride) p[i] = r[i] + beta * p[i];
   }
 }
 
@@ -298,17 +324,25 @@ struct CgBuffers {
   float* hist;
 };
 
+static bool cg_vec4(const CgBuffers& B, const Grid& g) {
+  const auto al = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
+  return g.N % 4 == 0 && al(B.psi) && al(B.r) && al(B.p) && al(B.Ap);
+}
+
 // One CG iteration = 5 kernels.  With `graph` they become the body of a WHILE conditional node: k_cg_finish<true>
 // (what = 3) re-arms the loop while the solve is neither converged nor at max_iters.
 template <int DIM>
 static cudaError_t iterate_plain(const CgBuffers& B, const PlaneLaunch& pl, int nb, int max_iters, double tol2,
                                  const Grid& g, cudaStream_t st) {
+  const bool vec4 = cg_vec4(B, g);
   for (int it = 0; it < max_iters; ++it) {
     k_cg_apply<DIM><<<pl.grid, pl.block, 0, st>>>(B.p, B.mask, B.Ap, B.part, nb, B.sc, g);
     k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, nb, 2, B.sc, nullptr, 0.0, max_iters, 0);
-    k_cg_update<DIM><<<pl.grid, pl.block, 0, st>>>(B.psi, B.r, B.p, B.Ap, B.mask, B.part, nb, B.sc, g);
+    if (vec4) k_cg_update<true><<<nb, kThreads, 0, st>>>(B.psi, B.r, B.p, B.Ap, g.N, B.part, nb, B.sc);
+    else k_cg_update<false><<<nb, kThreads, 0, st>>>(B.psi, B.r, B.p, B.Ap, g.N, B.part, nb, B.sc);
     k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, nb, 3, B.sc, B.hist, tol2, max_iters, 0);
-    k_cg_direction<<<pl.grid, pl.block, 0, st>>>(B.p, B.Ap, B.mask, B.sc, g);
+    if (vec4) k_cg_direction<true><<<nb, kThreads, 0, st>>>(B.p, B.r, g.N, B.sc);
+    else k_cg_direction<false><<<nb, kThreads, 0, st>>>(B.p, B.r, g.N, B.sc);
   }
   return cudaGetLastError();
 }
@@ -353,14 +387,20 @@ static cudaError_t iterate_graph(const CgBuffers& B, const PlaneLaunch& pl, int 
   CgBuffers b = B;
   void* a_apply[] = {&b.p, &b.mask, &b.Ap, &b.part, &nbv, &b.sc, &gv};
   void* a_fin2[] = {&b.part, &nbv, &what2, &b.sc, &nohist, &zero, &mi, &handle};
-  void* a_update[] = {&b.psi, &b.r, &b.p, &b.Ap, &b.mask, &b.part, &nbv, &b.sc, &gv};
+  long long nv = g.N;
+  const bool vec4 = cg_vec4(B, g);
+  void* a_update[] = {&b.psi, &b.r, &b.p, &b.Ap, &nv, &b.part, &nbv, &b.sc};
   void* a_fin3[] = {&b.part, &nbv, &what3, &b.sc, &b.hist, &t2, &mi, &handle};
-  void* a_dir[] = {&b.p, &b.Ap, &b.mask, &b.sc, &gv};
+  void* a_dir[] = {&b.p, &b.r, &nv, &b.sc};
   if ((e = add((void*)k_cg_apply<DIM>, pl.grid, pl.block, a_apply)) != cudaSuccess) return fail(e);
   if ((e = add((void*)k_cg_finish<true>, dim3(1), dim3(1024), a_fin2)) != cudaSuccess) return fail(e);
-  if ((e = add((void*)k_cg_update<DIM>, pl.grid, pl.block, a_update)) != cudaSuccess) return fail(e);
+  if ((e = add(vec4 ? (void*)k_cg_update<true> : (void*)k_cg_update<false>, dim3(nb), dim3(kThreads), a_update)) !=
+      cudaSuccess)
+    return fail(e);
   if ((e = add((void*)k_cg_finish<true>, dim3(1), dim3(1024), a_fin3)) != cudaSuccess) return fail(e);
-  if ((e = add((void*)k_cg_direction, pl.grid, pl.block, a_dir)) != cudaSuccess) return fail(e);
+  if ((e = add(vec4 ? (void*)k_cg_direction<true> : (void*)k_cg_direction<false>, dim3(nb), dim3(kThreads), a_dir)) !=
+      cudaSuccess)
+    return fail(e);
   if ((e = cudaGraphInstantiate(&exec, graph, 0)) != cudaSuccess) return fail(e);
   if ((e = cudaGraphLaunch(exec, st)) != cudaSuccess) return fail(e);
   // an in-flight launch keeps what it needs; the handles can go now
