@@ -1,15 +1,3 @@
-"""Stand-in for the reference's `renderutils.SoftRenderer` (CUDA soft rasteriser, out of the solver hot path).
-The constructor takes the reference's keyword arguments (renderutils/softrenderer.py:24-120); frames are produced
-headlessly by `src.LBM.utils.save_rendered_image`, which does not call the renderer."""
-
-
-class SoftRenderer:
-    def __init__(self, *args, **kwargs):
-        self.args, self.kwargs = args, kwargs
-        for k, v in kwargs.items():
-            setattr(self, k, v)
-
-    def forward(self, *args, **kwargs):
-        raise NotImplementedError("compat SoftRenderer: rendering is done by save_rendered_image (headless projection)")
-
-    __call__ = forward
+"""`renderutils.SoftRenderer` for the reference's demos: the host mirror of the reference class on top of this repo's
+tiled CUDA soft rasteriser (lbm_ferrofluid_b200/render.py, csrc/soft_raster.cu).  Forward (rendering) only."""
+from lbm_ferrofluid_b200.render import SoftRenderer, soft_rasterize  # noqa: F401

@@ -350,6 +350,29 @@ int lbmff_iso_surface_count_3d(const float* u, double iso, int* block_offsets, i
 int lbmff_iso_surface_emit_3d(const float* u, double iso, int flip, const int* block_offsets, float* triangles,
                               int capacity, int D, int H, int W, lbmff_stream_t stream);
 
+/* ---- soft rasteriser, forward (renderutils/cuda/soft_rasterize_cuda.cpp:72-110 ->
+ *      soft_rasterize_cuda_kernel.cu:236-475, as driven by renderutils/soft_rasterize.py:26-110).
+ * Same arguments as the reference's forward_soft_rasterize: face_vertices [B][F][3][3] projected vertices (x, y in
+ * [-1, 1], z = camera depth), textures [B][F][texture_size][3], soft_colors [B][4][is][is] PRE-FILLED by the caller
+ * with the background colour (alpha plane 1), aggrs_info [B][2][is][is] or NULL, the scalar options with the
+ * reference's meaning (func_id_dist 0 hard / 1 barycentric / 2 euclidean, func_id_rgb 0 hard / 1 softmax,
+ * func_id_alpha 0 hard / 1 sum / 2 prod, texture_sample_type 0 surface / 1 vertex; dist_eps is the already
+ * transformed log(1/dist_eps - 1) of soft_rasterize.py:54).  Instead of every pixel walking all faces, faces are
+ * binned into 16 x 16 pixel tiles first (ordered lists, so a pixel folds its faces in the reference's order):
+ *   bin    : fills face_info [B][F][24], face_box [B][F][4] and tile_offsets [B * tiles^2 + 1] (exclusive scan of
+ *            the per-tile face counts, last entry = total list length L), tiles = lbmff_soft_rasterize_tiles(is);
+ *   forward: tile_faces [L] ints of scratch; writes soft_colors (and aggrs_info). */
+int lbmff_soft_rasterize_tiles(int image_size);
+int lbmff_soft_rasterize_bin(const float* face_vertices, float* face_info, float* face_box, int* tile_offsets,
+                             int B, int F, int image_size, double sigma_val, double dist_eps,
+                             lbmff_stream_t stream);
+int lbmff_soft_rasterize_forward(const float* face_vertices, const float* textures, const float* face_info,
+                                 const float* face_box, const int* tile_offsets, int* tile_faces, float* soft_colors,
+                                 float* aggrs_info, int B, int F, int image_size, int texture_size, double near_,
+                                 double far_, double eps, double sigma_val, int func_id_dist, double dist_eps,
+                                 double gamma_val, int func_id_rgb, int func_id_alpha, int texture_sample_type,
+                                 int double_side, lbmff_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -48,15 +48,25 @@ def export_asset(save_path: str, vertices: torch.Tensor, faces: torch.Tensor):
 
 
 def save_rendered_image(renderer, phi, filename, res, dx):
-    """Headless stand-in for the reference's marching-cubes + soft-rasteriser frame (io.py:50-84): writes a
-    y-up projection of the liquid column height.  Returns empty (verts, faces)."""
+    """The reference's frame writer (src/LBM/utils/io.py:50-84) with every stage on the device: the interior of phi
+    padded by phi.max(), the zero level of -phi * 2 / (max(res) dx) extracted by the CUDA marching cubes
+    (isosurface.py; the reference goes through the host and PyMCubes), vertices centred and scaled into [-1, 1],
+    a uniform 0.68 grey surface texture, ``renderer.forward`` (render.SoftRenderer: tiled CUDA soft rasteriser), and
+    the RGB image written as 8 bit.  Returns [verts, faces] like the reference."""
     import cv2
+    import torch.nn.functional as F
 
-    liquid = (phi[0, 0, 1:-1, 1:-1, 1:-1] < 0).float().sum(dim=1)   # [D-2, W-2] column heights
-    img = (liquid / max(1.0, float(phi.shape[-2] - 2))).clamp(0, 1).cpu().numpy()
-    cv2.imwrite(filename, (img * 255.0).astype(np.uint8))
-    dev = phi.device
-    return [torch.zeros((0, 3), device=dev), torch.zeros((0, 3), dtype=torch.int32, device=dev)]
+    from .isosurface import marching_cubes
+
+    phi = F.pad(phi[..., 1:-1, 1:-1, 1:-1], pad=(1, 1, 1, 1, 1, 1), mode="constant", value=phi.max().item())
+    device = phi.device
+    verts, faces = marching_cubes((-phi * (2.0 / max(res) / dx))[0, 0].contiguous(), 0.0)
+    verts = (verts - torch.tensor([float(r) for r in res], device=device) / 2.0) * (2.0 / max(res))
+    textures = 0.68 * torch.ones(1, faces.shape[-2], 2, 3, dtype=torch.float32, device=device)
+    image = renderer.forward(verts.unsqueeze(0), faces.unsqueeze(0), textures)
+    rgb = (image[0, :3].permute(1, 2, 0).detach().clamp(0, 1).cpu().numpy() * 255).astype(np.uint8)
+    cv2.imwrite(filename, rgb[..., ::-1])            # imageio.imwrite takes RGB, cv2 BGR
+    return [verts, faces]
 
 
 def dump_2d_plt_file_single(filename, np_density, np_uv, B):

@@ -135,7 +135,36 @@ def cg(res, steps=6, tol=1e-4):
     print(f"30-sweep scalar step: {ms30:.2f} ms", flush=True)
 
 
+def render(n, image=256):
+    """The demo frame (save_rendered_image): iso-surface of a perturbed Rosensweig phi at n^3, then the SoftRenderer
+    chain at image^2 (x2 supersampling), each stage timed with CUDA events."""
+    import math
+    from lbm_ferrofluid_b200.isosurface import marching_cubes
+    from lbm_ferrofluid_b200.render import SoftRenderer, soft_rasterize
+    dev = torch.device("cuda")
+    res = (n, n, n)
+    flags = I.shell_flags(res, device=dev)
+    rho = I.rosensweig_rho(res, flags, perturb=0.03 * n)
+    u = (2.0 * (rho - 0.02381) / (0.2508 - 0.02381) - 1.0)[0, 0].contiguous() * (2.0 / n)
+    ms_mc = timed(lambda: marching_cubes(u, 0.0), reps=3)
+    verts, faces = marching_cubes(u, 0.0)
+    verts = (verts - n / 2.0) * (2.0 / n)
+    ren = SoftRenderer(image_size=image, camera_mode="look_at", eye=torch.tensor([1.6, 0.8, 1.6], device=dev), near=1.0,
+                       bg_color=torch.tensor([1.0, 1.0, 1.0], device=dev), device=dev)
+    tex = 0.68 * torch.ones(1, faces.shape[0], 2, 3, device=dev)
+    ms_all = timed(lambda: ren.forward(verts[None], faces[None], tex), reps=3)
+    lit = ren.lighting(verts[None], faces[None], tex)
+    fv = ren.vertices_to_faces(ren.project_to_image(ren.transform_to_camera_frame(verts[None])), faces[None]).contiguous()
+    ms_ras = timed(lambda: soft_rasterize(fv, lit, 2 * image, (1.0, 1.0, 1.0), 1.0, 100), reps=3)
+    F = faces.shape[0]
+    print(f"render n={n}: faces={F} marching_cubes {ms_mc:.3f} ms ({4 * n ** 3 / ms_mc / 1e6:.0f} GB/s of the field read "
+          f"twice = {8 * n ** 3 / ms_mc / 1e6:.0f} GB/s), renderer.forward {ms_all:.3f} ms, rasterise {(2 * image)}^2: "
+          f"{ms_ras:.3f} ms", flush=True)
+
+
 if __name__ == "__main__":
+    if sys.argv[1] == "render":
+        render(int(sys.argv[2]), int(sys.argv[3]) if len(sys.argv) > 3 else 256)
     if sys.argv[1] == "cg":
         cg(tuple(int(v) for v in sys.argv[2:5]), tol=float(sys.argv[5]) if len(sys.argv) > 5 else 1e-4)
     if sys.argv[1] == "single2d":
