@@ -359,7 +359,8 @@ int lbmff_iso_surface_emit_3d(const float* u, double iso, int flip, const int* b
  * func_id_alpha 0 hard / 1 sum / 2 prod, texture_sample_type 0 surface / 1 vertex; dist_eps is the already
  * transformed log(1/dist_eps - 1) of soft_rasterize.py:54).  Instead of every pixel walking all faces, faces are
  * binned into 16 x 16 pixel tiles first (ordered lists, so a pixel folds its faces in the reference's order):
- *   bin    : fills face_info [B][F][24], face_box [B][F][4] and tile_offsets [B * tiles^2 + 1] (exclusive scan of
+ *   bin    : fills face_info [B][F][24], face_box [B * F + B * ceil(F / 32)][4] (face boxes, then the union boxes
+ *            of groups of 32 consecutive faces) and tile_offsets [B * tiles^2 + 1] (exclusive scan of
  *            the per-tile face counts, last entry = total list length L), tiles = lbmff_soft_rasterize_tiles(is);
  *   forward: tile_faces [L] ints of scratch; writes soft_colors (and aggrs_info). */
 int lbmff_soft_rasterize_tiles(int image_size);

@@ -11,7 +11,7 @@
 //
 // Output is a triangle soup [F][3][3] in ARRAY-INDEX coordinates (axis 0, axis 1, axis 2) = (z, y, x), the order
 // PyMCubes returns; that is directly the `face_vertices` the soft rasteriser consumes.  Triangle order is
-// deterministic (cell-major): two passes (count per block -> exclusive scan -> emit), no atomics.
+// deterministic (cell-major): two passes (count per block of one cell row -> exclusive scan -> emit), no atomics.
 // Orientation: the counter-clockwise normal points towards INCREASING field values (outward for a signed distance
 // that is negative inside), flip = 1 reverses it.  [PyMCubes' own convention cannot be checked here: unpinned.]
 #include "capi.cuh"
@@ -178,17 +178,32 @@ __device__ __forceinline__ int mc_config(const float* __restrict__ u, const McGr
   return cfg;
 }
 
-// pass 1: triangles per block of 256 consecutive cells (x fastest)
+// Blocks: blockIdx.x = cell row (z * (H-1) + y), blockIdx.y = 256-cell chunk of the row; the block's rank in
+// cell-major order is row * chunks + chunk, so triangle order stays cell-major, and a thread's cell costs one
+// 32-bit division per block instead of two 64-bit ones per thread.
+struct McCell {
+  int x, y, z, rank;
+  bool live;
+};
+__device__ __forceinline__ McCell mc_cell(const McGrid g) {
+  McCell c;
+  const int ch = g.H - 1, row = blockIdx.x;
+  c.z = row / ch;
+  c.y = row - c.z * ch;
+  c.x = blockIdx.y * 256 + threadIdx.x;
+  c.live = c.x < g.W - 1;
+  c.rank = row * gridDim.y + blockIdx.y;
+  return c;
+}
+
+// pass 1: triangles per block
 __global__ void __launch_bounds__(256) k_mc_count(const float* __restrict__ u, McGrid g, float iso,
                                                   int* __restrict__ block_count) {
-  const int cw = g.W - 1, ch = g.H - 1;
-  const long long ncell = (long long)(g.D - 1) * ch * cw;
-  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  const McCell c = mc_cell(g);
   int n = 0;
-  if (i < ncell) {
-    const int x = (int)(i % cw), y = (int)((i / cw) % ch), z = (int)(i / ((long long)cw * ch));
+  if (c.live) {
     float val[8];
-    n = d_mc_table.ntri[mc_config(u, g, x, y, z, iso, val)];
+    n = d_mc_table.ntri[mc_config(u, g, c.x, c.y, c.z, iso, val)];
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) n += __shfl_down_sync(0xffffffffu, n, o);
@@ -198,7 +213,7 @@ __global__ void __launch_bounds__(256) k_mc_count(const float* __restrict__ u, M
   if (threadIdx.x == 0) {
     int t = 0;
     for (int w = 0; w < 8; ++w) t += sm[w];
-    block_count[blockIdx.x] = t;
+    block_count[c.rank] = t;
   }
 }
 
@@ -257,13 +272,11 @@ __device__ __forceinline__ void mc_edge_vertex(int e, int x, int y, int z, const
 __global__ void __launch_bounds__(256) k_mc_emit(const float* __restrict__ u, McGrid g, float iso, int flip,
                                                  const int* __restrict__ block_offset, float* __restrict__ tri,
                                                  int capacity) {
-  const int cw = g.W - 1, ch = g.H - 1;
-  const long long ncell = (long long)(g.D - 1) * ch * cw;
-  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
-  int n = 0, cfg = 0, x = 0, y = 0, z = 0;
+  const McCell c = mc_cell(g);
+  const int x = c.x, y = c.y, z = c.z;
+  int n = 0, cfg = 0;
   float val[8];
-  if (i < ncell) {
-    x = (int)(i % cw); y = (int)((i / cw) % ch); z = (int)(i / ((long long)cw * ch));
+  if (c.live) {
     cfg = mc_config(u, g, x, y, z, iso, val);
     n = d_mc_table.ntri[cfg];
   }
@@ -278,7 +291,7 @@ __global__ void __launch_bounds__(256) k_mc_emit(const float* __restrict__ u, Mc
   __shared__ int sm[8];
   if (lane == 31) sm[warp] = s;
   __syncthreads();
-  int before = block_offset[blockIdx.x] + (s - n);
+  int before = block_offset[c.rank] + (s - n);
   for (int w = 0; w < warp; ++w) before += sm[w];
   for (int t = 0; t < n; ++t) {
     if (before + t >= capacity) return;
@@ -314,8 +327,7 @@ int lbmff_mc_case_table(int* ntri, int* edges) {
 
 int lbmff_iso_surface_blocks(int D, int H, int W) {
   if (D < 2 || H < 2 || W < 2) return -1;
-  const long long ncell = (long long)(D - 1) * (H - 1) * (W - 1);
-  const long long nb = (ncell + 255) / 256;
+  const long long nb = (long long)(D - 1) * (H - 1) * ((W - 1 + 255) / 256);
   return nb > 0x7fffffffLL ? -1 : (int)nb;
 }
 
@@ -328,7 +340,8 @@ int lbmff_iso_surface_count_3d(const float* u, double iso, int* block_offsets, i
   if (e != cudaSuccess) { set_last_error(__func__, e); return (int)e; }
   const McGrid g{D, H, W};
   cudaStream_t st = (cudaStream_t)stream;
-  k_mc_count<<<nb, 256, 0, st>>>(u, g, (float)iso, block_offsets);
+  const dim3 grid((unsigned)((D - 1) * (H - 1)), (unsigned)((W - 1 + 255) / 256));
+  k_mc_count<<<grid, 256, 0, st>>>(u, g, (float)iso, block_offsets);
   k_mc_scan<<<1, 1024, 0, st>>>(block_offsets, nb, total);
   return check_launch(__func__);
 }
@@ -343,7 +356,8 @@ int lbmff_iso_surface_emit_3d(const float* u, double iso, int flip, const int* b
   cudaError_t e = ensure_device_table();
   if (e != cudaSuccess) { set_last_error(__func__, e); return (int)e; }
   const McGrid g{D, H, W};
-  k_mc_emit<<<nb, 256, 0, (cudaStream_t)stream>>>(u, g, (float)iso, flip, block_offsets, triangles, capacity);
+  const dim3 grid((unsigned)((D - 1) * (H - 1)), (unsigned)((W - 1 + 255) / 256));
+  k_mc_emit<<<grid, 256, 0, (cudaStream_t)stream>>>(u, g, (float)iso, flip, block_offsets, triangles, capacity);
   return check_launch(__func__);
 }
 

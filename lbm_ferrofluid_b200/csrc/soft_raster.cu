@@ -6,8 +6,9 @@
 // marching-cubes triangles per frame, of which a pixel is touched by a handful (a face is skipped unless the pixel
 // lies inside its bounding box grown by sqrt(threshold), soft_rasterize_cuda_kernel.cu:372).  Here:
 //   1. k_face_setup     per face: barycentric matrix, Gram matrix, obtuse-corner flag (:236-302) + the grown bbox;
-//   2. k_bin_count/fill per 16 x 16 pixel tile, one warp scans the face boxes IN FACE ORDER and compacts the faces
-//                       whose box touches the tile (ballot + popc): ordered per-tile lists, no atomics, deterministic;
+//   2. k_group_box/k_bin per 16 x 16 pixel tile, one warp scans the face boxes IN FACE ORDER (first the union boxes of
+//                       groups of 32 consecutive faces, then the faces of the groups that touch the tile) and compacts
+//                       the hits (ballot + popc): ordered per-tile lists, no atomics, deterministic;
 //   3. k_raster_tile    one block per tile, one thread per pixel: the tile's faces are staged through shared memory
 //                       in chunks and every pixel folds them in ascending face order -- the same aggregation order
 //                       as the reference's loop over all faces, so the running softmax rescaling sees the same
@@ -86,23 +87,51 @@ __device__ __forceinline__ bool touches(const float4 b, const TileSpan& s) {
   return !(s.xlo > b.y || s.xhi < b.x || s.ylo > b.w || s.yhi < b.z);
 }
 
-// one warp per (batch item, tile); FILL = false counts, FILL = true writes the ordered face list
+// union box of each group of 32 consecutive faces (one warp per group).  Marching-cubes faces arrive in cell order,
+// so a group is a compact patch of the surface and its box is tight: a tile warp rejects 32 faces with one test.
+__global__ void __launch_bounds__(256) k_group_box(const float4* __restrict__ box, float4* __restrict__ gbox, int F,
+                                                   int groups_per_item, int ngroups_total) {
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (w >= ngroups_total) return;
+  const int bn = w / groups_per_item, g = w - bn * groups_per_item, f = g * 32 + lane;
+  float4 b = make_float4(3.0e38f, -3.0e38f, 3.0e38f, -3.0e38f);  // empty
+  if (f < F) b = __ldg(box + (long long)bn * F + f);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    b.x = fminf(b.x, __shfl_xor_sync(0xffffffffu, b.x, o));
+    b.y = fmaxf(b.y, __shfl_xor_sync(0xffffffffu, b.y, o));
+    b.z = fminf(b.z, __shfl_xor_sync(0xffffffffu, b.z, o));
+    b.w = fmaxf(b.w, __shfl_xor_sync(0xffffffffu, b.w, o));
+  }
+  if (lane == 0) gbox[w] = b;
+}
+
+// one warp per (batch item, tile): scans the group boxes 32 at a time, then the 32 faces of every group that touches
+// the tile, all in ascending face order.  FILL = false counts, FILL = true writes the ordered face list.
 template <bool FILL>
-__global__ void __launch_bounds__(256) k_bin(const float4* __restrict__ box, int F, int is, int tiles, int ntile_total,
+__global__ void __launch_bounds__(256) k_bin(const float4* __restrict__ box, const float4* __restrict__ gbox, int F,
+                                             int groups_per_item, int is, int tiles, int ntile_total,
                                              int* __restrict__ count_or_offset, int* __restrict__ list) {
   const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (w >= ntile_total) return;
   const int per_img = tiles * tiles, bn = w / per_img, t = w - bn * per_img;
   const TileSpan s = tile_span(t % tiles, t / tiles, is);
   const float4* b = box + (long long)bn * F;
+  const float4* gb = gbox + (long long)bn * groups_per_item;
   int n = 0;
   const int base = FILL ? count_or_offset[w] : 0;
-  for (int f0 = 0; f0 < F; f0 += 32) {
-    const int f = f0 + lane;
-    const bool hit = f < F && touches(__ldg(b + f), s);
-    const unsigned m = __ballot_sync(0xffffffffu, hit);
-    if (FILL && hit) list[base + n + __popc(m & ((1u << lane) - 1u))] = f;
-    n += __popc(m);
+  for (int g0 = 0; g0 < groups_per_item; g0 += 32) {
+    const int g = g0 + lane;
+    unsigned gm = __ballot_sync(0xffffffffu, g < groups_per_item && touches(__ldg(gb + g), s));
+    while (gm) {
+      const int bit = __ffs(gm) - 1;
+      gm &= gm - 1;
+      const int f = (g0 + bit) * 32 + lane;
+      const bool hit = f < F && touches(__ldg(b + f), s);
+      const unsigned m = __ballot_sync(0xffffffffu, hit);
+      if (FILL && hit) list[base + n + __popc(m & ((1u << lane) - 1u))] = f;
+      n += __popc(m);
+    }
   }
   if (!FILL && lane == 0) count_or_offset[w] = n;
 }
@@ -235,14 +264,23 @@ __global__ void __launch_bounds__(kTile* kTile) k_raster_tile(const float* __res
   const int per_img = P.tiles * P.tiles;
   const int tile = blockIdx.x, bn = tile / per_img, t = tile - bn * per_img;
   const int tx = t % P.tiles, ty = t / P.tiles;
-  const int tid = threadIdx.x, lx = tid % kTile, ly = tid / kTile;
-  const int xi = tx * kTile + lx, row = ty * kTile + ly, is = P.is;
+  // a warp owns an 8 x 4 pixel footprint (2 x 4 warps per tile): a marching-cubes face (grown box ~6 x 6 pixels)
+  // then meets ~4 warps instead of the ~7 of a 16 x 2 footprint, and more of a visiting warp's lanes are inside it
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int fx0 = tx * kTile + (warp & 1) * 8, fy0 = ty * kTile + (warp >> 1) * 4;
+  const int xi = fx0 + (lane & 7), row = fy0 + (lane >> 3), is = P.is;
   const bool live = xi < is && row < is;
   const int pn = row * is + xi;
   const float xp = pix_coord(xi, is), yp = pix_coord(is - 1 - row, is);
   const long long plane = (long long)is * is;
   float* col = colors + (long long)bn * 4 * plane + pn;
 
+  TileSpan span;  // pixel-centre extremes of the warp's footprint, clipped to the image
+  {
+    const int x1 = min(fx0 + 8, is) - 1, r1 = min(fy0 + 4, is) - 1;
+    span.xlo = pix_coord(fx0, is); span.xhi = pix_coord(x1, is);
+    span.ylo = pix_coord(is - 1 - r1, is); span.yhi = pix_coord(is - 1 - fy0, is);
+  }
   const float threshold = P.dist_eps * P.sigma;
   float c[3] = {1.f, 1.f, 1.f};
   float alpha = P.alpha == 2 ? 1.f : 0.f;
@@ -269,8 +307,14 @@ __global__ void __launch_bounds__(kTile* kTile) k_raster_tile(const float* __res
       rec[k / kInfo].info[k % kInfo] = __ldg(ibase + (long long)ids[k / kInfo] * kInfo + k % kInfo);
     if (tid < n) rec[tid].box = __ldg(bbase + ids[tid]);
     __syncthreads();
+    // which of the chunk's faces can touch this warp's footprint at all (lane l tests faces l and l + 32)
+    const unsigned long long wmask =
+        (unsigned long long)__ballot_sync(0xffffffffu, lane < n && touches(rec[lane].box, span)) |
+        ((unsigned long long)__ballot_sync(0xffffffffu, lane + 32 < n && touches(rec[(lane + 32) % kChunk].box, span))
+         << 32);
     if (!live) continue;
-    for (int j = 0; j < n; ++j) {
+    for (unsigned long long rest = wmask; rest; rest &= rest - 1) {
+      const int j = __ffsll((long long)rest) - 1;
       const FaceRec& fr = rec[j];
       if (xp > fr.box.y || xp < fr.box.x || yp > fr.box.w || yp < fr.box.z) continue;
       float w[3];
@@ -362,8 +406,12 @@ int lbmff_soft_rasterize_bin(const float* face_vertices, float* face_info, float
   const float grow = sqrtf((float)dist_eps * (float)sigma_val);
   k_face_setup<<<(B * F + 255) / 256, 256, 0, st>>>(face_vertices, face_info, reinterpret_cast<float4*>(face_box),
                                                      B * F, grow);
-  k_bin<false><<<(ntile * 32 + 255) / 256, 256, 0, st>>>(reinterpret_cast<const float4*>(face_box), F, image_size,
-                                                         tiles, ntile, tile_offsets, nullptr);
+  const int groups = (F + 31) / 32;
+  float4* gbox = reinterpret_cast<float4*>(face_box) + (long long)B * F;  // group boxes live behind the face boxes
+  k_group_box<<<(B * groups * 32 + 255) / 256, 256, 0, st>>>(reinterpret_cast<const float4*>(face_box), gbox, F, groups,
+                                                             B * groups);
+  k_bin<false><<<(ntile * 32 + 255) / 256, 256, 0, st>>>(reinterpret_cast<const float4*>(face_box), gbox, F, groups,
+                                                         image_size, tiles, ntile, tile_offsets, nullptr);
   k_scan_exclusive<<<1, 1024, 0, st>>>(tile_offsets, ntile);
   return check_launch(__func__);
 }
@@ -391,8 +439,11 @@ int lbmff_soft_rasterize_forward(const float* face_vertices, const float* textur
   P.tiles = lbmff_soft_rasterize_tiles(image_size);
   const int ntile = B * P.tiles * P.tiles;
   cudaStream_t st = (cudaStream_t)stream;
-  k_bin<true><<<(ntile * 32 + 255) / 256, 256, 0, st>>>(reinterpret_cast<const float4*>(face_box), F, image_size,
-                                                        P.tiles, ntile, const_cast<int*>(tile_offsets), tile_faces);
+  const int groups = (F + 31) / 32;
+  const float4* gbox = reinterpret_cast<const float4*>(face_box) + (long long)B * F;
+  k_bin<true><<<(ntile * 32 + 255) / 256, 256, 0, st>>>(reinterpret_cast<const float4*>(face_box), gbox, F, groups,
+                                                        image_size, P.tiles, ntile, const_cast<int*>(tile_offsets),
+                                                        tile_faces);
   k_raster_tile<<<ntile, kTile * kTile, 0, st>>>(face_vertices, textures, face_info,
                                                  reinterpret_cast<const float4*>(face_box), tile_offsets, tile_faces,
                                                  soft_colors, aggrs_info, P);

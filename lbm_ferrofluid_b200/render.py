@@ -54,7 +54,7 @@ def soft_rasterize(face_vertices, textures, image_size=256, background_color=Non
     log_eps = math.log(1.0 / dist_eps - 1.0)                       # soft_rasterize.py:54
     tiles = _lib.load().lbmff_soft_rasterize_tiles(size)
     info = torch.empty((B, F, 24), dtype=torch.float32, device=dev)
-    box = torch.empty((B, F, 4), dtype=torch.float32, device=dev)
+    box = torch.empty((B * F + B * ((F + 31) // 32), 4), dtype=torch.float32, device=dev)   # face + group boxes
     offsets = torch.empty(B * tiles * tiles + 1, dtype=torch.int32, device=dev)
     H.launch("lbmff_soft_rasterize_bin", dev, H.ptr(fv), H.ptr(info), H.ptr(box), H.ptr(offsets), B, F, size,
              float(sigma_val), log_eps)

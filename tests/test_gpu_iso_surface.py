@@ -61,12 +61,11 @@ def test_sphere_at_demo_size_is_closed_oriented_and_has_the_right_area_and_volum
     assert abs(vol.item() / (4 / 3 * np.pi * r ** 3) - 1) < 1e-3
     assert abs(area.item() / (4 * np.pi * r ** 2) - 1) < 1e-3
     assert (t.reshape(-1, 3).norm(dim=1) - r).abs().max().item() < 2e-3
-    # directed edges as (key(a), key(b)) with a 64-bit key per vertex (21 bits per coordinate of round(v * 4096))
-    q = torch.round(tri.double() * 4096).long()
-    key = (q[..., 0] << 42) | (q[..., 1] << 21) | q[..., 2]
-    a, b = key, key.roll(-1, dims=1)
-    fwd = torch.stack([a.flatten(), b.flatten()], 1)
-    rev = torch.stack([b.flatten(), a.flatten()], 1)
+    # directed edges keyed by the exact fp32 bits of their two vertices (6 ints per edge)
+    bits = tri.contiguous().view(torch.int32).long()
+    a, b = bits, bits.roll(-1, dims=1)
+    fwd = torch.cat([a, b], dim=2).reshape(-1, 6)
+    rev = torch.cat([b, a], dim=2).reshape(-1, 6)
     uf, cf = torch.unique(fwd, dim=0, return_counts=True)
     ur = torch.unique(rev, dim=0)
     assert (cf == 1).all() and torch.equal(uf, ur)

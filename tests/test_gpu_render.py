@@ -35,12 +35,13 @@ def _close(got, want, what, mean_tol=2e-4, pix_tol=2e-3, frac=0.995):
     assert (d <= pix_tol).mean() >= frac, (what, "fraction within tol", (d <= pix_tol).mean())
 
 
-def _scene(B, F, seed, T=2):
+def _scene(B, F, seed, T=2, duplicate=True):
     rng = np.random.default_rng(seed)
     centre = rng.uniform(-0.9, 0.9, (B, F, 1, 2))
     fv = np.concatenate([centre + rng.uniform(-0.35, 0.35, (B, F, 3, 2)), rng.uniform(1.5, 6.0, (B, F, 3, 1))], axis=3)
     fv[:, : F // 6, :, :2] *= 0.2                         # some tiny faces (sub-pixel: the marching-cubes regime)
-    fv[:, -1] = fv[:, -2][:, ::-1]                       # an exact duplicate with opposite winding
+    if duplicate:                                        # an exact duplicate with opposite winding (a depth tie: only
+        fv[:, -1] = fv[:, -2][:, ::-1]                   # meaningful for the order-independent softmax aggregation)
     tex = rng.uniform(0, 1, (B, F, T, 3))
     return fv.astype(np.float32), tex.astype(np.float32)
 
@@ -63,9 +64,8 @@ def _reference_forward(mod, fv, tex, size, bg, near, far, fill_back, eps, sigma,
     colors = torch.ones(B, 4, size, size, device=dev)
     for k in range(3):
         colors[:, k] *= bg[k]
-    info, aggrs, colors = mod.forward_soft_rasterize(fv.clone(), tex.clone(), info, aggrs, colors, size, near, far, eps,
-                                                     sigma, dist, math.log(1.0 / dist_eps - 1.0), gamma, rgb, alpha, tt,
-                                                     fill_back)
+    info, aggrs, colors = mod.forward(fv.clone(), tex.clone(), info, aggrs, colors, size, near, far, eps,
+                                      sigma, dist, math.log(1.0 / dist_eps - 1.0), gamma, rgb, alpha, tt, fill_back)
     torch.cuda.synchronize()
     return colors, aggrs
 
@@ -84,7 +84,7 @@ def test_rasteriser_against_the_oracle_and_the_reference_kernel(case):
     from lbm_ferrofluid_b200.render import soft_rasterize
 
     T = 3 if case["tt"] == "vertex" else 2
-    fv, tex = _scene(case["B"], case["F"], seed=case["size"], T=T)
+    fv, tex = _scene(case["B"], case["F"], seed=case["size"], T=T, duplicate=case["rgb"] == "softmax")
     bg = (1.0, 0.5, 0.25)
     got, got_aggr = soft_rasterize(torch.from_numpy(fv).cuda(), torch.from_numpy(tex).cuda(), case["size"], bg, 1.0, 100.0,
                                    case["fb"], 1e-3, case["sigma"], case["dist"], 1e-4, case["gamma"], case["rgb"],
