@@ -358,12 +358,13 @@ int lbmff_iso_surface_emit_3d(const float* u, double iso, int flip, const int* b
  * reference's meaning (func_id_dist 0 hard / 1 barycentric / 2 euclidean, func_id_rgb 0 hard / 1 softmax,
  * func_id_alpha 0 hard / 1 sum / 2 prod, texture_sample_type 0 surface / 1 vertex; dist_eps is the already
  * transformed log(1/dist_eps - 1) of soft_rasterize.py:54).  Instead of every pixel walking all faces, faces are
- * binned into 16 x 16 pixel tiles first (ordered lists, so a pixel folds its faces in the reference's order):
+ * binned into 8 x 8 pixel tiles first (ordered lists, so a pixel folds its faces in the reference's order):
  *   bin    : fills face_info [B][F][24], face_box [B * F + B * ceil(F / 32)][4] (face boxes, then the union boxes
- *            of groups of 32 consecutive faces) and tile_offsets [B * tiles^2 + 1] (exclusive scan of
- *            the per-tile face counts, last entry = total list length L), tiles = lbmff_soft_rasterize_tiles(is);
+ *            of groups of 32 consecutive faces) and tile_offsets [lbmff_soft_rasterize_offsets(B, is)] (exclusive
+ *            scan of the face counts per tile and binning segment, last entry = total list length L);
  *   forward: tile_faces [L] ints of scratch; writes soft_colors (and aggrs_info). */
 int lbmff_soft_rasterize_tiles(int image_size);
+int lbmff_soft_rasterize_offsets(int B, int image_size);
 int lbmff_soft_rasterize_bin(const float* face_vertices, float* face_info, float* face_box, int* tile_offsets,
                              int B, int F, int image_size, double sigma_val, double dist_eps,
                              lbmff_stream_t stream);

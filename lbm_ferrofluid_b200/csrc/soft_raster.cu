@@ -6,21 +6,24 @@
 // marching-cubes triangles per frame, of which a pixel is touched by a handful (a face is skipped unless the pixel
 // lies inside its bounding box grown by sqrt(threshold), soft_rasterize_cuda_kernel.cu:372).  Here:
 //   1. k_face_setup     per face: barycentric matrix, Gram matrix, obtuse-corner flag (:236-302) + the grown bbox;
-//   2. k_group_box/k_bin per 16 x 16 pixel tile, one warp scans the face boxes IN FACE ORDER (first the union boxes of
+//   2. k_group_box/k_bin per 8 x 8 pixel tile, warps scan the face boxes IN FACE ORDER (first the union boxes of
 //                       groups of 32 consecutive faces, then the faces of the groups that touch the tile) and compacts
 //                       the hits (ballot + popc): ordered per-tile lists, no atomics, deterministic;
-//   3. k_raster_tile    one block per tile, one thread per pixel: the tile's faces are staged through shared memory
+//   3. k_raster_tile    one block (two warps) per tile, one thread per pixel: the tile's faces are staged through shared memory
 //                       in chunks and every pixel folds them in ascending face order -- the same aggregation order
 //                       as the reference's loop over all faces, so the running softmax rescaling sees the same
 //                       sequence of faces (those the reference skips by its bbox test contribute nothing there either).
 // Every option of the reference forward is kept: dist hard / barycentric / euclidean, rgb hard / softmax, alpha
-// hard / sum / prod, surface / vertex textures, near / far, double_side.  fp32 like the reference; the reference is
-// built with --use_fast_math, this file with IEEE division and expf (the comparison tolerance is in the tests).
+// hard / sum / prod, surface / vertex textures, near / far, double_side.  fp32 like the reference, and like the
+// reference (--use_fast_math) the per-pixel code uses approximate division / exp (the comparison tolerance against
+// the IEEE numpy oracle and the reference kernel is in the tests).
 #include "capi.cuh"
 
 namespace lbmff {
 
-constexpr int kTile = 16;        // pixels per tile edge
+constexpr int kTile = 8;         // pixels per tile edge: small tiles = short lists and thousands of blocks to balance
+constexpr int kFW = 8, kFH = 4;  // a warp's pixel footprint inside the tile
+constexpr int kSeg = 4;          // binning warps per tile: each scans a quarter of the faces
 constexpr int kChunk = 64;       // faces staged per shared-memory chunk
 constexpr int kInfo = 24;        // per-face record: 9 inverse, 9 Gram, 3 obtuse flags, 3 padding
 
@@ -106,23 +109,27 @@ __global__ void __launch_bounds__(256) k_group_box(const float4* __restrict__ bo
   if (lane == 0) gbox[w] = b;
 }
 
-// one warp per (batch item, tile): scans the group boxes 32 at a time, then the 32 faces of every group that touches
+// kSeg warps per (batch item, tile), each on its share of the faces: scans the group boxes 32 at a time, then the 32 faces of every group that touches
 // the tile, all in ascending face order.  FILL = false counts, FILL = true writes the ordered face list.
 template <bool FILL>
 __global__ void __launch_bounds__(256) k_bin(const float4* __restrict__ box, const float4* __restrict__ gbox, int F,
                                              int groups_per_item, int is, int tiles, int ntile_total,
                                              int* __restrict__ count_or_offset, int* __restrict__ list) {
   const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (w >= ntile_total) return;
-  const int per_img = tiles * tiles, bn = w / per_img, t = w - bn * per_img;
+  if (w >= ntile_total * kSeg) return;
+  const int tile = w / kSeg, seg = w - tile * kSeg;
+  const int per_img = tiles * tiles, bn = tile / per_img, t = tile - bn * per_img;
   const TileSpan s = tile_span(t % tiles, t / tiles, is);
   const float4* b = box + (long long)bn * F;
   const float4* gb = gbox + (long long)bn * groups_per_item;
+  // segment seg owns a contiguous range of face groups (multiples of 32 groups); list order = (tile, seg, face)
+  const int per_seg = ((groups_per_item + kSeg - 1) / kSeg + 31) / 32 * 32;
+  const int g_beg = seg * per_seg, g_end = min(groups_per_item, g_beg + per_seg);
   int n = 0;
   const int base = FILL ? count_or_offset[w] : 0;
-  for (int g0 = 0; g0 < groups_per_item; g0 += 32) {
+  for (int g0 = g_beg; g0 < g_end; g0 += 32) {
     const int g = g0 + lane;
-    unsigned gm = __ballot_sync(0xffffffffu, g < groups_per_item && touches(__ldg(gb + g), s));
+    unsigned gm = __ballot_sync(0xffffffffu, g < g_end && touches(__ldg(gb + g), s));
     while (gm) {
       const int bit = __ffs(gm) - 1;
       gm &= gm - 1;
@@ -174,6 +181,10 @@ __global__ void __launch_bounds__(1024) k_scan_exclusive(int* __restrict__ count
 }
 
 // ---- 3. per-pixel aggregation ---------------------------------------------------------------------------------
+// The reference builds its kernel with --use_fast_math (soft_rasterize.py:18-23): approximate division and exp are
+// what it runs; the same intrinsics here cut the per-visit instruction count by about a third.
+__device__ __forceinline__ float fdiv(float a, float b) { return __fdividef(a, b); }
+
 struct FaceRec {              // one staged face
   float v[9];                 // x0 y0 z0 x1 y1 z1 x2 y2 z2 (projected: x, y in [-1, 1], z = camera depth)
   float info[kInfo];
@@ -203,7 +214,7 @@ __device__ __forceinline__ void pixel_to_face(const FaceRec& fr, const float (&w
       const float d0 = g[3 * a + 0] - g[3 * b + 0], d1 = g[3 * a + 1] - g[3 * b + 1], d2 = g[3 * a + 2] - g[3 * b + 2];
       const float d[3] = {d0, d1, d2};
       float t[3];
-      t[a] = (w[0] * d0 + w[1] * d1 + w[2] * d2 - d[b]) / (d[a] - d[b]);
+      t[a] = fdiv(w[0] * d0 + w[1] * d1 + w[2] * d2 - d[b], d[a] - d[b]);
       t[b] = 1 - t[a];
       t[c] = 0;
       t[0] -= w[0]; t[1] -= w[1]; t[2] -= w[2];
@@ -231,7 +242,7 @@ __device__ __forceinline__ void pixel_to_face(const FaceRec& fr, const float (&w
   const int b = (a + 1) % 3, c = (a + 2) % 3;
   const float d[3] = {g[3 * a + 0] - g[3 * b + 0], g[3 * a + 1] - g[3 * b + 1], g[3 * a + 2] - g[3 * b + 2]};
   float t[3];
-  t[a] = (w[0] * d[0] + w[1] * d[1] + w[2] * d[2] - d[b]) / (d[a] - d[b]);
+  t[a] = fdiv(w[0] * d[0] + w[1] * d[1] + w[2] * d[2] - d[b], d[a] - d[b]);
   t[b] = 1 - t[a];
   t[c] = 0;
 #pragma unroll
@@ -264,11 +275,12 @@ __global__ void __launch_bounds__(kTile* kTile) k_raster_tile(const float* __res
   const int per_img = P.tiles * P.tiles;
   const int tile = blockIdx.x, bn = tile / per_img, t = tile - bn * per_img;
   const int tx = t % P.tiles, ty = t / P.tiles;
-  // a warp owns an 8 x 4 pixel footprint (2 x 4 warps per tile): a marching-cubes face (grown box ~6 x 6 pixels)
-  // then meets ~4 warps instead of the ~7 of a 16 x 2 footprint, and more of a visiting warp's lanes are inside it
+  // a warp owns an 8 x 4 pixel footprint: a marching-cubes face (grown box ~6 x 6 pixels) then meets ~4 warps
+  // instead of the ~7 of a 16 x 2 footprint, and more of a visiting warp's lanes are inside it
+  constexpr int kWarpsX = kTile / kFW;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int fx0 = tx * kTile + (warp & 1) * 8, fy0 = ty * kTile + (warp >> 1) * 4;
-  const int xi = fx0 + (lane & 7), row = fy0 + (lane >> 3), is = P.is;
+  const int fx0 = tx * kTile + (warp % kWarpsX) * kFW, fy0 = ty * kTile + (warp / kWarpsX) * kFH;
+  const int xi = fx0 + (lane % kFW), row = fy0 + (lane / kFW), is = P.is;
   const bool live = xi < is && row < is;
   const int pn = row * is + xi;
   const float xp = pix_coord(xi, is), yp = pix_coord(is - 1 - row, is);
@@ -277,11 +289,12 @@ __global__ void __launch_bounds__(kTile* kTile) k_raster_tile(const float* __res
 
   TileSpan span;  // pixel-centre extremes of the warp's footprint, clipped to the image
   {
-    const int x1 = min(fx0 + 8, is) - 1, r1 = min(fy0 + 4, is) - 1;
+    const int x1 = min(fx0 + kFW, is) - 1, r1 = min(fy0 + kFH, is) - 1;
     span.xlo = pix_coord(fx0, is); span.xhi = pix_coord(x1, is);
     span.ylo = pix_coord(is - 1 - r1, is); span.yhi = pix_coord(is - 1 - fy0, is);
   }
   const float threshold = P.dist_eps * P.sigma;
+  const float inv_sigma = 1.f / P.sigma, inv_gamma = 1.f / P.gamma, inv_depth = 1.f / (P.far_ - P.near_);
   float c[3] = {1.f, 1.f, 1.f};
   float alpha = P.alpha == 2 ? 1.f : 0.f;
   float ssum = expf(P.eps / P.gamma), smax = P.eps;
@@ -292,7 +305,7 @@ __global__ void __launch_bounds__(kTile* kTile) k_raster_tile(const float* __res
   float depth_min = 10000000.f;
   int face_min = -1;
 
-  const int beg = offsets[tile], end = offsets[tile + 1];
+  const int beg = offsets[tile * kSeg], end = offsets[(tile + 1) * kSeg];
   const float* fbase = faces + (long long)bn * P.F * 9;
   const float* ibase = info + (long long)bn * P.F * kInfo;
   const float4* bbase = box + (long long)bn * P.F;
@@ -328,13 +341,13 @@ __global__ void __launch_bounds__(kTile* kTile) k_raster_tile(const float* __res
         float d = w[0] > w[1] ? (w[1] > w[2] ? w[2] : w[1]) : (w[0] > w[2] ? w[2] : w[0]);
         d = d > 0 ? d * d : -(d * d);
         if (-d >= threshold) continue;
-        frag = 1.f / (1.f + expf(-d / P.sigma));
+        frag = fdiv(1.f, 1.f + __expf(-d * inv_sigma));
       } else {
         float sign, dx, dy;
         pixel_to_face(fr, w, xp, yp, sign, dx, dy);
         const float d = dx * dx + dy * dy;
         if (sign < 0 && d >= threshold) continue;
-        frag = 1.f / (1.f + expf(-sign * d / P.sigma));
+        frag = fdiv(1.f, 1.f + __expf(-sign * d * inv_sigma));
       }
       if (P.alpha == 0) { if (frag > 0.5f) alpha = 1.f; }
       else if (P.alpha == 1) alpha += frag;
@@ -345,8 +358,8 @@ __global__ void __launch_bounds__(kTile* kTile) k_raster_tile(const float* __res
       for (int k = 0; k < 3; ++k) wc[k] = fmaxf(fminf(w[k], 1.f), 0.f);
       const float wsum = fmaxf(wc[0] + wc[1] + wc[2], 1e-5f);
 #pragma unroll
-      for (int k = 0; k < 3; ++k) wc[k] /= wsum;
-      const float zp = 1.f / (wc[0] / fr.v[2] + wc[1] / fr.v[5] + wc[2] / fr.v[8]);
+      for (int k = 0; k < 3; ++k) wc[k] = fdiv(wc[k], wsum);
+      const float zp = fdiv(1.f, fdiv(wc[0], fr.v[2]) + fdiv(wc[1], fr.v[5]) + fdiv(wc[2], fr.v[8]));
       if (zp < P.near_ || zp > P.far_) continue;
       const float* tex = tbase + (long long)ids[j] * P.T * 3;
       if (P.rgb == 0) {
@@ -357,13 +370,13 @@ __global__ void __launch_bounds__(kTile* kTile) k_raster_tile(const float* __res
           for (int k = 0; k < 3; ++k) c[k] = sample_texture(tex, wc, P.R, P.T, k, P.sample);
         }
       } else if (front_facing(fr.v) || P.double_side) {
-        const float zn = (P.far_ - zp) / (P.far_ - P.near_);
+        const float zn = (P.far_ - zp) * inv_depth;
         float rescale = 1.f;
         if (zn > smax) {
-          rescale = expf((smax - zn) / P.gamma);
+          rescale = __expf((smax - zn) * inv_gamma);
           smax = zn;
         }
-        const float ez = expf((zn - smax) / P.gamma);
+        const float ez = __expf((zn - smax) * inv_gamma);
         ssum = rescale * ssum + ez * frag;
 #pragma unroll
         for (int k = 0; k < 3; ++k)
@@ -394,6 +407,11 @@ using namespace lbmff;
 extern "C" {
 
 int lbmff_soft_rasterize_tiles(int image_size) { return image_size < 1 ? -1 : (image_size + kTile - 1) / kTile; }
+int lbmff_soft_rasterize_offsets(int B, int image_size) {
+  const long long t = lbmff_soft_rasterize_tiles(image_size);
+  const long long n = t < 1 || B < 1 ? -1 : (long long)B * t * t * kSeg + 1;
+  return n > 0x7fffffffLL ? -1 : (int)n;
+}
 
 int lbmff_soft_rasterize_bin(const float* face_vertices, float* face_info, float* face_box, int* tile_offsets,
                              int B, int F, int image_size, double sigma_val, double dist_eps,
@@ -410,9 +428,10 @@ int lbmff_soft_rasterize_bin(const float* face_vertices, float* face_info, float
   float4* gbox = reinterpret_cast<float4*>(face_box) + (long long)B * F;  // group boxes live behind the face boxes
   k_group_box<<<(B * groups * 32 + 255) / 256, 256, 0, st>>>(reinterpret_cast<const float4*>(face_box), gbox, F, groups,
                                                              B * groups);
-  k_bin<false><<<(ntile * 32 + 255) / 256, 256, 0, st>>>(reinterpret_cast<const float4*>(face_box), gbox, F, groups,
-                                                         image_size, tiles, ntile, tile_offsets, nullptr);
-  k_scan_exclusive<<<1, 1024, 0, st>>>(tile_offsets, ntile);
+  k_bin<false><<<(ntile * kSeg * 32 + 255) / 256, 256, 0, st>>>(reinterpret_cast<const float4*>(face_box), gbox, F,
+                                                                groups, image_size, tiles, ntile, tile_offsets,
+                                                                nullptr);
+  k_scan_exclusive<<<1, 1024, 0, st>>>(tile_offsets, ntile * kSeg);
   return check_launch(__func__);
 }
 
@@ -441,9 +460,9 @@ int lbmff_soft_rasterize_forward(const float* face_vertices, const float* textur
   cudaStream_t st = (cudaStream_t)stream;
   const int groups = (F + 31) / 32;
   const float4* gbox = reinterpret_cast<const float4*>(face_box) + (long long)B * F;
-  k_bin<true><<<(ntile * 32 + 255) / 256, 256, 0, st>>>(reinterpret_cast<const float4*>(face_box), gbox, F, groups,
-                                                        image_size, P.tiles, ntile, const_cast<int*>(tile_offsets),
-                                                        tile_faces);
+  k_bin<true><<<(ntile * kSeg * 32 + 255) / 256, 256, 0, st>>>(reinterpret_cast<const float4*>(face_box), gbox, F,
+                                                               groups, image_size, P.tiles, ntile,
+                                                               const_cast<int*>(tile_offsets), tile_faces);
   k_raster_tile<<<ntile, kTile * kTile, 0, st>>>(face_vertices, textures, face_info,
                                                  reinterpret_cast<const float4*>(face_box), tile_offsets, tile_faces,
                                                  soft_colors, aggrs_info, P);

@@ -52,10 +52,12 @@ def soft_rasterize(face_vertices, textures, image_size=256, background_color=Non
         colors[:, 3] = 0.0                                         # no face: every aggregation leaves alpha 0
         return (colors, aggrs) if return_aggrs else colors
     log_eps = math.log(1.0 / dist_eps - 1.0)                       # soft_rasterize.py:54
-    tiles = _lib.load().lbmff_soft_rasterize_tiles(size)
+    n_off = _lib.load().lbmff_soft_rasterize_offsets(B, size)
+    if n_off <= 0:
+        raise RuntimeError("soft_rasterize: image too large")
     info = torch.empty((B, F, 24), dtype=torch.float32, device=dev)
     box = torch.empty((B * F + B * ((F + 31) // 32), 4), dtype=torch.float32, device=dev)   # face + group boxes
-    offsets = torch.empty(B * tiles * tiles + 1, dtype=torch.int32, device=dev)
+    offsets = torch.empty(n_off, dtype=torch.int32, device=dev)
     H.launch("lbmff_soft_rasterize_bin", dev, H.ptr(fv), H.ptr(info), H.ptr(box), H.ptr(offsets), B, F, size,
              float(sigma_val), log_eps)
     total = int(offsets[-1].item())                                # one 4-byte read: the list length
