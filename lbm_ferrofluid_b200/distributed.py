@@ -539,6 +539,25 @@ class SlabFerroSolver:
         return s.initialize(rho)
 
 
+def _two_droplets(cls, res_per_rank, path, device, world, rank, mag=1.0, n_sweeps=30):
+    """demo_3d_LBM_two_droplets.py scaled up (BASELINE.json configs[4]): two liquid spheres in gas, every wall closed in
+    both flag arrays (:113-121), kappa 0.5, tau_f = tau_g = 0.68, gravity 1e-4, uniform H_ext = mag along y (:166-168).
+    Every rank owns res_per_rank = (Dl, H, W) of the global (world * Dl, H, W) box."""
+    from . import initializers as I
+
+    Dl, Hh, W = res_per_rank
+    lay = SlabLayout(Dl * world, world, rank)
+    flags = slab_shell_flags(lay, Hh, W, device=device)
+    mflags = slab_shell_flags(lay, Hh, W, device=device)
+    rho = I.two_droplets_rho((lay.D, Hh, W), flags, global_depth=lay.Dg, z_offset=lay.zoff)
+    s = cls(lay, flags, exchanger=DistExchanger(lay, device), magnetic_flags=mflags, H_ext=[0.0, mag, 0.0],
+            n_sweeps=n_sweeps, magnetic_path=path, contact_angle=0.5 * math.pi, gravity=1e-4, kappa=0.5)
+    return s.initialize(rho)
+
+
+SlabFerroSolver.two_droplets = classmethod(_two_droplets)
+
+
 def step_virtual_ranks(solvers: Sequence[SlabFerroSolver], n: int = 1):
     """Advance P slab solvers living in ONE process (one GPU) in lockstep, halos by device copies.
     This is the bit-for-bit test vehicle of the decomposition."""

@@ -9,7 +9,8 @@ import os
 import numpy as np
 import torch
 
-__all__ = ["mkdir", "save_img", "export_asset", "save_rendered_image", "dump_2d_plt_file_single"]
+__all__ = ["mkdir", "save_img", "export_asset", "save_rendered_image", "dump_2d_plt_file_single",
+           "dump_3d_plt_file_single"]
 
 
 def mkdir(path: str):
@@ -70,14 +71,35 @@ def save_rendered_image(renderer, phi, filename, res, dx):
 
 
 def dump_2d_plt_file_single(filename, np_density, np_uv, B):
-    """Tecplot ASCII dump of a 2-D scalar + vector field."""
-    H, W = np_density.shape[-2:]
+    """Tecplot ASCII dump of batch item B of a 2-D scalar [B,1,H,W] + vector [B,2,H,W] field
+    (src/LBM/utils/io.py:107-121): same header and point order (x fastest)."""
+    rho, uv = np.asarray(np_density), np.asarray(np_uv)
+    H, W = rho.shape[-2:]
     with open(filename, "w") as fo:
         fo.write('TITLE ="Magnetic internal force"\n')
-        fo.write('VARIABLES = "X", "Y", "density", "U", "V"\n')
-        fo.write(f"ZONE I={W}, J={H}, F=POINT\n")
-        d = np.asarray(np_density).reshape(-1, H, W)[0]
-        uv = np.asarray(np_uv).reshape(-1, 2, H, W)[0]
+        fo.write('VARIABLES = "X" "Y" "RHO" "U" "V" \n')
+        fo.write("ZONE I={}, J={}\n".format(W, H))
+        fo.write("F=POINT\n")
         for j in range(H):
             for i in range(W):
-                fo.write(f"{i} {j} {d[j, i]} {uv[0, j, i]} {uv[1, j, i]}\n")
+                fo.write("{} {} {} {} {}\n".format(i, j, rho[B, 0, j, i], uv[B, 0, j, i], uv[B, 1, j, i]))
+
+
+def dump_3d_plt_file_single(filename, np_density, np_u, np_v, np_w, B, C):
+    """Tecplot ASCII dump of a 3-D scalar and a staggered (MAC) vector field averaged to cell centres
+    (src/LBM/utils/io.py:124-152): same header, same point order (x fastest), written in one vectorised pass."""
+    rho = np.asarray(np_density)
+    K, J, I = rho.shape[-3:]
+    u = np.asarray(np_u); v = np.asarray(np_v); w = np.asarray(np_w)
+    u = 0.5 * (u[..., 1:] + u[..., :-1])
+    v = 0.5 * (v[..., 1:, :] + v[..., :-1, :])
+    w = 0.5 * (w[..., 1:, :, :] + w[..., :-1, :, :])
+    k, j, i = np.meshgrid(np.arange(K), np.arange(J), np.arange(I), indexing="ij")
+    cols = [i.ravel(), j.ravel(), k.ravel(), rho[B, C].ravel(), u[B, C].ravel(), v[B, C].ravel(), w[B, C].ravel()]
+    with open(filename, "w") as fo:
+        fo.write('TITLE ="Magnetic internal force"\n')
+        fo.write('VARIABLES = "X" "Y" "Z" "RHO" "U" "V" "W" \n')
+        fo.write("ZONE I={}, J={}, K={}\n".format(I, J, K))
+        fo.write("F=POINT\n")
+        for row in zip(*cols):
+            fo.write("{} {} {} {} {} {} {}\n".format(*row))

@@ -355,6 +355,42 @@ class FerroSolver:
         """sum over ALL cells (walls included) of sum_q f: conserved to round-off."""
         return float(self.f.double().sum().item())
 
+    # ---- checkpoint / resume (SURVEY.md section 5: absent in the reference, which only writes frames) ----------
+    def state_dict(self) -> dict:
+        """Everything a later ``load_state_dict`` needs to continue BIT-IDENTICALLY: the current populations, the
+        fields one step reads from the previous one (rho, vel, pressure, psi: the warm start) and the magnetic
+        lattice state of the active path.  Tensors are clones on the solver's device; ``torch.save`` it as is."""
+        sd = dict(version=1, dim=self.dim, res=tuple(self.res), batch=self.B, steps_done=self.steps_done,
+                  magnetic_path=self.magnetic_path, f=self.f.clone(), g=self.g.clone(), rho=self.rho.clone(),
+                  vel=self.vel.clone(), pressure=self.pressure.clone())
+        if self.magnetic:
+            sd["psi"] = self.psi.clone()
+            if self.magnetic_path == "faithful":
+                sd["h"] = self._h[self._mcur].clone()
+            elif self.magnetic_path == "scalar":
+                sd["a_cur"], sd["a_prev"] = self._a[self._mcur].clone(), self._a[1 - self._mcur].clone()
+        return sd
+
+    def load_state_dict(self, sd: dict):
+        if sd.get("version") != 1 or sd["dim"] != self.dim or tuple(sd["res"]) != tuple(self.res) or \
+                sd["batch"] != self.B:
+            raise RuntimeError("checkpoint does not match this solver (version / dim / res / batch)")
+        if sd["magnetic_path"] != self.magnetic_path:
+            raise RuntimeError(f"checkpoint was written by magnetic_path={sd['magnetic_path']!r}, "
+                               f"this solver runs {self.magnetic_path!r}")
+        self._cur = 0
+        self._f[0].copy_(sd["f"]); self._g[0].copy_(sd["g"])
+        self.rho.copy_(sd["rho"]); self.vel.copy_(sd["vel"]); self.pressure.copy_(sd["pressure"])
+        if self.magnetic:
+            self.psi.copy_(sd["psi"])
+            self._mcur = 0
+            if self.magnetic_path == "faithful":
+                self._h[0].copy_(sd["h"])
+            elif self.magnetic_path == "scalar":
+                self._a[0].copy_(sd["a_cur"]); self._a[1].copy_(sd["a_prev"])
+        self.steps_done = int(sd["steps_done"])
+        return self
+
 
 class SinglePhaseSolver:
     """Single-phase BGK / KBC flow, D2Q9 or D3Q19: demo_2d_LBM.py / demo_2d_LBM_KBC.py loop in one kernel."""

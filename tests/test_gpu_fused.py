@@ -330,3 +330,21 @@ def test_kbc_zero_over_zero_quirk_is_reproduced():
     assert torch.equal(bad, bad_ref)
     ok = ~bad_ref
     assert (s.f.cpu()[ok] - f_ref[ok]).abs().max() <= 2e-6 * f_ref[ok].abs().max()
+
+
+@pytest.mark.parametrize("path", ["faithful", "scalar", "converged"])
+def test_checkpoint_resume_is_bit_identical(path, tmp_path):
+    """state_dict -> torch.save -> load_state_dict into a fresh solver continues the trajectory bit for bit."""
+    G = load_golden("traj_ros3d")
+    a = make_solver(G, path=path)
+    a.step(3)
+    torch.save(a.state_dict(), tmp_path / "ckpt.pt")
+    a.step(3)
+    b = make_solver(G, path=path)
+    b.load_state_dict(torch.load(tmp_path / "ckpt.pt"))
+    assert b.steps_done == 3
+    b.step(3)
+    for k in ("f", "g", "rho", "vel", "pressure", "psi"):
+        assert torch.equal(getattr(a, k), getattr(b, k)), k
+    with pytest.raises(RuntimeError, match="magnetic_path"):
+        make_solver(G, path="scalar" if path != "scalar" else "faithful").load_state_dict(a.state_dict())
