@@ -1,0 +1,4 @@
+set -x
+mkdir -p gpurun_out
+N=$1
+python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29521 bench.py --gpus $N --steps 5 --warmup 3 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; cut -c1-200 gpurun_out/bench_n$N.json; tail -3 gpurun_out/bench_n$N.err
