@@ -341,7 +341,7 @@ int lbmff_poisson_cg_3d(const float* rhs, const uint8_t* mflags, float* psi, flo
  * (axis 0, axis 1, axis 2), the order PyMCubes returns.  Two passes, deterministic triangle order, no atomics:
  *   count: block_offsets [lbmff_iso_surface_blocks(D,H,W)] ints receive the exclusive scan of the per-block triangle
  *          counts, *total (device int) the number of triangles F;
- *   emit : writes min(F, capacity) triangles.  flip = 0: counter-clockwise normal towards increasing u.
+ *   emit : writes min(F, capacity) triangles.  flip = 0: counter-clockwise normal towards DECREASING u (csrc/iso_surface.cu explains the choice).
  * lbmff_mc_case_table is host-only (no GPU): ntri [256], edges [256][24] cube-edge ids (-1 padded), for tests. */
 int lbmff_mc_case_table(int* ntri, int* edges);
 int lbmff_iso_surface_blocks(int D, int H, int W);

@@ -12,8 +12,11 @@
 // Output is a triangle soup [F][3][3] in ARRAY-INDEX coordinates (axis 0, axis 1, axis 2) = (z, y, x), the order
 // PyMCubes returns; that is directly the `face_vertices` the soft rasteriser consumes.  Triangle order is
 // deterministic (cell-major): two passes (count per block of one cell row -> exclusive scan -> emit), no atomics.
-// Orientation: the counter-clockwise normal points towards INCREASING field values (outward for a signed distance
-// that is negative inside), flip = 1 reverses it.  [PyMCubes' own convention cannot be checked here: unpinned.]
+// Orientation: the counter-clockwise normal points towards DECREASING field values, flip = 1 reverses it.
+// [PyMCubes' own convention cannot be checked here: unpinned.  The choice follows the reference's call site:
+// save_rendered_image passes MINUS phi (liquid positive, gas negative, io.py:60-62) to a renderer whose only light
+// shines along +y onto faces whose normal has a positive y component (lighting.py:190-196); the liquid's upper
+// surface is lit only if the normals point out of the liquid, i.e. towards decreasing values of the volume passed.]
 #include "capi.cuh"
 
 #include <mutex>
@@ -299,8 +302,8 @@ __global__ void __launch_bounds__(256) k_mc_emit(const float* __restrict__ u, Mc
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
       // the table's loops run with "inside" (below iso) on the left seen from outside the cube: their right-hand
-      // normal points towards increasing values (tests/test_iso_surface.py: positive enclosed volume)
-      const int kk = flip ? (k == 0 ? 0 : 3 - k) : k;
+      // normal points towards increasing values (tests/test_iso_surface.py); the default orientation is the reverse
+      const int kk = flip ? k : (k == 0 ? 0 : 3 - k);
       float p[3];
       mc_edge_vertex(d_mc_table.edge[cfg][3 * t + kk], x, y, z, val, iso, p);
       out[3 * k + 0] = p[0]; out[3 * k + 1] = p[1]; out[3 * k + 2] = p[2];

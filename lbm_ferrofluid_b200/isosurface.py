@@ -24,7 +24,8 @@ def case_table():
 
 def triangle_soup(volume: torch.Tensor, isovalue: float = 0.0, flip: bool = False) -> torch.Tensor:
     """[F, 3, 3] fp32 CUDA tensor: the triangles of {volume == isovalue} in array-index coordinates (axis 0, 1, 2).
-    Counter-clockwise normals point towards increasing values (``flip`` reverses).  One 4-byte device->host read
+    Counter-clockwise normals point towards DECREASING values -- out of the liquid for the -phi volume the frame
+    writer passes, so that its upper surface is lit (``flip`` reverses).  One 4-byte device->host read
     (the triangle count) separates the two passes."""
     vol = H.need_cuda(volume, "volume")
     if vol.dim() != 3:

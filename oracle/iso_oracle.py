@@ -31,7 +31,7 @@ def triangle_soup(u, iso, ntri, edges, flip=False):
                 for t in range(ntri[cfg]):
                     tri = []
                     for k in range(3):
-                        kk = (0 if k == 0 else 3 - k) if flip else k
+                        kk = k if flip else (0 if k == 0 else 3 - k)
                         e = int(edges[cfg, t, kk])
                         a = e // 4
                         c0, c1 = edge_corners(e)

@@ -53,8 +53,8 @@ def test_sphere_at_demo_size_is_closed_oriented_and_has_the_right_area_and_volum
     c = torch.tensor([127.63, 127.21, 127.84], device="cuda", dtype=torch.float64)
     u = (torch.sqrt((z - c[0]) ** 2 + (y - c[1]) ** 2 + (x - c[2]) ** 2) - r).float()
     del z, y, x
-    tri = triangle_soup(u, 0.0)
-    assert torch.equal(tri, triangle_soup(u, 0.0))
+    tri = triangle_soup(u, 0.0, flip=True)            # outward normals for a distance field
+    assert torch.equal(tri, triangle_soup(u, 0.0, flip=True))
     t = tri.double() - c
     vol = (t[:, 0] * torch.linalg.cross(t[:, 1], t[:, 2])).sum() / 6.0
     area = 0.5 * torch.linalg.cross(t[:, 1] - t[:, 0], t[:, 2] - t[:, 0]).norm(dim=1).sum()
@@ -84,8 +84,9 @@ def test_phi_of_a_rosensweig_state_gives_one_sheet():
     phi = F.pad(phi[..., 1:-1, 1:-1, 1:-1], pad=(1,) * 6, mode="constant", value=phi.max().item())
     tri = triangle_soup((-phi * (2.0 / max(res)))[0, 0], 0.0)
     assert tri.shape[0] > 2 * 46 * 54
-    # a closed surface around the liquid (u > 0 inside => normals point inwards => negative volume), volume = liquid
+    # a closed surface around the liquid (u > 0 inside, normals towards decreasing u = out of the liquid => positive
+    # signed volume), volume = liquid
     t = tri.double()
     vol = (t[:, 0] * torch.linalg.cross(t[:, 1], t[:, 2])).sum() / 6.0
     liquid = (rho[..., 1:-1, 1:-1, 1:-1] > 0.13).sum().item()
-    assert abs(-vol.item() / liquid - 1) < 0.05
+    assert abs(vol.item() / liquid - 1) < 0.05

@@ -141,7 +141,7 @@ def test_renderer_pipeline_on_a_sphere_mesh():
     ax = torch.arange(n, device="cuda", dtype=torch.float32)
     z, y, x = torch.meshgrid(ax, ax, ax, indexing="ij")
     u = torch.sqrt((z - 31.5) ** 2 + (y - 31.5) ** 2 + (x - 31.5) ** 2) - r
-    verts, faces = marching_cubes(u, 0.0)
+    verts, faces = marching_cubes(u, 0.0, flip=True)          # a distance field: outward = increasing values
     verts = (verts - n / 2.0) * (2.0 / n)
     tex = 0.68 * torch.ones(1, faces.shape[0], 2, 3, device="cuda")
     ren = _demo_renderer(128)

@@ -65,9 +65,9 @@ def test_random_fields_give_a_watertight_consistently_oriented_surface(table, se
     use = IO.edge_use(tri)
     assert all(v == 1 for v in use.values())
     assert all((b, a) in use for (a, b) in use)
-    # normals point towards increasing values: the surface encloses the u < 0 region(s) -> positive volume
-    assert IO.signed_volume(tri) > 0
-    assert IO.signed_volume(IO.triangle_soup(u, 0.0, ntri, edges, flip=True)) < 0
+    # normals point towards decreasing values, i.e. into the enclosed u < 0 region(s) -> negative signed volume
+    assert IO.signed_volume(tri) < 0
+    assert IO.signed_volume(IO.triangle_soup(u, 0.0, ntri, edges, flip=True)) > 0
 
 
 def test_sphere_area_volume_and_vertices_on_the_zero_crossing(table):
@@ -76,7 +76,7 @@ def test_sphere_area_volume_and_vertices_on_the_zero_crossing(table):
     z, y, x = np.meshgrid(*(np.arange(n, dtype=np.float64),) * 3, indexing="ij")
     c = (n - 1) / 2 + np.array([0.13, -0.21, 0.34])
     u = (np.sqrt((z - c[0]) ** 2 + (y - c[1]) ** 2 + (x - c[2]) ** 2) - r).astype(np.float32)
-    tri = IO.triangle_soup(u, 0.0, ntri, edges)
+    tri = IO.triangle_soup(u, 0.0, ntri, edges, flip=True)      # outward normals for a distance field
     assert abs(IO.signed_volume(tri) / (4 / 3 * np.pi * r ** 3) - 1) < 0.01
     assert abs(IO.area(tri) / (4 * np.pi * r ** 2) - 1) < 0.01
     d = np.linalg.norm(tri.reshape(-1, 3).astype(np.float64) - c, axis=1)
