@@ -271,11 +271,45 @@ class FerroSolver:
         self._cur = nxt
         self.steps_done += 1
 
-    def step(self, n: int = 1):
-        """Advance n outer steps.  Asynchronous on torch's current stream."""
-        for _ in range(int(n)):
+    def step(self, n: int = 1, graph: bool = False):
+        """Advance n outer steps.  Asynchronous on torch's current stream.
+
+        ``graph=True`` replays a CUDA graph of TWO steps (an A/B buffer round trip) captured on first use: the
+        ~45 launches of a step then cost one graph launch per pair.  Measured at the reference's default 130^3
+        demo size the step is already GPU-bound (2.2 ms of under-filled kernels), so the gain is ~5 %; it grows as
+        the grid shrinks.  Bit-identical to the eager path; any odd remainder runs eagerly."""
+        n = int(n)
+        if graph and n >= 2:
+            g = self._step_graph()
+            for _ in range(n // 2):
+                g.replay()
+            self.steps_done += 2 * (n // 2)
+            n -= 2 * (n // 2)
+        for _ in range(n):
             self._step_once()
         return self
+
+    def _step_graph(self):
+        """CUDA graph of two consecutive steps starting from the CURRENT buffer parity (one graph per parity)."""
+        if self.magnetic_path == "converged":
+            raise RuntimeError("graph=True is not available with magnetic_path='converged' "
+                               "(the CG solve launches its own conditional graph)")
+        if self._timing is not None:
+            raise RuntimeError("graph=True cannot be combined with enable_kernel_timing()")
+        graphs = self.__dict__.setdefault("_graphs", {})
+        key = (self._cur, getattr(self, "_mcur", 0))
+        if key not in graphs:
+            torch.cuda.synchronize(self.device)
+            saved = (self._cur, getattr(self, "_mcur", 0), self.steps_done)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):                      # capture only records: nothing below executes now
+                self._step_once()
+                self._step_once()
+            self._cur, self.steps_done = saved[0], saved[2]
+            if self.magnetic:
+                self._mcur = saved[1]
+            graphs[key] = g
+        return graphs[key]
 
     def set_H_ext_faces_from_host(self, faces_host: Sequence[torch.Tensor]):
         """Upload the staggered applied field (the H_ext_mac argument of get_H_int) from pinned host memory,
