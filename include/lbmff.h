@@ -375,6 +375,39 @@ int lbmff_soft_rasterize_forward(const float* face_vertices, const float* textur
                                  double gamma_val, int func_id_rgb, int func_id_alpha, int texture_sample_type,
                                  int double_side, lbmff_stream_t stream);
 
+/* =====================================================================================
+ * EXTENSION TIER -- named by the north star, absent from the reference (its only 3-D
+ * lattice is D3Q19, LBM_collision_3d.py:76-103; its only forcing is the velocity shift of
+ * LBM_collision_3d.py:141-143; its streaming is out of place, LBM_propagation_3d.py:18-111).
+ * Single-phase step in one pass (propagation + macro_compute + rebounce_obstacle + BGK collision with the
+ * reference's entropic product equilibrium) on D3Q19 or D3Q27, in the reference's [B][Q][D][H][W] layout.
+ * D3Q27 keeps the reference's D3Q19 order for q < 19 and appends the corners as opposite pairs
+ * (lbmff_ext_lattice_info returns the tables; host-only, needs no device).
+ *   collision 0 BGK | 1 entropic KBC (D3Q27 only): the reference's D2Q9 scheme (LBM_collision_MRT_2d.py:113-151,
+ *             184-226; s = {T, N, Pi} from centred second moments, stabiliser gamma per cell) carried to 3-D;
+ *             the reference's own factory has no 3-D KBC (simulation_runner.py:107-108)
+ *   forcing   0 none | 1 velocity shift u + tau F / rho (reference) | 2 Guo (half-force velocity + source term;
+ *             vel then holds the physical velocity (sum f e + F dt / 2) / rho)
+ *   force     per-cell [B][3][D][H][W], or NULL to use force_uniform[3] (x, y, z)
+ *   streaming 0 A/B pull (f_in != f_out) | 1 esoteric pull, IN PLACE (f_in == f_out): one buffer instead of
+ *             two; parity = number of steps already taken on this buffer (& 1).  The slot layout of an
+ *             esoteric buffer differs from the standard one; lbmff_ext_esoteric_convert_* translates
+ *             (to_esoteric = 1: standard -> layout expected by a step of that parity; 0: back), out of place.
+ * rho, vel are updated IN PLACE on non-OBSTACLE cells. */
+int lbmff_ext_lattice_info(int Q, int* e_out, int* opp_out, double* w_out);
+int lbmff_ext_stream_collide_d3q19(const float* f_in, float* f_out, const uint8_t* flags, const float* force,
+                                   const double* force_uniform, float* rho, float* vel, double tau, int collision,
+                                   int forcing, int streaming, int parity, double dx, double dt, int B, int D, int H,
+                                   int W, lbmff_stream_t stream);
+int lbmff_ext_stream_collide_d3q27(const float* f_in, float* f_out, const uint8_t* flags, const float* force,
+                                   const double* force_uniform, float* rho, float* vel, double tau, int collision,
+                                   int forcing, int streaming, int parity, double dx, double dt, int B, int D, int H,
+                                   int W, lbmff_stream_t stream);
+int lbmff_ext_esoteric_convert_d3q19(const float* src, float* dst, int parity, int to_esoteric, int B, int D, int H,
+                                     int W, lbmff_stream_t stream);
+int lbmff_ext_esoteric_convert_d3q27(const float* src, float* dst, int parity, int to_esoteric, int B, int D, int H,
+                                     int W, lbmff_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -77,6 +77,25 @@ __device__ __forceinline__ FeqFactors<DIM> feq_factors(const float* u, float c) 
   return F;
 }
 
+// Speed-ordered factors for the fused single-phase kernels: the same formula with the divisions shared, 2 per
+// axis instead of the reference sequence's 4 (u / c / c, 1 / (1 - u / c), 1 / A).  Differs from feq_factors by
+// fp32 rounding only; the kernels that use it are held to the trajectory parity bars, not to per-op bit parity.
+template <int DIM>
+__device__ __forceinline__ FeqFactors<DIM> feq_factors_fast(const float* u, float inv_c) {
+  FeqFactors<DIM> F;
+  F.base = 1.0f;
+#pragma unroll
+  for (int a = 0; a < DIM; ++a) {
+    const float ul = u[a] * inv_c;
+    const float s = sqrtf(fmaf(3.0f * ul, ul, 1.0f));
+    const float num = fmaf(2.0f, ul, s), den = 1.0f - ul;
+    F.base *= 2.0f - s;
+    F.A[a] = num / den;
+    F.invA[a] = den / num;
+  }
+  return F;
+}
+
 template <int DIM>
 __device__ __forceinline__ float feq_q(const FeqFactors<DIM>& F, float rho, int q) {
   using L = Lat<DIM>;
@@ -252,6 +271,7 @@ struct Consts {
   float mag_src;     // cs2 (0.5 - tau) dt        LBM_magnetic_3d.py:180
   // combined constants of the fused (speed-ordered) collision, formed in double
   float inv_cs2;     // 1 / cs2
+  float inv_c;       // 1 / c
   float c_f;         // dt (1 - 0.5/tau_f) dt / cs2
   float c_g;         // (1 - 0.5/tau_g) dt
   float vel_scale;   // 1 / cs2 (velocity from g-moments)
@@ -278,6 +298,7 @@ inline Consts make_consts(double dx, double dt, double tau = 1.0, double tau_f =
   k.grav_y = -(float)gravity; k.cot = (float)cot;
   k.mag_src = (float)(cs2 * (0.5 - tau) * dt);
   k.inv_cs2 = (float)(1.0 / cs2);
+  k.inv_c = (float)(1.0 / c);
   k.c_f = (float)(dt * (1.0 - 0.5 / tau_f) * dt / cs2);
   k.c_g = (float)((1.0 - 0.5 / tau_g) * dt);
   k.vel_scale = (float)(1.0 / cs2);

@@ -1,0 +1,168 @@
+"""GPU checks of the SURVEY 8(f) N4 extension tier (csrc/ext_lattice.cu, lbm_ferrofluid_b200/extensions.py).
+
+No reference oracle exists for D3Q27 / Guo forcing / esoteric-pull streaming, so they are pinned to
+  * the parity-pinned D3Q19 single-phase kernel where they overlap,
+  * oracle/ext_oracle.py (fp64 restatement built from the pinned oracle's blocks),
+  * esoteric pull == A/B pull BIT FOR BIT (same per-cell arithmetic, different addresses),
+  * mass and momentum balances.
+The 3-D KBC collision (D3Q27) is checked against the same oracle; its defining split (ds carries exactly the
+second-order moments, gamma = 2 is BGK) is checked on the CPU in tests/test_ext_oracle.py.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ext_oracle as X
+from oracle import lbm_oracle as O
+from tests.util import rel_l2
+
+pytestmark = pytest.mark.gpu
+
+LAT = {"D3Q19": X.D3Q19, "D3Q27": X.D3Q27}
+
+
+def _case(res, seed=3, B=1, wall_frac=0.05, shell=False):
+    rs = np.random.RandomState(seed)
+    flags = torch.ones((B, 1, *res), dtype=torch.uint8)
+    if wall_frac:
+        flags[torch.from_numpy(rs.uniform(size=(B, 1, *res)) < wall_frac)] = 2
+    if shell:
+        flags[:, :, 0] = 2; flags[:, :, -1] = 2
+        flags[:, :, :, 0] = 2; flags[:, :, :, -1] = 2
+    rho = torch.from_numpy(rs.uniform(0.2, 0.3, (B, 1, *res))).float()
+    vel = torch.from_numpy(rs.uniform(-0.05, 0.05, (B, 3, *res))).float()
+    force = torch.from_numpy(rs.uniform(-1e-4, 1e-4, (B, 3, *res))).float()
+    return flags, rho, vel, force
+
+
+def _solver(flags, lattice, forcing, streaming, force, tau=0.8, **kw):
+    from lbm_ferrofluid_b200.extensions import ExtSinglePhaseSolver
+    if force is not None and torch.is_tensor(force):
+        force = force.cuda()
+    return ExtSinglePhaseSolver(flags.cuda(), tau=tau, lattice=lattice, forcing=forcing, streaming=streaming,
+                                force=force if forcing else None, **kw)
+
+
+def test_d3q19_shift_ab_equals_the_pinned_single_phase_kernel():
+    from lbm_ferrofluid_b200.solver import SinglePhaseSolver
+    flags, rho, vel, force = _case((18, 22, 26))
+    a = SinglePhaseSolver(flags.cuda(), tau=0.8, force=force.cuda()).initialize(rho.cuda(), vel.cuda())
+    b = _solver(flags, "D3Q19", "shift", "ab", force).initialize(rho.cuda(), vel.cuda())
+    assert rel_l2(b.f, a.f) <= 1e-6          # the initial equilibrium is formed by two different routes
+    b.set_f(a.f)
+    a.step(6); b.step(6)
+    for k in ("f", "rho", "vel"):
+        assert rel_l2(getattr(b, k), getattr(a, k)) <= (2e-5 if k == "vel" else 1e-6), k   # vel: small difference of populations
+
+
+@pytest.mark.parametrize("lattice,collision", [("D3Q19", "bgk"), ("D3Q27", "bgk"), ("D3Q27", "kbc")])
+@pytest.mark.parametrize("forcing", [None, "shift", "guo"])
+def test_step_vs_fp64_oracle(lattice, collision, forcing):
+    lat = LAT[lattice]
+    flags, rho, vel, force = _case((14, 18, 21), seed=7, B=2)
+    tau, steps = 0.7, 6
+    s = _solver(flags, lattice, forcing, "ab", force, tau=tau, dx=0.5, dt=0.25, collision=collision)
+    s.initialize(rho.cuda(), vel.cuda())
+    f = s.f.cpu().double()
+    r, v, F = rho.double(), vel.double(), force.double()
+    for _ in range(steps):
+        f, r, v = X.ext_step(f, r, v, flags, F, 0.5, 0.25, tau, lat, forcing, collision)
+    s.step(steps)
+    # fp32 against the fp64 evaluation: the SURVEY 8(c) N = 10 bands (f, rho 5e-6; vel 2e-4).  KBC's stabiliser
+    # gamma is a ratio of two small sums, so its f band is the one the 2-D KBC goldens are held to (2e-5).
+    assert rel_l2(s.f, f) <= (2e-5 if collision == "kbc" else 5e-6)
+    assert rel_l2(s.rho, r) <= 5e-6
+    assert rel_l2(s.vel, v) <= 2e-4
+
+
+@pytest.mark.parametrize("lattice,collision", [("D3Q19", "bgk"), ("D3Q27", "bgk"), ("D3Q27", "kbc")])
+@pytest.mark.parametrize("forcing", [None, "shift", "guo"])
+@pytest.mark.parametrize("res", [(5, 6, 7), (16, 20, 33), (3, 40, 300)])
+def test_esoteric_pull_is_bit_identical_to_ab(lattice, collision, forcing, res):
+    flags, rho, vel, force = _case(res, seed=11, B=2, wall_frac=0.08, shell=res[0] > 4)
+    a = _solver(flags, lattice, forcing, "ab", force, collision=collision).initialize(rho.cuda(), vel.cuda())
+    b = _solver(flags, lattice, forcing, "esoteric", force, collision=collision).initialize(rho.cuda(), vel.cuda())
+    assert b.population_bytes * 2 == a.population_bytes
+    assert torch.equal(a.f, b.f)     # std -> esoteric -> std round trip
+    for n in (1, 1, 3, 2):           # both parities are visited and exported
+        a.step(n); b.step(n)
+        assert torch.equal(a.f, b.f), f"f after {a.steps_done} steps"
+        assert torch.equal(a.rho, b.rho) and torch.equal(a.vel, b.vel)
+
+
+@pytest.mark.parametrize("lattice", ["D3Q19", "D3Q27"])
+@pytest.mark.parametrize("parity", [0, 1])
+def test_esoteric_layout_matches_oracle(lattice, parity):
+    from lbm_ferrofluid_b200 import _host as H
+    lat = LAT[lattice]
+    f = torch.rand((2, lat.Q, 5, 6, 9))
+    out = torch.empty_like(f).cuda()
+    fc = f.cuda()
+    H.launch("lbmff_ext_esoteric_convert_" + lattice.lower(), fc.device, H.ptr(fc), H.ptr(out), parity, 1, 2, 5, 6, 9)
+    assert torch.equal(out.cpu(), X.esoteric_layout(f, lat, parity))
+    back = torch.empty_like(fc)
+    H.launch("lbmff_ext_esoteric_convert_" + lattice.lower(), fc.device, H.ptr(out), H.ptr(back), parity, 0, 2, 5, 6, 9)
+    assert torch.equal(back, fc)
+
+
+@pytest.mark.parametrize("lattice", ["D3Q19", "D3Q27"])
+@pytest.mark.parametrize("streaming", ["ab", "esoteric"])
+def test_guo_uniform_force_accelerates_a_periodic_box(lattice, streaming):
+    """All-FLUID periodic box at rest under a uniform body force: total mass constant, total momentum grows by
+    exactly F dt per cell per step, and the stored (physical) velocity is F (n - 1/2) dt / rho."""
+    res = (12, 10, 16)
+    flags = torch.ones((1, 1, *res), dtype=torch.uint8)
+    rho = torch.full((1, 1, *res), 0.25)
+    vel = torch.zeros((1, 3, *res))
+    Fu = (2e-5, -1e-5, 3e-5)
+    s = _solver(flags, lattice, "guo", streaming, Fu, tau=0.9).initialize(rho.cuda(), vel.cuda())
+    e = torch.tensor(LAT[lattice].e, dtype=torch.float64).cuda()
+    n = 40
+    s.step(n)
+    f = s.f.double()
+    ncell = res[0] * res[1] * res[2]
+    assert abs(f.sum().item() / (0.25 * ncell) - 1.0) < 3e-7 * n   # fp32 drift of the entropic feq, ~1.4e-7 per step
+    mom = torch.einsum("bqzyx,qa->a", f, e) / ncell
+    want = torch.tensor(Fu, dtype=torch.float64).cuda() * n
+    assert ((mom - want).abs() / want.abs()).max().item() < 2e-3
+    u = s.vel.double().mean(dim=(0, 2, 3, 4))
+    want_u = torch.tensor(Fu, dtype=torch.float64).cuda() * (n - 0.5) / 0.25
+    assert ((u - want_u).abs() / want_u.abs()).max().item() < 2e-3
+
+
+@pytest.mark.parametrize("collision", ["bgk", "kbc"])
+def test_d3q27_mass_conserved_with_walls(collision):
+    flags, rho, vel, force = _case((24, 20, 28), seed=5, wall_frac=0.1, shell=True)
+    s = _solver(flags, "D3Q27", "guo", "esoteric", force, collision=collision).initialize(rho.cuda(), vel.cuda())
+    m0 = s.f.double().sum().item()
+    s.step(51)
+    f = s.f
+    assert torch.isfinite(f).all()
+    assert abs(f.double().sum().item() / m0 - 1.0) < 3e-7 * 51
+
+
+def test_error_paths():
+    from lbm_ferrofluid_b200 import _host as H
+    from lbm_ferrofluid_b200.extensions import ExtSinglePhaseSolver
+    flags = torch.ones((1, 1, 4, 4, 4), dtype=torch.uint8)
+    with pytest.raises(RuntimeError):
+        ExtSinglePhaseSolver(flags, tau=0.8)                               # CPU tensor: no CPU fallback
+    with pytest.raises(ValueError):
+        ExtSinglePhaseSolver(flags.cuda(), tau=0.8, lattice="D3Q15")
+    with pytest.raises(ValueError):
+        ExtSinglePhaseSolver(flags.cuda(), tau=0.8, forcing="guo")        # no force given
+    with pytest.raises(ValueError):
+        ExtSinglePhaseSolver(flags.cuda(), tau=0.8, lattice="D3Q19", collision="kbc")
+    with pytest.raises(RuntimeError):
+        ExtSinglePhaseSolver(torch.ones((1, 1, 4, 4), dtype=torch.uint8).cuda(), tau=0.8)   # 2-D
+    s = ExtSinglePhaseSolver(flags.cuda(), tau=0.8, lattice="D3Q19")
+    f = s._f[0]
+    args = (H.ptr(s.flags), H.ptr(None), H.ptr(None), H.ptr(s.rho), H.ptr(s.vel))
+    with pytest.raises(RuntimeError, match="f_in != f_out"):
+        H.launch("lbmff_ext_stream_collide_d3q19", f.device, H.ptr(f), H.ptr(f), *args, 0.8, 0, 0, 0, 0, 1.0, 1.0, 1, 4, 4, 4)
+    with pytest.raises(RuntimeError, match="in place"):
+        H.launch("lbmff_ext_stream_collide_d3q19", f.device, H.ptr(f), H.ptr(s._f[1]), *args, 0.8, 0, 0, 1, 0, 1.0, 1.0, 1, 4, 4, 4)
+    with pytest.raises(RuntimeError, match="D3Q27"):
+        H.launch("lbmff_ext_stream_collide_d3q19", f.device, H.ptr(f), H.ptr(s._f[1]), *args, 0.8, 1, 0, 0, 0, 1.0, 1.0, 1, 4, 4, 4)
+    with pytest.raises(RuntimeError, match="without a force"):
+        H.launch("lbmff_ext_stream_collide_d3q19", f.device, H.ptr(f), H.ptr(s._f[1]), *args, 0.8, 0, 2, 0, 0, 1.0, 1.0, 1, 4, 4, 4)
