@@ -395,6 +395,11 @@ int lbmff_soft_rasterize_forward(const float* face_vertices, const float* textur
  *             (to_esoteric = 1: standard -> layout expected by a step of that parity; 0: back), out of place.
  * rho, vel are updated IN PLACE on non-OBSTACLE cells. */
 int lbmff_ext_lattice_info(int Q, int* e_out, int* opp_out, double* w_out);
+/* Shan-Chen interaction force on D3Q19: lbmff_sc_force_d2q9 (LBM_collision_SC_2d.py:22-97: C-S pseudopotential,
+ * G = -1/3, wall psi from the mean density, zero outside the array, force on FLUID cells) with the D3Q19
+ * weights; the reference's Shan-Chen model is 2-D only.  force_out: [B][3][D][H][W]. */
+int lbmff_sc_force_d3q19(const float* density, const uint8_t* flags, double density_liquid, double density_gas,
+                         double dx, double dt, float* force_out, int B, int D, int H, int W, lbmff_stream_t stream);
 int lbmff_ext_stream_collide_d3q19(const float* f_in, float* f_out, const uint8_t* flags, const float* force,
                                    const double* force_uniform, float* rho, float* vel, double tau, int collision,
                                    int forcing, int streaming, int parity, double dx, double dt, int B, int D, int H,

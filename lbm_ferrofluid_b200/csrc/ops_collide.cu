@@ -78,36 +78,41 @@ __device__ __forceinline__ float sc_psi(float d, const ScConsts& S) {
   const float v = S.RT * (1.0f + (4.0f * t - 2.0f * t * t) / (om * om * om)) - S.a * d - S.cs2;
   return sqrtf(2.0f * d * v / S.G1 / S.cs2);
 }
+template <int DIM>
 __global__ void __launch_bounds__(kThreads) k_sc_force(const float* __restrict__ density,
                                                        const uint8_t* __restrict__ flags, float* __restrict__ out,
                                                        ScConsts S, Grid g) {
-  using L = Lat<2>;
+  // DIM = 3 (D3Q19) is the SURVEY 8f N4 extension: the reference's Shan-Chen model is 2-D only
+  using L = Lat<DIM>;
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= g.N) return;
   const long long b = blockIdx.y;
   const float* d = density + b * g.N;
   const uint8_t* fl = flags + b * g.N;
-  float fx = 0.f, fy = 0.f;
+  float fv[DIM];
+#pragma unroll
+  for (int a = 0; a < DIM; ++a) fv[a] = 0.f;
   if (fl[i] == LBMFF_FLUID) {
     const Cell c = cell_of(i, g);
     const float psx = sc_psi(d[i], S);
-    float sx = 0.f, sy = 0.f;
+    float sv[3] = {0.f, 0.f, 0.f};
 #pragma unroll
-    for (int q = 1; q < 9; ++q) {
-      const int x = c.x + L::ex(q), y = c.y + L::ey(q);
+    for (int q = 1; q < L::Q; ++q) {
+      const int x = c.x + L::ex(q), y = c.y + L::ey(q), z = c.z + L::ez(q);
       float nb = 0.0f;  // zero padding outside the array (:62-67)
-      if (x >= 0 && x < g.W && y >= 0 && y < g.H) {
-        const long long j = lin(g, x, y, 0);
+      if (x >= 0 && x < g.W && y >= 0 && y < g.H && z >= 0 && z < g.D) {
+        const long long j = lin(g, x, y, z);
         nb = fl[j] == LBMFF_OBSTACLE ? S.psx_wall : sc_psi(d[j], S);
       }
-      sx += (L::w(q) * (float)L::ex(q)) * nb;
-      sy += (L::w(q) * (float)L::ey(q)) * nb;
+      if (L::ex(q) != 0) sv[0] += (L::w(q) * (float)L::ex(q)) * nb;
+      if (L::ey(q) != 0) sv[1] += (L::w(q) * (float)L::ey(q)) * nb;
+      if (DIM == 3 && L::ez(q) != 0) sv[2] += (L::w(q) * (float)L::ez(q)) * nb;
     }
-    fx = S.negG1 * psx * S.c * sx;
-    fy = S.negG1 * psx * S.c * sy;
+#pragma unroll
+    for (int a = 0; a < DIM; ++a) fv[a] = S.negG1 * psx * S.c * sv[a];
   }
-  out[(b * 2 + 0) * g.N + i] = fx;
-  out[(b * 2 + 1) * g.N + i] = fy;
+#pragma unroll
+  for (int a = 0; a < DIM; ++a) out[(b * DIM + a) * g.N + i] = fv[a];
 }
 
 // ---- a15 HCZ collision on FLUID cells
@@ -199,10 +204,7 @@ int lbmff_collision_kbc_d2q9(const float* f, const float* rho, const float* vel,
   return check_launch(__func__);
 }
 
-int lbmff_sc_force_d2q9(const float* density, const uint8_t* flags, double density_liquid, double density_gas,
-                        double dx, double dt, float* force_out, int B, int H, int W, lbmff_stream_t stream) {
-  LBMFF_REQUIRE(density && flags && force_out, "null pointer");
-  GRID_ARGS(B, 1, H, W);
+static ScConsts make_sc(double density_liquid, double density_gas, double dx, double dt) {
   const double c = dx / dt, cs2 = c * c / 3.0, RT = cs2, a = 12.0 * cs2, bb = 4.0, G1 = -1.0 / 3.0;
   const double dw = 0.5 * (density_gas + density_liquid);
   double pw = dw * bb / 4.0;
@@ -211,7 +213,21 @@ int lbmff_sc_force_d2q9(const float* density, const uint8_t* flags, double densi
   ScConsts S;
   S.RT = (float)RT; S.a = (float)a; S.cs2 = (float)cs2; S.G1 = (float)G1; S.negG1 = (float)(-G1); S.c = (float)c;
   S.psx_wall = (float)pw;
-  k_sc_force<<<grid, kThreads, 0, st>>>(density, flags, force_out, S, g);
+  return S;
+}
+
+int lbmff_sc_force_d2q9(const float* density, const uint8_t* flags, double density_liquid, double density_gas,
+                        double dx, double dt, float* force_out, int B, int H, int W, lbmff_stream_t stream) {
+  LBMFF_REQUIRE(density && flags && force_out, "null pointer");
+  GRID_ARGS(B, 1, H, W);
+  k_sc_force<2><<<grid, kThreads, 0, st>>>(density, flags, force_out, make_sc(density_liquid, density_gas, dx, dt), g);
+  return check_launch(__func__);
+}
+int lbmff_sc_force_d3q19(const float* density, const uint8_t* flags, double density_liquid, double density_gas,
+                         double dx, double dt, float* force_out, int B, int D, int H, int W, lbmff_stream_t stream) {
+  LBMFF_REQUIRE(density && flags && force_out, "null pointer");
+  GRID_ARGS(B, D, H, W);
+  k_sc_force<3><<<grid, kThreads, 0, st>>>(density, flags, force_out, make_sc(density_liquid, density_gas, dx, dt), g);
   return check_launch(__func__);
 }
 

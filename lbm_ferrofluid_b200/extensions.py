@@ -173,3 +173,33 @@ def _feq_torch(rho: torch.Tensor, vel: torch.Tensor, lattice: str, dx: float, dt
                 v = v / ratio[:, a:a + 1]
         out[:, q:q + 1] = rho * float(torch.tensor(w[q], dtype=torch.float32)) * v
     return out
+
+
+from .collision import LBMCollision3d  # noqa: E402
+
+
+class LBMCollisionSC3d(LBMCollision3d):
+    """Shan-Chen pseudopotential multiphase on D3Q19: ``LBMCollisionSC2d`` (LBM_collision_SC_2d.py) carried to
+    3-D with the same method names and argument meaning.  The reference's Shan-Chen model is 2-D only and its
+    factory returns ``None`` in 3-D (simulation_runner.py ``create_collision_SC``); this class is constructed
+    directly, the factory keeps the reference behaviour."""
+
+    def __init__(self, *args, **kwargs):
+        super().__init__(*args, **kwargs)
+        self._density_wall = 0.5 * (self._density_gas + self._density_liquid)
+
+    def calculate_force(self, dx, dt, density, flags, force=None) -> torch.Tensor:
+        d = H.need_cuda(density, "density")
+        flags = H.need_cuda(flags, "flags", torch.uint8)
+        dim, B, C, D, Hh, W = H.dims(d)
+        if dim != 3:
+            raise RuntimeError("LBMCollisionSC3d needs [B, 1, D, H, W] tensors")
+        out = torch.empty((B, 3, D, Hh, W), dtype=d.dtype, device=d.device)
+        H.launch("lbmff_sc_force_d3q19", d.device, H.ptr(d), H.ptr(flags), float(self._density_liquid),
+                 float(self._density_gas), float(dx), float(dt), H.ptr(out), B, D, Hh, W)
+        return out
+
+    def collision(self, dx, dt, f, rho, density, vel, flags, force=None, KBC_type: int = None):
+        """SC force then BGK, like LBM_collision_SC_2d.py:99-137."""
+        force = self.calculate_force(dx=dx, dt=dt, density=density, flags=flags, force=force)
+        return self._bgk(dx, dt, f, rho, vel, flags, force)

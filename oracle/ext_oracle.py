@@ -140,3 +140,36 @@ def esoteric_layout(f_std, lat, parity):
             out[:, o] = f_std[:, o]
             out[:, p] = moved
     return out
+
+
+def sc_force_3d(dx, dt, density, flags, density_liquid, density_gas):
+    """lbm_oracle.sc_force (LBM_collision_SC_2d.py:22-97) with the D3Q19 lattice and a 3-D zero pad."""
+    import math
+    import torch.nn.functional as F
+    lat = D3Q19
+    c = dx / dt
+    cs2 = c * c / 3.0
+    RT, a, b, G1 = cs2, 12.0 * cs2, 4.0, -1.0 / 3.0
+
+    def psi_of(d, sqrt, power):
+        t = d * b / 4.0
+        v = RT * (1.0 + (4.0 * t - 2.0 * t * t) / power(1.0 - t, 3)) - a * d - cs2
+        return sqrt(2.0 * d * v / G1 / cs2)
+
+    psx = psi_of(density, torch.sqrt, torch.pow)
+    wall = psi_of(0.5 * (density_gas + density_liquid), math.sqrt, math.pow)
+    pad = F.pad(torch.where(flags == O.OBSTACLE, wall * torch.ones_like(psx), psx), pad=(1, 1, 1, 1, 1, 1))
+    w = O._wt(lat, density)
+    D, Hh, W = density.shape[2:]
+    comps = []
+    for ax in range(3):
+        acc = torch.zeros_like(psx)
+        for q in range(1, lat.Q):
+            ex, ey, ez = lat.e[q]
+            if lat.e[q][ax] == 0:
+                continue
+            nb = pad[..., 1 + ez:1 + ez + D, 1 + ey:1 + ey + Hh, 1 + ex:1 + ex + W]
+            acc = acc + w[:, q:q + 1] * lat.e[q][ax] * nb
+        comps.append(acc)
+    force = -G1 * psx * c * torch.cat(comps, dim=1)
+    return torch.where(flags == O.FLUID, force, torch.zeros_like(force))

@@ -162,3 +162,19 @@ def test_kbc3_step_runs_and_conserves():
         f, rho, vel = X.ext_step(f, rho, vel, flags, force, 1.0, 1.0, 0.55, lat, None, "kbc")
     assert torch.isfinite(f).all()
     assert abs(f.sum().item() / m0 - 1.0) < 1e-7
+
+
+def test_sc_force_3d_reduces_to_the_pinned_2d_force():
+    """A field that does not vary along z: the x, y components of the D3Q19 force equal the pinned D2Q9 force
+    (the in-plane D3Q19 weights, summed over the z neighbours, are the D2Q9 weights) and F_z vanishes."""
+    g = torch.Generator().manual_seed(4)
+    d2 = 0.05 + 0.2 * torch.rand((1, 1, 9, 11), generator=g, dtype=torch.float64)
+    fl2 = torch.ones((1, 1, 9, 11), dtype=torch.uint8)
+    fl2[:, :, 3:5, 4:7] = O.OBSTACLE
+    F2 = O.sc_force(1.0, 1.0, d2, fl2, 0.265, 0.038)
+    d3 = d2.unsqueeze(2).repeat(1, 1, 7, 1, 1)
+    fl3 = fl2.unsqueeze(2).repeat(1, 1, 7, 1, 1)
+    F3 = X.sc_force_3d(1.0, 1.0, d3, fl3, 0.265, 0.038)
+    mid = F3[:, :, 3]                                     # away from the zero-padded z ends
+    assert (mid[:, :2] - F2).abs().max().item() < 1e-7   # fp32-rounded weights
+    assert mid[:, 2].abs().max().item() < 1e-12

@@ -166,3 +166,26 @@ def test_error_paths():
         H.launch("lbmff_ext_stream_collide_d3q19", f.device, H.ptr(f), H.ptr(s._f[1]), *args, 0.8, 1, 0, 0, 0, 1.0, 1.0, 1, 4, 4, 4)
     with pytest.raises(RuntimeError, match="without a force"):
         H.launch("lbmff_ext_stream_collide_d3q19", f.device, H.ptr(f), H.ptr(s._f[1]), *args, 0.8, 0, 2, 0, 0, 1.0, 1.0, 1, 4, 4, 4)
+
+
+def test_shan_chen_3d_force_and_collision_vs_oracle():
+    from lbm_ferrofluid_b200.extensions import LBMCollisionSC3d
+    rs = np.random.RandomState(9)
+    res = (10, 13, 17)
+    density = torch.from_numpy(rs.uniform(0.04, 0.27, (2, 1, *res))).float()
+    flags = torch.ones((2, 1, *res), dtype=torch.uint8)
+    flags[torch.from_numpy(rs.uniform(size=(2, 1, *res)) < 0.1)] = 2
+    flags[:, :, :, 0] = 2
+    col = LBMCollisionSC3d(tau=0.9, density_liquid=0.265, density_gas=0.038, device=torch.device("cuda"))
+    for dx, dt in ((1.0, 1.0), (0.5, 0.25)):
+        F = col.calculate_force(dx=dx, dt=dt, density=density.cuda(), flags=flags.cuda(), force=None)
+        want = X.sc_force_3d(dx, dt, density.double(), flags, 0.265, 0.038)
+        assert (F.cpu().double() - want).abs().max().item() <= 2e-6 * want.abs().max().item()
+        assert (F.cpu()[(flags != 1).expand(-1, 3, -1, -1, -1)] == 0).all()
+    vel = torch.from_numpy(rs.uniform(-0.03, 0.03, (2, 3, *res))).float()
+    f = O.get_feq(1.0, 1.0, density, vel, None, 1.0)
+    out = col.collision(dx=1.0, dt=1.0, f=f.cuda(), rho=density.cuda(), density=density.cuda(), vel=vel.cuda(),
+                        flags=flags.cuda(), force=None)
+    want = O.collision_bgk(1.0, 1.0, f.double(), density.double(), vel.double(), flags,
+                           X.sc_force_3d(1.0, 1.0, density.double(), flags, 0.265, 0.038), 0.9)
+    assert rel_l2(out, want) <= 2e-6

@@ -135,7 +135,7 @@ def cg(res, steps=6, tol=1e-4):
     print(f"30-sweep scalar step: {ms30:.2f} ms", flush=True)
 
 
-def ext(res, steps=20):
+def ext(res, steps=20, reps=3):
     """single-phase BGK on D3Q19 / D3Q27, forcing none / Guo, A/B pull vs esoteric pull in place."""
     from lbm_ferrofluid_b200.extensions import ExtSinglePhaseSolver
     from lbm_ferrofluid_b200.solver import SinglePhaseSolver
@@ -148,7 +148,7 @@ def ext(res, steps=20):
     vel = torch.zeros((1, 3, D, Hh, W), device=dev)
     vel[:, 0] = 0.05
     s = SinglePhaseSolver(flags, tau=0.8).initialize(rho, vel)
-    ms = timed(lambda: s.step(steps), reps=3) / steps
+    ms = timed(lambda: s.step(steps), reps=reps) / steps
     print(f"pinned D3Q19 BGK A/B {res}: {ms:.4f} ms/step {N / ms / 1e3:.0f} MLUPS {152 * N / ms / 1e6:.0f} GB/s", flush=True)
     del s
     for lattice, Q in (("D3Q19", 19), ("D3Q27", 27)):
@@ -156,7 +156,7 @@ def ext(res, steps=20):
             for streaming in ("ab", "esoteric"):
                 s = ExtSinglePhaseSolver(flags, tau=0.8, lattice=lattice, forcing=forcing, streaming=streaming,
                                          force=(1e-6, 0.0, 0.0) if forcing else None).initialize(rho, vel)
-                ms = timed(lambda: s.step(steps), reps=3) / steps
+                ms = timed(lambda: s.step(steps), reps=reps) / steps
                 print(f"ext {lattice} forcing={forcing} {streaming} {res}: {ms:.4f} ms/step {N / ms / 1e3:.0f} MLUPS "
                       f"{8 * Q * N / ms / 1e6:.0f} GB/s pop_bytes={s.population_bytes / 1e9:.2f} GB "
                       f"finite={bool(torch.isfinite(s.rho).all())}", flush=True)
@@ -165,7 +165,7 @@ def ext(res, steps=20):
     vel = vel + 0.01 * torch.rand_like(vel)      # KBC needs a non-equilibrium state to have work to do
     for streaming in ("ab", "esoteric"):
         s = ExtSinglePhaseSolver(flags, tau=0.51, lattice="D3Q27", collision="kbc", streaming=streaming).initialize(rho, vel)
-        ms = timed(lambda: s.step(steps), reps=3) / steps
+        ms = timed(lambda: s.step(steps), reps=reps) / steps
         print(f"ext D3Q27 KBC {streaming} {res}: {ms:.4f} ms/step {N / ms / 1e3:.0f} MLUPS {8 * 27 * N / ms / 1e6:.0f} GB/s "
               f"finite={bool(torch.isfinite(s.rho).all())}", flush=True)
         del s
@@ -203,7 +203,7 @@ if __name__ == "__main__":
     if sys.argv[1] == "render":
         render(int(sys.argv[2]), int(sys.argv[3]) if len(sys.argv) > 3 else 256)
     if sys.argv[1] == "ext":
-        ext(tuple(int(v) for v in sys.argv[2:5]))
+        ext(tuple(int(v) for v in sys.argv[2:5]), *( [int(sys.argv[5]), 1] if len(sys.argv) > 5 else []))
     if sys.argv[1] == "cg":
         cg(tuple(int(v) for v in sys.argv[2:5]), tol=float(sys.argv[5]) if len(sys.argv) > 5 else 1e-4)
     if sys.argv[1] == "single2d":
