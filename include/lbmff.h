@@ -413,6 +413,28 @@ int lbmff_ext_esoteric_convert_d3q19(const float* src, float* dst, int parity, i
 int lbmff_ext_esoteric_convert_d3q27(const float* src, float* dst, int parity, int to_esoteric, int B, int D, int H,
                                      int W, lbmff_stream_t stream);
 
+/* Mixed-precision population storage: the same step (BGK only) with populations STORED as fp16 and all arithmetic
+ * in fp32.  The buffers hold the shifted populations f_q - w_q rho0 (rho0: a reference density near the mean), so
+ * the 10-bit mantissa is spent on the part of f that carries the flow; bytes per cell update halve.
+ * f_in / f_out: [B][Q][D][H][W] fp16.  pack / unpack translate from / to the standard fp32 populations;
+ * layout 0 = standard slots (A/B pull), 1 / 2 = esoteric pull before an even / odd step. */
+int lbmff_ext_stream_collide_fp16_d3q19(const void* f_in, void* f_out, const uint8_t* flags, const float* force,
+                                        const double* force_uniform, float* rho, float* vel, double tau,
+                                        int forcing, int streaming, int parity, double rho0, double dx, double dt,
+                                        int B, int D, int H, int W, lbmff_stream_t stream);
+int lbmff_ext_stream_collide_fp16_d3q27(const void* f_in, void* f_out, const uint8_t* flags, const float* force,
+                                        const double* force_uniform, float* rho, float* vel, double tau,
+                                        int forcing, int streaming, int parity, double rho0, double dx, double dt,
+                                        int B, int D, int H, int W, lbmff_stream_t stream);
+int lbmff_ext_pack_fp16_d3q19(const float* f_std, void* f_packed, int layout, double rho0, int B, int D, int H, int W,
+                              lbmff_stream_t stream);
+int lbmff_ext_pack_fp16_d3q27(const float* f_std, void* f_packed, int layout, double rho0, int B, int D, int H, int W,
+                              lbmff_stream_t stream);
+int lbmff_ext_unpack_fp16_d3q19(const void* f_packed, float* f_std, int layout, double rho0, int B, int D, int H, int W,
+                                lbmff_stream_t stream);
+int lbmff_ext_unpack_fp16_d3q27(const void* f_packed, float* f_std, int layout, double rho0, int B, int D, int H, int W,
+                                lbmff_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

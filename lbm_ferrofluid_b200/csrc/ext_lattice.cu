@@ -14,6 +14,8 @@
 //
 // Layout: the reference's SoA [q][z][y][x] fp32.  D3Q27 keeps the reference's D3Q19 order for q < 19
 // (LBM_collision_3d.py:76-103) and appends the eight corners as opposite pairs.
+#include <cuda_fp16.h>
+
 #include "capi.cuh"
 #include "physics.cuh"
 
@@ -122,12 +124,38 @@ __device__ __forceinline__ void kbc3_relax(const float* fv, const float* fe, flo
   }
 }
 
-// in-place buffers are read and rewritten by the same kernel: a plain (coherent) load, still not mergeable
-__device__ __forceinline__ float ld_plain(const float* p) {
-  float v;
-  asm volatile("ld.global.f32 %0, [%1];" : "=f"(v) : "l"(p));
-  return v;
-}
+// Population storage.  float: the reference's fp32 populations.  __half: fp16 STORAGE with fp32 arithmetic
+// (SURVEY 8f N4 "mixed-precision population storage"): what is stored is the deviation f_q - w_q rho0 from the
+// rest equilibrium of a reference density rho0 (the shifted-DDF form of Lehmann et al. 2022), which keeps the
+// 10-bit mantissa on the part of f that carries the flow; bytes per cell update halve.
+// ld_nc: read-only path, issued ahead of the flag test (A/B pull).  ld: plain coherent load for the in-place
+// esoteric buffers, which the same kernel rewrites.  Both volatile so they are not merged or dropped.
+template <class ST>
+struct Pop;
+template <>
+struct Pop<float> {
+  __device__ static __forceinline__ float ld_nc(const float* p, float) { return ld_spec(p); }
+  __device__ static __forceinline__ float ld(const float* p, float) {
+    float v;
+    asm volatile("ld.global.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+  }
+  __device__ static __forceinline__ void st(float* p, float v, float) { *p = v; }
+};
+template <>
+struct Pop<__half> {
+  __device__ static __forceinline__ float ld_nc(const __half* p, float shift) {
+    unsigned short r;
+    asm volatile("ld.global.nc.u16 %0, [%1];" : "=h"(r) : "l"(p));
+    return __half2float(__ushort_as_half(r)) + shift;
+  }
+  __device__ static __forceinline__ float ld(const __half* p, float shift) {
+    unsigned short r;
+    asm volatile("ld.global.u16 %0, [%1];" : "=h"(r) : "l"(p));
+    return __half2float(__ushort_as_half(r)) + shift;
+  }
+  __device__ static __forceinline__ void st(__half* p, float v, float shift) { *p = __float2half_rn(v - shift); }
+};
 
 enum { FORCE_NONE = 0, FORCE_SHIFT = 1, FORCE_GUO = 2 };
 enum { STREAM_AB = 0, STREAM_EP_EVEN = 1, STREAM_EP_ODD = 2 };
@@ -139,6 +167,7 @@ struct ExtForce {
   float half_dt;
   float inv_c;
   float beta, inv_beta, two_m;  // KBC: 1/(2 tau), 2 tau, 2 - 2 tau
+  float rho0;                   // fp16 storage: reference density of the shifted populations
 };
 
 // Esoteric-pull addressing (Lehmann 2022).  For each opposite pair (p, o = opp(p)), p < o, a cell owns two
@@ -149,8 +178,8 @@ struct ExtForce {
 //   odd step:  load  f_p <- slot p @ x        f_o <- slot o @ x+e_p
 //              store f_p -> slot o @ x+e_p    f_o -> slot p @ x
 // (loaded values are the populations ARRIVING at x, stored ones are post-collision.)
-template <class LT, int COLL, int FORCING, int STREAM, bool IDX32>
-__global__ void __launch_bounds__(kThreads) k_ext_stream_collide(const float* fi, float* fo,
+template <class LT, class ST, int COLL, int FORCING, int STREAM, bool IDX32>
+__global__ void __launch_bounds__(kThreads) k_ext_stream_collide(const ST* fi, ST* fo,
                                                                  const uint8_t* __restrict__ flags,
                                                                  const float* __restrict__ force,
                                                                  float* __restrict__ rho_, float* __restrict__ vel,
@@ -164,20 +193,20 @@ __global__ void __launch_bounds__(kThreads) k_ext_stream_collide(const float* fi
   float fv[Q];
   if constexpr (STREAM == STREAM_AB) {
 #pragma unroll
-    for (int q = 0; q < Q; ++q) fv[q] = ld_spec(fi + at(q, i + nbr_delta<LT>(nb, q, 1)));
+    for (int q = 0; q < Q; ++q) fv[q] = Pop<ST>::ld_nc(fi + at(q, i + nbr_delta<LT>(nb, q, 1)), LT::w(q) * XF.rho0);
   } else {
-    fv[0] = ld_plain(fi + at(0, i));
+    fv[0] = Pop<ST>::ld(fi + at(0, i), LT::w(0) * XF.rho0);
 #pragma unroll
     for (int p = 1; p < Q; ++p) {
       const int o = LT::opp(p);
       if (p > o) continue;
       const int j = i + nbr_delta<LT>(nb, p, -1);
       if constexpr (STREAM == STREAM_EP_EVEN) {
-        fv[p] = ld_plain(fi + at(o, i));
-        fv[o] = ld_plain(fi + at(p, j));
+        fv[p] = Pop<ST>::ld(fi + at(o, i), LT::w(p) * XF.rho0);
+        fv[o] = Pop<ST>::ld(fi + at(p, j), LT::w(o) * XF.rho0);
       } else {
-        fv[p] = ld_plain(fi + at(p, i));
-        fv[o] = ld_plain(fi + at(o, j));
+        fv[p] = Pop<ST>::ld(fi + at(p, i), LT::w(p) * XF.rho0);
+        fv[o] = Pop<ST>::ld(fi + at(o, j), LT::w(o) * XF.rho0);
       }
     }
   }
@@ -249,96 +278,100 @@ __global__ void __launch_bounds__(kThreads) k_ext_stream_collide(const float* fi
   }
   if constexpr (STREAM == STREAM_AB) {
 #pragma unroll
-    for (int q = 0; q < Q; ++q) fo[at(q, i)] = out[q];
+    for (int q = 0; q < Q; ++q) Pop<ST>::st(fo + at(q, i), out[q], LT::w(q) * XF.rho0);
   } else {
-    fo[at(0, i)] = out[0];
+    Pop<ST>::st(fo + at(0, i), out[0], LT::w(0) * XF.rho0);
 #pragma unroll
     for (int p = 1; p < Q; ++p) {
       const int o = LT::opp(p);
       if (p > o) continue;
       const int j = i + nbr_delta<LT>(nb, p, -1);
       if constexpr (STREAM == STREAM_EP_EVEN) {
-        fo[at(p, j)] = out[p];
-        fo[at(o, i)] = out[o];
+        Pop<ST>::st(fo + at(p, j), out[p], LT::w(p) * XF.rho0);
+        Pop<ST>::st(fo + at(o, i), out[o], LT::w(o) * XF.rho0);
       } else {
-        fo[at(o, j)] = out[p];
-        fo[at(p, i)] = out[o];
+        Pop<ST>::st(fo + at(o, j), out[p], LT::w(p) * XF.rho0);
+        Pop<ST>::st(fo + at(p, i), out[o], LT::w(o) * XF.rho0);
       }
     }
   }
 }
 
-// Conversion between the state every other solver of this library carries (post-collision population q
-// stored at its own cell: "standard") and the esoteric-pull slot layout BEFORE the load of a step of the
-// given parity.  to_ep: std -> ep, else ep -> std.  Out of place.
-//   parity 0: slot p @ x = f_o(x),  slot o @ x+e_p = f_p(x)
-//   parity 1: slot o @ x = f_o(x),  slot p @ x+e_p = f_p(x)
-template <class LT, bool IDX32>
-__global__ void __launch_bounds__(kThreads) k_ext_ep_convert(const float* __restrict__ src, float* __restrict__ dst,
-                                                             int parity, int to_ep, Grid g) {
+// Conversion between the state every other solver of this library carries (fp32, post-collision population q
+// stored at its own cell: "standard") and a packed buffer of storage type ST in one of three layouts:
+//   layout 0: standard slots (A/B pull)
+//   layout 1: esoteric pull before an even step:  slot p @ x = f_o(x),  slot o @ x+e_p = f_p(x)
+//   layout 2: esoteric pull before an odd step:   slot o @ x = f_o(x),  slot p @ x+e_p = f_p(x)
+// to_packed: std -> packed, else packed -> std.  Out of place.  fp16 storage holds f_q - w_q rho0.
+template <class LT, class ST, bool IDX32>
+__global__ void __launch_bounds__(kThreads) k_ext_pack(const float* __restrict__ fstd_in, float* __restrict__ fstd_out,
+                                                       const ST* __restrict__ pk_in, ST* __restrict__ pk_out,
+                                                       int layout, int to_packed, float rho0, Grid g) {
   constexpr int Q = LT::Q;
   const PlaneCell c = plane_cell(g);
   if (!c.live) return;
   const int i = c.i;
   const Nbr nb(c, g);
   const PopIndex<IDX32> at(g);
-  dst[at(0, i)] = src[at(0, i)];
 #pragma unroll
-  for (int p = 1; p < Q; ++p) {
+  for (int p = 0; p < Q; ++p) {
     const int o = LT::opp(p);
     if (p > o) continue;
     const int j = i + nbr_delta<LT>(nb, p, -1);
-    const int slot_self = parity ? o : p;   // holds f_o(x) at x
-    const int slot_nbr = parity ? p : o;    // holds f_p(x) at x + e_p
-    if (to_ep) {
-      dst[at(slot_self, i)] = src[at(o, i)];
-      dst[at(slot_nbr, j)] = src[at(p, i)];
+    // (slot, cell) holding f_o(x) and f_p(x)
+    const int so = layout == 0 ? o : (layout == 1 ? p : o), co = i;
+    const int sp = layout == 0 ? p : (layout == 1 ? o : p), cp = layout == 0 ? i : j;
+    const float wo = LT::w(o) * rho0, wp = LT::w(p) * rho0;
+    if (to_packed) {
+      Pop<ST>::st(pk_out + at(so, co), fstd_in[at(o, i)], wo);
+      if (p != 0) Pop<ST>::st(pk_out + at(sp, cp), fstd_in[at(p, i)], wp);
     } else {
-      dst[at(o, i)] = src[at(slot_self, i)];
-      dst[at(p, i)] = src[at(slot_nbr, j)];
+      fstd_out[at(o, i)] = Pop<ST>::ld(pk_in + at(so, co), wo);
+      if (p != 0) fstd_out[at(p, i)] = Pop<ST>::ld(pk_in + at(sp, cp), wp);
     }
   }
 }
 
-template <class LT, int COLL, int FORCING, int STREAM>
-static void launch_sc(const PlaneLaunch& pl, bool ix, cudaStream_t st, const float* fi, float* fo,
+template <class LT, class ST, int COLL, int FORCING, int STREAM>
+static void launch_sc(const PlaneLaunch& pl, bool ix, cudaStream_t st, const ST* fi, ST* fo,
                       const uint8_t* flags, const float* force, float* rho, float* vel, const Consts& k,
                       const ExtForce& XF, const Grid& g) {
-  if (ix) k_ext_stream_collide<LT, COLL, FORCING, STREAM, true><<<pl.grid, pl.block, 0, st>>>(fi, fo, flags, force, rho, vel, k, XF, g);
-  else k_ext_stream_collide<LT, COLL, FORCING, STREAM, false><<<pl.grid, pl.block, 0, st>>>(fi, fo, flags, force, rho, vel, k, XF, g);
+  if (ix) k_ext_stream_collide<LT, ST, COLL, FORCING, STREAM, true><<<pl.grid, pl.block, 0, st>>>(fi, fo, flags, force, rho, vel, k, XF, g);
+  else k_ext_stream_collide<LT, ST, COLL, FORCING, STREAM, false><<<pl.grid, pl.block, 0, st>>>(fi, fo, flags, force, rho, vel, k, XF, g);
 }
 
-template <class LT, int COLL, int FORCING>
-static void launch_sc_stream(int stream_mode, const PlaneLaunch& pl, bool ix, cudaStream_t st, const float* fi,
-                             float* fo, const uint8_t* flags, const float* force, float* rho, float* vel,
+template <class LT, class ST, int COLL, int FORCING>
+static void launch_sc_stream(int stream_mode, const PlaneLaunch& pl, bool ix, cudaStream_t st, const ST* fi,
+                             ST* fo, const uint8_t* flags, const float* force, float* rho, float* vel,
                              const Consts& k, const ExtForce& XF, const Grid& g) {
-  if (stream_mode == STREAM_AB) launch_sc<LT, COLL, FORCING, STREAM_AB>(pl, ix, st, fi, fo, flags, force, rho, vel, k, XF, g);
-  else if (stream_mode == STREAM_EP_EVEN) launch_sc<LT, COLL, FORCING, STREAM_EP_EVEN>(pl, ix, st, fi, fo, flags, force, rho, vel, k, XF, g);
-  else launch_sc<LT, COLL, FORCING, STREAM_EP_ODD>(pl, ix, st, fi, fo, flags, force, rho, vel, k, XF, g);
+  if (stream_mode == STREAM_AB) launch_sc<LT, ST, COLL, FORCING, STREAM_AB>(pl, ix, st, fi, fo, flags, force, rho, vel, k, XF, g);
+  else if (stream_mode == STREAM_EP_EVEN) launch_sc<LT, ST, COLL, FORCING, STREAM_EP_EVEN>(pl, ix, st, fi, fo, flags, force, rho, vel, k, XF, g);
+  else launch_sc<LT, ST, COLL, FORCING, STREAM_EP_ODD>(pl, ix, st, fi, fo, flags, force, rho, vel, k, XF, g);
 }
 
-template <class LT, int COLL>
+template <class LT, class ST, int COLL>
 static void launch_sc_force(int forcing, int stream_mode, const PlaneLaunch& pl, bool ix, cudaStream_t st,
-                            const float* fi, float* fo, const uint8_t* flags, const float* force, float* rho,
+                            const ST* fi, ST* fo, const uint8_t* flags, const float* force, float* rho,
                             float* vel, const Consts& k, const ExtForce& XF, const Grid& g) {
-  if (forcing == FORCE_NONE) launch_sc_stream<LT, COLL, FORCE_NONE>(stream_mode, pl, ix, st, fi, fo, flags, force, rho, vel, k, XF, g);
-  else if (forcing == FORCE_SHIFT) launch_sc_stream<LT, COLL, FORCE_SHIFT>(stream_mode, pl, ix, st, fi, fo, flags, force, rho, vel, k, XF, g);
-  else launch_sc_stream<LT, COLL, FORCE_GUO>(stream_mode, pl, ix, st, fi, fo, flags, force, rho, vel, k, XF, g);
+  if (forcing == FORCE_NONE) launch_sc_stream<LT, ST, COLL, FORCE_NONE>(stream_mode, pl, ix, st, fi, fo, flags, force, rho, vel, k, XF, g);
+  else if (forcing == FORCE_SHIFT) launch_sc_stream<LT, ST, COLL, FORCE_SHIFT>(stream_mode, pl, ix, st, fi, fo, flags, force, rho, vel, k, XF, g);
+  else launch_sc_stream<LT, ST, COLL, FORCE_GUO>(stream_mode, pl, ix, st, fi, fo, flags, force, rho, vel, k, XF, g);
 }
 
-// collision: 0 = BGK, 1 = KBC (D3Q27 only).  streaming: 0 = A/B pull (f_in != f_out), 1 = esoteric-pull in
-// place (f_in == f_out), parity = steps done & 1
-template <class LT>
-static int ext_stream_collide_impl(const float* f_in, float* f_out, const uint8_t* flags, const float* force,
+// collision: 0 = BGK, 1 = KBC (D3Q27, fp32 storage only).  streaming: 0 = A/B pull (f_in != f_out), 1 = esoteric
+// pull in place (f_in == f_out), parity = steps done & 1.  rho0: reference density of fp16-stored populations.
+template <class LT, class ST>
+static int ext_stream_collide_impl(const ST* f_in, ST* f_out, const uint8_t* flags, const float* force,
                                    const double* force_uniform, float* rho, float* vel, double tau, int collision,
-                                   int forcing, int streaming, int parity, double dx, double dt, int B, int D, int H,
-                                   int W, cudaStream_t st, const char* where) {
+                                   int forcing, int streaming, int parity, double rho0, double dx, double dt, int B,
+                                   int D, int H, int W, cudaStream_t st, const char* where) {
+  constexpr bool kFp32 = sizeof(ST) == 4;
   if (!(f_in && f_out && flags && rho && vel)) return bad_arg(where, "null pointer");
   if (streaming == 0 && f_in == f_out) return bad_arg(where, "A/B pull streaming needs f_in != f_out");
   if (streaming == 1 && f_in != f_out) return bad_arg(where, "esoteric-pull streaming is in place: f_in must equal f_out");
   if (streaming != 0 && streaming != 1) return bad_arg(where, "streaming must be 0 (A/B pull) or 1 (esoteric pull)");
   if (collision != COLL_BGK && collision != COLL_KBC) return bad_arg(where, "collision must be 0 (BGK) or 1 (KBC)");
-  if (collision == COLL_KBC && LT::Q != 27) return bad_arg(where, "3-D KBC collision needs the D3Q27 lattice");
+  if (collision == COLL_KBC && (LT::Q != 27 || !kFp32)) return bad_arg(where, "3-D KBC collision needs the D3Q27 lattice and fp32 storage");
   if (forcing < FORCE_NONE || forcing > FORCE_GUO) return bad_arg(where, "forcing must be 0 (none), 1 (shift) or 2 (Guo)");
   if (forcing != FORCE_NONE && !force && !force_uniform) return bad_arg(where, "forcing requested without a force");
   if (!(tau > 0)) return bad_arg(where, "tau must be positive");
@@ -353,39 +386,48 @@ static int ext_stream_collide_impl(const float* f_in, float* f_out, const uint8_
   XF.half_dt = (float)(0.5 * dt);
   XF.inv_c = (float)(1.0 / c);
   XF.beta = (float)(0.5 / tau); XF.inv_beta = (float)(2.0 * tau); XF.two_m = (float)(2.0 - 2.0 * tau);
+  XF.rho0 = (float)rho0;
   const PlaneLaunch pl = plane_launch(g);
   const long long Q = LT::Q, N = g.N;
   const bool ix = Q * N < 0xffffffffLL;
   const int mode = streaming == 0 ? STREAM_AB : ((parity & 1) ? STREAM_EP_ODD : STREAM_EP_EVEN);
   for (long long b = 0; b < B; ++b) {
-    const float* fi = f_in + b * Q * N;
-    float* fo = f_out + b * Q * N;
+    const ST* fi = f_in + b * Q * N;
+    ST* fo = f_out + b * Q * N;
     const float* fc = force ? force + b * 3 * N : nullptr;
-    if constexpr (LT::Q == 27) {
+    if constexpr (LT::Q == 27 && kFp32) {
       if (collision == COLL_KBC) {
-        launch_sc_force<LT, COLL_KBC>(forcing, mode, pl, ix, st, fi, fo, flags + b * N, fc, rho + b * N, vel + b * 3 * N, k, XF, g);
+        launch_sc_force<LT, ST, COLL_KBC>(forcing, mode, pl, ix, st, fi, fo, flags + b * N, fc, rho + b * N, vel + b * 3 * N, k, XF, g);
         continue;
       }
     }
-    launch_sc_force<LT, COLL_BGK>(forcing, mode, pl, ix, st, fi, fo, flags + b * N, fc, rho + b * N, vel + b * 3 * N, k, XF, g);
+    launch_sc_force<LT, ST, COLL_BGK>(forcing, mode, pl, ix, st, fi, fo, flags + b * N, fc, rho + b * N, vel + b * 3 * N, k, XF, g);
   }
   return check_launch(where);
 }
 
-template <class LT>
-static int ext_ep_convert_impl(const float* src, float* dst, int parity, int to_ep, int B, int D, int H, int W,
-                               cudaStream_t st, const char* where) {
+// layout: 0 standard, 1 / 2 esoteric pull before an even / odd step
+template <class LT, class ST>
+static int ext_pack_impl(const float* fstd_in, float* fstd_out, const ST* pk_in, ST* pk_out, int layout, int to_packed,
+                         double rho0, int B, int D, int H, int W, cudaStream_t st, const char* where) {
+  const void* src = to_packed ? (const void*)fstd_in : (const void*)pk_in;
+  const void* dst = to_packed ? (const void*)pk_out : (const void*)fstd_out;
   if (!(src && dst && src != dst)) return bad_arg(where, "null or aliased pointer");
+  if (layout < 0 || layout > 2) return bad_arg(where, "layout must be 0 (standard), 1 or 2 (esoteric, even / odd step)");
   if (B < 1 || D < 1 || H < 1 || W < 1) return bad_arg(where, "non-positive extent");
   const Grid g = make_grid(B, D, H, W);
   if (g.N > 0x7fffffffLL / 3) return bad_arg(where, "more than (2^31-1)/3 cells per batch item");
   const PlaneLaunch pl = plane_launch(g);
   const long long Q = LT::Q, N = g.N;
   for (long long b = 0; b < B; ++b) {
+    const float* si = fstd_in ? fstd_in + b * Q * N : nullptr;
+    float* so = fstd_out ? fstd_out + b * Q * N : nullptr;
+    const ST* pi = pk_in ? pk_in + b * Q * N : nullptr;
+    ST* po = pk_out ? pk_out + b * Q * N : nullptr;
     if (Q * N < 0xffffffffLL)
-      k_ext_ep_convert<LT, true><<<pl.grid, pl.block, 0, st>>>(src + b * Q * N, dst + b * Q * N, parity & 1, to_ep, g);
+      k_ext_pack<LT, ST, true><<<pl.grid, pl.block, 0, st>>>(si, so, pi, po, layout, to_packed, (float)rho0, g);
     else
-      k_ext_ep_convert<LT, false><<<pl.grid, pl.block, 0, st>>>(src + b * Q * N, dst + b * Q * N, parity & 1, to_ep, g);
+      k_ext_pack<LT, ST, false><<<pl.grid, pl.block, 0, st>>>(si, so, pi, po, layout, to_packed, (float)rho0, g);
   }
   return check_launch(where);
 }
@@ -416,24 +458,60 @@ int lbmff_ext_stream_collide_d3q19(const float* f_in, float* f_out, const uint8_
                                    const double* force_uniform, float* rho, float* vel, double tau, int collision,
                                    int forcing, int streaming, int parity, double dx, double dt, int B, int D, int H,
                                    int W, lbmff_stream_t stream) {
-  return ext_stream_collide_impl<Q19>(f_in, f_out, flags, force, force_uniform, rho, vel, tau, collision, forcing,
-                                      streaming, parity, dx, dt, B, D, H, W, (cudaStream_t)stream, __func__);
+  return ext_stream_collide_impl<Q19, float>(f_in, f_out, flags, force, force_uniform, rho, vel, tau, collision,
+                                             forcing, streaming, parity, 0.0, dx, dt, B, D, H, W,
+                                             (cudaStream_t)stream, __func__);
 }
 int lbmff_ext_stream_collide_d3q27(const float* f_in, float* f_out, const uint8_t* flags, const float* force,
                                    const double* force_uniform, float* rho, float* vel, double tau, int collision,
                                    int forcing, int streaming, int parity, double dx, double dt, int B, int D, int H,
                                    int W, lbmff_stream_t stream) {
-  return ext_stream_collide_impl<Q27>(f_in, f_out, flags, force, force_uniform, rho, vel, tau, collision, forcing,
-                                      streaming, parity, dx, dt, B, D, H, W, (cudaStream_t)stream, __func__);
+  return ext_stream_collide_impl<Q27, float>(f_in, f_out, flags, force, force_uniform, rho, vel, tau, collision,
+                                             forcing, streaming, parity, 0.0, dx, dt, B, D, H, W,
+                                             (cudaStream_t)stream, __func__);
+}
+int lbmff_ext_stream_collide_fp16_d3q19(const void* f_in, void* f_out, const uint8_t* flags, const float* force,
+                                        const double* force_uniform, float* rho, float* vel, double tau,
+                                        int forcing, int streaming, int parity, double rho0, double dx, double dt,
+                                        int B, int D, int H, int W, lbmff_stream_t stream) {
+  return ext_stream_collide_impl<Q19, __half>((const __half*)f_in, (__half*)f_out, flags, force, force_uniform, rho,
+                                              vel, tau, COLL_BGK, forcing, streaming, parity, rho0, dx, dt, B, D, H,
+                                              W, (cudaStream_t)stream, __func__);
+}
+int lbmff_ext_stream_collide_fp16_d3q27(const void* f_in, void* f_out, const uint8_t* flags, const float* force,
+                                        const double* force_uniform, float* rho, float* vel, double tau,
+                                        int forcing, int streaming, int parity, double rho0, double dx, double dt,
+                                        int B, int D, int H, int W, lbmff_stream_t stream) {
+  return ext_stream_collide_impl<Q27, __half>((const __half*)f_in, (__half*)f_out, flags, force, force_uniform, rho,
+                                              vel, tau, COLL_BGK, forcing, streaming, parity, rho0, dx, dt, B, D, H,
+                                              W, (cudaStream_t)stream, __func__);
 }
 
 int lbmff_ext_esoteric_convert_d3q19(const float* src, float* dst, int parity, int to_esoteric, int B, int D, int H,
                                      int W, lbmff_stream_t stream) {
-  return ext_ep_convert_impl<Q19>(src, dst, parity, to_esoteric, B, D, H, W, (cudaStream_t)stream, __func__);
+  return to_esoteric ? ext_pack_impl<Q19, float>(src, nullptr, nullptr, dst, 1 + (parity & 1), 1, 0.0, B, D, H, W, (cudaStream_t)stream, __func__)
+                     : ext_pack_impl<Q19, float>(nullptr, dst, src, nullptr, 1 + (parity & 1), 0, 0.0, B, D, H, W, (cudaStream_t)stream, __func__);
 }
 int lbmff_ext_esoteric_convert_d3q27(const float* src, float* dst, int parity, int to_esoteric, int B, int D, int H,
                                      int W, lbmff_stream_t stream) {
-  return ext_ep_convert_impl<Q27>(src, dst, parity, to_esoteric, B, D, H, W, (cudaStream_t)stream, __func__);
+  return to_esoteric ? ext_pack_impl<Q27, float>(src, nullptr, nullptr, dst, 1 + (parity & 1), 1, 0.0, B, D, H, W, (cudaStream_t)stream, __func__)
+                     : ext_pack_impl<Q27, float>(nullptr, dst, src, nullptr, 1 + (parity & 1), 0, 0.0, B, D, H, W, (cudaStream_t)stream, __func__);
+}
+int lbmff_ext_pack_fp16_d3q19(const float* f_std, void* f_packed, int layout, double rho0, int B, int D, int H, int W,
+                              lbmff_stream_t stream) {
+  return ext_pack_impl<Q19, __half>(f_std, nullptr, nullptr, (__half*)f_packed, layout, 1, rho0, B, D, H, W, (cudaStream_t)stream, __func__);
+}
+int lbmff_ext_pack_fp16_d3q27(const float* f_std, void* f_packed, int layout, double rho0, int B, int D, int H, int W,
+                              lbmff_stream_t stream) {
+  return ext_pack_impl<Q27, __half>(f_std, nullptr, nullptr, (__half*)f_packed, layout, 1, rho0, B, D, H, W, (cudaStream_t)stream, __func__);
+}
+int lbmff_ext_unpack_fp16_d3q19(const void* f_packed, float* f_std, int layout, double rho0, int B, int D, int H, int W,
+                                lbmff_stream_t stream) {
+  return ext_pack_impl<Q19, __half>(nullptr, f_std, (const __half*)f_packed, nullptr, layout, 0, rho0, B, D, H, W, (cudaStream_t)stream, __func__);
+}
+int lbmff_ext_unpack_fp16_d3q27(const void* f_packed, float* f_std, int layout, double rho0, int B, int D, int H, int W,
+                                lbmff_stream_t stream) {
+  return ext_pack_impl<Q27, __half>(nullptr, f_std, (const __half*)f_packed, nullptr, layout, 0, rho0, B, D, H, W, (cudaStream_t)stream, __func__);
 }
 
 }  // extern "C"

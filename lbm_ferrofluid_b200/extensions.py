@@ -47,11 +47,14 @@ class ExtSinglePhaseSolver:
     flags: uint8 ``[B, 1, D, H, W]`` (FLUID = 1, OBSTACLE = 2).  force: ``None``, a 3-sequence (uniform body
     force x, y, z) or a ``[B, 3, D, H, W]`` tensor.  ``f`` always returns the populations in the standard layout
     (post-collision population q at its own cell), whatever the streaming mode holds internally.
+    storage="fp16": populations are STORED as fp16 deviations from the rest equilibrium of density ``rho0``
+    (arithmetic stays fp32); ``rho0`` defaults to the mean of the density given to ``initialize``.  BGK only.
     """
 
     def __init__(self, flags: torch.Tensor, *, tau: float, lattice: str = "D3Q27", collision: str = "bgk",
                  forcing: Optional[str] = None, streaming: str = "ab", dx: float = 1.0, dt: float = 1.0,
-                 force: Union[None, Sequence[float], torch.Tensor] = None):
+                 force: Union[None, Sequence[float], torch.Tensor] = None, storage: str = "fp32",
+                 rho0: Optional[float] = None):
         if lattice not in _LATTICES:
             raise ValueError(f"lattice must be one of {sorted(_LATTICES)}")
         if collision not in _COLLISION:
@@ -62,6 +65,12 @@ class ExtSinglePhaseSolver:
             raise ValueError("forcing must be None, 'shift' or 'guo'")
         if streaming not in _STREAMING:
             raise ValueError("streaming must be 'ab' or 'esoteric'")
+        if storage not in ("fp32", "fp16"):
+            raise ValueError("storage must be 'fp32' or 'fp16'")
+        if storage == "fp16" and collision != "bgk":
+            raise ValueError("fp16 population storage is built for the BGK collision only")
+        self.fp16, self.rho0 = storage == "fp16", (0.0 if rho0 is None else float(rho0))
+        self._auto_rho0 = self.fp16 and rho0 is None
         self.flags = H.need_cuda(flags, "flags", torch.uint8)
         if self.flags.dim() != 5:
             raise RuntimeError("ExtSinglePhaseSolver is 3-D: flags must be [B, 1, D, H, W]")
@@ -87,7 +96,8 @@ class ExtSinglePhaseSolver:
         self.rho = torch.zeros((self.B, 1, *self.res), **opts)
         self.vel = torch.zeros((self.B, 3, *self.res), **opts)
         nbuf = 1 if self.streaming else 2
-        self._f = [torch.zeros((self.B, self.Q, *self.res), **opts) for _ in range(nbuf)]
+        self._f = [torch.zeros((self.B, self.Q, *self.res), device=self.device,
+                               dtype=torch.float16 if self.fp16 else torch.float32) for _ in range(nbuf)]
         self._cur = 0
         self.steps_done = 0
 
@@ -101,10 +111,19 @@ class ExtSinglePhaseSolver:
     @property
     def population_bytes(self) -> int:
         """Bytes of population storage held (esoteric pull: one buffer; A/B: two)."""
-        return sum(t.numel() * 4 for t in self._f)
+        return sum(t.numel() * t.element_size() for t in self._f)
+
+    def _layout(self) -> int:
+        """0 standard slots (A/B pull); 1 / 2 esoteric pull before an even / odd step."""
+        return 1 + (self.steps_done & 1) if self.streaming else 0
 
     @property
     def f(self) -> torch.Tensor:
+        if self.fp16:
+            out = torch.empty(self._f[0].shape, dtype=torch.float32, device=self.device)
+            H.launch("lbmff_ext_unpack_fp16_" + self._suffix(), self.device, H.ptr(self._f[self._cur]), H.ptr(out),
+                     self._layout(), self.rho0, *self._sizes())
+            return out
         if not self.streaming:
             return self._f[self._cur]
         out = torch.empty_like(self._f[0])
@@ -115,9 +134,12 @@ class ExtSinglePhaseSolver:
     def set_f(self, f: torch.Tensor):
         """Load populations given in the standard layout."""
         f = H.need_cuda(f, "f")
-        if tuple(f.shape) != tuple(self._f[0].shape):
+        if tuple(f.shape) != tuple(self._f[0].shape):  # fp32 in the standard layout, whatever the storage
             raise RuntimeError(f"f must be {tuple(self._f[0].shape)}")
-        if not self.streaming:
+        if self.fp16:
+            H.launch("lbmff_ext_pack_fp16_" + self._suffix(), self.device, H.ptr(f), H.ptr(self._f[self._cur]),
+                     self._layout(), self.rho0, *self._sizes())
+        elif not self.streaming:
             self._f[self._cur].copy_(f)
         else:
             if f.data_ptr() == self._f[0].data_ptr():
@@ -132,6 +154,8 @@ class ExtSinglePhaseSolver:
         vel = H.need_cuda(vel, "vel")
         self.steps_done = 0
         self._cur = 0
+        if self._auto_rho0:
+            self.rho0 = float(rho.mean())          # one sync, at initialisation only
         self.set_f(_feq_torch(rho, vel, self.lattice, self.dx, self.dt))
         self.rho.copy_(rho)
         self.vel.copy_(vel)
@@ -139,16 +163,17 @@ class ExtSinglePhaseSolver:
 
     # ---- stepping ----------------------------------------------------------------------------------------
     def step(self, n: int = 1):
-        name = "lbmff_ext_stream_collide_" + self._suffix()
+        name = ("lbmff_ext_stream_collide_fp16_" if self.fp16 else "lbmff_ext_stream_collide_") + self._suffix()
         fu = ctypes.cast(self._force_u, ctypes.c_void_p) if self._force_u is not None else ctypes.c_void_p(0)
         for _ in range(int(n)):
             if self.streaming:
                 src = dst = self._f[0]
             else:
                 src, dst = self._f[self._cur], self._f[1 - self._cur]
+            mode = (self.forcing, self.streaming, self.steps_done & 1)
+            mode = (*mode, self.rho0) if self.fp16 else (self.collision, *mode)
             H.launch(name, self.device, H.ptr(src), H.ptr(dst), H.ptr(self.flags), H.ptr(self._force_t), fu,
-                     H.ptr(self.rho), H.ptr(self.vel), self.tau, self.collision, self.forcing, self.streaming, self.steps_done & 1,
-                     self.dx, self.dt, *self._sizes())
+                     H.ptr(self.rho), H.ptr(self.vel), self.tau, *mode, self.dx, self.dt, *self._sizes())
             if not self.streaming:
                 self._cur = 1 - self._cur
             self.steps_done += 1

@@ -162,6 +162,15 @@ def ext(res, steps=20, reps=3):
                       f"finite={bool(torch.isfinite(s.rho).all())}", flush=True)
                 del s
                 torch.cuda.empty_cache()
+    for lattice, Q in (("D3Q19", 19), ("D3Q27", 27)):
+        for streaming in ("ab", "esoteric"):
+            s = ExtSinglePhaseSolver(flags, tau=0.8, lattice=lattice, streaming=streaming, storage="fp16").initialize(rho, vel)
+            ms = timed(lambda: s.step(steps), reps=reps) / steps
+            print(f"ext {lattice} fp16 storage {streaming} {res}: {ms:.4f} ms/step {N / ms / 1e3:.0f} MLUPS "
+                  f"{4 * Q * N / ms / 1e6:.0f} GB/s pop_bytes={s.population_bytes / 1e9:.2f} GB "
+                  f"finite={bool(torch.isfinite(s.rho).all())}", flush=True)
+            del s
+            torch.cuda.empty_cache()
     vel = vel + 0.01 * torch.rand_like(vel)      # KBC needs a non-equilibrium state to have work to do
     for streaming in ("ab", "esoteric"):
         s = ExtSinglePhaseSolver(flags, tau=0.51, lattice="D3Q27", collision="kbc", streaming=streaming).initialize(rho, vel)
