@@ -408,6 +408,19 @@ int lbmff_ext_stream_collide_d3q27(const float* f_in, float* f_out, const uint8_
                                    const double* force_uniform, float* rho, float* vel, double tau, int collision,
                                    int forcing, int streaming, int parity, double dx, double dt, int B, int D, int H,
                                    int W, lbmff_stream_t stream);
+/* Three-rate MRT collision on the same step (D3Q19 and D3Q27, fp32 storage): the non-equilibrium part is split
+ * into its deviatoric second-order moments (relaxed with tau: shear viscosity cs2 (tau - 1/2) dt, as in BGK), the
+ * trace of the second-order moments (tau_bulk: bulk viscosity) and everything of higher order (tau_high).  All
+ * three equal reproduces BGK.  No reference counterpart (the reference's "MRT" class is the 2-D KBC scheme,
+ * LBM_collision_MRT_2d.py); north-star item (1). */
+int lbmff_ext_stream_collide_mrt_d3q19(const float* f_in, float* f_out, const uint8_t* flags, const float* force,
+                                       const double* force_uniform, float* rho, float* vel, double tau,
+                                       double tau_bulk, double tau_high, int forcing, int streaming, int parity,
+                                       double dx, double dt, int B, int D, int H, int W, lbmff_stream_t stream);
+int lbmff_ext_stream_collide_mrt_d3q27(const float* f_in, float* f_out, const uint8_t* flags, const float* force,
+                                       const double* force_uniform, float* rho, float* vel, double tau,
+                                       double tau_bulk, double tau_high, int forcing, int streaming, int parity,
+                                       double dx, double dt, int B, int D, int H, int W, lbmff_stream_t stream);
 int lbmff_ext_esoteric_convert_d3q19(const float* src, float* dst, int parity, int to_esoteric, int B, int D, int H,
                                      int W, lbmff_stream_t stream);
 int lbmff_ext_esoteric_convert_d3q27(const float* src, float* dst, int parity, int to_esoteric, int B, int D, int H,

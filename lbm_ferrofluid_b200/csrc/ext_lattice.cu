@@ -124,6 +124,43 @@ __device__ __forceinline__ void kbc3_relax(const float* fv, const float* fe, flo
   }
 }
 
+// Three-rate MRT on the same moment split (both lattices: only rest, axis and planar-diagonal populations carry
+// the stress part): out = f - w_s ds_dev - w_b ds_bulk - w_h dh, with ds_dev the deviatoric (N, Pi) and ds_bulk
+// the trace (T) piece of kbc3_relax's ds.  w_s = 1/tau sets the shear viscosity exactly as BGK does, w_b the bulk
+// viscosity, w_h damps the non-hydrodynamic moments; all equal is BGK (oracle/ext_oracle.py::mrt3_relax).
+template <class LT>
+__device__ __forceinline__ void mrt3_relax(const float* fv, const float* fe, float rho, const float* uc, float w_s,
+                                           float w_b, float w_h, float* out) {
+  constexpr int Q = LT::Q;
+  float xx = 0.f, yy = 0.f, zz = 0.f, xy = 0.f, xz = 0.f, yz = 0.f;
+  const float inv_rho = 1.0f / rho;
+#pragma unroll
+  for (int q = 0; q < Q; ++q) {
+    const float d = (fv[q] - fe[q]) * inv_rho;
+    const float cx = (float)LT::ex(q) - uc[0], cy = (float)LT::ey(q) - uc[1], cz = (float)LT::ez(q) - uc[2];
+    xx = fmaf(d * cx, cx, xx); yy = fmaf(d * cy, cy, yy); zz = fmaf(d * cz, cz, zz);
+    xy = fmaf(d * cx, cy, xy); xz = fmaf(d * cx, cz, xz); yz = fmaf(d * cy, cz, yz);
+  }
+  const float T = xx + yy + zz, Nxz = xx - zz, Nyz = yy - zz;
+  const float r6 = rho * (1.0f / 6.0f), r4 = 0.25f * rho;
+  // (w_s - w_h) ds_dev + (w_b - w_h) ds_bulk per population class; the rest is w_h (f - feq)
+  const float ds = w_s - w_h, db = w_b - w_h;
+  const float bulk_axis = db * r6 * T, bulk_rest = -db * rho * T;
+  const float ax = fmaf(ds * r6, 2.0f * Nxz - Nyz, bulk_axis), ay = fmaf(ds * r6, 2.0f * Nyz - Nxz, bulk_axis),
+              az = fmaf(ds * r6, -Nxz - Nyz, bulk_axis);
+  const float pxy = ds * r4 * xy, pxz = ds * r4 * xz, pyz = ds * r4 * yz;
+#pragma unroll
+  for (int q = 0; q < Q; ++q) {
+    const int ex = LT::ex(q), ey = LT::ey(q), ez = LT::ez(q);
+    const int n = (ex != 0) + (ey != 0) + (ez != 0);
+    float v = 0.f;
+    if (n == 0) v = bulk_rest;
+    else if (n == 1) v = ex != 0 ? ax : (ey != 0 ? ay : az);
+    else if (n == 2) v = ez == 0 ? (float)(ex * ey) * pxy : (ey == 0 ? (float)(ex * ez) * pxz : (float)(ey * ez) * pyz);
+    out[q] = fv[q] - fmaf(w_h, fv[q] - fe[q], v);
+  }
+}
+
 // Population storage.  float: the reference's fp32 populations.  __half: fp16 STORAGE with fp32 arithmetic
 // (SURVEY 8f N4 "mixed-precision population storage"): what is stored is the deviation f_q - w_q rho0 from the
 // rest equilibrium of a reference density rho0 (the shifted-DDF form of Lehmann et al. 2022), which keeps the
@@ -159,7 +196,7 @@ struct Pop<__half> {
 
 enum { FORCE_NONE = 0, FORCE_SHIFT = 1, FORCE_GUO = 2 };
 enum { STREAM_AB = 0, STREAM_EP_EVEN = 1, STREAM_EP_ODD = 2 };
-enum { COLL_BGK = 0, COLL_KBC = 1 };
+enum { COLL_BGK = 0, COLL_KBC = 1, COLL_MRT = 2 };
 
 struct ExtForce {
   float u[3];       // uniform body force (used when the per-cell pointer is NULL)
@@ -168,6 +205,7 @@ struct ExtForce {
   float inv_c;
   float beta, inv_beta, two_m;  // KBC: 1/(2 tau), 2 tau, 2 - 2 tau
   float rho0;                   // fp16 storage: reference density of the shifted populations
+  float w_s, w_b, w_h;          // MRT: 1/tau, 1/tau_bulk, 1/tau_high
 };
 
 // Esoteric-pull addressing (Lehmann 2022).  For each opposite pair (p, o = opp(p)), p < o, a cell owns two
@@ -242,7 +280,7 @@ __global__ void __launch_bounds__(kThreads) k_ext_stream_collide(const ST* fi, S
       }
     }
     const FeqFactors<3> F = feq_factors_fast<3>(u, XF.inv_c);  // physics.cuh: divisions shared
-    if constexpr (COLL == COLL_KBC) {
+    if constexpr (COLL == COLL_KBC || COLL == COLL_MRT) {
       float fe[Q];
 #pragma unroll
       for (int q = 0; q < Q; ++q) fe[q] = feq_lt<LT>(F, rho, q);
@@ -251,7 +289,8 @@ __global__ void __launch_bounds__(kThreads) k_ext_stream_collide(const ST* fi, S
       float uc[3];
 #pragma unroll
       for (int a = 0; a < 3; ++a) uc[a] = (FORCING == FORCE_GUO ? u[a] : m[a] * scale) * XF.inv_c;
-      kbc3_relax<LT>(fv, fe, rho, uc, XF.beta, XF.inv_beta, XF.two_m, out);
+      if constexpr (COLL == COLL_KBC) kbc3_relax<LT>(fv, fe, rho, uc, XF.beta, XF.inv_beta, XF.two_m, out);
+      else mrt3_relax<LT>(fv, fe, rho, uc, XF.w_s, XF.w_b, XF.w_h, out);
     } else {
 #pragma unroll
       for (int q = 0; q < Q; ++q) out[q] = fmaf(k.keep, fv[q], feq_lt<LT>(F, rho, q) * k.relax);
@@ -364,13 +403,16 @@ template <class LT, class ST>
 static int ext_stream_collide_impl(const ST* f_in, ST* f_out, const uint8_t* flags, const float* force,
                                    const double* force_uniform, float* rho, float* vel, double tau, int collision,
                                    int forcing, int streaming, int parity, double rho0, double dx, double dt, int B,
-                                   int D, int H, int W, cudaStream_t st, const char* where) {
+                                   int D, int H, int W, cudaStream_t st, const char* where, double tau_bulk = 0.0,
+                                   double tau_high = 0.0) {
   constexpr bool kFp32 = sizeof(ST) == 4;
   if (!(f_in && f_out && flags && rho && vel)) return bad_arg(where, "null pointer");
   if (streaming == 0 && f_in == f_out) return bad_arg(where, "A/B pull streaming needs f_in != f_out");
   if (streaming == 1 && f_in != f_out) return bad_arg(where, "esoteric-pull streaming is in place: f_in must equal f_out");
   if (streaming != 0 && streaming != 1) return bad_arg(where, "streaming must be 0 (A/B pull) or 1 (esoteric pull)");
-  if (collision != COLL_BGK && collision != COLL_KBC) return bad_arg(where, "collision must be 0 (BGK) or 1 (KBC)");
+  if (collision < COLL_BGK || collision > COLL_MRT) return bad_arg(where, "collision must be 0 (BGK), 1 (KBC) or 2 (MRT)");
+  if (collision == COLL_MRT && !kFp32) return bad_arg(where, "the MRT collision needs fp32 storage");
+  if (collision == COLL_MRT && !(tau_bulk > 0 && tau_high > 0)) return bad_arg(where, "tau_bulk and tau_high must be positive");
   if (collision == COLL_KBC && (LT::Q != 27 || !kFp32)) return bad_arg(where, "3-D KBC collision needs the D3Q27 lattice and fp32 storage");
   if (forcing < FORCE_NONE || forcing > FORCE_GUO) return bad_arg(where, "forcing must be 0 (none), 1 (shift) or 2 (Guo)");
   if (forcing != FORCE_NONE && !force && !force_uniform) return bad_arg(where, "forcing requested without a force");
@@ -387,6 +429,9 @@ static int ext_stream_collide_impl(const ST* f_in, ST* f_out, const uint8_t* fla
   XF.inv_c = (float)(1.0 / c);
   XF.beta = (float)(0.5 / tau); XF.inv_beta = (float)(2.0 * tau); XF.two_m = (float)(2.0 - 2.0 * tau);
   XF.rho0 = (float)rho0;
+  XF.w_s = (float)(1.0 / tau);
+  XF.w_b = collision == COLL_MRT ? (float)(1.0 / tau_bulk) : XF.w_s;
+  XF.w_h = collision == COLL_MRT ? (float)(1.0 / tau_high) : XF.w_s;
   const PlaneLaunch pl = plane_launch(g);
   const long long Q = LT::Q, N = g.N;
   const bool ix = Q * N < 0xffffffffLL;
@@ -398,6 +443,12 @@ static int ext_stream_collide_impl(const ST* f_in, ST* f_out, const uint8_t* fla
     if constexpr (LT::Q == 27 && kFp32) {
       if (collision == COLL_KBC) {
         launch_sc_force<LT, ST, COLL_KBC>(forcing, mode, pl, ix, st, fi, fo, flags + b * N, fc, rho + b * N, vel + b * 3 * N, k, XF, g);
+        continue;
+      }
+    }
+    if constexpr (kFp32) {
+      if (collision == COLL_MRT) {
+        launch_sc_force<LT, ST, COLL_MRT>(forcing, mode, pl, ix, st, fi, fo, flags + b * N, fc, rho + b * N, vel + b * 3 * N, k, XF, g);
         continue;
       }
     }
@@ -469,6 +520,22 @@ int lbmff_ext_stream_collide_d3q27(const float* f_in, float* f_out, const uint8_
   return ext_stream_collide_impl<Q27, float>(f_in, f_out, flags, force, force_uniform, rho, vel, tau, collision,
                                              forcing, streaming, parity, 0.0, dx, dt, B, D, H, W,
                                              (cudaStream_t)stream, __func__);
+}
+int lbmff_ext_stream_collide_mrt_d3q19(const float* f_in, float* f_out, const uint8_t* flags, const float* force,
+                                       const double* force_uniform, float* rho, float* vel, double tau,
+                                       double tau_bulk, double tau_high, int forcing, int streaming, int parity,
+                                       double dx, double dt, int B, int D, int H, int W, lbmff_stream_t stream) {
+  return ext_stream_collide_impl<Q19, float>(f_in, f_out, flags, force, force_uniform, rho, vel, tau, COLL_MRT,
+                                             forcing, streaming, parity, 0.0, dx, dt, B, D, H, W,
+                                             (cudaStream_t)stream, __func__, tau_bulk, tau_high);
+}
+int lbmff_ext_stream_collide_mrt_d3q27(const float* f_in, float* f_out, const uint8_t* flags, const float* force,
+                                       const double* force_uniform, float* rho, float* vel, double tau,
+                                       double tau_bulk, double tau_high, int forcing, int streaming, int parity,
+                                       double dx, double dt, int B, int D, int H, int W, lbmff_stream_t stream) {
+  return ext_stream_collide_impl<Q27, float>(f_in, f_out, flags, force, force_uniform, rho, vel, tau, COLL_MRT,
+                                             forcing, streaming, parity, 0.0, dx, dt, B, D, H, W,
+                                             (cudaStream_t)stream, __func__, tau_bulk, tau_high);
 }
 int lbmff_ext_stream_collide_fp16_d3q19(const void* f_in, void* f_out, const uint8_t* flags, const float* force,
                                         const double* force_uniform, float* rho, float* vel, double tau,

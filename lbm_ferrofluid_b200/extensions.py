@@ -1,6 +1,6 @@
 """SURVEY 8(f) N4 -- extensions the north star names and the reference does not contain.
 
-``ExtSinglePhaseSolver``: single-phase flow on **D3Q19 or D3Q27**, **BGK or (D3Q27) entropic KBC** collision
+``ExtSinglePhaseSolver``: single-phase flow on **D3Q19 or D3Q27**, **BGK, three-rate MRT or (D3Q27) entropic KBC** collision
 (the reference's D2Q9 KBC scheme, ``LBM_collision_MRT_2d.py:113-226``, carried to 3-D), with **no / velocity-shift /
 Guo** forcing, streamed **A/B pull or esoteric-pull in place** (one population buffer instead of two).  One kernel
 per step (``csrc/ext_lattice.cu``), the reference's tensor layout ``[B, Q, D, H, W]``, its entropic product
@@ -23,7 +23,7 @@ from . import _lib
 
 _FORCING = {None: 0, "none": 0, "shift": 1, "guo": 2}
 _STREAMING = {"ab": 0, "esoteric": 1}
-_COLLISION = {"bgk": 0, "kbc": 1}
+_COLLISION = {"bgk": 0, "kbc": 1, "mrt": 2}
 _LATTICES = {"D3Q19": 19, "D3Q27": 27}
 
 
@@ -42,7 +42,10 @@ def lattice_tables(lattice: str):
 
 
 class ExtSinglePhaseSolver:
-    """Single-phase BGK / KBC on D3Q19 / D3Q27 with selectable forcing and streaming (3-D only).
+    """Single-phase BGK / MRT / KBC on D3Q19 / D3Q27 with selectable forcing and streaming (3-D only).
+
+    collision="mrt": three relaxation times -- ``tau`` for the deviatoric second-order moments (shear viscosity
+    cs2 (tau - 1/2) dt, as in BGK), ``tau_bulk`` for their trace, ``tau_high`` for every higher-order moment.
 
     flags: uint8 ``[B, 1, D, H, W]`` (FLUID = 1, OBSTACLE = 2).  force: ``None``, a 3-sequence (uniform body
     force x, y, z) or a ``[B, 3, D, H, W]`` tensor.  ``f`` always returns the populations in the standard layout
@@ -54,11 +57,11 @@ class ExtSinglePhaseSolver:
     def __init__(self, flags: torch.Tensor, *, tau: float, lattice: str = "D3Q27", collision: str = "bgk",
                  forcing: Optional[str] = None, streaming: str = "ab", dx: float = 1.0, dt: float = 1.0,
                  force: Union[None, Sequence[float], torch.Tensor] = None, storage: str = "fp32",
-                 rho0: Optional[float] = None):
+                 rho0: Optional[float] = None, tau_bulk: Optional[float] = None, tau_high: Optional[float] = None):
         if lattice not in _LATTICES:
             raise ValueError(f"lattice must be one of {sorted(_LATTICES)}")
         if collision not in _COLLISION:
-            raise ValueError("collision must be 'bgk' or 'kbc'")
+            raise ValueError("collision must be 'bgk', 'kbc' or 'mrt'")
         if collision == "kbc" and lattice != "D3Q27":
             raise ValueError("the 3-D KBC collision needs lattice='D3Q27'")
         if forcing not in _FORCING:
@@ -81,6 +84,11 @@ class ExtSinglePhaseSolver:
         self.forcing, self.streaming = _FORCING[forcing], _STREAMING[streaming]
         self.collision = _COLLISION[collision]
         self.tau, self.dx, self.dt = float(tau), float(dx), float(dt)
+        if collision != "mrt" and (tau_bulk is not None or tau_high is not None):
+            raise ValueError("tau_bulk / tau_high belong to collision='mrt'")
+        # MRT: relaxation times of the trace and of the higher-order moments (default: tau, i.e. BGK)
+        self.tau_bulk = self.tau if tau_bulk is None else float(tau_bulk)
+        self.tau_high = self.tau if tau_high is None else float(tau_high)
         self._force_t, self._force_u = None, None
         if self.forcing:
             if force is None:
@@ -163,7 +171,9 @@ class ExtSinglePhaseSolver:
 
     # ---- stepping ----------------------------------------------------------------------------------------
     def step(self, n: int = 1):
-        name = ("lbmff_ext_stream_collide_fp16_" if self.fp16 else "lbmff_ext_stream_collide_") + self._suffix()
+        mrt = self.collision == _COLLISION["mrt"]
+        name = ("lbmff_ext_stream_collide_fp16_" if self.fp16 else
+                ("lbmff_ext_stream_collide_mrt_" if mrt else "lbmff_ext_stream_collide_")) + self._suffix()
         fu = ctypes.cast(self._force_u, ctypes.c_void_p) if self._force_u is not None else ctypes.c_void_p(0)
         for _ in range(int(n)):
             if self.streaming:
@@ -171,7 +181,12 @@ class ExtSinglePhaseSolver:
             else:
                 src, dst = self._f[self._cur], self._f[1 - self._cur]
             mode = (self.forcing, self.streaming, self.steps_done & 1)
-            mode = (*mode, self.rho0) if self.fp16 else (self.collision, *mode)
+            if self.fp16:
+                mode = (*mode, self.rho0)
+            elif mrt:
+                mode = (self.tau_bulk, self.tau_high, *mode)
+            else:
+                mode = (self.collision, *mode)
             H.launch(name, self.device, H.ptr(src), H.ptr(dst), H.ptr(self.flags), H.ptr(self._force_t), fu,
                      H.ptr(self.rho), H.ptr(self.vel), self.tau, *mode, self.dx, self.dt, *self._sizes())
             if not self.streaming:

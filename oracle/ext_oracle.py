@@ -90,8 +90,50 @@ def kbc3_relax(f, feq, rho, uc, tau, lat, gamma_override=None):
     return f - beta * (2.0 * ds + gamma * dh), ds, dh
 
 
-def ext_step(f, rho, vel, flags, force, dx, dt, tau, lat, forcing="shift", collision="bgk"):
-    """stream -> macro -> bounce -> BGK / KBC; forcing in {None, "shift", "guo"}.  Returns (f, rho, vel)."""
+def mrt3_split(f, feq, rho, uc, lat):
+    """Moment split of f - feq used by the three-rate MRT collision (D3Q19 and D3Q27): the same {T, N, Pi}
+    representation as kbc3_relax, with the stress part separated into its deviatoric (N, Pi: shear) and trace (T:
+    bulk) pieces; dh is everything else (third- and higher-order moments).  Only rest, axis and planar-diagonal
+    populations carry ds, so the split exists on both lattices.  Returns (ds_dev, ds_bulk, dh)."""
+    e = _e_tensor(lat, f)
+    d = ((f - feq) / rho).unsqueeze(2)
+    cen = e - uc.unsqueeze(1)
+    M = lambda a, b: (d[:, :, 0] * cen[:, :, a] * cen[:, :, b]).sum(dim=1, keepdim=True)
+    xx, yy, zz, xy, xz, yz = M(0, 0), M(1, 1), M(2, 2), M(0, 1), M(0, 2), M(1, 2)
+    T, Nxz, Nyz = xx + yy + zz, xx - zz, yy - zz
+    dev, bulk = torch.zeros_like(f), torch.zeros_like(f)
+    for q in range(lat.Q):
+        ex, ey, ez = lat.e[q]
+        n = abs(ex) + abs(ey) + abs(ez)
+        if n == 0:
+            bulk[:, q:q + 1] = -rho * T
+        elif n == 1:
+            bulk[:, q:q + 1] = rho / 6.0 * T
+            dev[:, q:q + 1] = rho / 6.0 * ((2 * Nxz - Nyz) if ex else ((2 * Nyz - Nxz) if ey else (-Nxz - Nyz)))
+        elif n == 2:
+            dev[:, q:q + 1] = rho / 4.0 * ((ex * ey * xy) if ez == 0 else ((ex * ez * xz) if ey == 0 else (ey * ez * yz)))
+    return dev, bulk, (f - feq) - dev - bulk
+
+
+def mrt3_relax(f, feq, rho, uc, tau, tau_bulk, tau_high, lat):
+    """Three-rate MRT: f - ds_dev / tau - ds_bulk / tau_bulk - dh / tau_high.  tau sets the shear viscosity
+    cs2 (tau - 1/2) dt exactly as in BGK; tau_bulk the bulk viscosity; tau_high damps the non-hydrodynamic
+    moments.  All three equal is BGK; tau_high = 1 / (gamma beta) with the entropic gamma is kbc3_relax."""
+    dev, bulk, dh = mrt3_split(f, feq, rho, uc, lat)
+    return f - dev / tau - bulk / tau_bulk - dh / tau_high
+
+
+def ext_step(f, rho, vel, flags, force, dx, dt, tau, lat, forcing="shift", collision="bgk", tau_bulk=None,
+             tau_high=None):
+    """stream -> macro -> bounce -> BGK / KBC / MRT; forcing in {None, "shift", "guo"}.  Returns (f, rho, vel)."""
+    def relax(f, feq, rho, uc):
+        if collision == "kbc":
+            return kbc3_relax(f, feq, rho, uc, tau, lat)[0]
+        if collision == "mrt":
+            return mrt3_relax(f, feq, rho, uc, tau, tau if tau_bulk is None else tau_bulk,
+                              tau if tau_high is None else tau_high, lat)
+        return (1.0 - 1.0 / tau) * f + feq / tau
+
     c = dx / dt
     cs2 = c * c / 3.0
     f = propagation(f, lat)
@@ -111,14 +153,11 @@ def ext_step(f, rho, vel, flags, force, dx, dt, tau, lat, forcing="shift", colli
         eu = (ec * vel.unsqueeze(1)).sum(dim=2)
         uF = (vel * force).sum(dim=1, keepdim=True)
         S = (1.0 - 0.5 / tau) * w * ((eF - uF) / cs2 + eu * eF / cs2 / cs2)
-        relaxed = kbc3_relax(f, feq, rho, vel / c, tau, lat)[0] if collision == "kbc" else \
-            (1.0 - 1.0 / tau) * f + feq / tau
-        post = relaxed + dt * S
+        post = relax(f, feq, rho, vel / c) + dt * S
     else:
         vel = torch.where(obst, vel, mom / rho_new)
         feq = O.get_feq(dx, dt, rho, vel, force if forcing == "shift" else None, tau, lat=lat)
-        post = kbc3_relax(f, feq, rho, vel / c, tau, lat)[0] if collision == "kbc" else \
-            (1.0 - 1.0 / tau) * f + feq / tau
+        post = relax(f, feq, rho, vel / c)
     return torch.where(obst, f, post), rho, vel
 
 

@@ -178,3 +178,58 @@ def test_sc_force_3d_reduces_to_the_pinned_2d_force():
     mid = F3[:, :, 3]                                     # away from the zero-padded z ends
     assert (mid[:, :2] - F2).abs().max().item() < 1e-7   # fp32-rounded weights
     assert mid[:, 2].abs().max().item() < 1e-12
+
+
+@pytest.mark.parametrize("lat", [X.D3Q19, X.D3Q27], ids=["D3Q19", "D3Q27"])
+def test_mrt3_split_properties(lat):
+    """The stress pieces of the MRT split are mass- and momentum-free; ds_dev carries exactly the traceless part of
+    the second-moment difference, ds_bulk exactly its trace (isotropically), dh none of it; equal rates are BGK;
+    on D3Q27, tau_high = 1 / (gamma beta) with gamma fixed reproduces kbc3_relax."""
+    f, rho, vel, flags, force = _state(lat, walls=False)
+    fs = X.propagation(f, lat)
+    rho = fs.sum(1, keepdim=True)
+    e = X._e_tensor(lat, fs)
+    vel = (fs.unsqueeze(2) * e).sum(1) / rho
+    feq = O.get_feq(1.0, 1.0, rho, vel, None, 1.0, lat=lat)
+    dev, bulk, dh = X.mrt3_split(fs, feq, rho, vel, lat)
+    cen = e - vel.unsqueeze(1)   # moments about the velocity, like the split itself (on D3Q19 f - feq carries feq's
+    second = lambda t: torch.einsum("bqzyx,bqizyx,bqjzyx->bijzyx", t, cen, cen)   # small mass / momentum defect)
+    for t in (dev, bulk):   # (dh keeps whatever mass / momentum defect f - feq itself has: feq's, on D3Q19)
+        assert t.sum(1).abs().max().item() < 1e-15
+        assert (t.unsqueeze(2) * e).sum(1).abs().max().item() < 1e-15
+    eye = torch.eye(3, dtype=f.dtype).view(1, 3, 3, 1, 1, 1)
+    P = second(fs - feq)
+    tr = (P * eye).sum(dim=(1, 2), keepdim=True)
+    assert (second(dev) - (P - eye * tr / 3.0)).abs().max().item() < 1e-15
+    assert (second(bulk) - eye * tr / 3.0).abs().max().item() < 1e-15
+    assert second(dh).abs().max().item() < 1e-15
+    tau = 0.7
+    bgk = (1.0 - 1.0 / tau) * fs + feq / tau
+    assert (X.mrt3_relax(fs, feq, rho, vel, tau, tau, tau, lat) - bgk).abs().max().item() < 1e-15
+    if lat.Q == 27:
+        gamma, beta = 1.6, 0.5 / tau
+        kbc = X.kbc3_relax(fs, feq, rho, vel, tau, lat, gamma_override=gamma)[0]
+        assert (X.mrt3_relax(fs, feq, rho, vel, tau, tau, 1.0 / (gamma * beta), lat) - kbc).abs().max().item() < 1e-15
+
+
+@pytest.mark.parametrize("lat", [X.D3Q19, X.D3Q27], ids=["D3Q19", "D3Q27"])
+@pytest.mark.parametrize("tau_bulk,tau_high", [(0.6, 0.6), (1.0, 1.0), (0.9, 1.4)])
+def test_mrt_shear_wave_decays_with_the_viscosity_of_tau_alone(lat, tau_bulk, tau_high):
+    """u_x(y) = U sin(2 pi y / L) in a periodic box decays as exp(-nu k^2 t), nu = cs2 (tau - 1/2) dt, whatever the
+    bulk and higher-order rates are."""
+    import math
+    tau, L, U, steps = 0.6, 32, 1e-3, 120
+    res = (2, L, 2)
+    flags = torch.full((1, 1, *res), O.FLUID, dtype=torch.uint8)
+    rho = torch.full((1, 1, *res), 0.25, dtype=torch.float64)
+    vel = torch.zeros((1, 3, *res), dtype=torch.float64)
+    y = torch.arange(L, dtype=torch.float64).view(1, L, 1)
+    vel[0, 0] = U * torch.sin(2 * math.pi * y / L)
+    f = O.get_feq(1.0, 1.0, rho, vel, None, 1.0, lat=lat)
+    force = torch.zeros_like(vel)
+    for _ in range(steps):
+        f, rho, vel = X.ext_step(f, rho, vel, flags, force, 1.0, 1.0, tau, lat, None, "mrt", tau_bulk, tau_high)
+    amp = (vel[0, 0] * torch.sin(2 * math.pi * y / L)).mean().item() * 2.0
+    k2 = (2 * math.pi / L) ** 2
+    want = U * math.exp(-(tau - 0.5) / 3.0 * k2 * steps)
+    assert abs(amp / want - 1.0) < 5e-3

@@ -55,18 +55,26 @@ def test_d3q19_shift_ab_equals_the_pinned_single_phase_kernel():
         assert rel_l2(getattr(b, k), getattr(a, k)) <= (2e-5 if k == "vel" else 1e-6), k   # vel: small difference of populations
 
 
-@pytest.mark.parametrize("lattice,collision", [("D3Q19", "bgk"), ("D3Q27", "bgk"), ("D3Q27", "kbc")])
+MRT_RATES = dict(tau_bulk=0.95, tau_high=1.3)
+
+
+def _rates(collision):
+    return MRT_RATES if collision == "mrt" else {}
+
+
+@pytest.mark.parametrize("lattice,collision", [("D3Q19", "bgk"), ("D3Q27", "bgk"), ("D3Q27", "kbc"),
+                                               ("D3Q19", "mrt"), ("D3Q27", "mrt")])
 @pytest.mark.parametrize("forcing", [None, "shift", "guo"])
 def test_step_vs_fp64_oracle(lattice, collision, forcing):
     lat = LAT[lattice]
     flags, rho, vel, force = _case((14, 18, 21), seed=7, B=2)
     tau, steps = 0.7, 6
-    s = _solver(flags, lattice, forcing, "ab", force, tau=tau, dx=0.5, dt=0.25, collision=collision)
+    s = _solver(flags, lattice, forcing, "ab", force, tau=tau, dx=0.5, dt=0.25, collision=collision, **_rates(collision))
     s.initialize(rho.cuda(), vel.cuda())
     f = s.f.cpu().double()
     r, v, F = rho.double(), vel.double(), force.double()
     for _ in range(steps):
-        f, r, v = X.ext_step(f, r, v, flags, F, 0.5, 0.25, tau, lat, forcing, collision)
+        f, r, v = X.ext_step(f, r, v, flags, F, 0.5, 0.25, tau, lat, forcing, collision, **_rates(collision))
     s.step(steps)
     # fp32 against the fp64 evaluation: the SURVEY 8(c) N = 10 bands (f, rho 5e-6; vel 2e-4).  KBC's stabiliser
     # gamma is a ratio of two small sums, so its f band is the one the 2-D KBC goldens are held to (2e-5).
@@ -75,13 +83,15 @@ def test_step_vs_fp64_oracle(lattice, collision, forcing):
     assert rel_l2(s.vel, v) <= 2e-4
 
 
-@pytest.mark.parametrize("lattice,collision", [("D3Q19", "bgk"), ("D3Q27", "bgk"), ("D3Q27", "kbc")])
+@pytest.mark.parametrize("lattice,collision", [("D3Q19", "bgk"), ("D3Q27", "bgk"), ("D3Q27", "kbc"),
+                                               ("D3Q19", "mrt"), ("D3Q27", "mrt")])
 @pytest.mark.parametrize("forcing", [None, "shift", "guo"])
 @pytest.mark.parametrize("res", [(5, 6, 7), (16, 20, 33), (3, 40, 300)])
 def test_esoteric_pull_is_bit_identical_to_ab(lattice, collision, forcing, res):
     flags, rho, vel, force = _case(res, seed=11, B=2, wall_frac=0.08, shell=res[0] > 4)
-    a = _solver(flags, lattice, forcing, "ab", force, collision=collision).initialize(rho.cuda(), vel.cuda())
-    b = _solver(flags, lattice, forcing, "esoteric", force, collision=collision).initialize(rho.cuda(), vel.cuda())
+    kw = dict(collision=collision, **_rates(collision))
+    a = _solver(flags, lattice, forcing, "ab", force, **kw).initialize(rho.cuda(), vel.cuda())
+    b = _solver(flags, lattice, forcing, "esoteric", force, **kw).initialize(rho.cuda(), vel.cuda())
     assert b.population_bytes * 2 == a.population_bytes
     assert torch.equal(a.f, b.f)     # std -> esoteric -> std round trip
     for n in (1, 1, 3, 2):           # both parities are visited and exported
@@ -130,10 +140,39 @@ def test_guo_uniform_force_accelerates_a_periodic_box(lattice, streaming):
     assert ((u - want_u).abs() / want_u.abs()).max().item() < 2e-3
 
 
-@pytest.mark.parametrize("collision", ["bgk", "kbc"])
+@pytest.mark.parametrize("lattice", ["D3Q19", "D3Q27"])
+def test_mrt_with_equal_rates_is_bgk(lattice):
+    """tau_bulk = tau_high = tau: the three-rate MRT relaxes every moment alike, i.e. BGK (rounding apart)."""
+    flags, rho, vel, force = _case((12, 15, 19), seed=2, B=1)
+    a = _solver(flags, lattice, "guo", "ab", force, tau=0.75).initialize(rho.cuda(), vel.cuda())
+    b = _solver(flags, lattice, "guo", "ab", force, tau=0.75, collision="mrt").initialize(rho.cuda(), vel.cuda())
+    a.step(8); b.step(8)
+    assert rel_l2(b.f, a.f) <= 2e-6 and rel_l2(b.rho, a.rho) <= 2e-6 and rel_l2(b.vel, a.vel) <= 5e-5
+
+
+@pytest.mark.parametrize("lattice", ["D3Q19", "D3Q27"])
+def test_mrt_shear_wave_viscosity(lattice):
+    """The decay of u_x(y) = U sin(2 pi y / L) is set by tau alone (nu = cs2 (tau - 1/2) dt), not by the bulk or
+    higher-order rates (same statement as the oracle's CPU test, here on the kernel at a longer time)."""
+    import math
+    tau, L, U, steps = 0.6, 64, 1e-3, 400
+    res = (4, L, 4)
+    flags = torch.ones((1, 1, *res), dtype=torch.uint8)
+    rho = torch.full((1, 1, *res), 0.25)
+    vel = torch.zeros((1, 3, *res))
+    y = torch.arange(L, dtype=torch.float32).view(1, L, 1)
+    vel[0, 0] = U * torch.sin(2 * math.pi * y / L)
+    s = _solver(flags, lattice, None, "esoteric", None, tau=tau, collision="mrt", tau_bulk=0.9, tau_high=1.4)
+    s.initialize(rho.cuda(), vel.cuda()).step(steps)
+    amp = (s.vel[0, 0].double().cpu() * torch.sin(2 * math.pi * y.double() / L)).mean().item() * 2.0
+    want = U * math.exp(-(tau - 0.5) / 3.0 * (2 * math.pi / L) ** 2 * steps)
+    assert abs(amp / want - 1.0) < 1e-2
+
+
+@pytest.mark.parametrize("collision", ["bgk", "kbc", "mrt"])
 def test_d3q27_mass_conserved_with_walls(collision):
     flags, rho, vel, force = _case((24, 20, 28), seed=5, wall_frac=0.1, shell=True)
-    s = _solver(flags, "D3Q27", "guo", "esoteric", force, collision=collision).initialize(rho.cuda(), vel.cuda())
+    s = _solver(flags, "D3Q27", "guo", "esoteric", force, collision=collision, **_rates(collision)).initialize(rho.cuda(), vel.cuda())
     m0 = s.f.double().sum().item()
     s.step(51)
     f = s.f
@@ -153,6 +192,10 @@ def test_error_paths():
         ExtSinglePhaseSolver(flags.cuda(), tau=0.8, forcing="guo")        # no force given
     with pytest.raises(ValueError):
         ExtSinglePhaseSolver(flags.cuda(), tau=0.8, lattice="D3Q19", collision="kbc")
+    with pytest.raises(ValueError):
+        ExtSinglePhaseSolver(flags.cuda(), tau=0.8, tau_bulk=0.9)            # rates without collision="mrt"
+    with pytest.raises(ValueError):
+        ExtSinglePhaseSolver(flags.cuda(), tau=0.8, collision="mrt", storage="fp16")
     with pytest.raises(RuntimeError):
         ExtSinglePhaseSolver(torch.ones((1, 1, 4, 4), dtype=torch.uint8).cuda(), tau=0.8)   # 2-D
     s = ExtSinglePhaseSolver(flags.cuda(), tau=0.8, lattice="D3Q19")

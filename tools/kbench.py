@@ -179,6 +179,15 @@ def ext(res, steps=20, reps=3):
               f"finite={bool(torch.isfinite(s.rho).all())}", flush=True)
         del s
         torch.cuda.empty_cache()
+    for lattice, Q in (("D3Q19", 19), ("D3Q27", 27)):
+        for streaming in ("ab", "esoteric"):
+            s = ExtSinglePhaseSolver(flags, tau=0.55, lattice=lattice, collision="mrt", tau_bulk=0.9, tau_high=1.0,
+                                     streaming=streaming).initialize(rho, vel)
+            ms = timed(lambda: s.step(steps), reps=reps) / steps
+            print(f"ext {lattice} MRT {streaming} {res}: {ms:.4f} ms/step {N / ms / 1e3:.0f} MLUPS {8 * Q * N / ms / 1e6:.0f} GB/s "
+                  f"finite={bool(torch.isfinite(s.rho).all())}", flush=True)
+            del s
+            torch.cuda.empty_cache()
 
 
 def render(n, image=256):
