@@ -84,22 +84,46 @@ __device__ __forceinline__ float feq_lt(const FeqFactors<3>& F, float rho, int q
 //   rest: -rho T;  (s,0,0): rho/6 (2 Nxz - Nyz + T);  (0,s,0): rho/6 (-Nxz + 2 Nyz + T);  (0,0,s): rho/6 (-Nxz - Nyz + T);
 //   (s,l,0): rho/4 s l Pxy;  (s,0,d): rho/4 s d Pxz;  (0,l,d): rho/4 l d Pyz;  corners: 0,
 // T = Mxx + Myy + Mzz, Nxz = Mxx - Mzz, Nyz = Myy - Mzz.  ds is linear in the moments, so it is formed once from
-// the moments of (f - feq) / rho about the velocity uc (lattice units).  gamma = 2 (BGK) where dh vanishes.
+// the moments of f - feq about the velocity uc (lattice units; these are rho M, so rho drops out of ds).
+// gamma = 2 (BGK) where dh vanishes.
+//
+// stress_moments: d_q = f_q - feq_q and the six second moments of d about uc = rho M_ab of the oracle's statement.  Raw moments with the integer lattice vectors are signed adds; the centring
+// C_ab = S_ab - u_a S_b - u_b S_a + u_a u_b S is done once.
+struct Stress { float xx, yy, zz, xy, xz, yz; };
+template <class LT>
+__device__ __forceinline__ Stress stress_moments(const float* fv, const float* fe, const float* uc, float* d) {
+  float S = 0.f, Sx = 0.f, Sy = 0.f, Sz = 0.f;
+  Stress m{0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int q = 0; q < LT::Q; ++q) {
+    const int ex = LT::ex(q), ey = LT::ey(q), ez = LT::ez(q);
+    d[q] = fv[q] - fe[q];
+    S += d[q];
+    if (ex != 0) { Sx += (float)ex * d[q]; m.xx += d[q]; }
+    if (ey != 0) { Sy += (float)ey * d[q]; m.yy += d[q]; }
+    if (ez != 0) { Sz += (float)ez * d[q]; m.zz += d[q]; }
+    if (ex * ey != 0) m.xy += (float)(ex * ey) * d[q];
+    if (ex * ez != 0) m.xz += (float)(ex * ez) * d[q];
+    if (ey * ez != 0) m.yz += (float)(ey * ez) * d[q];
+  }
+  const float ux = uc[0], uy = uc[1], uz = uc[2];
+  m.xx += ux * fmaf(ux, S, -2.0f * Sx); m.yy += uy * fmaf(uy, S, -2.0f * Sy); m.zz += uz * fmaf(uz, S, -2.0f * Sz);
+  m.xy += fmaf(ux * uy, S, -fmaf(ux, Sy, uy * Sx));
+  m.xz += fmaf(ux * uz, S, -fmaf(ux, Sz, uz * Sx));
+  m.yz += fmaf(uy * uz, S, -fmaf(uy, Sz, uz * Sy));
+  return m;
+}
+
 template <class LT>
 __device__ __forceinline__ void kbc3_relax(const float* fv, const float* fe, float rho, const float* uc, float beta,
                                            float inv_beta, float two_m, float* out) {
   constexpr int Q = LT::Q;
-  float xx = 0.f, yy = 0.f, zz = 0.f, xy = 0.f, xz = 0.f, yz = 0.f;
-  const float inv_rho = 1.0f / rho;
-#pragma unroll
-  for (int q = 0; q < Q; ++q) {
-    const float d = (fv[q] - fe[q]) * inv_rho;
-    const float cx = (float)LT::ex(q) - uc[0], cy = (float)LT::ey(q) - uc[1], cz = (float)LT::ez(q) - uc[2];
-    xx = fmaf(d * cx, cx, xx); yy = fmaf(d * cy, cy, yy); zz = fmaf(d * cz, cz, zz);
-    xy = fmaf(d * cx, cy, xy); xz = fmaf(d * cx, cz, xz); yz = fmaf(d * cy, cz, yz);
-  }
-  const float T = xx + yy + zz, Nxz = xx - zz, Nyz = yy - zz;
-  const float r6 = rho * (1.0f / 6.0f), r4 = 0.25f * rho;
+  float d[Q];
+  const Stress m = stress_moments<LT>(fv, fe, uc, d);
+  (void)rho;
+  const float xy = m.xy, xz = m.xz, yz = m.yz;
+  const float T = m.xx + m.yy + m.zz, Nxz = m.xx - m.zz, Nyz = m.yy - m.zz;
+  const float r6 = 1.0f / 6.0f, r4 = 0.25f;
   const float ax = r6 * (2.0f * Nxz - Nyz + T), ay = r6 * (2.0f * Nyz - Nxz + T), az = r6 * (T - Nxz - Nyz);
   float num = 0.f, den = 0.f, ds[Q];
 #pragma unroll
@@ -107,11 +131,11 @@ __device__ __forceinline__ void kbc3_relax(const float* fv, const float* fe, flo
     const int ex = LT::ex(q), ey = LT::ey(q), ez = LT::ez(q);
     const int n = (ex != 0) + (ey != 0) + (ez != 0);
     float v = 0.f;
-    if (n == 0) v = -rho * T;
+    if (n == 0) v = -T;
     else if (n == 1) v = ex != 0 ? ax : (ey != 0 ? ay : az);
     else if (n == 2) v = ez == 0 ? r4 * (float)(ex * ey) * xy : (ey == 0 ? r4 * (float)(ex * ez) * xz : r4 * (float)(ey * ez) * yz);
     ds[q] = v;
-    const float dh = (fv[q] - fe[q]) - v;
+    const float dh = d[q] - v;
     const float inv_fe = 1.0f / fe[q];
     num = fmaf(v * dh, inv_fe, num);
     den = fmaf(dh * dh, inv_fe, den);
@@ -119,7 +143,7 @@ __device__ __forceinline__ void kbc3_relax(const float* fv, const float* fe, flo
   const float gamma = den > 0.f ? inv_beta - two_m * num / den : 2.0f;
 #pragma unroll
   for (int q = 0; q < Q; ++q) {
-    const float dh = (fv[q] - fe[q]) - ds[q];
+    const float dh = d[q] - ds[q];
     out[q] = fv[q] - beta * fmaf(gamma, dh, 2.0f * ds[q]);
   }
 }
@@ -132,23 +156,17 @@ template <class LT>
 __device__ __forceinline__ void mrt3_relax(const float* fv, const float* fe, float rho, const float* uc, float w_s,
                                            float w_b, float w_h, float* out) {
   constexpr int Q = LT::Q;
-  float xx = 0.f, yy = 0.f, zz = 0.f, xy = 0.f, xz = 0.f, yz = 0.f;
-  const float inv_rho = 1.0f / rho;
-#pragma unroll
-  for (int q = 0; q < Q; ++q) {
-    const float d = (fv[q] - fe[q]) * inv_rho;
-    const float cx = (float)LT::ex(q) - uc[0], cy = (float)LT::ey(q) - uc[1], cz = (float)LT::ez(q) - uc[2];
-    xx = fmaf(d * cx, cx, xx); yy = fmaf(d * cy, cy, yy); zz = fmaf(d * cz, cz, zz);
-    xy = fmaf(d * cx, cy, xy); xz = fmaf(d * cx, cz, xz); yz = fmaf(d * cy, cz, yz);
-  }
+  float d[Q];
+  const Stress m = stress_moments<LT>(fv, fe, uc, d);
+  const float xx = m.xx, yy = m.yy, zz = m.zz, xy = m.xy, xz = m.xz, yz = m.yz;
+  (void)rho;
   const float T = xx + yy + zz, Nxz = xx - zz, Nyz = yy - zz;
-  const float r6 = rho * (1.0f / 6.0f), r4 = 0.25f * rho;
   // (w_s - w_h) ds_dev + (w_b - w_h) ds_bulk per population class; the rest is w_h (f - feq)
-  const float ds = w_s - w_h, db = w_b - w_h;
-  const float bulk_axis = db * r6 * T, bulk_rest = -db * rho * T;
-  const float ax = fmaf(ds * r6, 2.0f * Nxz - Nyz, bulk_axis), ay = fmaf(ds * r6, 2.0f * Nyz - Nxz, bulk_axis),
-              az = fmaf(ds * r6, -Nxz - Nyz, bulk_axis);
-  const float pxy = ds * r4 * xy, pxz = ds * r4 * xz, pyz = ds * r4 * yz;
+  const float ds6 = (w_s - w_h) * (1.0f / 6.0f), ds4 = (w_s - w_h) * 0.25f, db = w_b - w_h;
+  const float bulk_axis = db * (1.0f / 6.0f) * T, bulk_rest = -db * T;
+  const float ax = fmaf(ds6, 2.0f * Nxz - Nyz, bulk_axis), ay = fmaf(ds6, 2.0f * Nyz - Nxz, bulk_axis),
+              az = fmaf(ds6, -Nxz - Nyz, bulk_axis);
+  const float pxy = ds4 * xy, pxz = ds4 * xz, pyz = ds4 * yz;
 #pragma unroll
   for (int q = 0; q < Q; ++q) {
     const int ex = LT::ex(q), ey = LT::ey(q), ez = LT::ez(q);
@@ -157,7 +175,7 @@ __device__ __forceinline__ void mrt3_relax(const float* fv, const float* fe, flo
     if (n == 0) v = bulk_rest;
     else if (n == 1) v = ex != 0 ? ax : (ey != 0 ? ay : az);
     else if (n == 2) v = ez == 0 ? (float)(ex * ey) * pxy : (ey == 0 ? (float)(ex * ez) * pxz : (float)(ey * ez) * pyz);
-    out[q] = fv[q] - fmaf(w_h, fv[q] - fe[q], v);
+    out[q] = fv[q] - fmaf(w_h, d[q], v);
   }
 }
 
