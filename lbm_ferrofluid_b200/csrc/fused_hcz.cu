@@ -172,29 +172,37 @@ struct Centred32 {
   }
 };
 
-template <int DIM, bool MAGNETIC, bool IDX32>
-__global__ void __launch_bounds__(kThreads, 2)
-k_hcz_collide_stream(const float* __restrict__ fi, const float* __restrict__ gi, float* __restrict__ fo,
-                     float* __restrict__ go, const float* __restrict__ rho_, const uint8_t* __restrict__ flags,
-                     const float* __restrict__ ws, const float* __restrict__ chi, const float* __restrict__ psi,
-                     const float* __restrict__ Hext, HextUniform Hu, float* __restrict__ vel,
-                     float* __restrict__ pressure, float* __restrict__ force_out, Consts k, int kbc_on_g,
-                     KbcScalars K, Grid g) {
+// Everything of k_hcz_collide_stream after the 2Q pulls, for one cell.  gv: the pulled g populations (registers);
+// fv(q): the pulled f population q (registers, or the thread's shared-memory slots in the prefetching kernel,
+// where f is first needed in the final loop).
+struct CsArgs {
+  float* __restrict__ fo; float* __restrict__ go;
+  const float* __restrict__ rho_; const uint8_t* __restrict__ flags; const float* __restrict__ ws;
+  const float* __restrict__ chi; const float* __restrict__ psi; const float* __restrict__ Hext;
+  HextUniform Hu;
+  float* __restrict__ vel; float* __restrict__ pressure; float* __restrict__ force_out;
+  int kbc_on_g;
+};
+struct RegPop {
+  const float* v;
+  __device__ __forceinline__ float operator()(int q) const { return v[q]; }
+};
+struct SmemPop {   // slot q of this thread: s[q * kThreads]
+  const float* s;
+  __device__ __forceinline__ float operator()(int q) const { return s[q * kThreads]; }
+};
+
+template <int DIM, bool MAGNETIC, bool IDX32, class FV>
+__device__ __forceinline__ void hcz_cs_cell(const PlaneCell& c, const PopIndex<IDX32>& at, float* gv, const FV fv,
+                                            const CsArgs& A, const Consts& k, const KbcScalars& K, const Grid& g) {
   using L = Lat<DIM>;
-  const PlaneCell c = plane_cell(g);
-  if (!c.live) return;
   const int i = c.i;
-  const Nbr nb(c, g);
-  const PopIndex<IDX32> at(g);
-  // All 2Q pulls are issued first, before the flag byte is known: they are the only HBM-latency loads of the
-  // kernel (the stencil fields below mostly hit L1/L2); at 512 threads/SM this keeps ~78 KB per SM in flight.
-  float gv[L::Q], fv[L::Q];
-#pragma unroll
-  for (int q = 0; q < L::Q; ++q) {
-    const auto j = at(q, i + nb.at<DIM>(q, 1));
-    gv[q] = ld_spec(gi + j);
-    fv[q] = ld_spec(fi + j);
-  }
+  float* __restrict__ fo = A.fo; float* __restrict__ go = A.go;
+  const float* __restrict__ rho_ = A.rho_; const uint8_t* __restrict__ flags = A.flags;
+  const float* __restrict__ ws = A.ws; const float* __restrict__ chi = A.chi; const float* __restrict__ psi = A.psi;
+  const float* __restrict__ Hext = A.Hext; const HextUniform& Hu = A.Hu;
+  float* __restrict__ vel = A.vel; float* __restrict__ pressure = A.pressure; float* __restrict__ force_out = A.force_out;
+  const int kbc_on_g = A.kbc_on_g;
   const uint8_t fl = flags[i];
   if (fl != LBMFF_FLUID) {
     // OBSTACLE: stream then full-way bounce, out_q(x) = in_opp(q)(x + e_q) -- the value pulled for opp(q).
@@ -202,7 +210,7 @@ k_hcz_collide_stream(const float* __restrict__ fi, const float* __restrict__ gi,
     const bool obst = fl == LBMFF_OBSTACLE;
 #pragma unroll
     for (int q = 0; q < L::Q; ++q) {
-      fo[at(q, i)] = obst ? fv[L::opp(q)] : fv[q];
+      fo[at(q, i)] = obst ? fv(L::opp(q)) : fv(q);
       go[at(q, i)] = obst ? gv[L::opp(q)] : gv[q];
     }
     return;
@@ -273,11 +281,96 @@ k_hcz_collide_stream(const float* __restrict__ fi, const float* __restrict__ gi,
   }
 #pragma unroll
   for (int q = 0; q < L::Q; ++q) {
-    float fq = fv[q];
+    float fq = fv(q);
     float gq = gv[q];
     hcz_collide_q<DIM>(q, C, k, fq, gq, relaxed);
     fo[at(q, i)] = fq;
     go[at(q, i)] = gq;
+  }
+}
+
+template <int DIM, bool MAGNETIC, bool IDX32>
+__global__ void __launch_bounds__(kThreads, 2)
+k_hcz_collide_stream(const float* __restrict__ fi, const float* __restrict__ gi, CsArgs A, Consts k, KbcScalars K,
+                     Grid g) {
+  using L = Lat<DIM>;
+  const PlaneCell c = plane_cell(g);
+  if (!c.live) return;
+  const int i = c.i;
+  const Nbr nb(c, g);
+  const PopIndex<IDX32> at(g);
+  // All 2Q pulls are issued first, before the flag byte is known: they are the only HBM-latency loads of the
+  // kernel (the stencil fields below mostly hit L1/L2); at 512 threads/SM this keeps ~78 KB per SM in flight.
+  float gv[L::Q], fv[L::Q];
+#pragma unroll
+  for (int q = 0; q < L::Q; ++q) {
+    const auto j = at(q, i + nb.at<DIM>(q, 1));
+    gv[q] = ld_spec(gi + j);
+    fv[q] = ld_spec(fi + j);
+  }
+  hcz_cs_cell<DIM, MAGNETIC, IDX32>(c, at, gv, RegPop{fv}, A, k, K, g);
+}
+
+// The same step with the 2Q pulls of the NEXT cell in flight while the current one is computed: a block marches
+// along z over `kz` planes; each thread copies the 38 populations its next cell pulls into its own shared-memory
+// slots with cp.async (4-byte LDGSTS: the pulls are shifted by one cell, so wider or bulk copies would be
+// misaligned) and waits only for its own copies -- no block barrier, the slots are thread-private.  Two stages of
+// 2Q x 256 floats = 76 KB per block, two blocks per SM.  Marching along z also turns the z-1 / z / z+1 planes of
+// the five stencil fields into L1 re-reads of the same block.
+__device__ __forceinline__ void cp_async4(float* smem, const float* gmem) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <bool MAGNETIC, bool IDX32>
+__global__ void __launch_bounds__(kThreads, 2)
+k_hcz_collide_stream_pf(const float* __restrict__ fi, const float* __restrict__ gi, CsArgs A, Consts k, KbcScalars K,
+                        Grid g, int kz) {
+  constexpr int DIM = 3, Q = 19;
+  extern __shared__ float pf_smem[];   // [2 stages][g: Q | f: Q][kThreads]
+  PlaneCell c;
+  c.x = blockIdx.x * blockDim.x + threadIdx.x;
+  c.y = blockIdx.y * blockDim.y + threadIdx.y;
+  c.live = c.x < g.W && c.y < g.H;
+  if (!c.live) return;
+  const int z0 = g.zb + blockIdx.z * kz;
+  const int z1 = min(z0 + kz, g.zb + g.zn);
+  const int tid = threadIdx.y * blockDim.x + threadIdx.x;
+  const PopIndex<IDX32> at(g);
+  float* slot = pf_smem + tid;
+  auto prefetch = [&](int z, int stage) {
+    PlaneCell n = c;
+    n.z = z;
+    n.i = (z * g.H + c.y) * g.W + c.x;
+    const Nbr nb(n, g);
+    float* s = slot + stage * (2 * Q * kThreads);
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+      const auto j = at(q, n.i + nb.at<DIM>(q, 1));
+      cp_async4(s + q * kThreads, gi + j);
+      cp_async4(s + (Q + q) * kThreads, fi + j);
+    }
+    cp_async_commit();
+  };
+  prefetch(z0, 0);
+  for (int z = z0; z < z1; ++z) {
+    const int stage = (z - z0) & 1;
+    if (z + 1 < z1) {
+      prefetch(z + 1, stage ^ 1);
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    c.z = z;
+    c.i = (z * g.H + c.y) * g.W + c.x;
+    const float* s = slot + stage * (2 * Q * kThreads);
+    float gv[Q];
+#pragma unroll
+    for (int q = 0; q < Q; ++q) gv[q] = s[q * kThreads];
+    hcz_cs_cell<DIM, MAGNETIC, IDX32>(c, at, gv, SmemPop{s + Q * kThreads}, A, k, K, g);
   }
 }
 
@@ -400,6 +493,19 @@ static int shell_rule_impl(float* field, const uint8_t* flags, const Grid& g, cu
   return check_launch(where);
 }
 
+// LBMFF_HCZ_PREFETCH=0/1 and LBMFF_HCZ_KZ=<planes per block> override the defaults (tuning, and the test that
+// holds the two kernels bit-identical)
+struct CsPrefetch { bool on; int kz, bx; };
+static CsPrefetch cs_prefetch_config() {
+  const char* e = getenv("LBMFF_HCZ_PREFETCH");
+  const char* z = getenv("LBMFF_HCZ_KZ");
+  const char* x = getenv("LBMFF_HCZ_BX");
+  CsPrefetch c{e ? atoi(e) != 0 : true, z ? atoi(z) : 16, x ? atoi(x) : 64};
+  if (c.kz < 1) c.kz = 1;
+  if (c.bx != 32 && c.bx != 64 && c.bx != 128 && c.bx != 256) c.bx = 64;
+  return c;
+}
+
 template <int DIM>
 static int collide_stream_impl(const float* f_in, const float* g_in, float* f_out, float* g_out, const float* rho,
                                const uint8_t* flags, const uint8_t* mflags, const float* ws, float* chi,
@@ -419,16 +525,39 @@ static int collide_stream_impl(const float* f_in, const float* g_in, float* f_ou
     launch_shell_rule<DIM>(psi, mflags, g, st);
     launch_shell_rule<DIM>(chi, flags, g, st);
   }
-  const PlaneLaunch pl = plane_launch(g, 64)  /* 64 x 4 blocks share y neighbours in L1: 14.3 ms vs 15.2 ms for 256 x 1 at 512^3 */;
+  const CsPrefetch pf = cs_prefetch_config();
+  const PlaneLaunch pl = plane_launch(g, pf.bx)  /* 64 x 4 blocks share y neighbours in L1: 14.3 ms vs 15.2 ms for 256 x 1 at 512^3 */;
   const long long Q = Lat<DIM>::Q, N = g.N;
   const KbcScalars K = make_kbc(p->tau_g);
+  const bool ix = Q * N < 0xffffffffLL;
   for (long long b = 0; b < g.B; ++b) {
-#define LBMFF_CS(MAG, IX)                                                                                         \
-  k_hcz_collide_stream<DIM, MAG, IX><<<pl.grid, pl.block, 0, st>>>(                                               \
-      f_in + b * Q * N, g_in + b * Q * N, f_out + b * Q * N, g_out + b * Q * N, rho + b * N, flags + b * N,       \
-      ws + b * 3 * N, MAG ? chi + b * N : nullptr, MAG ? psi + b * N : nullptr, Hext ? Hext + b * DIM * N : nullptr, \
-      hu, vel + b * DIM * N, pressure + b * N, force_out ? force_out + b * DIM * N : nullptr, k, kbc_on_g, K, g)
-    const bool ix = Q * N < 0xffffffffLL;
+    const CsArgs A{f_out + b * Q * N, g_out + b * Q * N, rho + b * N, flags + b * N, ws + b * 3 * N,
+                   magnetic ? chi + b * N : nullptr, magnetic ? psi + b * N : nullptr,
+                   Hext ? Hext + b * DIM * N : nullptr, hu, vel + b * DIM * N, pressure + b * N,
+                   force_out ? force_out + b * DIM * N : nullptr, kbc_on_g};
+    const float* fi = f_in + b * Q * N;
+    const float* gi = g_in + b * Q * N;
+    if constexpr (DIM == 3) {
+      if (pf.on && g.zn >= 2) {   // z-marching blocks with the next cell's pulls in flight (cp.async)
+        const int kz = g.zn < pf.kz ? g.zn : pf.kz;
+        const dim3 grid(pl.grid.x, pl.grid.y, (unsigned)((g.zn + kz - 1) / kz));
+        constexpr int smem = 2 * 2 * 19 * kThreads * (int)sizeof(float);
+#define LBMFF_CSPF(MAG, IX)                                                                                         \
+  do {                                                                                                              \
+    static bool once = false;                                                                                       \
+    if (!once) {                                                                                                    \
+      cudaFuncSetAttribute(k_hcz_collide_stream_pf<MAG, IX>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);    \
+      once = true;                                                                                                  \
+    }                                                                                                               \
+    k_hcz_collide_stream_pf<MAG, IX><<<grid, pl.block, smem, st>>>(fi, gi, A, k, K, g, kz);                         \
+  } while (0)
+        if (magnetic) { if (ix) LBMFF_CSPF(true, true); else LBMFF_CSPF(true, false); }
+        else { if (ix) LBMFF_CSPF(false, true); else LBMFF_CSPF(false, false); }
+#undef LBMFF_CSPF
+        continue;
+      }
+    }
+#define LBMFF_CS(MAG, IX) k_hcz_collide_stream<DIM, MAG, IX><<<pl.grid, pl.block, 0, st>>>(fi, gi, A, k, K, g)
     if (magnetic) { if (ix) LBMFF_CS(true, true); else LBMFF_CS(true, false); }
     else { if (ix) LBMFF_CS(false, true); else LBMFF_CS(false, false); }
 #undef LBMFF_CS

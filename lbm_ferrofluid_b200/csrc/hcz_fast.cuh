@@ -23,7 +23,11 @@ template <int DIM>
 __device__ __forceinline__ HczCell<DIM> hcz_prepare(float rho, const float* u, float dn, float p, const float* F,
                                                     const float* gfai, const float* gprho, const Consts& k) {
   HczCell<DIM> C;
+#ifdef LBMFF_HCZ_FEQ_REF   // A/B switch for tuning rebuilds (build.py: LBMFF_NVCC_EXTRA)
   const FeqFactors<DIM> f = feq_factors<DIM>(u, k.c);
+#else
+  const FeqFactors<DIM> f = feq_factors_fast<DIM>(u, k.inv_c);   // divisions shared: 2 per axis instead of 6
+#endif
   C.rb = rho * f.base;
   C.X[0] = f.invA[0]; C.X[1] = 1.0f; C.X[2] = f.A[0];
   C.Y[0] = f.invA[1]; C.Y[1] = 1.0f; C.Y[2] = f.A[1];

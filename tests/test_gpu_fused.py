@@ -367,3 +367,20 @@ def test_cuda_graph_stepping_is_bit_identical(path):
     assert len(b._graphs) == 2
     with pytest.raises(RuntimeError, match="converged"):
         make_solver(G, path="converged").step(2, graph=True)
+
+
+@pytest.mark.parametrize("name", ["traj_ros3d", "traj_multiphase3d", "traj_drop3d"])
+@pytest.mark.parametrize("kz", [1, 3, 16])
+def test_prefetching_collide_stream_is_bit_identical(name, kz, monkeypatch):
+    """LBMFF_HCZ_PREFETCH selects between the one-cell-per-thread collide-stream kernel and the z-marching one
+    that keeps the next cell's 2Q pulls in flight with cp.async; the cell arithmetic is the same function."""
+    G = load_golden(name)
+    out = {}
+    for pf in ("0", "1"):
+        monkeypatch.setenv("LBMFF_HCZ_PREFETCH", pf)
+        monkeypatch.setenv("LBMFF_HCZ_KZ", str(kz))
+        s = make_solver(G).step(int(G["steps"]))
+        torch.cuda.synchronize()
+        out[pf] = [t.clone() for t in (s.f, s.g, s.rho, s.vel, s.pressure)]
+    for a, b in zip(out["0"], out["1"]):
+        assert torch.equal(a, b)
