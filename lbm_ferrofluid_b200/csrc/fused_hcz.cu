@@ -495,14 +495,12 @@ static int shell_rule_impl(float* field, const uint8_t* flags, const Grid& g, cu
 
 // LBMFF_HCZ_PREFETCH=0/1 and LBMFF_HCZ_KZ=<planes per block> override the defaults (tuning, and the test that
 // holds the two kernels bit-identical)
-struct CsPrefetch { bool on; int kz, bx; };
+struct CsPrefetch { bool on; int kz; };
 static CsPrefetch cs_prefetch_config() {
   const char* e = getenv("LBMFF_HCZ_PREFETCH");
   const char* z = getenv("LBMFF_HCZ_KZ");
-  const char* x = getenv("LBMFF_HCZ_BX");
-  CsPrefetch c{e ? atoi(e) != 0 : true, z ? atoi(z) : 16, x ? atoi(x) : 64};
+  CsPrefetch c{e ? atoi(e) != 0 : true, z ? atoi(z) : 16};
   if (c.kz < 1) c.kz = 1;
-  if (c.bx != 32 && c.bx != 64 && c.bx != 128 && c.bx != 256) c.bx = 64;
   return c;
 }
 
@@ -526,7 +524,7 @@ static int collide_stream_impl(const float* f_in, const float* g_in, float* f_ou
     launch_shell_rule<DIM>(chi, flags, g, st);
   }
   const CsPrefetch pf = cs_prefetch_config();
-  const PlaneLaunch pl = plane_launch(g, pf.bx)  /* 64 x 4 blocks share y neighbours in L1: 14.3 ms vs 15.2 ms for 256 x 1 at 512^3 */;
+  const PlaneLaunch pl = plane_launch(g, 64)  /* 64 x 4 blocks share y neighbours in L1 (one-cell kernel: 14.3 ms vs 15.2 ms for 256 x 1 at 512^3; the marching kernel is insensitive: 12.2-12.5 ms for 32 ... 256) */;
   const long long Q = Lat<DIM>::Q, N = g.N;
   const KbcScalars K = make_kbc(p->tau_g);
   const bool ix = Q * N < 0xffffffffLL;
