@@ -264,7 +264,7 @@ def run_ours(args):
         bytes_cell = BYTES_D3Q19 if path == "faithful" else BYTES_SCALAR_SWEEP
         kname = "k_mag_sweep<3>" if path == "faithful" else "k_mag_sweep_scalar<3>"
     else:
-        per_launch_ms, bytes_cell, kname = cs_ms, BYTES_HCZ, "k_hcz_collide_stream<3>"
+        per_launch_ms, bytes_cell, kname = cs_ms, BYTES_HCZ, "k_hcz_collide_stream_pf"
     achieved = bytes_cell * cells_rank / (per_launch_ms * 1e-3) / 1e9
     # DRAM traffic of the same kernel from the committed `ncu --set full` capture (bytes per cell, measured at
     # 256^3), scaled to this launch: GB per launch

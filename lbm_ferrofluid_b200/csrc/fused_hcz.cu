@@ -194,16 +194,15 @@ struct SmemPop {   // slot q of this thread: s[q * kThreads]
 
 template <int DIM, bool MAGNETIC, bool IDX32, class FV>
 __device__ __forceinline__ void hcz_cs_cell(const PlaneCell& c, const PopIndex<IDX32>& at, float* gv, const FV fv,
-                                            const CsArgs& A, const Consts& k, const KbcScalars& K, const Grid& g) {
+                                            const uint8_t fl, const float rho, const CsArgs& A, const Consts& k,
+                                            const KbcScalars& K, const Grid& g) {
   using L = Lat<DIM>;
   const int i = c.i;
   float* __restrict__ fo = A.fo; float* __restrict__ go = A.go;
-  const float* __restrict__ rho_ = A.rho_; const uint8_t* __restrict__ flags = A.flags;
   const float* __restrict__ ws = A.ws; const float* __restrict__ chi = A.chi; const float* __restrict__ psi = A.psi;
   const float* __restrict__ Hext = A.Hext; const HextUniform& Hu = A.Hu;
   float* __restrict__ vel = A.vel; float* __restrict__ pressure = A.pressure; float* __restrict__ force_out = A.force_out;
   const int kbc_on_g = A.kbc_on_g;
-  const uint8_t fl = flags[i];
   if (fl != LBMFF_FLUID) {
     // OBSTACLE: stream then full-way bounce, out_q(x) = in_opp(q)(x + e_q) -- the value pulled for opp(q).
     // Other non-FLUID cells are only streamed (HCZ collides FLUID cells only, HCZ_3d.py:357-359).
@@ -225,7 +224,6 @@ __device__ __forceinline__ void hcz_cs_cell(const PlaneCell& c, const PopIndex<I
   grad_at_fast<DIM>(Centred32{w, g.W, HW, x, y, z}, x, y, z, k.inv12dx, glap);
   grad_at_fast<DIM>(Centred32{w + g.N, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gfai);
   grad_at_fast<DIM>(Centred32{w + 2 * g.N, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gprho);
-  const float rho = rho_[i];
   const float dn = affine_density(rho, k.aff);
   float F[DIM];
 #pragma unroll
@@ -308,7 +306,8 @@ k_hcz_collide_stream(const float* __restrict__ fi, const float* __restrict__ gi,
     gv[q] = ld_spec(gi + j);
     fv[q] = ld_spec(fi + j);
   }
-  hcz_cs_cell<DIM, MAGNETIC, IDX32>(c, at, gv, RegPop{fv}, A, k, K, g);
+  const float rho = A.rho_[i];   // (harmless on non-FLUID cells, and not behind the flag's round trip)
+  hcz_cs_cell<DIM, MAGNETIC, IDX32>(c, at, gv, RegPop{fv}, A.flags[i], rho, A, k, K, g);
 }
 
 // The same step with the 2Q pulls of the NEXT cell in flight while the current one is computed: a block marches
@@ -356,8 +355,18 @@ k_hcz_collide_stream_pf(const float* __restrict__ fi, const float* __restrict__ 
     cp_async_commit();
   };
   prefetch(z0, 0);
+  // flag byte and rho of the next cell ride one iteration ahead too (the flag decides the branch every other
+  // load sits behind: 14 % of the stall samples of the first version were the wait for it)
+  uint8_t fl_next = A.flags[(z0 * g.H + c.y) * g.W + c.x];
+  float rho_next = A.rho_[(z0 * g.H + c.y) * g.W + c.x];
   for (int z = z0; z < z1; ++z) {
     const int stage = (z - z0) & 1;
+    const uint8_t fl = fl_next;
+    const float rho = rho_next;
+    if (z + 1 < z1) {
+      fl_next = A.flags[((z + 1) * g.H + c.y) * g.W + c.x];
+      rho_next = A.rho_[((z + 1) * g.H + c.y) * g.W + c.x];
+    }
     if (z + 1 < z1) {
       prefetch(z + 1, stage ^ 1);
       cp_async_wait<1>();
@@ -370,7 +379,7 @@ k_hcz_collide_stream_pf(const float* __restrict__ fi, const float* __restrict__ 
     float gv[Q];
 #pragma unroll
     for (int q = 0; q < Q; ++q) gv[q] = s[q * kThreads];
-    hcz_cs_cell<DIM, MAGNETIC, IDX32>(c, at, gv, SmemPop{s + Q * kThreads}, A, k, K, g);
+    hcz_cs_cell<DIM, MAGNETIC, IDX32>(c, at, gv, SmemPop{s + Q * kThreads}, fl, rho, A, k, K, g);
   }
 }
 
@@ -542,10 +551,12 @@ static int collide_stream_impl(const float* f_in, const float* g_in, float* f_ou
         constexpr int smem = 2 * 2 * 19 * kThreads * (int)sizeof(float);
 #define LBMFF_CSPF(MAG, IX)                                                                                         \
   do {                                                                                                              \
-    static bool once = false;                                                                                       \
-    if (!once) {                                                                                                    \
+    static bool done[64] = {};   /* the attribute is per device; set once per device, outside any graph capture */ \
+    int dev = 0;                                                                                                    \
+    cudaGetDevice(&dev);                                                                                            \
+    if (dev < 0 || dev >= 64 || !done[dev]) {                                                                       \
       cudaFuncSetAttribute(k_hcz_collide_stream_pf<MAG, IX>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);    \
-      once = true;                                                                                                  \
+      if (dev >= 0 && dev < 64) done[dev] = true;                                                                   \
     }                                                                                                               \
     k_hcz_collide_stream_pf<MAG, IX><<<grid, pl.block, smem, st>>>(fi, gi, A, k, K, g, kz);                         \
   } while (0)

@@ -1,8 +1,8 @@
 set -x
 mkdir -p gpurun_out
-show() { python tools/show_bench.py $1; }
+timeout 900 python -m pytest tests/test_gpu_fused.py tests/test_gpu_slab.py -m gpu -x -q 2>&1 | tail -3
 B="python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-e2e --no-fast-path"
-for bx in 32 64 128 256; do
-LBMFF_HCZ_BX=$bx $B > gpurun_out/pf_bx$bx.json 2>/dev/null; show gpurun_out/pf_bx$bx.json
+for i in 1 2; do
+LBMFF_HCZ_PREFETCH=1 $B > gpurun_out/pf_on$i.json 2>/dev/null; python tools/show_bench.py gpurun_out/pf_on$i.json
+LBMFF_HCZ_PREFETCH=0 $B > gpurun_out/pf_off$i.json 2>/dev/null; python tools/show_bench.py gpurun_out/pf_off$i.json
 done
-LBMFF_HCZ_BX=32 LBMFF_HCZ_KZ=32 $B > gpurun_out/pf_bx32kz32.json 2>/dev/null; show gpurun_out/pf_bx32kz32.json
