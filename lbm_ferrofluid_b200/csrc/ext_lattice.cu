@@ -235,7 +235,7 @@ struct ExtForce {
 //              store f_p -> slot o @ x+e_p    f_o -> slot p @ x
 // (loaded values are the populations ARRIVING at x, stored ones are post-collision.)
 template <class LT, class ST, int COLL, int FORCING, int STREAM, bool IDX32>
-__global__ void __launch_bounds__(kThreads) k_ext_stream_collide(const ST* fi, ST* fo,
+__global__ void __launch_bounds__(kThreads, (COLL == 2 && LT::Q == 19) ? 4 : 1) k_ext_stream_collide(const ST* fi, ST* fo,
                                                                  const uint8_t* __restrict__ flags,
                                                                  const float* __restrict__ force,
                                                                  float* __restrict__ rho_, float* __restrict__ vel,
