@@ -13,8 +13,13 @@ of the array (wall shell included) x outer steps.  Prints ONE JSON line (rank 0)
                field (the three H_ext_mac face arrays get_H_int takes) from pinned memory and reads the order
                parameter phi (what the demos render) back to pinned memory.
  * roofline  : dominant kernel, algorithmic bytes / CUDA-event duration vs MEASURED_PEAKS.json.
- * cpu_baseline / --impl reference : the CPU oracle port (oracle/lbm_oracle.py, a torch-CPU restatement of the
-               reference pinned against its golden vectors) on the host cores, bounded sample.
+ * cpu_baseline / --impl reference : the REFERENCE's own PyTorch implementation on the host cores (kind "reference":
+               the byte-compiled copy oracle/_ref/pyref run by oracle/ref_runner.py in its own process), bounded
+               sample; the oracle port (oracle/lbm_oracle.py, kind "port") only if that copy is absent.
+ * configs   : (N = 1) the other BASELINE.json configurations, each a short timed run with its own byte model.
+ * slab_verify (N > 1) : before timing, a small case is run through the real NCCL exchanger and compared bit for
+               bit with a one-GPU run (lbm_ferrofluid_b200.distributed.verify_against_single_gpu).
+The timed region of `value` is repeated --reps times (default 3); value / ms_per_step are the MEDIAN repetition.
 """
 from __future__ import annotations
 
@@ -57,6 +62,10 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-fast-path", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the block of the other BASELINE configs")
+    ap.add_argument("--no-ref-eager", action="store_true", help="skip the reference-eager-on-this-GPU number")
+    ap.add_argument("--no-verify", action="store_true", help="skip the N-rank bit-identity check")
+    ap.add_argument("--reps", type=int, default=3, help="repetitions of the K-step timed region (median reported)")
     return ap.parse_args()
 
 
@@ -71,12 +80,36 @@ def peaks():
 # ---------------------------------------------------------------------------------------------------
 # CPU arm: the oracle port on the host cores
 # ---------------------------------------------------------------------------------------------------
+def _ref_runner(argv, timeout):
+    """Run oracle/ref_runner.py (the unmodified reference in its own process) and parse its JSON line."""
+    env = {k: v for k, v in os.environ.items() if k not in ("PYTHONPATH", "RANK", "WORLD_SIZE", "LOCAL_RANK")}
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "oracle", "ref_runner.py"), *argv], capture_output=True,
+                       text=True, env=env, timeout=timeout)
+    if r.returncode != 0:
+        raise RuntimeError(r.stderr.strip().splitlines()[-1] if r.stderr.strip() else "ref_runner failed")
+    return json.loads(r.stdout.strip().splitlines()[-1])
+
+
+def reference_present():
+    return os.path.exists(os.path.join(ROOT, "oracle", "_ref", "pyref", "MANIFEST.json")) or \
+        os.path.isdir("/root/reference/src/LBM")
+
+
 def cpu_rosensweig_mlups(res, steps, warmup):
-    """Times oracle.hcz_step (the reference algorithm restated in torch-CPU) on a bounded grid."""
+    """The reference's own CPU path on a bounded grid: (MLUPS, ms/step, cores, kind).  kind "reference" = the
+    unmodified reference classes driven through the demo loop (oracle/ref_runner.py); "port" = oracle.hcz_step,
+    only when the byte-compiled reference did not travel."""
+    cores = os.cpu_count() or 1
+    if reference_present():
+        try:
+            j = _ref_runner(["time", "--dim", "3", "--res", *map(str, res), "--mag", str(MAG), "--steps", str(steps),
+                             "--warmup", str(warmup), "--device", "cpu", "--flush-denormal"], timeout=1500)
+            return j["mlups"], j["ms_per_step"], j["cores"], "reference"
+        except Exception as e:                               # fall back to the port, loudly
+            sys.stderr.write(f"bench.py: reference CPU run failed ({e}); timing the oracle port instead\n")
     from oracle import lbm_oracle as O
     from oracle.make_golden import perturbed_interface, shell_flags
 
-    cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     # psi decays exponentially away from the interface, so the first steps are full of denormals, which the
     # host cores process ~50x slower (measured: 22 s vs 0.39 s per step at 48^3).  Flush-to-zero favours the
@@ -99,7 +132,7 @@ def cpu_rosensweig_mlups(res, steps, warmup):
         s = O.hcz_step(s, p)
     dt = time.perf_counter() - t0
     cells = res[0] * res[1] * res[2]
-    return cells * steps / dt / 1e6, dt / steps * 1e3, cores
+    return cells * steps / dt / 1e6, dt / steps * 1e3, cores, "port"
 
 
 def run_reference(args):
@@ -110,16 +143,21 @@ def run_reference(args):
     steps, warmup = max(1, args.steps), max(0, args.warmup)
     # bound the whole run to a few minutes: ~3.5 s per step at 96^3 on 8 cores
     steps, warmup = min(steps, 10), min(warmup, 3)
-    mlups, ms, cores = cpu_rosensweig_mlups(res, steps, warmup)
-    sample = f"same workload at {res[0]}x{res[1]}x{res[2]} (bounded sample), {warmup} warm-up + {steps} timed steps"
+    mlups, ms, cores, kind = cpu_rosensweig_mlups(res, steps, warmup)
+    sample = (f"same workload at {res[0]}x{res[1]}x{res[2]} (bounded sample), {warmup} warm-up + {steps} timed steps, "
+              f"torch CPU threads = {cores}, denormals flushed to zero (timing only)")
+    note = ("the reference's own src/LBM classes driven through the demo loop on the host cores (byte-compiled copy "
+            "oracle/_ref/pyref, unmodified; 512^3 is out of its reach: three [1,19,3,D,H,W] temporaries of 30 GB)"
+            if kind == "reference" else
+            "oracle port (torch-CPU restatement pinned against the reference's golden vectors): the byte-compiled "
+            "reference oracle/_ref/pyref was not found")
     line = {
         "impl": "reference", "metric": METRIC, "value": mlups, "unit": "MLUPS", "n_gpus": args.gpus,
         "steps": steps, "warmup": warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": "demo_3d_LBM_Rosensweig_instability D3Q19 HCZ+magnetic mg100, 30 sweeps/step",
-                   "res": list(res), "note": "reference CPU path = oracle port (torch-CPU restatement pinned "
-                   "against the reference's golden vectors); the Python reference cannot travel to the GPU box"},
-        "cpu_baseline": {"value": mlups, "unit": "MLUPS", "cores": cores, "kind": "port", "sample": sample},
+                   "res": list(res), "note": note},
+        "cpu_baseline": {"value": mlups, "unit": "MLUPS", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": mlups, "unit": "MLUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -176,7 +214,7 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------
-def build_solver(res, path, device, world=1, rank=0, workload="rosensweig"):
+def build_solver(res, path, device, world=1, rank=0, workload="rosensweig", mag=MAG):
     from lbm_ferrofluid_b200 import initializers as I
     from lbm_ferrofluid_b200.solver import FerroSolver
 
@@ -184,7 +222,7 @@ def build_solver(res, path, device, world=1, rank=0, workload="rosensweig"):
         from lbm_ferrofluid_b200.distributed import SlabFerroSolver
         if workload == "two_droplets":
             return SlabFerroSolver.two_droplets(res, path, device, world, rank, mag=1.0, n_sweeps=N_SWEEPS)
-        return SlabFerroSolver.rosensweig(res, path, device, world, rank, mag=MAG, n_sweeps=N_SWEEPS)
+        return SlabFerroSolver.rosensweig(res, path, device, world, rank, mag=mag, n_sweeps=N_SWEEPS)
     if workload == "two_droplets":
         flags = I.shell_flags(res, device=device)
         s = FerroSolver(flags, magnetic_flags=flags.clone(), H_ext=[0.0, 1.0, 0.0], n_sweeps=N_SWEEPS,
@@ -193,10 +231,85 @@ def build_solver(res, path, device, world=1, rank=0, workload="rosensweig"):
     flags = I.shell_flags(res, device=device)
     mflags = I.shell_flags(res, open_axes=(1,), device=device)
     rho = I.rosensweig_rho(res, flags)
-    s = FerroSolver(flags, magnetic_flags=mflags, H_ext=[0.0, MAG, 0.0], n_sweeps=N_SWEEPS, magnetic_path=path,
+    s = FerroSolver(flags, magnetic_flags=mflags, H_ext=[0.0, mag, 0.0], n_sweeps=N_SWEEPS, magnetic_path=path,
                     contact_angle=0.5 * math.pi, gravity=1e-4, keep_force=False)
     s.initialize(rho)
     return s
+
+
+def _event_ms(fn, steps):
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    a.record()
+    fn(steps)
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b)
+
+
+def other_configs(device, peak):
+    """The other BASELINE.json configurations on one GPU: a short timed run each (3 warm-up
+    steps, median of 3 repetitions, CUDA events; every state is far larger than the 126 MB L2), with the byte model of
+    DESIGN.md section 3 and the fraction of the measured copy bandwidth that model reaches."""
+    from lbm_ferrofluid_b200 import initializers as I
+    from lbm_ferrofluid_b200.solver import FerroSolver, SinglePhaseSolver
+    from lbm_ferrofluid_b200.types import KBCType
+
+    out = {}
+
+    def measure(name, solver, cells, bytes_cell, steps, note):
+        solver.step(3)
+        ms = statistics.median(_event_ms(solver.step, steps) for _ in range(3)) / steps
+        v = cells / ms / 1e3
+        fld = solver.rho if hasattr(solver, "rho") else solver.f
+        out[name] = {"value": v, "unit": "MLUPS", "ms_per_step": ms, "cells": cells, "steps_timed": steps,
+                     "model_bytes_per_cell": bytes_cell, "model_gbs": v * 1e6 * bytes_cell / 1e9,
+                     "frac_of_hbm_peak": v * 1e6 * bytes_cell / 1e9 / peak, "note": note,
+                     "finite": bool(torch.isfinite(fld).all().item())}
+
+    n = 4096
+    flags = torch.ones((1, 1, n, n), dtype=torch.uint8, device=device)
+    tau = 0.5 + 3 * 0.2 * n / 3000
+    vel = I.double_shear_layer((n, n), device=device)
+    rho = torch.full((1, 1, n, n), 0.265, device=device)
+    measure("demo_2d_LBM 4096^2 D2Q9 BGK", SinglePhaseSolver(flags, tau=tau).initialize(rho, vel), n * n, 72, 100,
+            "double shear layer, Re 3000, one fused stream+macro+collide kernel per step")
+    measure("demo_2d_LBM_KBC 4096^2 D2Q9 KBC_A", SinglePhaseSolver(flags, tau=tau, KBC_type=int(KBCType.KBC_A))
+            .initialize(rho, vel), n * n, 72, 100,
+            "entropic KBC; the reference's 0/0 = NaN stabiliser cells are reproduced, so finite may be false")
+    del flags, vel, rho
+    res = (n, n)
+    flags = I.shell_flags(res, device=device)
+    mflags = I.shell_flags(res, open_axes=(1,), device=device)
+    s = FerroSolver(flags, magnetic_flags=mflags, H_ext=[0.0, MAG], tau_f=0.7, tau_g=0.8,
+                    contact_angle=0.75 * math.pi, KBC_type=int(KBCType.KBC_A), magnetic_path="faithful",
+                    n_sweeps=N_SWEEPS, keep_force=False).initialize(I.rosensweig_rho(res, flags, frac=0.45))
+    measure("demo_2d_LBM_Rosensweig_instability 4096^2 mg100 (HCZ + magnetic + KBC on g)", s, n * n,
+            (2 + N_SWEEPS) * 72, 10, "population-faithful 30 sweeps; model (2+30) x 72 B")
+    del s, flags, mflags
+    torch.cuda.empty_cache()
+    res = (256, 256, 256)
+    s = build_solver(res, "faithful", device, mag=85.0)
+    measure("demo_3d_LBM_Rosensweig_instability 256^3 mg85", s, 256 ** 3, (2 + N_SWEEPS) * BYTES_D3Q19, 10,
+            "population-faithful 30 sweeps; model (2+30) x 152 B")
+    del s
+    torch.cuda.empty_cache()
+    return out
+
+
+def reference_eager_on_gpu(res=(256, 256, 256)):
+    """BASELINE.md section 3's optional second baseline: the unmodified reference with device='cuda' on this GPU
+    (eager PyTorch, ~4 400 launches per step), in its own process."""
+    if not reference_present():
+        return None
+    try:
+        j = _ref_runner(["time", "--dim", "3", "--res", *map(str, res), "--mag", str(MAG), "--steps", "3", "--warmup",
+                         "1", "--device", "cuda"], timeout=900)
+        return {"value": j["mlups"], "unit": "MLUPS", "ms_per_step": j["ms_per_step"], "res": list(res),
+                "what": "unmodified reference (oracle/_ref/pyref), eager PyTorch, device='cuda', fp32, same "
+                        "workload; 512^3 is out of its reach (three [1,19,3,D,H,W] temporaries of 30 GB each)"}
+    except Exception as e:
+        return {"value": None, "error": str(e)[:200]}
 
 
 def run_ours(args):
@@ -221,6 +334,14 @@ def run_ours(args):
     res = tuple(args.res) if args.res else (512, 512, 512)
     cells_rank = res[0] * res[1] * res[2]
     cells = cells_rank * world
+
+    # ---- N > 1: the data plane is checked against a one-GPU run, bit for bit, before anything is timed
+    slab_verify = None
+    if world > 1 and not args.no_verify:
+        from lbm_ferrofluid_b200.distributed import verify_against_single_gpu
+        slab_verify = verify_against_single_gpu(device, world, rank, (8 * world if world > 8 else 64, 48, 56), 3)
+        torch.cuda.empty_cache()
+
     solver = build_solver(res, args.magnetic_path, device, world, rank, args.workload)
     path = solver.magnetic_path
 
@@ -241,21 +362,22 @@ def run_ours(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
-    # ---- device-resident throughput
+    # ---- device-resident throughput: --reps repetitions of the K-step timed region, median reported
     solver.step(args.warmup)
     solver.enable_kernel_timing(True)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    ms_total = timed(solver.step, args.steps)
+    reps_ms = [timed(solver.step, args.steps) for _ in range(max(1, args.reps))]
     clocks = sampler.stop() if rank == 0 else None
     ktimes = solver.kernel_times_ms()
     solver.enable_kernel_timing(False)
+    ms_total = statistics.median(reps_ms)
     ms_step = ms_total / args.steps
     mlups = cells * args.steps / (ms_total * 1e-3) / 1e6
     finite = bool(torch.isfinite(solver.rho).all().item())
 
-    # ---- roofline of the dominant kernel (CUDA events bracketing it inside the timed region)
+    # ---- roofline of the dominant kernel (CUDA events bracketing it inside the timed region, all repetitions)
     peak, peak_src = peaks()
     sweeps_ms = statistics.mean(ktimes["sweeps"]) if ktimes.get("sweeps") else 0.0
     cs_ms = statistics.mean(ktimes["collide_stream"])
@@ -266,22 +388,39 @@ def run_ours(args):
     else:
         per_launch_ms, bytes_cell, kname = cs_ms, BYTES_HCZ, "k_hcz_collide_stream_pf"
     achieved = bytes_cell * cells_rank / (per_launch_ms * 1e-3) / 1e9
-    # DRAM traffic of the same kernel from the committed `ncu --set full` capture (bytes per cell, measured at
-    # 256^3), scaled to this launch: GB per launch
-    traffic = None
-    try:
-        with open(os.path.join(ROOT, "profiles", "ncu_traffic_r01.json")) as fh:
-            per_cell = json.load(fh)["dram_bytes_per_cell"].get(kname)
-        traffic = per_cell * cells_rank / 1e9 if per_cell else None
-    except Exception:
-        pass
+    # DRAM traffic of the same kernel (dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` launch):
+    # profiles/ncu_traffic_r02.json is measured AT 512^3, so for the default workload the figure is that launch's own
+    # traffic; other grids scale the measured bytes per cell
+    traffic, traffic_src = None, None
+    for fn in ("ncu_traffic_r02.json", "ncu_traffic_r01.json"):
+        try:
+            with open(os.path.join(ROOT, "profiles", fn)) as fh:
+                tj = json.load(fh)
+            per_cell = tj["dram_bytes_per_cell"].get(kname)
+            if per_cell:
+                traffic = per_cell * cells_rank / 1e9
+                traffic_src = f"profiles/{fn}: {per_cell:.2f} B/cell measured at {tj.get('res', '256^3')}"
+                break
+        except Exception:
+            pass
     roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "traffic_unit": "GB per launch (ncu dram bytes)",
+                "traffic_source": traffic_src,
                 "algorithmic_gb_per_launch": bytes_cell * cells_rank / 1e9, "peak_source": peak_src,
                 "algorithmic_bytes_per_cell": bytes_cell, "avg_launch_ms": per_launch_ms,
-                "share_of_step": {"sweeps": sweeps_ms / ms_step, "collide_stream": cs_ms / ms_step}}
+                "share_of_step": {"sweeps": sweeps_ms / ms_step, "collide_stream": cs_ms / ms_step},
+                "collide_stream": {"kernel": "k_hcz_collide_stream_pf", "avg_launch_ms": cs_ms,
+                                   "algorithmic_bytes_per_cell": BYTES_HCZ,
+                                   "achieved": BYTES_HCZ * cells_rank / (cs_ms * 1e-3) / 1e9,
+                                   "frac": BYTES_HCZ * cells_rank / (cs_ms * 1e-3) / 1e9 / peak}}
 
     launches_per_step = solver.launches_per_step
+    exch = None
+    if world > 1 and getattr(solver, "exchanger", None) is not None:
+        ex = solver.exchanger
+        done = max(1, solver.steps_done)
+        exch = {"exchanges_per_step": ex.calls / done, "bytes_per_direction_per_step": ex.bytes_per_direction / done,
+                "transport": getattr(ex, "transport", "nccl p2p (batch_isend_irecv)")}
     # ---- end to end through host buffers
     e2e = None
     if not args.no_e2e:
@@ -301,12 +440,13 @@ def run_ours(args):
         e2e = {"value": cells * args.steps / (ms_e2e * 1e-3) / 1e6, "unit": "MLUPS", "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps,
                "api": "FerroSolver.step_host(H_ext_mac faces from pinned host, phi to pinned host)"}
+        del faces, phi_host
 
     # ---- tau == 1 scalar form of the sweeps (bit-identical psi), reported separately
     fast = None
+    del solver
+    torch.cuda.empty_cache()
     if not args.no_fast_path and path == "faithful":
-        del solver
-        torch.cuda.empty_cache()
         fs = build_solver(res, "scalar", device, world, rank, args.workload)
         fs.step(args.warmup)
         ms_fast = timed(fs.step, args.steps)
@@ -320,14 +460,19 @@ def run_ours(args):
         del fs
         torch.cuda.empty_cache()
 
-    # ---- CPU baseline (rank 0, N = 1 only)
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cres = tuple(args.cpu_res)
-        v, ms_cpu, cores = cpu_rosensweig_mlups(cres, 3, 1)
-        cpu = {"value": v, "unit": "MLUPS", "cores": cores, "kind": "port",
-               "sample": f"same workload at {cres[0]}x{cres[1]}x{cres[2]}, 1 warm-up + 3 timed steps, "
-                         f"{ms_cpu:.0f} ms/step, torch CPU threads = {cores}, denormals flushed to zero"}
+    # ---- the other BASELINE configurations, the CPU baseline and the eager reference (rank 0, N = 1 only)
+    cfgs = cpu = eager = None
+    if rank == 0 and world == 1:
+        if not args.no_configs and args.workload == "rosensweig":
+            cfgs = other_configs(device, peak)
+        if not args.no_ref_eager:
+            eager = reference_eager_on_gpu()
+        if not args.no_cpu_baseline:
+            cres = tuple(args.cpu_res)
+            v, ms_cpu, cores, kind = cpu_rosensweig_mlups(cres, 3, 1)
+            cpu = {"value": v, "unit": "MLUPS", "cores": cores, "kind": kind,
+                   "sample": f"same workload at {cres[0]}x{cres[1]}x{cres[2]}, 1 warm-up + 3 timed steps, "
+                             f"{ms_cpu:.0f} ms/step, torch CPU threads = {cores}, denormals flushed to zero"}
 
     if rank == 0:
         model_bytes = (2 + N_SWEEPS) * BYTES_D3Q19
@@ -343,13 +488,23 @@ def run_ours(args):
                        "res_per_gpu": list(res), "cells": cells, "magnetic_path": path,
                        "parallelism": f"z-slab x{world}" if world > 1 else "single GPU",
                        "l2": "state (tens of GB) far larger than the 126 MB L2; no flush needed"},
+            "repetitions": {"n": len(reps_ms), "ms_per_rep": reps_ms, "reported": "median",
+                            "steps_per_rep": args.steps},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "fast_path": fast,
-            "gpu_launches": launches_per_step * args.steps, "clocks": clocks,
+            "gpu_launches": launches_per_step * args.steps * len(reps_ms), "clocks": clocks,
             "step_roofline": {"model_bytes_per_cell": model_bytes,
                               "mlups_at_peak": peak * 1e9 / model_bytes / 1e6,
                               "frac_of_model_roofline": mlups / world / (peak * 1e9 / model_bytes / 1e6)},
             "finite": finite,
         }
+        if world > 1:
+            line["slab_bit_identical"] = None if slab_verify is None else slab_verify["slab_bit_identical"]
+            line["slab_verify"] = slab_verify
+            line["exchange"] = exch
+        if cfgs is not None:
+            line["configs"] = cfgs
+        if eager is not None:
+            line["reference_eager_b200"] = eager
         emit(line)
     if world > 1:
         dist.destroy_process_group()

@@ -73,13 +73,22 @@ _lib = None
 
 
 def load():
-    """Load liblbmff.so (building it with nvcc first if it is missing and nvcc exists)."""
+    """Load liblbmff.so (rebuilding it with nvcc first when it is missing or older than csrc/ / include/)."""
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
-        from . import build as _build
-        _build.build()
+    from . import build as _build
+    if _build.needs_build():
+        # missing, or older than a source / header: never run a stale binary against an edited csrc/ (the GPU box
+        # has nvcc too).  Without nvcc a missing library is fatal, a stale one only warned about.
+        if _build.find_nvcc() is not None:
+            _build.build()
+        elif not os.path.exists(LIB_PATH):
+            raise RuntimeError("liblbmff.so is missing and nvcc was not found: build it with "
+                               "`python -m lbm_ferrofluid_b200.build` (there is no CPU fallback)")
+        else:
+            import warnings
+            warnings.warn("liblbmff.so is older than its sources and nvcc is not available to rebuild it")
     lib = ctypes.CDLL(LIB_PATH)
     for name, (restype, argtypes) in parse_header().items():
         fn = getattr(lib, name)   # AttributeError here = header/library mismatch: fail loudly

@@ -246,6 +246,8 @@ class SlabFerroSolver:
             raise RuntimeError(f"flags must be the slab-local [B,1,{layout.D},H,W] array")
         if layout.Dl < 4:
             raise RuntimeError("need at least 4 owned planes per slab")
+        if ((self.flags != FLUID) & (self.flags != OBSTACLE)).any().item():
+            raise RuntimeError("SlabFerroSolver supports FLUID / OBSTACLE flags only")
         self.dim, self.Q = 3, 19
         self.res = (self.D, self.Hh, self.W)
         self.dx, self.dt = float(dx), float(dt)
@@ -279,12 +281,23 @@ class SlabFerroSolver:
             self.H_ext_mac = [torch.full((self.B, 1, D, Hh, W + 1), vec[0], **opts),
                               torch.full((self.B, 1, D, Hh + 1, W), vec[1], **opts),
                               torch.full((self.B, 1, D + 1, Hh, W), vec[2], **opts)]
+            # same validity rule as FerroSolver: the scalar sweep kernels test neighbour flags only next to the
+            # GLOBAL outer shell, so every OBSTACLE cell of magnetic_flags must lie on it (global z = 0 / Dg-1, or
+            # the x / y rim), and only FLUID / OBSTACLE may occur
+            gz = layout.global_planes().to(self.device)
+            z_inner = ((gz != 0) & (gz != layout.Dg - 1)).reshape(1, 1, -1, 1, 1)
+            inner = self.mflags[:, :, :, 1:-1, 1:-1]
+            walls_on_shell = not ((inner == OBSTACLE) & z_inner).any().item()
+            if ((self.mflags != FLUID) & (self.mflags != OBSTACLE)).any().item():
+                raise RuntimeError("SlabFerroSolver supports FLUID / OBSTACLE magnetic_flags only")
+            scalar_ok = float(tau) == 1.0 and walls_on_shell
             if magnetic_path == "auto":
-                magnetic_path = "scalar" if float(tau) == 1.0 else "faithful"
+                magnetic_path = "scalar" if scalar_ok else "faithful"
             if magnetic_path not in ("scalar", "faithful"):
                 raise ValueError("magnetic_path must be 'auto', 'faithful' or 'scalar'")
-            if magnetic_path == "scalar" and float(tau) != 1.0:
-                raise RuntimeError("magnetic_path='scalar' needs tau == 1")
+            if magnetic_path == "scalar" and not scalar_ok:
+                raise RuntimeError("magnetic_path='scalar' needs tau == 1 and every OBSTACLE cell of magnetic_flags "
+                                   "on the outer shell of the global domain")
             self.magnetic_path = magnetic_path
             self.psi, self._rhs, self._chi = sc(1), sc(1), sc(1)
             self._h = [sc(19), sc(19)] if magnetic_path == "faithful" else [sc(2), sc(2)]
@@ -575,3 +588,74 @@ def step_virtual_ranks(solvers: Sequence[SlabFerroSolver], n: int = 1):
                 if r.overlap is not None:
                     r.overlap()
     return solvers
+
+
+# ---------------------------------------------------------------------------------------------------
+# hardware check of the N-rank data plane ("P ranks == 1 rank, bit for bit")
+# ---------------------------------------------------------------------------------------------------
+def verify_against_single_gpu(device, world: int, rank: int, res_global=(64, 48, 56), steps: int = 3,
+                              paths: Sequence[str] = ("faithful", "scalar"), n_sweeps: int = 30, group=None,
+                              exchanger_factory=None) -> dict:
+    """Run a small perturbed-interface Rosensweig case on ``world`` ranks through the REAL exchanger (NCCL between
+    processes, boundary planes first, halos travelling on the side stream under the interior kernels), gather the
+    owned planes and compare them BIT FOR BIT with a one-GPU FerroSolver run of the global domain on rank 0.
+    Collective: every rank of the process group must call it.  Returns (on every rank) a dict with
+    ``slab_bit_identical`` and, per magnetic path, the first differing field if any.  bench.py calls this before its
+    timed region whenever WORLD_SIZE > 1; tools/verify_slab.py is the torchrun entry point."""
+    import torch.distributed as dist
+
+    from . import initializers as I
+    from .solver import FerroSolver
+
+    Dg, Hh, W = res_global
+    dev = torch.device(device)
+    # identical global initial condition on every rank (seeded noise comes from the CPU generator)
+    flags = I.shell_flags(res_global, device=dev)
+    mflags = I.shell_flags(res_global, open_axes=(1,), device=dev)
+    rho = I.rosensweig_rho(res_global, flags, noise=1e-3, seed=11)
+    kw = dict(H_ext=[0.0, 100.0, 0.0], n_sweeps=n_sweeps, contact_angle=0.55 * math.pi, gravity=1e-4)
+    names = ("f", "g", "rho", "pressure", "vel", "psi")
+    report = {"res_global": list(res_global), "steps": steps, "world": world, "n_sweeps": n_sweeps, "paths": {}}
+    ok_all = True
+    for path in paths:
+        lay = SlabLayout(Dg, world, rank)
+        ex = (exchanger_factory or DistExchanger)(lay, dev) if group is None else DistExchanger(lay, dev, group)
+        slab = SlabFerroSolver(lay, lay.take(flags), exchanger=ex, magnetic_flags=lay.take(mflags),
+                               magnetic_path=path, **kw).initialize(lay.take(rho))
+        slab.step(steps)
+        if dev.type == "cuda":
+            torch.cuda.synchronize(dev)
+        mine = torch.cat([slab.owned(n).reshape(-1) for n in names] +
+                         ([slab.owned("h").reshape(-1)] if path == "faithful" else []))
+        parts = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(parts, mine, group=group)
+        verdict = torch.zeros(1, dtype=torch.int32, device=dev)
+        first_bad = None
+        if rank == 0:
+            one = FerroSolver(flags, magnetic_flags=mflags, magnetic_path=path, keep_force=False,
+                              **kw).initialize(rho).step(steps)
+            fluid = (mflags != OBSTACLE)
+            chans = [getattr(one, n).shape[1] for n in names] + ([19] if path == "faithful" else [])
+            fields = list(names) + (["h"] if path == "faithful" else [])
+            got = {n: [] for n in fields}
+            for part in parts:
+                o = 0
+                for n, c in zip(fields, chans):
+                    cnt = c * lay.Dl * Hh * W
+                    got[n].append(part[o:o + cnt].reshape(1, c, lay.Dl, Hh, W))
+                    o += cnt
+            for n in fields:
+                a, b = torch.cat(got[n], dim=2), getattr(one, n)
+                if n == "psi":      # wall-cell psi is never observed (the shell rule overwrites it)
+                    a, b = a * fluid, b * fluid
+                if not torch.equal(a, b):
+                    first_bad = first_bad or n
+            verdict[0] = 0 if first_bad is None else 1
+        dist.broadcast(verdict, src=0, group=group)
+        ok = int(verdict.item()) == 0
+        ok_all &= ok
+        report["paths"][path] = {"bit_identical": ok, "first_differing_field": first_bad,
+                                 "exchanges": ex.calls, "bytes_per_direction": ex.bytes_per_direction}
+        del slab, ex
+    report["slab_bit_identical"] = bool(ok_all)
+    return report

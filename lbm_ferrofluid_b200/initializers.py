@@ -57,30 +57,42 @@ def rosensweig_rho(res, flags, rho_liquid=0.2508, rho_gas=0.02381, frac=0.5, per
 
 
 def two_droplets_rho(res, flags, rho_liquid=0.2508, rho_gas=0.02381, global_depth=None, z_offset=0):
-    """Two spheres (discs in 2-D) of radius min(res)//4 centred at 3/8 and 5/8 of W
-    (demo_3d_LBM_two_droplets.py:134-149), walls at the liquid value."""
+    """The initial density of demo_3d_LBM_two_droplets.py:130-149 (2-D: demo_2d_LBM_two_droplets.py:117-134), cell
+    for cell: two spheres (discs) of radius min(res)//4 around the INTEGER centres (res[0]//2, res[1]//2,
+    3*res[2]//8) and (.., 5*res[2]//8), a cell being liquid when its squared integer distance is <= radius^2; walls
+    at the liquid value (:151).  Integer arithmetic throughout, so the field equals the demo's loop exactly
+    (tests/test_initializers.py).  ``global_depth`` / ``z_offset`` place a z-slab inside a larger periodic domain."""
     dev = flags.device
-    x, y, z = _coords(res, dev, z_offset)
+    three = len(res) == 3
     H, W = res[-2], res[-1]
-    D = global_depth if global_depth is not None else (res[0] if len(res) == 3 else 1)
-    full = (D, H, W) if len(res) == 3 else (H, W)
+    D = global_depth if global_depth is not None else (res[0] if three else 1)
+    full = (D, H, W) if three else (H, W)
     r = min(full) // 4
-    liquid = torch.zeros_like(x, dtype=torch.bool)
-    for cx in (0.375 * W, 0.625 * W):
-        d2 = (x - cx) ** 2 + (y - 0.5 * H) ** 2
-        if len(res) == 3:
-            d2 = d2 + (z - 0.5 * D) ** 2
-        liquid |= d2 < r * r
+    ax = [torch.arange(n, dtype=torch.int64, device=dev) for n in res]
+    if three:
+        z = ((ax[0] + int(z_offset)) % D).reshape(-1, 1, 1)
+        y, x = ax[1].reshape(1, -1, 1), ax[2].reshape(1, 1, -1)
+    else:
+        y, x = ax[0].reshape(-1, 1), ax[1].reshape(1, -1)
+    liquid = torch.zeros(tuple(res), dtype=torch.bool, device=dev)
+    for cx in (3 * W // 8, 5 * W // 8):
+        d2 = (x - cx) ** 2 + (y - H // 2) ** 2
+        if three:
+            d2 = d2 + (z - D // 2) ** 2
+        liquid |= d2 <= r * r
     rho = torch.where(liquid, rho_liquid, rho_gas).to(torch.float32).reshape(1, 1, *res)
     rho[flags == OBSTACLE] = rho_liquid
     return rho.contiguous()
 
 
-def double_shear_layer(res, device="cuda", u0=0.2):
-    """Velocity field of demo_2d_LBM.py:85-98."""
+def double_shear_layer(res, device="cuda", u0=0.2, sigma=0.05, kappa=80.0):
+    """Velocity field of demo_2d_LBM.py:85-98 (same in demo_2d_LBM_KBC.py).  The demo evaluates each value with
+    ``math`` in double precision and stores it into the fp32 tensor; here the same expressions, in the same order,
+    are evaluated in float64 on the device and rounded once."""
     H, W = res
-    j = torch.arange(H, dtype=torch.float32, device=device).reshape(H, 1).expand(H, W)
-    i = torch.arange(W, dtype=torch.float32, device=device).reshape(1, W).expand(H, W)
-    ux = torch.where(j <= H / 2, u0 * torch.tanh(80.0 * (j / H - 0.25)), u0 * torch.tanh(80.0 * (0.75 - j / H)))
-    uy = 0.05 * u0 * torch.sin(2 * math.pi * (i / W + 0.25))
-    return torch.stack([ux, uy]).reshape(1, 2, H, W).contiguous()
+    j = torch.arange(H, dtype=torch.float64, device=device).reshape(H, 1).expand(H, W)
+    i = torch.arange(W, dtype=torch.float64, device=device).reshape(1, W).expand(H, W)
+    ux = torch.where(j <= H / 2.0, u0 * torch.tanh(kappa * (1.0 * j / H - 0.25)),
+                     u0 * torch.tanh(kappa * (-1.0 * j / H + 0.75)))
+    uy = sigma * u0 * torch.sin(2.0 * math.pi * (1.0 * i / W + 0.25))
+    return torch.stack([ux, uy]).to(torch.float32).reshape(1, 2, H, W).contiguous()

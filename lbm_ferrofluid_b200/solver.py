@@ -313,11 +313,16 @@ class FerroSolver:
 
     def set_H_ext_faces_from_host(self, faces_host: Sequence[torch.Tensor]):
         """Upload the staggered applied field (the H_ext_mac argument of get_H_int) from pinned host memory,
-        asynchronously on the current stream.  Uniform-vector mode is switched to field mode: the cell-centred
-        field used for H2 is rebuilt as the mean of the two faces of each cell."""
+        asynchronously on the current stream.  Only the FACES are replaced: they feed the Poisson source
+        (get_H_int).  The cell-centred field of the Kelvin force, H2 = |H_ext + H_int|^2
+        (demo_3d_LBM_Rosensweig_instability.py:174-178), stays the ``H_ext`` given at construction -- exactly as in
+        the demos, where ``H_ext_const_real`` and ``H_ext_mac`` are two separate tensors the caller keeps
+        consistent.  For a time-varying applied field also update ``solver.H_ext`` (field mode) yourself."""
         if not self.magnetic:
             raise RuntimeError("solver was built without a magnetic subsystem")
         for dst, src in zip(self.H_ext_mac, faces_host):
+            if tuple(dst.shape) != tuple(src.shape):
+                raise RuntimeError(f"face array of shape {tuple(src.shape)} given, {tuple(dst.shape)} expected")
             dst.copy_(src, non_blocking=True)
 
     def step_host(self, faces_host: Optional[Sequence[torch.Tensor]], phi_host: Optional[torch.Tensor]):

@@ -19,11 +19,17 @@ import types
 import numpy as np
 import torch
 
-REF = os.environ.get("LBMFF_REFERENCE", "/root/reference")
-OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
+HERE = os.path.dirname(os.path.abspath(__file__))
+PYREF = os.path.join(HERE, "_ref", "pyref")          # sourceless bytecode of the reference (build_ref_solver.py)
+REF = os.environ.get("LBMFF_REFERENCE") or ("/root/reference" if os.path.isdir("/root/reference/src") else PYREF)
+OUT = os.path.join(HERE, "..", "tests", "golden")
 
 
 def import_reference():
+    """Import the UNMODIFIED reference solver from REF.  The repo ships its own ``src/LBM`` (the drop-in shim, a
+    regular package), which would shadow the reference's namespace package whenever the repo root is on sys.path --
+    so the result is checked: ``src`` must resolve inside REF, else this raises instead of silently testing the
+    product against itself."""
     for name in ("matplotlib", "matplotlib.colors", "matplotlib.ticker", "mcubes", "imageio"):
         if name not in sys.modules:
             sys.modules[name] = types.ModuleType(name)
@@ -32,6 +38,12 @@ def import_reference():
     sys.modules["matplotlib"].ticker = sys.modules["matplotlib.ticker"]
     if REF not in sys.path:
         sys.path.insert(0, REF)
+    import src.LBM.simulation as _sim
+    where = os.path.realpath(os.path.dirname(_sim.__file__))
+    if not where.startswith(os.path.realpath(REF) + os.sep):
+        raise ImportError(f"`src.LBM` resolved to {where}, not inside the reference at {REF}: the repo's own src/ shim "
+                          "is shadowing it (run this file as a script, or through oracle/ref_runner.py, with the "
+                          "repo root OFF sys.path)")
     from src.LBM.simulation import SimulationParameters, SimulationRunner  # noqa
     from src.LBM.utils import CellType, KBCType, get_staggered  # noqa
     return SimulationParameters, SimulationRunner, CellType, KBCType, get_staggered
@@ -57,11 +69,12 @@ def shell_flags(res, open_axes=(), interior_obstacles=0, rs=None):
 
 
 def make_runner(SimulationParameters, SimulationRunner, dim, dtype, res, **kw):
+    device = torch.device(kw.get("device", "cpu"))
     params = SimulationParameters(
-        dim=dim, dtype=dtype, device=torch.device("cpu"), simulation_size=(1, 1, *res),
+        dim=dim, dtype=dtype, device=device, simulation_size=(1, 1, *res),
         dt=kw.get("dt", 1.0),
         density_gas=kw.get("density_gas", 0.02381), density_fluid=kw.get("density_fluid", 0.2508),
-        contact_angle=torch.tensor([kw.get("contact_angle", 0.5 * math.pi)]).to(dtype),
+        contact_angle=torch.tensor([kw.get("contact_angle", 0.5 * math.pi)]).to(dtype).to(device),
         Q=9 if dim == 2 else 19, tau=kw.get("tau", 1.0),
         rho_gas=kw.get("rho_gas", 0.02381), rho_fluid=kw.get("rho_fluid", 0.2508),
         kappa=kw.get("kappa", 0.01), tau_g=kw.get("tau_g", 0.68), tau_f=kw.get("tau_f", 0.68), k=0.33)
@@ -180,12 +193,12 @@ def perturbed_interface(res, frac, rho_l, rho_g, dtype, droplets=False):
         z = torch.zeros_like(x)
         H, W = res
         D = 1
-    if droplets:
+    if droplets:   # the rule of demo_3d_LBM_two_droplets.py:130-149: integer centres, <= radius^2
         r = min(res) // 4
         liquid = torch.zeros_like(x, dtype=torch.bool)
-        for cx in (0.375 * W, 0.625 * W):
-            d2 = (x - cx) ** 2 + (y - 0.5 * H) ** 2 + ((z - 0.5 * D) ** 2 if dim == 3 else 0)
-            liquid |= d2 < r * r
+        for cx in (3 * W // 8, 5 * W // 8):
+            d2 = (x - cx) ** 2 + (y - H // 2) ** 2 + ((z - D // 2) ** 2 if dim == 3 else 0)
+            liquid |= d2 <= r * r
     else:
         height = frac * H + 2.0 * torch.sin(4 * math.pi * x / W) * (torch.cos(4 * math.pi * z / D) if dim == 3 else 1.0)
         liquid = y < height
@@ -193,12 +206,17 @@ def perturbed_interface(res, frac, rho_l, rho_g, dtype, droplets=False):
     return rho.to(dtype).reshape(1, 1, *res)
 
 
-def traj_hcz(name, dim, res, steps, dtype=torch.float32, *, magnetic=True, mag=100.0, gravity=1e-4, kappa=0.01,
-             tau_f=0.68, tau_g=0.68, contact_angle=0.5 * math.pi, frac=0.5, open_axes=(1,), kbc=False,
-             droplets=False, n_sweeps=30, seed=0):
+def run_hcz(dim, res, steps, dtype=torch.float32, *, magnetic=True, mag=100.0, gravity=1e-4, kappa=0.01,
+            tau_f=0.68, tau_g=0.68, contact_angle=0.5 * math.pi, frac=0.5, open_axes=(1,), kbc=False,
+            droplets=False, n_sweeps=30, seed=0, device="cpu", snapshots=(), noise=1e-3, timer=None):
+    """The demo loop (demo_3d_LBM_Rosensweig_instability.py:151-209 and its 2-D / two-droplet / multiphase siblings)
+    driven through the reference's own classes on ``device``.  Returns {step: state dict} for every step listed in
+    ``snapshots`` plus the final one; ``timer(step)`` (optional) is called before every step (ref_runner's clock)."""
     SP, SR, CellType, KBCType, get_staggered = import_reference()
     rho_g, rho_l = 0.02381, 0.2508
-    runner = make_runner(SP, SR, dim, dtype, res, kappa=kappa, tau_f=tau_f, tau_g=tau_g, contact_angle=contact_angle)
+    dev = torch.device(device)
+    runner = make_runner(SP, SR, dim, dtype, res, kappa=kappa, tau_f=tau_f, tau_g=tau_g, contact_angle=contact_angle,
+                         device=dev)
     prop, macro = runner.create_propagation(), runner.create_macro_compute()
     col, mgf = runner.create_collision_HCZ(), runner.create_LBM_magnetic()
     if kbc:
@@ -210,21 +228,27 @@ def traj_hcz(name, dim, res, steps, dtype=torch.float32, *, magnetic=True, mag=1
     mflags = shell_flags(res, open_axes=open_axes)
     rho = perturbed_interface(res, frac, rho_l, rho_g, dtype, droplets)
     torch.manual_seed(seed)
-    rho = rho * (1.0 + 1e-3 * (torch.rand(rho.shape, dtype=torch.float64).to(dtype) - 0.5))
+    rho = rho * (1.0 + noise * (torch.rand(rho.shape, dtype=torch.float64).to(dtype) - 0.5))
     rho[flags == 2] = rho_l
+    init = dict(rho0=rho.clone(), flags=flags, mflags=mflags)
+    flags, mflags, rho = flags.to(dev), mflags.to(dev), rho.to(dev)
     density = rho.clone()
-    vel = torch.zeros((1, dim, *res), dtype=dtype)
-    force = torch.zeros((1, dim, *res), dtype=dtype)
+    vel = torch.zeros((1, dim, *res), dtype=dtype, device=dev)
+    force = torch.zeros((1, dim, *res), dtype=dtype, device=dev)
     pressure = macro.get_pressure(dx=dx, dt=dt, density=density)
     f = col.get_feq_(dx=dx, dt=dt, rho=density, vel=vel, force=force)
     g = col.get_geq_(dx=dx, dt=dt, rho=rho, vel=vel, density=density, pressure=pressure, force=force, feq=f)
-    h = torch.zeros((1, Q, *res), dtype=dtype)
-    Hext = torch.zeros((1, dim, *res), dtype=dtype)
+    h = torch.zeros((1, Q, *res), dtype=dtype, device=dev)
+    Hext = torch.zeros((1, dim, *res), dtype=dtype, device=dev)
     Hext[:, 1] = mag
     Hmac = get_staggered(Hext, mode="replicate")
-    init = dict(rho0=rho.clone(), flags=flags, mflags=mflags)
     psi = torch.zeros_like(rho)
-    for _ in range(steps):
+    meta = dict(res=np.array(res), mag=mag, gravity=gravity, kappa=kappa, tau_f=tau_f, tau_g=tau_g,
+                contact_angle=contact_angle, magnetic=int(magnetic), kbc=int(kbc), n_sweeps=n_sweeps)
+    out = {}
+    for step in range(1, steps + 1):
+        if timer is not None:
+            timer(step)
         f = prop.propagation(f=f)
         g = prop.propagation(f=g)
         rho, vel, density = macro.macro_compute(dx=dx, dt=dt, f=f, rho=rho, vel=vel, flags=flags, density=density)
@@ -246,12 +270,20 @@ def traj_hcz(name, dim, res, steps, dtype=torch.float32, *, magnetic=True, mag=1
         f, g = col.collision(dx=dx, dt=dt, f=f, rho=rho, vel=vel, density=density, flags=flags, force=force, g=g,
                              pressure=pressure, dfai=dfai, dprho=dprho,
                              KBC_type=int(KBCType.KBC_A) if kbc else None)
-    meta = dict(steps=steps, res=np.array(res), mag=mag, gravity=gravity, kappa=kappa, tau_f=tau_f, tau_g=tau_g,
-                contact_angle=contact_angle, magnetic=int(magnetic), kbc=int(kbc), n_sweeps=n_sweeps)
-    out = dict(init, f=f, g=g, rho=rho, vel=vel, density=density, pressure=pressure, force=force, **meta)
-    if magnetic:
-        out.update(h=h, psi=psi, H2=H2, phi=phi)
-    np.savez_compressed(os.path.join(OUT, f"traj_{name}.npz"), **t2n(out))
+        if step in snapshots or step == steps:
+            st = dict(init, f=f, g=g, rho=rho, vel=vel, density=density, pressure=pressure, force=force, steps=step,
+                      **meta)
+            if magnetic:
+                st.update(h=h, psi=psi, H2=H2, phi=phi)
+            out[step] = t2n(st)
+    if timer is not None:
+        timer(steps + 1)
+    return out
+
+
+def traj_hcz(name, dim, res, steps, dtype=torch.float32, **kw):
+    out = run_hcz(dim, res, steps, dtype, **kw)[steps]
+    np.savez_compressed(os.path.join(OUT, f"traj_{name}.npz"), **out)
 
 
 def shear_layer(res, dtype):
@@ -306,6 +338,68 @@ def traj_single(name, res, steps, kbc, sc=False, dtype=torch.float32):
                         **t2n(dict(init, f=f, rho=rho, vel=vel, steps=steps, res=np.array(res))))
 
 
+# ---------------------------------------------------------------------------
+# initial conditions: the demos' OWN python loops, executed unmodified
+# ---------------------------------------------------------------------------
+class _Captured(Exception):
+    pass
+
+
+def demo_initial_fields(demo, res):
+    """Run ``<reference>/demo/<demo>.py::main(res=res, total_steps=0)`` unmodified on the CPU and capture the
+    arguments of its first ``get_feq_`` call -- the fields its O(N) python initialisation loops produced
+    (demo_3d_LBM_two_droplets.py:130-157, demo_2d_LBM.py:85-99).  The run is cut short right there."""
+    import importlib.util
+
+    import_reference()
+    rs = types.ModuleType("renderutils")
+    rs.SoftRenderer = lambda *a, **k: None
+    sys.modules.setdefault("renderutils", rs)
+    from src.LBM.LBM_collision import LBMCollision2d, LBMCollision3d
+
+    got = {}
+
+    def recorder(self, dx, dt, rho, vel, force=None):
+        got.update(rho=rho.clone(), vel=vel.clone())
+        raise _Captured
+
+    base = os.path.join(REF, "demo", demo)
+    path = base + ".py" if os.path.exists(base + ".py") else base + ".pyc"
+    spec = importlib.util.spec_from_file_location("_demo_" + demo, path)
+    mod = importlib.util.module_from_spec(spec)
+    saved = LBMCollision2d.get_feq_, LBMCollision3d.get_feq_, torch.cuda.is_available
+    cwd = os.getcwd()
+    try:
+        import tempfile
+        os.chdir(tempfile.mkdtemp())             # the demos mkdir next to __file__ only; cwd is irrelevant but keep clean
+        torch.cuda.is_available = lambda: False  # the demos pick their device from this
+        spec.loader.exec_module(mod)
+        LBMCollision2d.get_feq_ = LBMCollision3d.get_feq_ = recorder
+        try:
+            mod.main(res=list(res), total_steps=0)
+        except _Captured:
+            pass
+    finally:
+        LBMCollision2d.get_feq_, LBMCollision3d.get_feq_, torch.cuda.is_available = saved
+        os.chdir(cwd)
+    return got
+
+
+def gen_inits():
+    out = {}
+    for tag, demo, res in (("drop3d_a", "demo_3d_LBM_two_droplets", (12, 10, 26)),
+                           ("drop3d_b", "demo_3d_LBM_two_droplets", (9, 13, 21)),
+                           ("drop2d_a", "demo_2d_LBM_two_droplets", (22, 50)),
+                           ("drop2d_b", "demo_2d_LBM_two_droplets", (17, 37)),
+                           ("shear_a", "demo_2d_LBM", (20, 26)),
+                           ("shear_b", "demo_2d_LBM_KBC", (33, 17))):
+        got = demo_initial_fields(demo, res)
+        out[tag + "_res"] = np.array(res)
+        out[tag + "_rho"] = got["rho"].numpy()
+        out[tag + "_vel"] = got["vel"].numpy()
+    np.savez_compressed(os.path.join(OUT, "init_demos.npz"), **out)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(max(1, os.cpu_count() or 1))
@@ -323,6 +417,7 @@ def main():
     traj_single("bgk2d", (32, 32), 20, kbc=False)
     traj_single("kbc2d", (32, 32), 20, kbc=True)
     traj_single("sc2d", (24, 24), 10, kbc=False, sc=True)
+    gen_inits()
     print("golden vectors written to", os.path.normpath(OUT))
     for fn in sorted(os.listdir(OUT)):
         print(f"  {fn:28s} {os.path.getsize(os.path.join(OUT, fn)) / 1024:8.1f} KiB")

@@ -78,3 +78,47 @@ def test_slab_entry_argument_errors():
     with pytest.raises(RuntimeError, match="D <= Dg"):
         H.launch("lbmff_slab_shell_rule_3d", t.device, H.ptr(t), H.ptr(fl), ctypes.byref(Slab(4, 0, 0, 8)),
                  1, 8, 8, 8)
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_nccl_ranks_bit_identical_to_one_gpu(world):
+    """The REAL data plane (one process per GPU, NCCL halos on the side stream overlapping the interior kernels)
+    against the one-GPU run, bit for bit (tools/verify_slab.py).  Needs `world` GPUs on the box; bench.py runs the
+    same check before every N > 1 timing."""
+    import json
+    import os
+    import socket
+    import subprocess
+    import sys
+
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port),
+                        os.path.join(root, "tools", "verify_slab.py")], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    rep = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+    assert rep["slab_bit_identical"] and all(p["bit_identical"] for p in rep["paths"].values())
+
+
+def test_slab_scalar_path_refused_with_interior_magnetic_wall():
+    """the scalar sweep kernels assume magnetic walls on the global shell only; the slab solver must
+    check it like FerroSolver does."""
+    from lbm_ferrofluid_b200.distributed import SlabFerroSolver, SlabLayout, slab_shell_flags
+
+    dev = torch.device("cuda")
+    lay = SlabLayout(24, 2, 0)
+    lf = slab_shell_flags(lay, 14, 18, device=dev)
+    lm = slab_shell_flags(lay, 14, 18, open_axes=(1,), device=dev)
+    lm[0, 0, 6, 5, 5] = 2
+    kw = dict(H_ext=[0.0, 100.0, 0.0], n_sweeps=6)
+    with pytest.raises(RuntimeError, match="outer shell"):
+        SlabFerroSolver(lay, lf, magnetic_flags=lm, magnetic_path="scalar", **kw)
+    assert SlabFerroSolver(lay, lf, magnetic_flags=lm, magnetic_path="auto", **kw).magnetic_path == "faithful"
+    lm[0, 0, 6, 5, 5] = 7
+    with pytest.raises(RuntimeError, match="FLUID / OBSTACLE"):
+        SlabFerroSolver(lay, lf, magnetic_flags=lm, magnetic_path="faithful", **kw)
