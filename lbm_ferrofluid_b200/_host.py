@@ -75,3 +75,16 @@ def fluid_params(op, dx=1.0, dt=1.0, cot=0.0, gravity=0.0) -> FluidParams:
         kappa=float(getattr(op, "_kappa", 0.0)), tau=float(op._tau),
         tau_f=float(getattr(op, "_tau_f", 1.0)), tau_g=float(getattr(op, "_tau_g", 1.0)),
         gravity=float(gravity), cot_theta=float(cot))
+
+
+class nvtx:
+    """NVTX range around a stage of the step (visible in nsys / ncu --nvtx; a no-op without a profiler)."""
+
+    def __init__(self, name: str):
+        self.name = name
+
+    def __enter__(self):
+        torch.cuda.nvtx.range_push(self.name)
+
+    def __exit__(self, *exc):
+        torch.cuda.nvtx.range_pop()

@@ -227,11 +227,13 @@ class FerroSolver:
         d, sz, suf = self.dim, self._sizes(), H.suffix(self.dim)
         cur, nxt = self._cur, 1 - self._cur
         dev = self.device
-        H.launch("lbmff_hcz_moments_" + suf, dev, H.ptr(self._f[cur]), H.ptr(self.flags), H.ptr(self.rho),
-                 H.ptr(self._chi if self.magnetic else None), self.params, *sz)
+        with H.nvtx("lbmff:moments"):
+            H.launch("lbmff_hcz_moments_" + suf, dev, H.ptr(self._f[cur]), H.ptr(self.flags), H.ptr(self.rho),
+                     H.ptr(self._chi if self.magnetic else None), self.params, *sz)
         # capillary_process part 1 does not depend on the magnetic subsystem: issue it first
-        H.launch(f"lbmff_hcz_capillary_fields_{d}d", dev, H.ptr(self.rho), H.ptr(self.flags),
-                 H.ptr(self.pressure), self.params, H.ptr(self._ws), *sz)
+        with H.nvtx("lbmff:capillary_fields"):
+            H.launch(f"lbmff_hcz_capillary_fields_{d}d", dev, H.ptr(self.rho), H.ptr(self.flags),
+                     H.ptr(self.pressure), self.params, H.ptr(self._ws), *sz)
         if after_rho_final is not None:
             after_rho_final()
         chi = psi = mfl = hext = None
@@ -239,13 +241,14 @@ class FerroSolver:
         if self.magnetic:
             if before_source is not None:
                 before_source()
-            H.launch(f"lbmff_magnetic_source_{d}d", dev, H.ptr(self._chi), H.ptr(self.mflags),
-                     *[H.ptr(t) for t in self.H_ext_mac], self.dx, H.ptr(self._rhs), *sz)
+            with H.nvtx("lbmff:magnetic_source"):
+                H.launch(f"lbmff_magnetic_source_{d}d", dev, H.ptr(self._chi), H.ptr(self.mflags),
+                         *[H.ptr(t) for t in self.H_ext_mac], self.dx, H.ptr(self._rhs), *sz)
             if before_source is not None:   # the faces are free again: the next upload may start under the sweeps
                 self._faces_read = torch.cuda.Event()
                 self._faces_read.record()
             m = self._mcur
-            with self._timed("sweeps"):
+            with H.nvtx("lbmff:magnetic_sweeps"), self._timed("sweeps"):
                 if self.magnetic_path == "converged":
                     self.cg.solve(self._rhs, self.psi)
                 elif self.magnetic_path == "faithful":
@@ -265,7 +268,7 @@ class FerroSolver:
                 self.params]
         if d == 2:
             args.append(self._kbc_mode)
-        with self._timed("collide_stream"):
+        with H.nvtx("lbmff:collide_stream"), self._timed("collide_stream"):
             H.launch("lbmff_hcz_collide_stream_" + suf, dev, *args, H.ptr(self.vel), H.ptr(self.pressure),
                      H.ptr(self.force), *sz)
         self._cur = nxt
