@@ -14,7 +14,7 @@ of the array (wall shell included) x outer steps.  Prints ONE JSON line (rank 0)
                parameter phi (what the demos render) back to pinned memory.
  * roofline  : dominant kernel, algorithmic bytes / CUDA-event duration vs MEASURED_PEAKS.json.
  * cpu_baseline / --impl reference : the REFERENCE's own PyTorch implementation on the host cores (kind "reference":
-               the byte-compiled copy oracle/_ref/pyref run by oracle/ref_runner.py in its own process), bounded
+               the byte-compiled copy oracle/_ref/pyref.zip run by oracle/ref_runner.py in its own process), bounded
                sample; the oracle port (oracle/lbm_oracle.py, kind "port") only if that copy is absent.
  * configs   : (N = 1) the other BASELINE.json configurations, each a short timed run with its own byte model.
  * slab_verify (N > 1) : before timing, a small case is run through the real NCCL exchanger and compared bit for
@@ -91,7 +91,7 @@ def _ref_runner(argv, timeout):
 
 
 def reference_present():
-    return os.path.exists(os.path.join(ROOT, "oracle", "_ref", "pyref", "MANIFEST.json")) or \
+    return os.path.exists(os.path.join(ROOT, "oracle", "_ref", "pyref.zip")) or \
         os.path.isdir("/root/reference/src/LBM")
 
 
@@ -147,10 +147,10 @@ def run_reference(args):
     sample = (f"same workload at {res[0]}x{res[1]}x{res[2]} (bounded sample), {warmup} warm-up + {steps} timed steps, "
               f"torch CPU threads = {cores}, denormals flushed to zero (timing only)")
     note = ("the reference's own src/LBM classes driven through the demo loop on the host cores (byte-compiled copy "
-            "oracle/_ref/pyref, unmodified; 512^3 is out of its reach: three [1,19,3,D,H,W] temporaries of 30 GB)"
+            "oracle/_ref/pyref.zip, unmodified; 512^3 is out of its reach: three [1,19,3,D,H,W] temporaries of 30 GB)"
             if kind == "reference" else
             "oracle port (torch-CPU restatement pinned against the reference's golden vectors): the byte-compiled "
-            "reference oracle/_ref/pyref was not found")
+            "reference oracle/_ref/pyref.zip was not found")
     line = {
         "impl": "reference", "metric": METRIC, "value": mlups, "unit": "MLUPS", "n_gpus": args.gpus,
         "steps": steps, "warmup": warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
@@ -306,7 +306,7 @@ def reference_eager_on_gpu(res=(256, 256, 256)):
         j = _ref_runner(["time", "--dim", "3", "--res", *map(str, res), "--mag", str(MAG), "--steps", "3", "--warmup",
                          "1", "--device", "cuda"], timeout=900)
         return {"value": j["mlups"], "unit": "MLUPS", "ms_per_step": j["ms_per_step"], "res": list(res),
-                "what": "unmodified reference (oracle/_ref/pyref), eager PyTorch, device='cuda', fp32, same "
+                "what": "unmodified reference (oracle/_ref/pyref.zip), eager PyTorch, device='cuda', fp32, same "
                         "workload; 512^3 is out of its reach (three [1,19,3,D,H,W] temporaries of 30 GB each)"}
     except Exception as e:
         return {"value": None, "error": str(e)[:200]}

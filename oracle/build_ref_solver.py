@@ -4,14 +4,14 @@
 
 The reference solver (/root/reference/src/LBM/**, pure PyTorch) and its demos (/root/reference/demo/demo_*.py) exist
 only in the build container; the GPU box gets a snapshot of this repo.  Same pattern as build_ref_rasterizer.py: the
-reference is *compiled from the sources where they lie* -- here with CPython's byte compiler -- into the git-ignored
-``oracle/_ref/pyref/`` (sourceless ``.pyc`` files in the legacy layout ``pkg/mod.pyc``, which the import system loads
-without the ``.py``), so no reference source enters this repository or its history, yet the unmodified code runs on the
-box:
+reference is *compiled from the sources where they lie* -- here with CPython's byte compiler -- into ONE git-ignored
+archive, ``oracle/_ref/pyref.zip`` (sourceless ``.pyc`` members in the legacy layout ``pkg/mod.pyc``, which zipimport
+loads without the ``.py``; an archive because the gpurun snapshot drops loose ``*.pyc`` files), so no reference source
+enters this repository or its history, yet the unmodified code runs on the box:
 
-    oracle/_ref/pyref/src/LBM/**.pyc        the solver classes   (import root: oracle/_ref/pyref)
-    oracle/_ref/pyref/demo/demo_*.pyc       the demo scripts     (run as ``python demo_x.pyc`` with cwd = a copy of demo/)
-    oracle/_ref/pyref/MANIFEST.json         what was compiled, from where, with which interpreter
+    pyref.zip/src/LBM/**.pyc        the solver classes   (import root: the archive itself, put on sys.path)
+    pyref.zip/demo/demo_*.pyc       the demo scripts     (executed by oracle/run_ref_demo.py with cwd = a temp demo/)
+    pyref.zip/MANIFEST.json         what was compiled, from where, with which interpreter
 
 Consumers (all test / measurement infrastructure, never the product path): oracle/ref_runner.py (the reference run in
 a subprocess on CPU or CUDA: parity trajectories and the reference arm of bench.py), tests/test_gpu_reference.py,
@@ -26,11 +26,12 @@ import json
 import os
 import py_compile
 import sys
+import tempfile
+import zipfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 REF = os.environ.get("LBMFF_REFERENCE", "/root/reference")
-OUT = os.path.join(HERE, "_ref", "pyref")
-MANIFEST = os.path.join(OUT, "MANIFEST.json")
+OUT = os.path.join(HERE, "_ref", "pyref.zip")
 
 
 def _sources():
@@ -39,38 +40,61 @@ def _sources():
     return srcs, demos
 
 
+def manifest():
+    try:
+        with zipfile.ZipFile(OUT) as z:
+            return json.loads(z.read("MANIFEST.json"))
+    except Exception:
+        return None
+
+
 def available() -> bool:
     """True when a usable byte-compiled reference is present (built here or shipped with the snapshot)."""
-    try:
-        with open(MANIFEST) as fh:
-            m = json.load(fh)
-    except Exception:
-        return False
-    return m.get("magic") == importlib.util.MAGIC_NUMBER.hex() and os.path.isdir(os.path.join(OUT, "src", "LBM"))
+    m = manifest()
+    return bool(m) and m.get("magic") == importlib.util.MAGIC_NUMBER.hex()
 
 
 def build(force: bool = False):
-    """Byte-compile the reference into oracle/_ref/pyref.  Returns the directory, or None when the reference
-    checkout is absent (the GPU box: the prebuilt directory travelled with the snapshot)."""
+    """Byte-compile the reference into oracle/_ref/pyref.zip.  Returns the archive path, or None when the reference
+    checkout is absent and no archive travelled (the GPU box uses the prebuilt one)."""
     if not os.path.isdir(os.path.join(REF, "src", "LBM")):
         return OUT if available() else None
     srcs, demos = _sources()
     newest = max(os.path.getmtime(p) for p in srcs + demos)
-    if not force and available() and os.path.getmtime(MANIFEST) >= newest:
+    if not force and available() and os.path.getmtime(OUT) >= newest:
         return OUT
-    files = []
-    for p in srcs + demos:
-        rel = os.path.relpath(p, REF)
-        dst = os.path.join(OUT, rel[:-3] + ".pyc")
-        os.makedirs(os.path.dirname(dst), exist_ok=True)
-        # dfile: the path shown in tracebacks -- point at the reference checkout so a failure is attributable
-        py_compile.compile(p, cfile=dst, dfile=os.path.join("<reference>", rel), doraise=True,
-                           invalidation_mode=py_compile.PycInvalidationMode.UNCHECKED_HASH)
-        files.append(rel)
-    with open(MANIFEST, "w") as fh:
-        json.dump({"reference": REF, "python": sys.version.split()[0], "magic": importlib.util.MAGIC_NUMBER.hex(),
-                   "files": files}, fh, indent=1)
+    os.makedirs(os.path.dirname(OUT), exist_ok=True)
+    files, dirs = [], set()
+    with tempfile.TemporaryDirectory() as tmp, zipfile.ZipFile(OUT + ".tmp", "w", zipfile.ZIP_DEFLATED) as z:
+        for p in srcs + demos:
+            rel = os.path.relpath(p, REF)
+            # explicit directory members: zipimport recognises the reference's namespace packages (src/ and src/LBM/
+            # have no __init__) only through them
+            parts = rel.split(os.sep)[:-1]
+            for n in range(1, len(parts) + 1):
+                d = "/".join(parts[:n]) + "/"
+                if d not in dirs:
+                    dirs.add(d)
+                    z.writestr(d, "")
+            dst = os.path.join(tmp, rel[:-3] + ".pyc")
+            os.makedirs(os.path.dirname(dst), exist_ok=True)
+            # dfile: the path shown in tracebacks -- point at the reference checkout so a failure is attributable
+            py_compile.compile(p, cfile=dst, dfile=os.path.join("<reference>", rel), doraise=True,
+                               invalidation_mode=py_compile.PycInvalidationMode.UNCHECKED_HASH)
+            z.write(dst, rel[:-3] + ".pyc")
+            files.append(rel)
+        z.writestr("MANIFEST.json", json.dumps(
+            {"reference": REF, "python": sys.version.split()[0], "magic": importlib.util.MAGIC_NUMBER.hex(),
+             "files": files}, indent=1))
+    os.replace(OUT + ".tmp", OUT)
     return OUT
+
+
+def demo_code(name: str):
+    """Code object of demo/<name>.py from the archive (run_ref_demo.py executes it as __main__)."""
+    import marshal
+    with zipfile.ZipFile(OUT) as z:
+        return marshal.loads(z.read(f"demo/{name}.pyc")[16:])
 
 
 if __name__ == "__main__":

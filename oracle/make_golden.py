@@ -20,7 +20,7 @@ import numpy as np
 import torch
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-PYREF = os.path.join(HERE, "_ref", "pyref")          # sourceless bytecode of the reference (build_ref_solver.py)
+PYREF = os.path.join(HERE, "_ref", "pyref.zip")      # sourceless bytecode of the reference (build_ref_solver.py)
 REF = os.environ.get("LBMFF_REFERENCE") or ("/root/reference" if os.path.isdir("/root/reference/src") else PYREF)
 OUT = os.path.join(HERE, "..", "tests", "golden")
 

@@ -4,7 +4,7 @@
 The repo ships a ``src/LBM`` package of its own (the drop-in shim), so the reference's ``src.LBM`` can never be
 imported into a process that has the repo root on sys.path.  This script is therefore always run as a *script*
 (sys.path[0] = oracle/, repo root absent); it imports the reference from /root/reference when that exists (build
-container) or from the byte-compiled copy oracle/_ref/pyref (GPU box; oracle/build_ref_solver.py) and drives the
+container) or from the byte-compiled copy oracle/_ref/pyref.zip (GPU box; oracle/build_ref_solver.py) and drives the
 reference's own classes through the demo loop (make_golden.run_hcz).
 
     python oracle/ref_runner.py traj --dim 3 --res 130 66 130 --mag 100 --steps 10 50 --dtype float32 \

@@ -1,15 +1,14 @@
 """The reference's UNMODIFIED demo scripts run their time loops on the GPU on top of this repo (SURVEY.md 8b,
 VERDICT r1 next-round item 1b).
 
-The scripts are the byte-compiled copies under oracle/_ref/pyref/demo (oracle/build_ref_solver.py: compiled from
+The scripts are the byte-compiled members of oracle/_ref/pyref.zip (oracle/build_ref_solver.py: compiled from
 /root/reference/demo/*.py where they lie; sourceless, so nothing of the reference enters this repository).  Each one is
-copied to a temp ``demo/`` directory (the scripts write frames next to themselves), started there with this repo and
-``compat/`` ahead of everything on PYTHONPATH -- so ``src.LBM.*`` is our shim over the C ABI and ``imageio`` /
+executed by oracle/run_ref_demo.py as ``__main__`` in a temp ``demo/`` directory (the scripts write frames next to
+themselves), with this repo and ``compat/`` ahead of everything on PYTHONPATH -- so ``src.LBM.*`` is our shim over the C ABI and ``imageio`` /
 ``renderutils`` / ``mcubes`` are the stand-ins -- and must run 20 steps, exit 0 and leave at least one frame and the
 MP4 it assembles on disk.  tests/test_demo_compat.py is the CPU-side half of the same contract."""
 import glob
 import os
-import shutil
 import subprocess
 import sys
 
@@ -18,7 +17,8 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-PYREF_DEMOS = os.path.join(ROOT, "oracle", "_ref", "pyref", "demo")
+PYREF = os.path.join(ROOT, "oracle", "_ref", "pyref.zip")
+LAUNCH = os.path.join(ROOT, "oracle", "run_ref_demo.py")
 DEMOS = ["demo_2d_LBM", "demo_2d_LBM_KBC", "demo_2d_LBM_Rosensweig_instability", "demo_2d_LBM_droplet_spread",
          "demo_2d_LBM_multiphase_HCZ", "demo_2d_LBM_multiphase_SC", "demo_2d_LBM_two_droplets", "demo_2d_wave",
          "demo_3d_LBM_Rosensweig_instability", "demo_3d_LBM_droplet_spread", "demo_3d_LBM_multiphase",
@@ -32,14 +32,12 @@ ARGS = {"demo_3d_LBM_two_droplets": ["--res", "24", "24", "48"],
 
 @pytest.mark.parametrize("name", DEMOS)
 def test_unmodified_demo_runs_its_time_loop_on_the_gpu(name, tmp_path):
-    pyc = os.path.join(PYREF_DEMOS, name + ".pyc")
-    if not os.path.exists(pyc):
-        pytest.fail(f"{pyc} is missing: run __graft_entry__.build() in the build container")
+    if not os.path.exists(PYREF):
+        pytest.fail(f"{PYREF} is missing: run __graft_entry__.build() in the build container")
     demo_dir = tmp_path / "demo"
     demo_dir.mkdir()
-    shutil.copy(pyc, demo_dir / (name + ".pyc"))
     env = dict(os.environ, PYTHONPATH=os.pathsep.join([ROOT, os.path.join(ROOT, "compat")]))
-    r = subprocess.run([sys.executable, name + ".pyc", "--total_steps", "20", *ARGS.get(name, [])], cwd=demo_dir,
+    r = subprocess.run([sys.executable, LAUNCH, name, "--total_steps", "20", *ARGS.get(name, [])], cwd=demo_dir,
                        env=env, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, f"{name} failed:\n{r.stderr[-3000:]}"
     frames = glob.glob(str(demo_dir / "demo_data_*" / "*.png"))

@@ -1,6 +1,6 @@
 """Parity at DEMO SIZE against the reference itself, run on the same GPU.
 
-The unmodified reference (byte-compiled into oracle/_ref/pyref by oracle/build_ref_solver.py; run in its own
+The unmodified reference (byte-compiled into oracle/_ref/pyref.zip by oracle/build_ref_solver.py; run in its own
 process by oracle/ref_runner.py because its package is called ``src`` like our shim) executes the demo loop on CUDA in
 fp32 and in fp64 at the demos' default grids -- 130 x 66 x 130 (demo_3d_LBM_Rosensweig_instability.py:253) and 130^2
 (demo_2d_LBM_Rosensweig_instability.py:218) -- for mg 85 and mg 100, with snapshots after N = 10 and N = 50 steps.
@@ -72,7 +72,7 @@ def _run_reference(case, dtype, tmp):
 @pytest.fixture(scope="module")
 def refdir(tmp_path_factory):
     if not _have_reference():
-        pytest.fail("oracle/_ref/pyref is missing: run __graft_entry__.build() (oracle/build_ref_solver.py) in the "
+        pytest.fail("oracle/_ref/pyref.zip is missing: run __graft_entry__.build() (oracle/build_ref_solver.py) in the "
                     "build container so the byte-compiled reference travels with the snapshot")
     return str(tmp_path_factory.mktemp("ref"))
 
