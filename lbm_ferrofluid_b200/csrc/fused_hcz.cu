@@ -15,6 +15,7 @@
 #include "capillary.cuh"
 #include "collide.cuh"
 #include "hcz_fast.cuh"
+#include "tma.cuh"
 
 namespace lbmff {
 
@@ -192,10 +193,34 @@ struct SmemPop {   // slot q of this thread: s[q * kThreads]
   __device__ __forceinline__ float operator()(int q) const { return s[q * kThreads]; }
 };
 
-template <int DIM, bool MAGNETIC, bool IDX32, class GV, class FV>
+// The five gradients of capillary_process part 2 at a FLUID cell (HCZ_3d.py:228-242): lap, fai, prho and, with the
+// magnetic subsystem, chi and psi.  All stencil inputs carry the get_grad shell rule in their data, so the 18-point
+// stencils are plain constant-offset reads around the interior-clamped centre.  GlobalStencil reads them from
+// global memory (L1/L2); the TMA kernel below supplies a shared-memory sampler with the same arithmetic.
+template <int DIM, bool MAGNETIC>
+struct GlobalStencil {
+  __device__ __forceinline__ void operator()(const PlaneCell& c, const Grid& g, const float* __restrict__ ws,
+                                             const float* __restrict__ chi, const float* __restrict__ psi,
+                                             float inv12dx, float* glap, float* gfai, float* gprho, float* gchi,
+                                             float* gpsi) const {
+    const int x = interior(c.x, g.W), y = interior(c.y, g.H), z = DIM == 3 ? interior_z(g, c.z) : 0;
+    const int HW = g.H * g.W;
+    const int j0 = c.i + (x - c.x) + (y - c.y) * g.W + (z - c.z) * HW;
+    const float* w = ws + j0;
+    grad_at_fast<DIM>(Centred32{w, g.W, HW, x, y, z}, x, y, z, inv12dx, glap);
+    grad_at_fast<DIM>(Centred32{w + g.N, g.W, HW, x, y, z}, x, y, z, inv12dx, gfai);
+    grad_at_fast<DIM>(Centred32{w + 2 * g.N, g.W, HW, x, y, z}, x, y, z, inv12dx, gprho);
+    if (MAGNETIC) {
+      grad_at_fast<DIM>(Centred32{chi + j0, g.W, HW, x, y, z}, x, y, z, inv12dx, gchi);
+      grad_at_fast<DIM>(Centred32{psi + j0, g.W, HW, x, y, z}, x, y, z, inv12dx, gpsi);
+    }
+  }
+};
+
+template <int DIM, bool MAGNETIC, bool IDX32, class GV, class FV, class ST>
 __device__ __forceinline__ void hcz_cs_cell(const PlaneCell& c, const PopIndex<IDX32>& at, const GV gv, const FV fv,
                                             const uint8_t fl, const float rho, const CsArgs& A, const Consts& k,
-                                            const KbcScalars& K, const Grid& g) {
+                                            const KbcScalars& K, const Grid& g, const ST& stencil) {
   using L = Lat<DIM>;
   const int i = c.i;
   float* __restrict__ fo = A.fo; float* __restrict__ go = A.go;
@@ -216,14 +241,8 @@ __device__ __forceinline__ void hcz_cs_cell(const PlaneCell& c, const PopIndex<I
   }
   // ---- capillary_process part 2 at a FLUID cell (HCZ_3d.py:217-261); all stencil inputs carry the
   // get_grad shell rule in their data, so the 18-point stencils are plain constant-offset loads
-  const int x = interior(c.x, g.W), y = interior(c.y, g.H), z = DIM == 3 ? interior_z(g, c.z) : 0;
-  const int HW = g.H * g.W;
-  const int j0 = i + (x - c.x) + (y - c.y) * g.W + (z - c.z) * HW;
-  const float* w = ws + j0;
-  float glap[3], gfai[3], gprho[3];
-  grad_at_fast<DIM>(Centred32{w, g.W, HW, x, y, z}, x, y, z, k.inv12dx, glap);
-  grad_at_fast<DIM>(Centred32{w + g.N, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gfai);
-  grad_at_fast<DIM>(Centred32{w + 2 * g.N, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gprho);
+  float glap[3], gfai[3], gprho[3], gchi[3], gpsi[3];
+  stencil(c, g, ws, chi, psi, k.inv12dx, glap, gfai, gprho, gchi, gpsi);
   const float dn = affine_density(rho, k.aff);
   float F[DIM];
 #pragma unroll
@@ -232,9 +251,7 @@ __device__ __forceinline__ void hcz_cs_cell(const PlaneCell& c, const PopIndex<I
     if (a == 1) F[a] += k.grav_y * dn;
   }
   if (MAGNETIC) {
-    float gchi[3], gpsi[3], H2 = 0.0f;
-    grad_at_fast<DIM>(Centred32{chi + j0, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gchi);
-    grad_at_fast<DIM>(Centred32{psi + j0, g.W, HW, x, y, z}, x, y, z, k.inv12dx, gpsi);
+    float H2 = 0.0f;
 #pragma unroll
     for (int a = 0; a < DIM; ++a) {
       const float he = Hext ? __ldg(Hext + a * g.N + i) : Hu.v[a];
@@ -307,7 +324,8 @@ k_hcz_collide_stream(const float* __restrict__ fi, const float* __restrict__ gi,
     fv[q] = ld_spec(fi + j);
   }
   const float rho = A.rho_[i];   // (harmless on non-FLUID cells, and not behind the flag's round trip)
-  hcz_cs_cell<DIM, MAGNETIC, IDX32>(c, at, RegPop{gv}, RegPop{fv}, A.flags[i], rho, A, k, K, g);
+  hcz_cs_cell<DIM, MAGNETIC, IDX32>(c, at, RegPop{gv}, RegPop{fv}, A.flags[i], rho, A, k, K, g,
+                                    GlobalStencil<DIM, MAGNETIC>{});
 }
 
 // The same step with the 2Q pulls of the NEXT cell in flight while the current one is computed: a block marches
@@ -381,7 +399,163 @@ k_hcz_collide_stream_pf(const float* __restrict__ fi, const float* __restrict__ 
     float gv[Q];
 #pragma unroll
     for (int q = 0; q < Q; ++q) gv[q] = s[q * kThreads];
-    hcz_cs_cell<DIM, MAGNETIC, IDX32>(c, at, RegPop{gv}, SmemPop{s + Q * kThreads}, fl, rho, A, k, K, g);
+    hcz_cs_cell<DIM, MAGNETIC, IDX32>(c, at, RegPop{gv}, SmemPop{s + Q * kThreads}, fl, rho, A, k, K, g,
+                                      GlobalStencil<DIM, MAGNETIC>{});
+  }
+}
+
+// ---- the same step with every tile brought in by the TMA unit --------------------------------------------------
+// 64 x 4 blocks march along z like k_hcz_collide_stream_pf, but no thread computes a load address on the hot path:
+//  * the 38 pulled populations of the next plane arrive as 38 box loads (cp.async.bulk.tensor.4d) of the 64 x 4 tile
+//    of population q at element coordinates (x0 - e_x, y0 - e_y, z - e_z, q) -- tiled tensor maps take unaligned
+//    start coordinates -- into a two-stage [2Q][4][64] buffer; a thread reads its value at [q][ty][tx];
+//  * the five stencil fields (lap | fai | prho of ws, chi, psi) arrive as rim-extended 68 x 6 boxes, one z plane per
+//    step, into a four-slot ring holding planes z-1, z, z+1 (+ the one in flight), so the 90 stencil reads per cell
+//    are LDS with immediate offsets instead of L1/L2 round trips behind per-load address arithmetic;
+//  * completion is tracked by two mbarriers (expect_tx); one __syncthreads per plane frees the stage for refill.
+// TMA zero-fills outside the tensor while the lattice is periodic: a cell whose pull source wraps around the array
+// (x = 0 / W-1, y = 0 / H-1, local z = 0 / D-1: ~13 % of the warps at 512^3, all of them wall cells in the named
+// configurations) re-reads the wrapped populations directly.  Stencil centres are clamped to the interior exactly
+// as in GlobalStencil: in x / y the clamp is an index shift inside the rim-extended tile, planes on the global z
+// shell (block-uniform test) take the global sampler.  The cell arithmetic is the same hcz_cs_cell, so results are
+// bit-identical to the other two kernels (tests/test_gpu_fused.py).
+constexpr int kTileX = 64, kTileY = 4;
+constexpr int kStW = 68, kStH = 6;                    // rim-extended stencil tile; 68 * 4 B is a multiple of 16
+constexpr int kStWs = 1248;                           // [lap | fai | prho] = 3 * 408 floats, padded to 4992 B
+constexpr int kStSc = 416;                            // one scalar field, padded to 1664 B (multiples of 128 B)
+constexpr int kStSlot = kStWs + 2 * kStSc;            // 2080 floats = 8320 B per z plane
+constexpr int kPullStage = 2 * 19 * kThreads;         // 9728 floats = 38912 B
+constexpr int kTmaSmemFloats = 2 * kPullStage + 4 * kStSlot;
+constexpr int kTmaSmemBytes = kTmaSmemFloats * 4 + 16 /* two mbarriers */ + 128 /* alignment slack */;
+
+struct SmemField {   // sampler around the thread's (clamped) centre: offsets are compile-time after inlining
+  const float* c;    // centre element in the slot of plane z
+  int dm, dp;        // float offsets from the slot of plane z to the slots of planes z-1 / z+1
+  __device__ __forceinline__ float operator()(int dx, int dy, int dz) const {
+    const float* p = c + (dz < 0 ? dm : (dz > 0 ? dp : 0));
+    return p[dy * kStW + dx];
+  }
+};
+template <bool MAGNETIC>
+struct SmemStencil {
+  const float* c;
+  int dm, dp;
+  __device__ __forceinline__ void operator()(const PlaneCell&, const Grid&, const float*, const float*, const float*,
+                                             float inv12dx, float* glap, float* gfai, float* gprho, float* gchi,
+                                             float* gpsi) const {
+    grad_at_fast<3>(SmemField{c, dm, dp}, 0, 0, 0, inv12dx, glap);
+    grad_at_fast<3>(SmemField{c + kStW * kStH, dm, dp}, 0, 0, 0, inv12dx, gfai);
+    grad_at_fast<3>(SmemField{c + 2 * kStW * kStH, dm, dp}, 0, 0, 0, inv12dx, gprho);
+    if (MAGNETIC) {
+      grad_at_fast<3>(SmemField{c + kStWs, dm, dp}, 0, 0, 0, inv12dx, gchi);
+      grad_at_fast<3>(SmemField{c + kStWs + kStSc, dm, dp}, 0, 0, 0, inv12dx, gpsi);
+    }
+  }
+};
+
+struct TmaMaps {
+  CUtensorMap f, g, ws, chi, psi;
+};
+
+template <bool MAGNETIC, bool IDX32>
+__global__ void __launch_bounds__(kThreads, 2)
+k_hcz_collide_stream_tma(const __grid_constant__ TmaMaps M, const float* __restrict__ fi,
+                         const float* __restrict__ gi, CsArgs A, Consts k, KbcScalars K, Grid g, int kz) {
+  constexpr int DIM = 3, Q = 19;
+  extern __shared__ float tma_raw[];
+  // 128-byte aligned start, derived from the shared-space address so that accesses stay LDS/STS
+  float* sm = tma_raw + (((128u - (tma::smem_u32(tma_raw) & 127u)) & 127u) >> 2);
+  float* pull = sm;
+  float* ring = sm + 2 * kPullStage;
+  const unsigned bar0 = tma::smem_u32(ring + 4 * kStSlot);
+  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * kTileX + tx;
+  const int x0 = blockIdx.x * kTileX, y0 = blockIdx.y * kTileY;
+  PlaneCell c;
+  c.x = x0 + tx;
+  c.y = y0 + ty;
+  c.live = c.x < g.W && c.y < g.H;
+  const int z0 = g.zb + blockIdx.z * kz;
+  const int z1 = min(z0 + kz, g.zb + g.zn);
+  if (tid == 0) {
+    tma::mbar_init(bar0, 1);
+    tma::mbar_init(bar0 + 8, 1);
+    tma::fence_barrier_init();
+  }
+  __syncthreads();
+  const PopIndex<IDX32> at(g);
+  constexpr unsigned kStBytes = (3 * kStW * kStH + (MAGNETIC ? 2 * kStW * kStH : 0)) * 4;
+  // one elected thread arms the barrier and issues the boxes (TMA instructions are warp-uniform: issuing them from
+  // several lanes only makes the compiler serialise the lanes): 2Q pull boxes of plane zpull and the stencil planes
+  // [zs, zs + ns) of ws / chi / psi
+  auto issue = [&](int zpull, int zs, int ns) {
+    const unsigned bar = bar0 + 8 * (zpull & 1);
+    tma::mbar_expect_tx(bar, 2 * Q * kThreads * 4 + ns * kStBytes);
+    const unsigned dst = tma::smem_u32(pull + (zpull & 1) * kPullStage);
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+      const int cx = x0 - Lat<3>::ex(q), cy = y0 - Lat<3>::ey(q), cz = zpull - Lat<3>::ez(q);
+      tma::load_4d(dst + q * kThreads * 4, &M.g, bar, cx, cy, cz, q);
+      tma::load_4d(dst + (Q + q) * kThreads * 4, &M.f, bar, cx, cy, cz, q);
+    }
+    for (int n = 0; n < ns; ++n) {
+      const int z = zs + n;
+      const unsigned slot = tma::smem_u32(ring + (z & 3) * kStSlot);
+      tma::load_4d(slot, &M.ws, bar, x0 - 1, y0 - 1, z, 0);
+      if (MAGNETIC) {
+        tma::load_3d(slot + kStWs * 4, &M.chi, bar, x0 - 1, y0 - 1, z);
+        tma::load_3d(slot + (kStWs + kStSc) * 4, &M.psi, bar, x0 - 1, y0 - 1, z);
+      }
+    }
+  };
+  if (tid == 0) issue(z0, z0 - 1, 3);
+  // stencil centre of this thread inside the rim-extended tile (x / y clamp = index shift, see above)
+  const int ccx = tx + 1 + (interior(c.x, g.W) - c.x), ccy = ty + 1 + (interior(c.y, g.H) - c.y);
+  const int cell0 = (z0 * g.H + c.y) * g.W + c.x;
+  uint8_t fl_next = c.live ? A.flags[cell0] : (uint8_t)0;
+  float rho_next = c.live ? A.rho_[cell0] : 0.f;
+  const bool sx0 = c.x == 0, sx1 = c.x == g.W - 1, sy0 = c.y == 0, sy1 = c.y == g.H - 1;
+  for (int z = z0; z < z1; ++z) {
+    __syncthreads();   // every thread is done with the stage and the ring slot about to be refilled
+    if (z + 1 < z1 && tid == 0) issue(z + 1, z + 2, 1);
+    const uint8_t fl = fl_next;
+    const float rho = rho_next;
+    if (c.live && z + 1 < z1) {
+      fl_next = A.flags[((z + 1) * g.H + c.y) * g.W + c.x];
+      rho_next = A.rho_[((z + 1) * g.H + c.y) * g.W + c.x];
+    }
+    if (!c.live) continue;
+    tma::mbar_wait(bar0 + 8 * (z & 1), ((z - z0) >> 1) & 1);
+    c.z = z;
+    c.i = (z * g.H + c.y) * g.W + c.x;
+    float* s = pull + (z & 1) * kPullStage + tid;
+    float gv[Q];
+#pragma unroll
+    for (int q = 0; q < Q; ++q) gv[q] = s[q * kThreads];
+    const bool sz0 = z == 0, sz1 = z == g.D - 1;
+    if (sx0 | sx1 | sy0 | sy1 | sz0 | sz1) {   // periodic seam: the box was zero-filled where the pull wraps
+      const Nbr nb(c, g);
+#pragma unroll
+      for (int q = 1; q < Q; ++q) {
+        const int ex = Lat<3>::ex(q), ey = Lat<3>::ey(q), ez = Lat<3>::ez(q);
+        const bool wraps = (ex == 1 && sx0) || (ex == -1 && sx1) || (ey == 1 && sy0) || (ey == -1 && sy1) ||
+                           (ez == 1 && sz0) || (ez == -1 && sz1);
+        if (wraps) {
+          const auto j = at(q, c.i + nb.at<DIM>(q, 1));
+          gv[q] = ld_spec(gi + j);
+          s[(Q + q) * kThreads] = ld_spec(fi + j);
+        }
+      }
+      tma::fence_proxy_async();   // generic writes to a stage the TMA unit refills later
+    }
+    const SmemPop fv{s + Q * kThreads};
+    if (interior_z(g, z) == z) {
+      const float* slot = ring + (z & 3) * kStSlot;
+      const SmemStencil<MAGNETIC> st{slot + ccy * kStW + ccx, (((z - 1) & 3) - (z & 3)) * kStSlot,
+                                     (((z + 1) & 3) - (z & 3)) * kStSlot};
+      hcz_cs_cell<DIM, MAGNETIC, IDX32>(c, at, RegPop{gv}, fv, fl, rho, A, k, K, g, st);
+    } else {
+      hcz_cs_cell<DIM, MAGNETIC, IDX32>(c, at, RegPop{gv}, fv, fl, rho, A, k, K, g, GlobalStencil<DIM, MAGNETIC>{});
+    }
   }
 }
 
@@ -506,13 +680,32 @@ static int shell_rule_impl(float* field, const uint8_t* flags, const Grid& g, cu
 
 // LBMFF_HCZ_PREFETCH=0/1 and LBMFF_HCZ_KZ=<planes per block> override the defaults (tuning, and the test that
 // holds the two kernels bit-identical)
-struct CsPrefetch { bool on; int kz; };
+struct CsPrefetch { bool on; int kz; bool tma, tma_required; };
 static CsPrefetch cs_prefetch_config() {
   const char* e = getenv("LBMFF_HCZ_PREFETCH");
   const char* z = getenv("LBMFF_HCZ_KZ");
-  CsPrefetch c{e ? atoi(e) != 0 : true, z ? atoi(z) : 16};
+  const char* t = getenv("LBMFF_HCZ_TMA");   // 0: keep the cp.async kernel even where the TMA kernel applies;
+                                             // 2: fail instead of falling back (the bit-identity tests)
+  CsPrefetch c{e ? atoi(e) != 0 : true, z ? atoi(z) : 16, t ? atoi(t) != 0 : true, t ? atoi(t) == 2 : false};
   if (c.kz < 1) c.kz = 1;
   return c;
+}
+
+// Tensor maps of one batch item for k_hcz_collide_stream_tma; false when the layout does not meet the TMA rules
+// (row pitch W * 4 B must be a multiple of 16, bases 16-byte aligned) or the driver entry point is unavailable.
+static bool make_tma_maps(TmaMaps* M, const float* fi, const float* gi, const float* ws, const float* chi,
+                          const float* psi, const Grid& g) {
+  if (g.W % 4 || g.W < kStW || g.H < kStH || g.D < 4) return false;
+  const unsigned long long d4[4] = {(unsigned long long)g.W, (unsigned long long)g.H, (unsigned long long)g.D, 19};
+  const unsigned long long w4[4] = {d4[0], d4[1], d4[2], 3};
+  const unsigned bpop[4] = {kTileX, kTileY, 1, 1}, bws[4] = {kStW, kStH, 1, 3}, bsc[3] = {kStW, kStH, 1};
+  if (!tma::make_map_f32(&M->f, fi, 4, d4, bpop) || !tma::make_map_f32(&M->g, gi, 4, d4, bpop) ||
+      !tma::make_map_f32(&M->ws, ws, 4, w4, bws))
+    return false;
+  if (chi && psi) return tma::make_map_f32(&M->chi, chi, 3, d4, bsc) && tma::make_map_f32(&M->psi, psi, 3, d4, bsc);
+  M->chi = M->ws;
+  M->psi = M->ws;
+  return true;
 }
 
 template <int DIM>
@@ -547,6 +740,32 @@ static int collide_stream_impl(const float* f_in, const float* g_in, float* f_ou
     const float* fi = f_in + b * Q * N;
     const float* gi = g_in + b * Q * N;
     if constexpr (DIM == 3) {
+      TmaMaps maps;
+      if (pf.on && pf.tma && g.zn >= 2 && make_tma_maps(&maps, fi, gi, A.ws, A.chi, A.psi, g)) {
+        // z-marching 64 x 4 blocks, every tile staged by the TMA unit
+        const int kz = g.zn < pf.kz ? g.zn : pf.kz;
+        const dim3 grid((unsigned)((g.W + kTileX - 1) / kTileX), (unsigned)((g.H + kTileY - 1) / kTileY),
+                        (unsigned)((g.zn + kz - 1) / kz));
+        const dim3 block(kTileX, kTileY, 1);
+#define LBMFF_CSTMA(MAG, IX)                                                                                        \
+  do {                                                                                                              \
+    static bool done[64] = {};                                                                                      \
+    int dev = 0;                                                                                                    \
+    cudaGetDevice(&dev);                                                                                            \
+    if (dev < 0 || dev >= 64 || !done[dev]) {                                                                       \
+      cudaFuncSetAttribute(k_hcz_collide_stream_tma<MAG, IX>, cudaFuncAttributeMaxDynamicSharedMemorySize,          \
+                           kTmaSmemBytes);                                                                          \
+      if (dev >= 0 && dev < 64) done[dev] = true;                                                                   \
+    }                                                                                                               \
+    k_hcz_collide_stream_tma<MAG, IX><<<grid, block, kTmaSmemBytes, st>>>(maps, fi, gi, A, k, K, g, kz);            \
+  } while (0)
+        if (magnetic) { if (ix) LBMFF_CSTMA(true, true); else LBMFF_CSTMA(true, false); }
+        else { if (ix) LBMFF_CSTMA(false, true); else LBMFF_CSTMA(false, false); }
+#undef LBMFF_CSTMA
+        continue;
+      }
+      if (pf.tma_required && g.zn >= 2)
+        return bad_arg(where, "LBMFF_HCZ_TMA=2 but the TMA kernel does not apply (needs W % 4 == 0, W >= 68, H >= 6)");
       if (pf.on && g.zn >= 2) {   // z-marching blocks with the next cell's pulls in flight (cp.async)
         const int kz = g.zn < pf.kz ? g.zn : pf.kz;
         const dim3 grid(pl.grid.x, pl.grid.y, (unsigned)((g.zn + kz - 1) / kz));

@@ -243,6 +243,7 @@ def run_hcz(dim, res, steps, dtype=torch.float32, *, magnetic=True, mag=100.0, g
     Hext[:, 1] = mag
     Hmac = get_staggered(Hext, mode="replicate")
     psi = torch.zeros_like(rho)
+    mass0 = float(f.double().sum().item())       # total mass over ALL cells, walls included
     meta = dict(res=np.array(res), mag=mag, gravity=gravity, kappa=kappa, tau_f=tau_f, tau_g=tau_g,
                 contact_angle=contact_angle, magnetic=int(magnetic), kbc=int(kbc), n_sweeps=n_sweeps)
     out = {}
@@ -273,6 +274,8 @@ def run_hcz(dim, res, steps, dtype=torch.float32, *, magnetic=True, mag=100.0, g
         if step in snapshots or step == steps:
             st = dict(init, f=f, g=g, rho=rho, vel=vel, density=density, pressure=pressure, force=force, steps=step,
                       **meta)
+            if device != "cpu" or snapshots:     # (the committed traj_* goldens keep their original key set)
+                st.update(mass0=mass0, mass=float(f.double().sum().item()))
             if magnetic:
                 st.update(h=h, psi=psi, H2=H2, phi=phi)
             out[step] = t2n(st)

@@ -384,3 +384,46 @@ def test_prefetching_collide_stream_is_bit_identical(name, kz, monkeypatch):
         out[pf] = [t.clone() for t in (s.f, s.g, s.rho, s.vel, s.pressure)]
     for a, b in zip(out["0"], out["1"]):
         assert torch.equal(a, b)
+
+
+def _eq_nan(a, b):
+    return bool(((a == b) | (a.isnan() & b.isnan())).all())
+
+
+@pytest.mark.parametrize("res,open_flags", [((12, 10, 72), ()), ((9, 13, 140), ()), ((10, 12, 68), (2,)),
+                                            ((12, 8, 132), (0, 1))])
+@pytest.mark.parametrize("magnetic", [True, False])
+@pytest.mark.parametrize("kz", [16, 3])
+def test_tma_collide_stream_is_bit_identical(res, open_flags, magnetic, kz, monkeypatch):
+    """k_hcz_collide_stream_tma (pull tiles and rim-extended stencil planes staged by cp.async.bulk.tensor, mbarrier
+    pipeline) against the cp.async kernel: same cell arithmetic, so every field must agree bit for bit -- on grids
+    with ragged tiles (W not a multiple of 64, H not a multiple of 4), with FLUID cells on the periodic seam and on
+    the global z shell (open hydrodynamic flags: zero-filled boxes re-read, global-sampler planes) and with and
+    without the magnetic fields.  LBMFF_HCZ_TMA=2 makes the library fail instead of silently falling back."""
+    from lbm_ferrofluid_b200 import initializers as I
+    from lbm_ferrofluid_b200.solver import FerroSolver
+
+    dev = torch.device("cuda")
+    flags = I.shell_flags(res, open_axes=open_flags, device=dev)
+    mflags = I.shell_flags(res, open_axes=(1,), device=dev)
+    rho = I.rosensweig_rho(res, flags, noise=1e-3, seed=5)
+    out = {}
+    for tma in ("0", "2"):
+        monkeypatch.setenv("LBMFF_HCZ_TMA", tma)
+        monkeypatch.setenv("LBMFF_HCZ_KZ", str(kz))
+        kw = dict(magnetic_flags=mflags, H_ext=[0.0, 100.0, 0.0], n_sweeps=8) if magnetic else {}
+        s = FerroSolver(flags, contact_angle=0.55 * math.pi, **kw).initialize(rho).step(3)
+        torch.cuda.synchronize()
+        out[tma] = [t.clone() for t in (s.f, s.g, s.rho, s.vel, s.pressure)]
+        assert torch.isfinite(s.rho).all()
+    for name, a, b in zip(("f", "g", "rho", "vel", "pressure"), out["0"], out["2"]):
+        assert _eq_nan(a, b), f"{name}: TMA kernel differs (max {float((a - b).abs().nan_to_num().max()):.3e})"
+
+
+def test_tma_kernel_falls_back_where_it_does_not_apply(monkeypatch):
+    """W % 4 != 0 (the demos' 130 x 66 x 130): the row pitch breaks the 16-byte stride rule of tensor maps, the
+    cp.async kernel runs instead -- and LBMFF_HCZ_TMA=2 says so."""
+    G = load_golden("traj_ros3d")
+    monkeypatch.setenv("LBMFF_HCZ_TMA", "2")
+    with pytest.raises(RuntimeError, match="TMA kernel does not apply"):
+        make_solver(G).step(1)

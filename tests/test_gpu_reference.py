@@ -134,12 +134,35 @@ def test_demo_size_trajectory_vs_reference_on_cuda(case, path, refdir):
 
 @pytest.mark.parametrize("case", ["ros3d_mg100", "ros2d_mg100"])
 def test_total_mass_over_100_steps_at_demo_size(case, refdir):
+    """sum over ALL cells (walls included) of sum_q f over 100 steps.  The algorithm itself does not conserve mass to
+    round-off -- the reference's entropic product equilibrium on the pruned D3Q19 lattice sums to rho only up to
+    O(u^4), and its fp32 run drifts too -- so the bar is the reference's own drift measured here (fp32 and fp64 on the
+    same GPU): ours must stay within 1e-6 or within 1.5 x the larger of the two, whichever is larger, and must agree
+    with the reference-fp64 total mass after 100 steps to 2e-6 relative."""
+    out = os.path.join(refdir, f"{case}_mass")
+    ref = {}
+    for dtype in ("float32", "float64"):
+        env = {k: v for k, v in os.environ.items() if k != "PYTHONPATH"}
+        cmd = [sys.executable, RUNNER, "traj", *CASES[case][0], "--steps", "100", "--dtype", dtype, "--device", "cuda",
+               "--out", f"{out}_{dtype}", "--keys", "rho0", "flags", "mflags"]
+        r = subprocess.run(cmd, capture_output=True, text=True, env=env, cwd=refdir, timeout=1800)
+        assert r.returncode == 0, r.stderr[-3000:]
+        z = np.load(f"{out}_{dtype}_100.npz")
+        ref[dtype] = (float(z["mass0"]), float(z["mass"]))
     G = _run_reference(case, "float32", refdir)[STEPS[0]]
     s = _solver(G, "faithful")
     m0 = s.total_mass()
     s.step(100)
     m1 = s.total_mass()
     drift = abs(m1 - m0) / abs(m0)
-    REPORT[f"{case}/mass100"] = dict(drift=drift)
+    d32 = abs(ref["float32"][1] - ref["float32"][0]) / abs(ref["float32"][0])
+    d64 = abs(ref["float64"][1] - ref["float64"][0]) / abs(ref["float64"][0])
+    vs64 = abs(m1 - ref["float64"][1]) / abs(ref["float64"][1])
+    REPORT[f"{case}/mass100"] = dict(drift=drift, reference_fp32_drift=d32, reference_fp64_drift=d64,
+                                     ours_vs_reference_fp64_total=vs64)
+    print(f"{case}: total-mass drift over 100 steps  ours {drift:.2e}  reference fp32 {d32:.2e}  reference fp64 "
+          f"{d64:.2e}  |ours - ref64| / ref64 {vs64:.2e}")
     _dump_report()
-    assert math.isfinite(m1) and drift <= 1e-6, f"total mass drifted by {drift:.2e} over 100 steps"
+    assert math.isfinite(m1) and drift <= max(1e-6, 1.5 * max(d32, d64)), \
+        f"total mass drifted by {drift:.2e} over 100 steps (reference: fp32 {d32:.2e}, fp64 {d64:.2e})"
+    assert vs64 <= 2e-6, f"total mass after 100 steps differs from the reference fp64 run by {vs64:.2e}"

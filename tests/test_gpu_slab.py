@@ -122,3 +122,15 @@ def test_slab_scalar_path_refused_with_interior_magnetic_wall():
     lm[0, 0, 6, 5, 5] = 7
     with pytest.raises(RuntimeError, match="FLUID / OBSTACLE"):
         SlabFerroSolver(lay, lf, magnetic_flags=lm, magnetic_path="faithful", **kw)
+
+
+@pytest.mark.parametrize("path", ["faithful", "scalar"])
+def test_virtual_ranks_bit_identical_with_the_tma_kernel(path, monkeypatch):
+    """Same contract on a grid wide enough (W = 72) for k_hcz_collide_stream_tma to run on the interior planes."""
+    one, slabs = build((24, 12, 72), 2, path, (1,), steps=3)
+    fluid = (one.mflags != 2)
+    for name in ("f", "g", "rho", "pressure", "vel", "psi"):
+        got, want = torch.cat([s.owned(name) for s in slabs], dim=2), getattr(one, name)
+        if name == "psi":
+            got, want = got * fluid, want * fluid
+        assert torch.equal(got, want), name

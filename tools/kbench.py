@@ -190,6 +190,32 @@ def ext(res, steps=20, reps=3):
             torch.cuda.empty_cache()
 
 
+def cs(res, steps=5):
+    """The HCZ collide-stream stage inside real steps (scalar magnetic path): cp.async kernel vs TMA kernel, per kz."""
+    import math
+    import statistics
+    from lbm_ferrofluid_b200.solver import FerroSolver
+    dev = torch.device("cuda")
+    flags = I.shell_flags(res, device=dev)
+    mflags = I.shell_flags(res, open_axes=(1,), device=dev)
+    rho = I.rosensweig_rho(res, flags)
+    N = res[0] * res[1] * res[2]
+    s = FerroSolver(flags, magnetic_flags=mflags, H_ext=[0.0, 100.0, 0.0], magnetic_path="scalar",
+                    contact_angle=0.5 * math.pi, gravity=1e-4, keep_force=False).initialize(rho)
+    s.step(3)
+    for tma in os.environ.get("KB_TMA", "0 1").split():
+        for kz in os.environ.get("KB_KZ", "8 16 32").split():
+            os.environ["LBMFF_HCZ_TMA"], os.environ["LBMFF_HCZ_KZ"] = tma, kz
+            s.step(1)
+            s.enable_kernel_timing(True)
+            s.step(steps)
+            torch.cuda.synchronize()
+            ms = statistics.median(s.kernel_times_ms()["collide_stream"])
+            s.enable_kernel_timing(False)
+            print(f"collide-stream tma={tma} kz={kz} {res}: {ms:.3f} ms  {304 * N / ms / 1e6:.0f} GB/s of the 304 B/cell "
+                  f"model  finite={bool(torch.isfinite(s.rho).all())}", flush=True)
+
+
 def render(n, image=256):
     """The demo frame (save_rendered_image): iso-surface of a perturbed Rosensweig phi at n^3, then the SoftRenderer
     chain at image^2 (x2 supersampling), each stage timed with CUDA events."""
@@ -220,6 +246,8 @@ def render(n, image=256):
 if __name__ == "__main__":
     if sys.argv[1] == "render":
         render(int(sys.argv[2]), int(sys.argv[3]) if len(sys.argv) > 3 else 256)
+    if sys.argv[1] == "cs":
+        cs(tuple(int(v) for v in sys.argv[2:5]))
     if sys.argv[1] == "ext":
         ext(tuple(int(v) for v in sys.argv[2:5]), *( [int(sys.argv[5]), 1] if len(sys.argv) > 5 else []))
     if sys.argv[1] == "cg":
