@@ -135,10 +135,11 @@ def test_demo_size_trajectory_vs_reference_on_cuda(case, path, refdir):
 @pytest.mark.parametrize("case", ["ros3d_mg100", "ros2d_mg100"])
 def test_total_mass_over_100_steps_at_demo_size(case, refdir):
     """sum over ALL cells (walls included) of sum_q f over 100 steps.  The algorithm itself does not conserve mass to
-    round-off -- the reference's entropic product equilibrium on the pruned D3Q19 lattice sums to rho only up to
-    O(u^4), and its fp32 run drifts too -- so the bar is the reference's own drift measured here (fp32 and fp64 on the
-    same GPU): ours must stay within 1e-6 or within 1.5 x the larger of the two, whichever is larger, and must agree
-    with the reference-fp64 total mass after 100 steps to 2e-6 relative."""
+    round-off in fp32: measured here on the same GPU, the reference's own fp32 run drifts by ~1e-5 at 130 x 66 x 130
+    (7e-6 at 130^2) over 100 steps while its fp64 run drifts by 1-2e-6 (the entropic product equilibrium on the pruned
+    D3Q19 lattice sums to rho only up to O(u^4)) -- SURVEY's 1e-7 was a 34^3 / few-step figure.  So the bar is the
+    reference's own behaviour: our drift must stay within 1e-6 or 1.5 x the reference's fp32 drift, whichever is
+    larger, and our total mass after 100 steps must equal the reference-fp32 total to 2e-6 relative."""
     out = os.path.join(refdir, f"{case}_mass")
     ref = {}
     for dtype in ("float32", "float64"):
@@ -158,11 +159,12 @@ def test_total_mass_over_100_steps_at_demo_size(case, refdir):
     d32 = abs(ref["float32"][1] - ref["float32"][0]) / abs(ref["float32"][0])
     d64 = abs(ref["float64"][1] - ref["float64"][0]) / abs(ref["float64"][0])
     vs64 = abs(m1 - ref["float64"][1]) / abs(ref["float64"][1])
+    vs32 = abs(m1 - ref["float32"][1]) / abs(ref["float32"][1])
     REPORT[f"{case}/mass100"] = dict(drift=drift, reference_fp32_drift=d32, reference_fp64_drift=d64,
-                                     ours_vs_reference_fp64_total=vs64)
+                                     ours_vs_reference_fp32_total=vs32, ours_vs_reference_fp64_total=vs64)
     print(f"{case}: total-mass drift over 100 steps  ours {drift:.2e}  reference fp32 {d32:.2e}  reference fp64 "
-          f"{d64:.2e}  |ours - ref64| / ref64 {vs64:.2e}")
+          f"{d64:.2e}  |ours - ref32| / ref32 {vs32:.2e}  |ours - ref64| / ref64 {vs64:.2e}")
     _dump_report()
-    assert math.isfinite(m1) and drift <= max(1e-6, 1.5 * max(d32, d64)), \
+    assert math.isfinite(m1) and drift <= max(1e-6, 1.5 * d32), \
         f"total mass drifted by {drift:.2e} over 100 steps (reference: fp32 {d32:.2e}, fp64 {d64:.2e})"
-    assert vs64 <= 2e-6, f"total mass after 100 steps differs from the reference fp64 run by {vs64:.2e}"
+    assert vs32 <= 2e-6, f"total mass after 100 steps differs from the reference fp32 run by {vs32:.2e}"
