@@ -90,6 +90,79 @@ __device__ __forceinline__ void kbc_relax(const float* f, const float* feq, floa
   for (int i = 0; i < 9; ++i) out[i] = f[i] + K.beta * (-2.0f * ds[i] - gamma * dh[i]);
 }
 
+// The same relaxation, speed-ordered, for the fused single-phase kernel (demo_2d_LBM_KBC.py at 4096^2).
+// kbc_relax spends its time in 47 IEEE divisions per cell (f / rho and feq / rho for two moment sets, 1 / feq in
+// both sums).  None of them is needed:
+//  * s is linear in the populations and the rho of "rho * M(f / rho)" cancels, so ds = s(f) - s(feq) is formed from
+//    signed adds of d_i = f_i - feq_i over the lattice vectors (raw sums), centred once per cell:
+//    sum d (e-u)_a (e-u)_b = D_ab - u_a D_b - u_b D_a + u_a u_b D_0;
+//  * 1 / feq_i = 1 / (rho base) * (1 / w_i) * X_i^-1 Y_i^-1 and the inverse axis factors are already there
+//    (F.invA = 1 / F.A), so ONE division serves the nine weights of <.|.>.
+// feq itself is still evaluated in the reference's operation order: the reference's stabiliser is gamma = 0/0 = NaN
+// exactly where the pulled populations equal their equilibrium bit for bit (LBM_collision_MRT_2d.py:213-222), and
+// that pattern is pinned cell by cell (test_kbc_zero_over_zero_quirk_is_reproduced): with d == 0 every raw sum, ds
+// and dh vanish and num / den is the same 0/0.  Elsewhere the result differs from kbc_relax by fp32 rounding
+// (gamma is a ratio of two small numbers; it multiplies dh, which is as small), held to the trajectory bars.
+template <class FE>
+__device__ __forceinline__ void kbc_relax_fast(const float* f, const float* feq, const FE& F, float rho,
+                                               const float* u, float c, int kbc, const KbcScalars& K, float* out) {
+  using L = Lat<2>;
+  float d[9];
+#pragma unroll
+  for (int i = 0; i < 9; ++i) d[i] = f[i] - feq[i];
+  // raw sums of d over the lattice vectors (signed adds; e is a compile-time constant in the unrolled loops)
+  float D0 = 0.f, Dx = 0.f, Dy = 0.f, Dxx = 0.f, Dyy = 0.f, Dxy = 0.f, Dxxy = 0.f, Dxyy = 0.f, Dxxyy = 0.f;
+#pragma unroll
+  for (int i = 0; i < 9; ++i) {
+    const int ex = L::ex(i), ey = L::ey(i);
+    D0 += d[i];
+    if (ex == 1) Dx += d[i]; else if (ex == -1) Dx -= d[i];
+    if (ey == 1) Dy += d[i]; else if (ey == -1) Dy -= d[i];
+    if (ex != 0) Dxx += d[i];
+    if (ey != 0) Dyy += d[i];
+    if (ex * ey == 1) Dxy += d[i]; else if (ex * ey == -1) Dxy -= d[i];
+    if (ex != 0 && ey == 1) Dxxy += d[i]; else if (ex != 0 && ey == -1) Dxxy -= d[i];
+    if (ey != 0 && ex == 1) Dxyy += d[i]; else if (ey != 0 && ex == -1) Dxyy -= d[i];
+    if (ex != 0 && ey != 0) Dxxyy += d[i];
+  }
+  float ds[9];
+  const float c2 = c * c;
+  if (kbc) {   // centred second moments; s owns {T, N, Pi_xy}
+    const float m20 = c2 * (Dxx - 2.0f * u[0] * Dx + u[0] * u[0] * D0);
+    const float m02 = c2 * (Dyy - 2.0f * u[1] * Dy + u[1] * u[1] * D0);
+    const float m11 = c2 * (Dxy - u[0] * Dy - u[1] * Dx + u[0] * u[1] * D0);
+    const float T = m20 + m02, N = m20 - m02;
+    ds[0] = -T;
+    const float t4 = 0.25f * T, n4 = 0.25f * N, p4 = 0.25f * m11;
+    ds[1] = t4 + n4; ds[3] = t4 + n4; ds[2] = t4 - n4; ds[4] = t4 - n4;
+    ds[5] = p4; ds[7] = p4; ds[6] = -p4; ds[8] = -p4;
+  } else {     // raw moments (preset_KBC); s owns {T, Pi_xy, Q_xxy, Q_xyy, A}; the u terms cancel in the difference
+    const float c3 = c * c2, c4 = c2 * c2;
+    const float m20 = c2 * Dxx, m02 = c2 * Dyy, m11 = c2 * Dxy, m21 = c3 * Dxxy, m12 = c3 * Dxyy, m22 = c4 * Dxxyy;
+    const float T = m20 + m02, t4 = 0.25f * T, p4 = 0.25f * m11;
+    ds[0] = -T + m22;
+    ds[1] = t4 + 0.5f * (-m12 - m22); ds[3] = t4 + 0.5f * (m12 - m22);
+    ds[2] = t4 + 0.5f * (-m21 - m22); ds[4] = t4 + 0.5f * (m21 - m22);
+    ds[5] = p4 + 0.25f * (m22 + m12 + m21);  ds[6] = -p4 + 0.25f * (m22 - m12 + m21);
+    ds[7] = p4 + 0.25f * (m22 - m12 - m21);  ds[8] = -p4 + 0.25f * (m22 + m12 - m21);
+  }
+  const float irb = 1.0f / (rho * F.base);
+  float num = 0.f, den = 0.f, dh[9];
+#pragma unroll
+  for (int i = 0; i < 9; ++i) {
+    const int ex = L::ex(i), ey = L::ey(i);
+    float iw = irb * (1.0f / L::w(i));            // 1 / w_i is a compile-time constant
+    if (ex == 1) iw *= F.invA[0]; else if (ex == -1) iw *= F.A[0];
+    if (ey == 1) iw *= F.invA[1]; else if (ey == -1) iw *= F.A[1];
+    dh[i] = d[i] - ds[i];
+    num += ds[i] * dh[i] * iw;
+    den += dh[i] * dh[i] * iw;
+  }
+  const float gamma = K.inv_beta - K.two_m * num / den;   // 0/0 = NaN where f == feq, like the reference
+#pragma unroll
+  for (int i = 0; i < 9; ++i) out[i] = f[i] + K.beta * (-2.0f * ds[i] - gamma * dh[i]);
+}
+
 // ---- HCZ collision of one cell (HCZ_3d.py:283-361, HCZ_2d.py:193-286).
 // f, g hold the pre-collision populations and receive the post-collision ones.
 template <int DIM>

@@ -77,6 +77,22 @@ __device__ __forceinline__ FeqFactors<DIM> feq_factors(const float* u, float c) 
   return F;
 }
 
+// feq_factors for c == 1 (every demo: dx = dt = 1): x / 1.0f == x exactly, so dropping the divisions by c leaves
+// every bit of the reference-ordered result in place; 2 IEEE divisions per axis instead of 4.
+template <int DIM>
+__device__ __forceinline__ FeqFactors<DIM> feq_factors_c1(const float* u) {
+  FeqFactors<DIM> F;
+  F.base = 1.0f;
+#pragma unroll
+  for (int a = 0; a < DIM; ++a) {
+    const float s = sqrtf(1.0f + 3.0f * u[a] * u[a]);
+    F.base = (a == 0) ? (2.0f - s) : F.base * (2.0f - s);
+    F.A[a] = (2.0f * u[a] + s) / (1.0f - u[a]);
+    F.invA[a] = 1.0f / F.A[a];
+  }
+  return F;
+}
+
 // Speed-ordered factors for the fused single-phase kernels: the same formula with the divisions shared, 2 per
 // axis instead of the reference sequence's 4 (u / c / c, 1 / (1 - u / c), 1 / A).  Differs from feq_factors by
 // fp32 rounding only; the kernels that use it are held to the trajectory parity bars, not to per-op bit parity.
