@@ -140,12 +140,26 @@ class _Pending:
         self.finish = finish
 
 
+Z_UP = (9, 10, 11, 12, 13)       # D3Q19 populations with e_z = +1: pulled from plane z-1, i.e. needed in a LOWER halo
+Z_DOWN = (14, 15, 16, 17, 18)    # e_z = -1: pulled from plane z+1, needed in an UPPER halo
+
+
 class DistExchanger:
-    """Ring halo exchange with torch.distributed point-to-point ops (NCCL: one grouped send/recv pair per
-    neighbour over NVLink; gloo on CPU).  All tensors of one call travel in ONE message per direction.
-    On CUDA the exchange runs on its own high-priority stream: ``start`` makes that stream wait for the work
-    queued so far (the boundary planes), the caller then queues the interior planes on its stream, and
-    ``finish`` makes the caller's stream wait for the halos."""
+    """Ring halo exchange with torch.distributed point-to-point ops (NCCL over NVLink between GPUs; gloo in the
+    CPU tests), IN PLACE: a z-plane range of one channel is a contiguous block of the reference layout, so every
+    message is sent from and received into the state tensors themselves -- no staging buffers, no pack / unpack
+    kernels.  For population lattices only the five z-moving populations per direction travel (``pops=True``).  All
+    messages of one call form ONE grouped NCCL operation.
+
+    Two schedules:
+      * ``start`` / ``finish``: the exchange stream waits for the work queued so far, the caller queues work that does
+        not touch the halos, ``finish`` makes the caller's stream wait for the halos;
+      * ``pipelined`` (the magnetic sweeps): boundary planes AND their exchange run on the high-priority exchange
+        stream while the interior planes run on the caller's stream; the only cross-stream edges are
+        boundary(s) <- interior(s-1) and interior(s) <- boundary(s-1), so neither the two small boundary launches nor
+        the NVLink round trip ever sit on the interior kernels' critical path."""
+
+    transport = "nccl p2p, in place (5 z-moving populations per direction), boundary planes + exchange on a side stream"
 
     def __init__(self, layout: SlabLayout, device, group=None):
         import torch.distributed as dist
@@ -154,74 +168,109 @@ class DistExchanger:
         self.layout = layout
         self.device = torch.device(device)
         self.group = group
-        self._bufs = {}
         self.stream = torch.cuda.Stream(device=self.device, priority=-1) if self.device.type == "cuda" else None
         self.calls = 0
         self.bytes_per_direction = 0
+        self._pipe = None          # (event after the last interior launch, event after the last boundary launch)
 
-    def _buffers(self, key, n):
-        b = self._bufs.get(key)
-        if b is None or b[0].numel() != n:
-            b = [torch.empty(n, dtype=torch.float32, device=self.device) for _ in range(4)]
-            self._bufs[key] = b
-        return b
-
-    def _run(self, tensors: Sequence[torch.Tensor], depth: int):
+    def _run(self, tensors: Sequence[torch.Tensor], depth: int, pops: bool = False):
         lay, dist = self.layout, self.dist
         to_up, to_down, from_down, from_up = _send_slices(lay, depth)
-        sizes = [t[:, :, to_up].numel() for t in tensors]
-        n = sum(sizes)
-        key = (tuple(t.data_ptr() for t in tensors), depth)
-        s_up, s_down, r_down, r_up = self._buffers(key, n)
-        o = 0
-        for t, sz in zip(tensors, sizes):
-            s_up[o:o + sz].view_as(t[:, :, to_up]).copy_(t[:, :, to_up])
-            s_down[o:o + sz].view_as(t[:, :, to_down]).copy_(t[:, :, to_down])
-            o += sz
-        ops = [dist.P2POp(dist.isend, s_up, lay.up, self.group), dist.P2POp(dist.isend, s_down, lay.down, self.group),
-               dist.P2POp(dist.irecv, r_down, lay.down, self.group), dist.P2POp(dist.irecv, r_up, lay.up, self.group)]
+        s_up, s_down, r_down, r_up = [], [], [], []
+        for t in tensors:
+            if pops and t.shape[1] != 19:
+                raise RuntimeError("pops=True is for D3Q19 population lattices")
+            for b in range(t.shape[0]):
+                for c in (Z_UP if pops else range(t.shape[1])):       # what the upper neighbour's lower halo needs
+                    s_up.append(t[b, c, to_up])
+                    r_down.append(t[b, c, from_down])
+                for c in (Z_DOWN if pops else range(t.shape[1])):     # what the lower neighbour's upper halo needs
+                    s_down.append(t[b, c, to_down])
+                    r_up.append(t[b, c, from_up])
+        # matching order between a pair of ranks: (to_up -> from_down) first, then (to_down -> from_up); with two
+        # ranks both neighbours are the same peer and the order is what pairs the messages
+        ops = [dist.P2POp(dist.isend, v, lay.up, self.group) for v in s_up] + \
+              [dist.P2POp(dist.isend, v, lay.down, self.group) for v in s_down] + \
+              [dist.P2POp(dist.irecv, v, lay.down, self.group) for v in r_down] + \
+              [dist.P2POp(dist.irecv, v, lay.up, self.group) for v in r_up]
         for w in dist.batch_isend_irecv(ops):
             w.wait()
-        o = 0
-        for t, sz in zip(tensors, sizes):
-            t[:, :, from_down].copy_(r_down[o:o + sz].view_as(t[:, :, from_down]))
-            t[:, :, from_up].copy_(r_up[o:o + sz].view_as(t[:, :, from_up]))
-            o += sz
         self.calls += 1
-        self.bytes_per_direction += 4 * n
+        self.bytes_per_direction += 4 * sum(v.numel() for v in s_up)
 
-    def start(self, tensors, depth) -> _Pending:
+    def start(self, tensors, depth, pops=False) -> _Pending:
         if self.stream is None:
-            self._run(tensors, depth)
+            self._run(tensors, depth, pops)
             return _Pending(lambda: None)
         cur = torch.cuda.current_stream(self.device)
+        self.flush()
         self.stream.wait_stream(cur)
         with torch.cuda.stream(self.stream):
-            self._run(tensors, depth)
+            self._run(tensors, depth, pops)
         return _Pending(lambda: cur.wait_stream(self.stream))
 
-    def exchange(self, tensors, depth):
-        self.start(tensors, depth).finish()
+    def exchange(self, tensors, depth, pops=False):
+        self.start(tensors, depth, pops).finish()
+
+    def pipelined(self, req: "HaloRequest"):
+        """One sweep of the pipelined schedule: req.pre (boundary planes) and the exchange on the side stream,
+        req.overlap (interior planes) on the caller's stream."""
+        if self.stream is None:                    # CPU (gloo) tests: plain order
+            req.pre()
+            self._run(req.tensors, req.depth, req.pops)
+            req.overlap()
+            return
+        cur, side = torch.cuda.current_stream(self.device), self.stream
+        if self._pipe is None:
+            side.wait_stream(cur)                  # first sweep: everything queued so far
+        else:
+            side.wait_event(self._pipe[0])         # boundary(s) reads interior(s-1) and overwrites what it read
+        with torch.cuda.stream(side):
+            req.pre()
+            e_bnd = torch.cuda.Event()
+            e_bnd.record(side)
+            self._run(req.tensors, req.depth, req.pops)
+        if self._pipe is not None:
+            cur.wait_event(self._pipe[1])          # interior(s) reads boundary(s-1) and overwrites what it read
+        req.overlap()
+        e_int = torch.cuda.Event()
+        e_int.record(cur)
+        self._pipe = (e_int, e_bnd)
+
+    def flush(self):
+        """End of a pipelined section: the caller's stream waits for the last boundary launch and its halos."""
+        if self._pipe is not None:
+            torch.cuda.current_stream(self.device).wait_stream(self.stream)
+            self._pipe = None
 
 
-def loopback_exchange(layouts: Sequence[SlabLayout], tensor_sets: Sequence[Sequence[torch.Tensor]], depth: int):
-    """Halo exchange between P virtual ranks living in one process (tensor_sets[r] = rank r's tensors)."""
+def loopback_exchange(layouts: Sequence[SlabLayout], tensor_sets: Sequence[Sequence[torch.Tensor]], depth: int,
+                      pops: bool = False):
+    """Halo exchange between P virtual ranks living in one process (tensor_sets[r] = rank r's tensors); with
+    ``pops`` exactly the channels DistExchanger sends, so a population the real exchange leaves stale is stale here."""
     P = len(layouts)
+    up_ch, down_ch = (list(Z_UP), list(Z_DOWN)) if pops else (slice(None), slice(None))
     for r in range(P):
         lay = layouts[r]
         to_up, to_down, from_down, from_up = _send_slices(lay, depth)
         for mine, below, above in zip(tensor_sets[r], tensor_sets[lay.down], tensor_sets[lay.up]):
-            mine[:, :, from_down].copy_(below[:, :, to_up])
-            mine[:, :, from_up].copy_(above[:, :, to_down])
+            mine[:, up_ch, from_down] = below[:, up_ch, to_up]
+            mine[:, down_ch, from_up] = above[:, down_ch, to_down]
 
 
 @dataclass
 class HaloRequest:
     """Yielded by SlabFerroSolver._step_gen: fill `depth` halo planes of `tensors`; `overlap` (optional)
-    queues work that does not touch those halos and may run while they travel."""
+    queues work that does not touch those halos and may run while they travel.  ``pops``: the tensors are D3Q19
+    population lattices whose halos are only ever pulled from, so the five z-moving populations per direction
+    suffice.  ``pre`` (with ``pipelined``): the boundary-plane launches that produce the planes to be sent; the
+    exchanger may run them, and the exchange, on its own stream (DistExchanger.pipelined)."""
     tensors: List[torch.Tensor]
     depth: int
     overlap: Optional[Callable[[], None]] = None
+    pops: bool = False
+    pre: Optional[Callable[[], None]] = None
+    pipelined: bool = False
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -390,7 +439,7 @@ class SlabFerroSolver:
                          planes=planes)
 
         # f, g halos travel while the interior moments are taken
-        yield HaloRequest([f, g], 1, overlap=lambda: moments(interior))
+        yield HaloRequest([f, g], 1, overlap=lambda: moments(interior), pops=True)
         for e in edges:
             moments(e)
         yield HaloRequest([self.rho, self.pressure] + ([chi] if self.magnetic else []), L.halo)
@@ -413,10 +462,14 @@ class SlabFerroSolver:
                 def run(planes, src=src, dst=dst, psi=psi, tail=tail):
                     self._launch(sweep, p(src), p(dst), p(self.mflags), p(self._rhs), psi, *tail, planes=planes)
 
-                for e in edges:
-                    run(e)
+                def boundary(run=run):
+                    for e in edges:
+                        run(e)
+
                 self._mcur = 1 - m
-                yield HaloRequest([dst], 1, overlap=lambda run=run: run(interior))
+                yield HaloRequest([dst], 1, overlap=lambda run=run: run(interior), pre=boundary, pipelined=True,
+                                  pops=self.magnetic_path == "faithful")
+            yield HaloRequest([], 0)      # join: the caller's stream waits for the last boundary planes and halos
             t1 = self._mark()
             if self._timing is not None:
                 self._timing["sweeps"].append((t0, t1))
@@ -456,12 +509,24 @@ class SlabFerroSolver:
         if self.exchanger is None:
             raise RuntimeError("SlabFerroSolver.step needs an exchanger (DistExchanger); virtual ranks use "
                                "step_virtual_ranks")
+        ex = self.exchanger
         for _ in range(int(n)):
             for req in self._step_gen():
-                pending = self.exchanger.start(req.tensors, req.depth)
+                if req.pipelined and hasattr(ex, "pipelined"):
+                    ex.pipelined(req)
+                    continue
+                if not req.tensors:               # join point after a pipelined section
+                    if hasattr(ex, "flush"):
+                        ex.flush()
+                    continue
+                if req.pre is not None:
+                    req.pre()
+                pending = ex.start(req.tensors, req.depth, req.pops)
                 if req.overlap is not None:
                     req.overlap()
                 pending.finish()
+            if hasattr(ex, "flush"):
+                ex.flush()
         return self
 
     @property
@@ -583,7 +648,12 @@ def step_virtual_ranks(solvers: Sequence[SlabFerroSolver], n: int = 1):
                 break
             if any(r is None for r in reqs):
                 raise RuntimeError("virtual ranks fell out of lockstep")
-            loopback_exchange(layouts, [r.tensors for r in reqs], reqs[0].depth)
+            if not reqs[0].tensors:
+                continue
+            for r in reqs:
+                if r.pre is not None:
+                    r.pre()
+            loopback_exchange(layouts, [r.tensors for r in reqs], reqs[0].depth, reqs[0].pops)
             for r in reqs:
                 if r.overlap is not None:
                     r.overlap()

@@ -79,6 +79,27 @@ def _worker(rank, world, port, Dg, out):
         pend.finish()
         ok = ok and torch.equal(b, lay.take(glob_b)) and ex.calls == 2
         ok = ok and ex.bytes_per_direction == 4 * (20 * 35 + 2 * 35)
+        # population lattices: only the five z-moving populations per direction travel, in place
+        from lbm_ferrofluid_b200.distributed import HaloRequest, Z_DOWN, Z_UP
+        c = torch.full((1, 19, lay.D, 5, 7), -7.0)
+        c[:, :, lay.own] = lay.owned(want_a)
+        ex.exchange([c], 1, pops=True)
+        h = lay.halo
+        ok = ok and torch.equal(c[:, list(Z_UP), h - 1], want_a[:, list(Z_UP), h - 1])
+        ok = ok and torch.equal(c[:, list(Z_DOWN), h + lay.Dl], want_a[:, list(Z_DOWN), h + lay.Dl])
+        ok = ok and bool((c[:, list(Z_DOWN), h - 1] == -7).all()) and bool((c[:, :9, h - 1] == -7).all())
+        ok = ok and ex.bytes_per_direction == 4 * (20 * 35 + 2 * 35 + 5 * 35)
+        # the pipelined schedule (CPU: plain order): pre -> exchange -> overlap, then a join
+        order = []
+        d = torch.full((1, 1, lay.D, 5, 7), -7.0)
+
+        def pre():
+            d[:, :, lay.own] = lay.owned(lay.take(glob_b))
+            order.append("pre")
+
+        ex.pipelined(HaloRequest([d], 1, overlap=lambda: order.append("overlap"), pre=pre, pipelined=True))
+        ex.flush()
+        ok = ok and order == ["pre", "overlap"] and torch.equal(d[:, :, 1:-1], lay.take(glob_b)[:, :, 1:-1])
         out[rank] = bool(ok)
     finally:
         dist.destroy_process_group()
