@@ -109,7 +109,8 @@ __device__ __forceinline__ void kbc_relax_fast(const float* f, const float* feq,
   using L = Lat<2>;
   float d[9];
 #pragma unroll
-  for (int i = 0; i < 9; ++i) d[i] = f[i] - feq[i];
+  for (int i = 0; i < 9; ++i) d[i] = __fsub_rn(f[i], feq[i]);   // never fused with the product that formed feq:
+                                                                 // fma(-rho w, v, f) would be its rounding error, not 0
   // raw sums of d over the lattice vectors (signed adds; e is a compile-time constant in the unrolled loops)
   float D0 = 0.f, Dx = 0.f, Dy = 0.f, Dxx = 0.f, Dyy = 0.f, Dxy = 0.f, Dxxy = 0.f, Dxyy = 0.f, Dxxyy = 0.f;
 #pragma unroll

@@ -85,9 +85,11 @@ __device__ __forceinline__ FeqFactors<DIM> feq_factors_c1(const float* u) {
   F.base = 1.0f;
 #pragma unroll
   for (int a = 0; a < DIM; ++a) {
-    const float s = sqrtf(1.0f + 3.0f * u[a] * u[a]);
+    // explicit round-to-nearest multiplies / adds: in feq_factors the divisions by c sit between the multiply and
+    // the add, so nothing there can contract into an FMA -- and nothing may here
+    const float s = sqrtf(__fadd_rn(1.0f, __fmul_rn(__fmul_rn(3.0f, u[a]), u[a])));
     F.base = (a == 0) ? (2.0f - s) : F.base * (2.0f - s);
-    F.A[a] = (2.0f * u[a] + s) / (1.0f - u[a]);
+    F.A[a] = __fadd_rn(__fmul_rn(2.0f, u[a]), s) / (1.0f - u[a]);
     F.invA[a] = 1.0f / F.A[a];
   }
   return F;
