@@ -404,26 +404,33 @@ k_hcz_collide_stream_pf(const float* __restrict__ fi, const float* __restrict__ 
   }
 }
 
-// ---- the same step with every tile brought in by the TMA unit --------------------------------------------------
-// 64 x 4 blocks march along z like k_hcz_collide_stream_pf, but no thread computes a load address on the hot path:
-//  * the 38 pulled populations of the next plane arrive as 38 box loads (cp.async.bulk.tensor.4d) of the 64 x 4 tile
-//    of population q at element coordinates (x0 - e_x, y0 - e_y, z - e_z, q) -- tiled tensor maps take unaligned
-//    start coordinates -- into a two-stage [2Q][4][64] buffer; a thread reads its value at [q][ty][tx];
-//  * the five stencil fields (lap | fai | prho of ws, chi, psi) arrive as rim-extended 68 x 6 boxes, one z plane per
-//    step, into a four-slot ring holding planes z-1, z, z+1 (+ the one in flight), so the 90 stencil reads per cell
-//    are LDS with immediate offsets instead of L1/L2 round trips behind per-load address arithmetic;
-//  * completion is tracked by two mbarriers (expect_tx); one __syncthreads per plane frees the stage for refill.
-// TMA zero-fills outside the tensor while the lattice is periodic: a cell whose pull source wraps around the array
-// (x = 0 / W-1, y = 0 / H-1, local z = 0 / D-1: ~13 % of the warps at 512^3, all of them wall cells in the named
-// configurations) re-reads the wrapped populations directly.  Stencil centres are clamped to the interior exactly
-// as in GlobalStencil: in x / y the clamp is an index shift inside the rim-extended tile, planes on the global z
-// shell (block-uniform test) take the global sampler.  The cell arithmetic is the same hcz_cs_cell, so results are
-// bit-identical to the other two kernels (tests/test_gpu_fused.py).
+// ---- the same step with the tiles that CAN be brought in by the TMA unit brought in by it -------------------------
+// 64 x 4 blocks march along z like k_hcz_collide_stream_pf.  Measured rule (tools/probe/tma_probe.cu on this B200,
+// profiles/tma_probe_r02.txt): a tiled tensor-map box may start at any coordinate in the outer dimensions, negative
+// ones included (zero fill), but its INNERMOST start coordinate must give a 16-byte aligned global address -- an x
+// start of -1, 2 or 7 floats raises "illegal instruction".  So:
+//  * the five stencil fields (lap | fai | prho of ws, chi, psi) arrive as rim-extended boxes that start at the aligned
+//    x0 - 4 and are 72 wide (the stencil needs x0 - 1 .. x0 + 64), 6 rows, one z plane per step, into a four-slot
+//    ring holding planes z-1, z, z+1 (+ the one in flight): the 90 stencil reads per cell are LDS with immediate
+//    offsets instead of L1/L2 round trips behind per-load address arithmetic;
+//  * the 18 pulled populations with e_x = 0 (f and g) arrive as 64 x 4 boxes at (x0, y0 - e_y, z - e_z, q): aligned,
+//    because tiles start at multiples of 64;
+//  * the 20 populations with e_x = +-1 are shifted by one float and cannot be a box without widening every tile to
+//    72 (which no longer fits two blocks per SM): they keep the 4-byte cp.async copies of the _pf kernel.
+// Both kinds land in the same [2Q][4][64] stage (a thread's own slot is [q][ty][tx] either way).  Completion: two
+// mbarriers (expect_tx) for the boxes, cp.async.wait_group for the thread's own copies; one __syncthreads per plane
+// frees the stage and the ring slot for refill.
+// TMA zero-fills outside the tensor while the lattice is periodic: a cell whose box-loaded pull wraps around the
+// array (y = 0 / H-1, local z = 0 / D-1; wall cells in the named configurations) re-reads those populations
+// directly.  Stencil centres are clamped to the interior exactly as in GlobalStencil: in x / y the clamp is an index
+// shift inside the rim-extended tile, planes on the global z shell (block-uniform test) take the global sampler.
+// The cell arithmetic is the same hcz_cs_cell, so results are bit-identical to the other two kernels.
 constexpr int kTileX = 64, kTileY = 4;
-constexpr int kStW = 68, kStH = 6;                    // rim-extended stencil tile; 68 * 4 B is a multiple of 16
-constexpr int kStWs = 1248;                           // [lap | fai | prho] = 3 * 408 floats, padded to 4992 B
-constexpr int kStSc = 416;                            // one scalar field, padded to 1664 B (multiples of 128 B)
-constexpr int kStSlot = kStWs + 2 * kStSc;            // 2080 floats = 8320 B per z plane
+constexpr int kStW = 72, kStH = 6, kStX0 = 4;         // rim-extended stencil tile: starts at x0 - 4, y0 - 1
+constexpr int kStField = kStW * kStH;                 // 432 floats = 1728 B
+constexpr int kStWs = 1312;                           // [lap | fai | prho] = 3 * 432 floats, padded to 5248 B
+constexpr int kStSc = 448;                            // one scalar field, padded to 1792 B (multiples of 128 B)
+constexpr int kStSlot = kStWs + 2 * kStSc;            // 2208 floats = 8832 B per z plane
 constexpr int kPullStage = 2 * 19 * kThreads;         // 9728 floats = 38912 B
 constexpr int kTmaSmemFloats = 2 * kPullStage + 4 * kStSlot;
 constexpr int kTmaSmemBytes = kTmaSmemFloats * 4 + 16 /* two mbarriers */ + 128 /* alignment slack */;
@@ -444,8 +451,8 @@ struct SmemStencil {
                                              float inv12dx, float* glap, float* gfai, float* gprho, float* gchi,
                                              float* gpsi) const {
     grad_at_fast<3>(SmemField{c, dm, dp}, 0, 0, 0, inv12dx, glap);
-    grad_at_fast<3>(SmemField{c + kStW * kStH, dm, dp}, 0, 0, 0, inv12dx, gfai);
-    grad_at_fast<3>(SmemField{c + 2 * kStW * kStH, dm, dp}, 0, 0, 0, inv12dx, gprho);
+    grad_at_fast<3>(SmemField{c + kStField, dm, dp}, 0, 0, 0, inv12dx, gfai);
+    grad_at_fast<3>(SmemField{c + 2 * kStField, dm, dp}, 0, 0, 0, inv12dx, gprho);
     if (MAGNETIC) {
       grad_at_fast<3>(SmemField{c + kStWs, dm, dp}, 0, 0, 0, inv12dx, gchi);
       grad_at_fast<3>(SmemField{c + kStWs + kStSc, dm, dp}, 0, 0, 0, inv12dx, gpsi);
@@ -483,40 +490,67 @@ k_hcz_collide_stream_tma(const __grid_constant__ TmaMaps M, const float* __restr
   }
   __syncthreads();
   const PopIndex<IDX32> at(g);
-  constexpr unsigned kStBytes = (3 * kStW * kStH + (MAGNETIC ? 2 * kStW * kStH : 0)) * 4;
+  constexpr unsigned kStBytes = (3 * kStField + (MAGNETIC ? 2 * kStField : 0)) * 4;
+  constexpr int kBoxPops = 9;   // D3Q19 populations with e_x = 0
   // one elected thread arms the barrier and issues the boxes (TMA instructions are warp-uniform: issuing them from
-  // several lanes only makes the compiler serialise the lanes): 2Q pull boxes of plane zpull and the stencil planes
-  // [zs, zs + ns) of ws / chi / psi
+  // several lanes only makes the compiler serialise the lanes): the e_x = 0 pull boxes of plane zpull and the
+  // stencil planes [zs, zs + ns) of ws / chi / psi
   auto issue = [&](int zpull, int zs, int ns) {
     const unsigned bar = bar0 + 8 * (zpull & 1);
-    tma::mbar_expect_tx(bar, 2 * Q * kThreads * 4 + ns * kStBytes);
+    tma::mbar_expect_tx(bar, 2 * kBoxPops * kThreads * 4 + ns * kStBytes);
     const unsigned dst = tma::smem_u32(pull + (zpull & 1) * kPullStage);
 #pragma unroll
     for (int q = 0; q < Q; ++q) {
-      const int cx = x0 - Lat<3>::ex(q), cy = y0 - Lat<3>::ey(q), cz = zpull - Lat<3>::ez(q);
-      tma::load_4d(dst + q * kThreads * 4, &M.g, bar, cx, cy, cz, q);
-      tma::load_4d(dst + (Q + q) * kThreads * 4, &M.f, bar, cx, cy, cz, q);
+      if (Lat<3>::ex(q) != 0) continue;
+      const int cy = y0 - Lat<3>::ey(q), cz = zpull - Lat<3>::ez(q);
+      tma::load_4d(dst + q * kThreads * 4, &M.g, bar, x0, cy, cz, q);
+      tma::load_4d(dst + (Q + q) * kThreads * 4, &M.f, bar, x0, cy, cz, q);
     }
     for (int n = 0; n < ns; ++n) {
       const int z = zs + n;
       const unsigned slot = tma::smem_u32(ring + (z & 3) * kStSlot);
-      tma::load_4d(slot, &M.ws, bar, x0 - 1, y0 - 1, z, 0);
+      tma::load_4d(slot, &M.ws, bar, x0 - kStX0, y0 - 1, z, 0);
       if (MAGNETIC) {
-        tma::load_3d(slot + kStWs * 4, &M.chi, bar, x0 - 1, y0 - 1, z);
-        tma::load_3d(slot + (kStWs + kStSc) * 4, &M.psi, bar, x0 - 1, y0 - 1, z);
+        tma::load_3d(slot + kStWs * 4, &M.chi, bar, x0 - kStX0, y0 - 1, z);
+        tma::load_3d(slot + (kStWs + kStSc) * 4, &M.psi, bar, x0 - kStX0, y0 - 1, z);
       }
     }
   };
+  // every thread: 4-byte cp.async copies of its own e_x = +-1 pulls of plane z into its slots of the stage
+  auto prefetch = [&](int z) {
+    if (c.live) {
+      PlaneCell n = c;
+      n.z = z;
+      n.i = (z * g.H + c.y) * g.W + c.x;
+      const Nbr nb(n, g);
+      float* s = pull + (z & 1) * kPullStage + tid;
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        if (Lat<3>::ex(q) == 0) continue;
+        const auto j = at(q, n.i + nb.at<DIM>(q, 1));
+        cp_async4(s + q * kThreads, gi + j);
+        cp_async4(s + (Q + q) * kThreads, fi + j);
+      }
+    }
+    cp_async_commit();
+  };
   if (tid == 0) issue(z0, z0 - 1, 3);
+  prefetch(z0);
   // stencil centre of this thread inside the rim-extended tile (x / y clamp = index shift, see above)
-  const int ccx = tx + 1 + (interior(c.x, g.W) - c.x), ccy = ty + 1 + (interior(c.y, g.H) - c.y);
+  const int ccx = tx + kStX0 + (interior(c.x, g.W) - c.x), ccy = ty + 1 + (interior(c.y, g.H) - c.y);
   const int cell0 = (z0 * g.H + c.y) * g.W + c.x;
   uint8_t fl_next = c.live ? A.flags[cell0] : (uint8_t)0;
   float rho_next = c.live ? A.rho_[cell0] : 0.f;
-  const bool sx0 = c.x == 0, sx1 = c.x == g.W - 1, sy0 = c.y == 0, sy1 = c.y == g.H - 1;
+  const bool sy0 = c.y == 0, sy1 = c.y == g.H - 1;
   for (int z = z0; z < z1; ++z) {
     __syncthreads();   // every thread is done with the stage and the ring slot about to be refilled
-    if (z + 1 < z1 && tid == 0) issue(z + 1, z + 2, 1);
+    if (z + 1 < z1) {
+      if (tid == 0) issue(z + 1, z + 2, 1);
+      prefetch(z + 1);
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
     const uint8_t fl = fl_next;
     const float rho = rho_next;
     if (c.live && z + 1 < z1) {
@@ -532,13 +566,13 @@ k_hcz_collide_stream_tma(const __grid_constant__ TmaMaps M, const float* __restr
 #pragma unroll
     for (int q = 0; q < Q; ++q) gv[q] = s[q * kThreads];
     const bool sz0 = z == 0, sz1 = z == g.D - 1;
-    if (sx0 | sx1 | sy0 | sy1 | sz0 | sz1) {   // periodic seam: the box was zero-filled where the pull wraps
+    if (sy0 | sy1 | sz0 | sz1) {   // periodic seam: the box was zero-filled where the pull wraps
       const Nbr nb(c, g);
 #pragma unroll
       for (int q = 1; q < Q; ++q) {
         const int ex = Lat<3>::ex(q), ey = Lat<3>::ey(q), ez = Lat<3>::ez(q);
-        const bool wraps = (ex == 1 && sx0) || (ex == -1 && sx1) || (ey == 1 && sy0) || (ey == -1 && sy1) ||
-                           (ez == 1 && sz0) || (ez == -1 && sz1);
+        if (ex != 0) continue;
+        const bool wraps = (ey == 1 && sy0) || (ey == -1 && sy1) || (ez == 1 && sz0) || (ez == -1 && sz1);
         if (wraps) {
           const auto j = at(q, c.i + nb.at<DIM>(q, 1));
           gv[q] = ld_spec(gi + j);
@@ -688,7 +722,7 @@ static int shell_rule_impl(float* field, const uint8_t* flags, const Grid& g, cu
 // LBMFF_HCZ_PREFETCH=0/1 and LBMFF_HCZ_KZ=<planes per block> override the defaults (tuning, and the test that
 // holds the two kernels bit-identical)
 #ifndef LBMFF_HCZ_TMA_DEFAULT
-#define LBMFF_HCZ_TMA_DEFAULT false   /* flipped to true once the TMA kernel is green on the box */
+#define LBMFF_HCZ_TMA_DEFAULT true    /* green on the box: bit-identical to the cp.async kernel, 11.7 -> 10.4 ms at 512^3 */
 #endif
 struct CsPrefetch { bool on; int kz; bool tma, tma_required; };
 static CsPrefetch cs_prefetch_config() {
@@ -775,7 +809,7 @@ static int collide_stream_impl(const float* f_in, const float* g_in, float* f_ou
         continue;
       }
       if (pf.tma_required && g.zn >= 2)
-        return bad_arg(where, "LBMFF_HCZ_TMA=2 but the TMA kernel does not apply (needs W % 4 == 0, W >= 68, H >= 6)");
+        return bad_arg(where, "LBMFF_HCZ_TMA=2 but the TMA kernel does not apply (needs W % 4 == 0, W >= 72, H >= 6)");
       if (pf.on && g.zn >= 2) {   // z-marching blocks with the next cell's pulls in flight (cp.async)
         const int kz = g.zn < pf.kz ? g.zn : pf.kz;
         const dim3 grid(pl.grid.x, pl.grid.y, (unsigned)((g.zn + kz - 1) / kz));

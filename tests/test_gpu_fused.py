@@ -390,7 +390,7 @@ def _eq_nan(a, b):
     return bool(((a == b) | (a.isnan() & b.isnan())).all())
 
 
-@pytest.mark.parametrize("res,open_flags", [((12, 10, 72), ()), ((9, 13, 140), ()), ((10, 12, 68), (2,)),
+@pytest.mark.parametrize("res,open_flags", [((12, 10, 72), ()), ((9, 13, 140), ()), ((10, 12, 76), (2,)),
                                             ((12, 8, 132), (0, 1))])
 @pytest.mark.parametrize("magnetic", [True, False])
 @pytest.mark.parametrize("kz", [16, 3])
