@@ -65,6 +65,9 @@ def parse():
     ap.add_argument("--no-configs", action="store_true", help="skip the block of the other BASELINE configs")
     ap.add_argument("--no-ref-eager", action="store_true", help="skip the reference-eager-on-this-GPU number")
     ap.add_argument("--no-verify", action="store_true", help="skip the N-rank bit-identity check")
+    ap.add_argument("--streaming", default="ab", choices=["ab", "compressed"],
+                    help="N > 1: 'compressed' keeps ONE f and ONE g buffer with chunk+1 spare planes (1024^3 on 2 GPUs)")
+    ap.add_argument("--chunk", type=int, default=32, help="planes per launch of the compressed passes")
     ap.add_argument("--reps", type=int, default=3, help="repetitions of the K-step timed region (median reported)")
     return ap.parse_args()
 
@@ -214,15 +217,15 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------
-def build_solver(res, path, device, world=1, rank=0, workload="rosensweig", mag=MAG):
+def build_solver(res, path, device, world=1, rank=0, workload="rosensweig", mag=MAG, **slab_kw):
     from lbm_ferrofluid_b200 import initializers as I
     from lbm_ferrofluid_b200.solver import FerroSolver
 
     if world > 1:
         from lbm_ferrofluid_b200.distributed import SlabFerroSolver
         if workload == "two_droplets":
-            return SlabFerroSolver.two_droplets(res, path, device, world, rank, mag=1.0, n_sweeps=N_SWEEPS)
-        return SlabFerroSolver.rosensweig(res, path, device, world, rank, mag=mag, n_sweeps=N_SWEEPS)
+            return SlabFerroSolver.two_droplets(res, path, device, world, rank, mag=1.0, n_sweeps=N_SWEEPS, **slab_kw)
+        return SlabFerroSolver.rosensweig(res, path, device, world, rank, mag=mag, n_sweeps=N_SWEEPS, **slab_kw)
     if workload == "two_droplets":
         flags = I.shell_flags(res, device=device)
         s = FerroSolver(flags, magnetic_flags=flags.clone(), H_ext=[0.0, 1.0, 0.0], n_sweeps=N_SWEEPS,
@@ -342,8 +345,10 @@ def run_ours(args):
         slab_verify = verify_against_single_gpu(device, world, rank, (8 * world if world > 8 else 64, 48, 56), 3)
         torch.cuda.empty_cache()
 
-    solver = build_solver(res, args.magnetic_path, device, world, rank, args.workload)
+    slab_kw = dict(streaming=args.streaming, chunk=args.chunk) if world > 1 else {}
+    solver = build_solver(res, args.magnetic_path, device, world, rank, args.workload, **slab_kw)
     path = solver.magnetic_path
+    state_gb = solver.state_bytes / 1e9 if hasattr(solver, "state_bytes") else None
 
     def barrier():
         if world > 1:
@@ -386,7 +391,7 @@ def run_ours(args):
         bytes_cell = BYTES_D3Q19 if path == "faithful" else BYTES_SCALAR_SWEEP
         kname = "k_mag_sweep<3>" if path == "faithful" else "k_mag_sweep_scalar<3>"
     else:
-        per_launch_ms, bytes_cell, kname = cs_ms, BYTES_HCZ, "k_hcz_collide_stream_pf"
+        per_launch_ms, bytes_cell, kname = cs_ms, BYTES_HCZ, "k_hcz_collide_stream_tma"
     achieved = bytes_cell * cells_rank / (per_launch_ms * 1e-3) / 1e9
     # DRAM traffic of the same kernel (dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` launch):
     # profiles/ncu_traffic_r02.json is measured AT 512^3, so for the default workload the figure is that launch's own
@@ -409,7 +414,7 @@ def run_ours(args):
                 "algorithmic_gb_per_launch": bytes_cell * cells_rank / 1e9, "peak_source": peak_src,
                 "algorithmic_bytes_per_cell": bytes_cell, "avg_launch_ms": per_launch_ms,
                 "share_of_step": {"sweeps": sweeps_ms / ms_step, "collide_stream": cs_ms / ms_step},
-                "collide_stream": {"kernel": "k_hcz_collide_stream_pf", "avg_launch_ms": cs_ms,
+                "collide_stream": {"kernel": "k_hcz_collide_stream_tma", "avg_launch_ms": cs_ms,
                                    "algorithmic_bytes_per_cell": BYTES_HCZ,
                                    "achieved": BYTES_HCZ * cells_rank / (cs_ms * 1e-3) / 1e9,
                                    "frac": BYTES_HCZ * cells_rank / (cs_ms * 1e-3) / 1e9 / peak}}
@@ -447,7 +452,7 @@ def run_ours(args):
     del solver
     torch.cuda.empty_cache()
     if not args.no_fast_path and path == "faithful":
-        fs = build_solver(res, "scalar", device, world, rank, args.workload)
+        fs = build_solver(res, "scalar", device, world, rank, args.workload, **slab_kw)
         fs.step(args.warmup)
         ms_fast = timed(fs.step, args.steps)
         own_bytes = BYTES_HCZ + N_SWEEPS * BYTES_SCALAR_SWEEP
@@ -487,6 +492,7 @@ def run_ours(args):
                                     f"{res[0] * world}x{res[1]}x{res[2]}"),
                        "res_per_gpu": list(res), "cells": cells, "magnetic_path": path,
                        "parallelism": f"z-slab x{world}" if world > 1 else "single GPU",
+                       "streaming": args.streaming if world > 1 else "ab", "state_gb_per_gpu": state_gb,
                        "l2": "state (tens of GB) far larger than the 126 MB L2; no flush needed"},
             "repetitions": {"n": len(reps_ms), "ms_per_rep": reps_ms, "reported": "median",
                             "steps_per_rep": args.steps},

@@ -286,7 +286,7 @@ class SlabFerroSolver:
                  density_gas=0.02381, rho_liquid=0.2508, rho_gas=0.02381, kappa=0.01, tau_f=0.68, tau_g=0.68,
                  tau=1.0, contact_angle=0.5 * math.pi, gravity=1e-4, dx=1.0, dt=1.0,
                  magnetic_flags: Optional[torch.Tensor] = None, H_ext=None, n_sweeps: int = 30,
-                 magnetic_path: str = "faithful", keep_force: bool = False):
+                 magnetic_path: str = "faithful", keep_force: bool = False, streaming: str = "ab", chunk: int = 32):
         self.layout = layout
         self.flags = H.need_cuda(flags, "flags", torch.uint8)
         self.device = self.flags.device
@@ -309,12 +309,33 @@ class SlabFerroSolver:
         self.params = H.fluid_params(self, self.dx, self.dt, cot=self.cot, gravity=self.gravity)
         self.exchanger = exchanger
         opts = dict(dtype=torch.float32, device=self.device)
+        # ---- streaming mode.  "ab": two buffers per lattice.  "compressed" (the compressed-grid scheme of Pohl et
+        # al. 2003, in chunks): ONE buffer per lattice with S = chunk + 1 spare planes; a pass over the slab is issued
+        # as launches of `chunk` planes in ascending z whose output goes to the same buffer displaced by -S planes (a
+        # launch reads planes [a-1, a+chunk] and writes [a-S, a+chunk-S): nothing it or a later launch still needs),
+        # the next step runs descending with +S.  Same kernels, same per-cell arithmetic and access pattern (so the
+        # same roofline), (D + S) / 2D of the A/B memory -- what puts 1024^3 on two 180 GB GPUs.
+        if streaming not in ("ab", "compressed"):
+            raise ValueError("streaming must be 'ab' or 'compressed'")
+        self.streaming, self.chunk = streaming, int(chunk)
+        self.S = self.chunk + 1 if streaming == "compressed" else 0
+        if streaming == "compressed" and (self.chunk < 1 or self.D + self.S > layout.Dg):
+            raise RuntimeError(f"compressed streaming: chunk + 1 spare planes on top of the {self.D} local planes must "
+                               f"not exceed the global depth {layout.Dg}")
+        self.Dk = self.D + self.S       # planes per channel in memory = the channel stride the kernels are given
         sc = lambda c: torch.zeros((self.B, c, *self.res), **opts)  # noqa: E731
-        self.rho, self.pressure, self.vel = sc(1), sc(1), sc(3)
-        self.force = sc(3) if keep_force else None
-        self._ws = sc(3)
-        self._f, self._g = [sc(19), sc(19)], [sc(19), sc(19)]
+        # multi-channel arrays share the kernels' channel stride (Dk planes); the solver works on views of D planes
+        mc = lambda c: torch.zeros((self.B, c, self.Dk, self.Hh, self.W), **opts)  # noqa: E731
+        self._mc = mc
+        self.rho, self.pressure, self.vel = sc(1), sc(1), mc(3)[:, :, :self.D]
+        self.force = mc(3)[:, :, :self.D] if keep_force else None
+        self._ws = mc(3)[:, :, :self.D]
+        if streaming == "ab":
+            self._f, self._g = [mc(19), mc(19)], [mc(19), mc(19)]
+        else:
+            self._f, self._g = [mc(19)], [mc(19)]
         self._cur = 0
+        self._off = self.S              # compressed: plane offset of the current population view (S: home, 0: displaced)
         self.steps_done = 0
         self._timing = None
         self._hook_before_source = self._hook_after_source = self._hook_after_rho_final = None
@@ -349,19 +370,41 @@ class SlabFerroSolver:
                                    "on the outer shell of the global domain")
             self.magnetic_path = magnetic_path
             self.psi, self._rhs, self._chi = sc(1), sc(1), sc(1)
-            self._h = [sc(19), sc(19)] if magnetic_path == "faithful" else [sc(2), sc(2)]
+            # the magnetic lattice stays A/B in both modes (its sweeps alternate boundary-first on two streams)
+            self._h = [mc(19)[:, :, :self.D] for _ in range(2)] if magnetic_path == "faithful" else \
+                      [mc(2)[:, :, :self.D] for _ in range(2)]
             self._mcur = 0
         else:
             self.magnetic_path, self.mflags = None, None
 
     # ---- state (slab-local views; *_owned drop the halo planes) -----------------------------------
+    def _pop(self, bufs, nxt=False):
+        """View (D planes) of the current (or, nxt, the next) state of a hydrodynamic lattice."""
+        if self.streaming == "ab":
+            return bufs[(1 - self._cur) if nxt else self._cur][:, :, :self.D]
+        off = (self.S - self._off) if nxt else self._off
+        return bufs[0][:, :, off:off + self.D]
+
     @property
     def f(self):
-        return self._f[self._cur]
+        return self._pop(self._f)
 
     @property
     def g(self):
-        return self._g[self._cur]
+        return self._pop(self._g)
+
+    @property
+    def state_bytes(self) -> int:
+        """Device bytes held by this slab's state arrays."""
+        seen, total = set(), 0
+        for v in vars(self).values():
+            for t in (v if isinstance(v, (list, tuple)) else [v]):
+                if torch.is_tensor(t) and t.is_cuda:
+                    st = t.untyped_storage()
+                    if st.data_ptr() not in seen:
+                        seen.add(st.data_ptr())
+                        total += st.nbytes()
+        return total
 
     @property
     def h(self):
@@ -382,15 +425,22 @@ class SlabFerroSolver:
         kw = dict(density_liquid=self._density_liquid, density_gas=self._density_gas, rho_liquid=self._rho_liquid,
                   rho_gas=self._rho_gas, device=self.device)
         macro, col = LBMMacroCompute3d(**kw), LBMCollision3d(tau=1.0, **kw)
-        self.pressure.copy_(macro.get_pressure(dx=self.dx, dt=self.dt, density=rho))
-        zero = torch.zeros_like(self.vel)
-        f0 = col.get_feq_(dx=self.dx, dt=self.dt, rho=rho, vel=self.vel, force=zero)
-        g0 = col.get_geq_(dx=self.dx, dt=self.dt, rho=self.rho, vel=self.vel, density=rho, pressure=self.pressure,
-                          force=zero, feq=f0)
-        self._cur = 0
-        self._f[0].copy_(f0)
-        self._g[0].copy_(g0)
-        del f0, g0
+        self._cur, self._off = 0, self.S
+        f, g = self.f, self.g
+        # pointwise, so done in chunks of planes: no full-size [19, D, H, W] temporaries (at 1024^3 on two GPUs the
+        # two of them would be 87 GB on top of the state)
+        step = 16
+        for z0 in range(0, self.D, step):
+            sl = slice(z0, min(self.D, z0 + step))
+            r = self.rho[:, :, sl].contiguous()
+            zero = torch.zeros((self.B, 3, *r.shape[2:]), dtype=torch.float32, device=self.device)
+            pr = macro.get_pressure(dx=self.dx, dt=self.dt, density=r)
+            self.pressure[:, :, sl] = pr
+            f0 = col.get_feq_(dx=self.dx, dt=self.dt, rho=r, vel=zero, force=zero)
+            g[:, :, sl] = col.get_geq_(dx=self.dx, dt=self.dt, rho=r, vel=zero, density=r, pressure=pr, force=zero,
+                                       feq=f0)
+            f[:, :, sl] = f0
+            del f0, pr, r, zero
         if self.magnetic:
             for t in self._h:
                 t.zero_()
@@ -419,7 +469,7 @@ class SlabFerroSolver:
         if zn <= 0:
             return
         slab = self.layout.slab(zb, zn)
-        H.launch(name, self.device, *args, ctypes.byref(slab), self.B, self.D, self.Hh, self.W)
+        H.launch(name, self.device, *args, ctypes.byref(slab), self.B, self.Dk, self.Hh, self.W)
 
     def _split(self):
         """(interior planes, [boundary plane ranges]) of the owned block"""
@@ -430,8 +480,10 @@ class SlabFerroSolver:
         L, p = self.layout, H.ptr
         own, d1 = L.planes_owned(), L.planes_depth(1)
         interior, edges = self._split()
-        cur, nxt = self._cur, 1 - self._cur
-        f, g = self._f[cur], self._g[cur]
+        f, g = self.f, self.g
+        fo, go = self._pop(self._f, nxt=True), self._pop(self._g, nxt=True)
+        compressed = self.streaming == "compressed"
+        ascending = self._off == self.S          # compressed: this pass moves the populations by -S planes
         chi = self._chi if self.magnetic else None
 
         def moments(planes):
@@ -486,22 +538,37 @@ class SlabFerroSolver:
         hu = ctypes.cast(self._H_uniform, ctypes.c_void_p) if self.magnetic else ctypes.c_void_p(0)
 
         def collide(planes):
-            self._launch("lbmff_slab_hcz_collide_stream_d3q19", p(f), p(g), p(self._f[nxt]), p(self._g[nxt]),
+            self._launch("lbmff_slab_hcz_collide_stream_d3q19", p(f), p(g), p(fo), p(go),
                          p(self.rho), p(self.flags), p(self.mflags), p(self._ws), p(chi),
                          p(self.psi if self.magnetic else None), hu, self.params, p(self.vel), p(self.pressure),
                          p(self.force), planes=planes)
 
         t0 = self._mark()
-        if self.magnetic:   # psi halos travel while the interior planes collide
-            yield HaloRequest([self.psi], 1, overlap=lambda: collide(interior))
+        if not compressed:
+            if self.magnetic:   # psi halos travel while the interior planes collide
+                yield HaloRequest([self.psi], 1, overlap=lambda: collide(interior))
+            else:
+                collide(interior)
+            for e in edges:
+                collide(e)
         else:
-            collide(interior)
-        for e in edges:
-            collide(e)
+            # one buffer: the launches must follow the pass direction (see __init__) -- first edge plane, interior in
+            # chunks, last edge plane -- so the psi halos are fetched before the first of them (one exposed exchange
+            # per step instead of an overlapped one)
+            if self.magnetic:
+                yield HaloRequest([self.psi], 1)
+            zb, zn = interior
+            starts = list(range(zb, zb + zn, self.chunk))
+            order = [edges[0]] + [(a, min(self.chunk, zb + zn - a)) for a in starts] + [edges[1]]
+            for planes in (order if ascending else order[::-1]):
+                collide(planes)
         t1 = self._mark()
         if self._timing is not None:
             self._timing["collide_stream"].append((t0, t1))
-        self._cur = nxt
+        if compressed:
+            self._off = self.S - self._off
+        else:
+            self._cur = 1 - self._cur
         self.steps_done += 1
 
     def step(self, n: int = 1):
@@ -603,7 +670,7 @@ class SlabFerroSolver:
 
     # ---- benchmark constructor --------------------------------------------------------------------
     @classmethod
-    def rosensweig(cls, res_per_rank, path, device, world, rank, mag=100.0, n_sweeps=30):
+    def rosensweig(cls, res_per_rank, path, device, world, rank, mag=100.0, n_sweeps=30, **kw):
         """Weak-scaling Rosensweig case: every rank owns res_per_rank = (Dl, H, W); global depth world*Dl."""
         from . import initializers as I
 
@@ -613,11 +680,11 @@ class SlabFerroSolver:
         mflags = slab_shell_flags(lay, Hh, W, open_axes=(1,), device=device)
         rho = I.rosensweig_rho((lay.D, Hh, W), flags, global_depth=lay.Dg, z_offset=lay.zoff)
         s = cls(lay, flags, exchanger=DistExchanger(lay, device), magnetic_flags=mflags, H_ext=[0.0, mag, 0.0],
-                n_sweeps=n_sweeps, magnetic_path=path, contact_angle=0.5 * math.pi, gravity=1e-4)
+                n_sweeps=n_sweeps, magnetic_path=path, contact_angle=0.5 * math.pi, gravity=1e-4, **kw)
         return s.initialize(rho)
 
 
-def _two_droplets(cls, res_per_rank, path, device, world, rank, mag=1.0, n_sweeps=30):
+def _two_droplets(cls, res_per_rank, path, device, world, rank, mag=1.0, n_sweeps=30, **kw):
     """demo_3d_LBM_two_droplets.py scaled up (BASELINE.json configs[4]): two liquid spheres in gas, every wall closed in
     both flag arrays (:113-121), kappa 0.5, tau_f = tau_g = 0.68, gravity 1e-4, uniform H_ext = mag along y (:166-168).
     Every rank owns res_per_rank = (Dl, H, W) of the global (world * Dl, H, W) box."""
@@ -629,7 +696,7 @@ def _two_droplets(cls, res_per_rank, path, device, world, rank, mag=1.0, n_sweep
     mflags = slab_shell_flags(lay, Hh, W, device=device)
     rho = I.two_droplets_rho((lay.D, Hh, W), flags, global_depth=lay.Dg, z_offset=lay.zoff)
     s = cls(lay, flags, exchanger=DistExchanger(lay, device), magnetic_flags=mflags, H_ext=[0.0, mag, 0.0],
-            n_sweeps=n_sweeps, magnetic_path=path, contact_angle=0.5 * math.pi, gravity=1e-4, kappa=0.5)
+            n_sweeps=n_sweeps, magnetic_path=path, contact_angle=0.5 * math.pi, gravity=1e-4, kappa=0.5, **kw)
     return s.initialize(rho)
 
 

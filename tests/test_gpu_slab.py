@@ -7,7 +7,7 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-def build(res, P, path, walls_open, steps, kappa=0.01, gravity=1e-4, droplets=False):
+def build(res, P, path, walls_open, steps, kappa=0.01, gravity=1e-4, droplets=False, **slab_kw):
     from lbm_ferrofluid_b200 import initializers as I
     from lbm_ferrofluid_b200.distributed import SlabFerroSolver, SlabLayout, slab_shell_flags, step_virtual_ranks
     from lbm_ferrofluid_b200.solver import FerroSolver
@@ -28,7 +28,7 @@ def build(res, P, path, walls_open, steps, kappa=0.01, gravity=1e-4, droplets=Fa
         lf = slab_shell_flags(lay, res[1], res[2], device=dev)
         lm = slab_shell_flags(lay, res[1], res[2], open_axes=walls_open, device=dev)
         assert torch.equal(lf, lay.take(flags)) and torch.equal(lm, lay.take(mflags))
-        slabs.append(SlabFerroSolver(lay, lf, magnetic_flags=lm, **kw).initialize(lay.take(rho)))
+        slabs.append(SlabFerroSolver(lay, lf, magnetic_flags=lm, **kw, **slab_kw).initialize(lay.take(rho)))
     step_virtual_ranks(slabs, steps)
     torch.cuda.synchronize()
     return one, slabs
@@ -134,3 +134,31 @@ def test_virtual_ranks_bit_identical_with_the_tma_kernel(path, monkeypatch):
         if name == "psi":
             got, want = got * fluid, want * fluid
         assert torch.equal(got, want), name
+
+
+@pytest.mark.parametrize("path", ["faithful", "scalar"])
+@pytest.mark.parametrize("P,res,chunk,steps", [(2, (24, 14, 18), 3, 3), (2, (32, 12, 72), 5, 4), (3, (48, 10, 20), 7, 3)])
+def test_compressed_streaming_is_bit_identical(P, res, chunk, steps, path):
+    """streaming="compressed": ONE f and ONE g buffer with chunk + 1 spare planes, passes issued in chunks whose output
+    is displaced by -/+ (chunk + 1) planes (ascending / descending steps alternate).  Same kernels, so every owned
+    cell must equal the one-GPU A/B run bit for bit -- after odd and even numbers of steps (both displacements)."""
+    one, slabs = build(res, P, path, (1,), steps, streaming="compressed", chunk=chunk)
+    fluid = (one.mflags != 2)
+    for name in ("f", "g", "rho", "pressure", "vel", "psi"):
+        got, want = torch.cat([s.owned(name) for s in slabs], dim=2), getattr(one, name)
+        if name == "psi":
+            got, want = got * fluid, want * fluid
+        assert torch.equal(got, want), f"{name} differs (P={P}, chunk={chunk}, {steps} steps)"
+    ab = build(res, P, path, (1,), 1)[1][0]
+    assert slabs[0].state_bytes < 0.8 * ab.state_bytes
+
+
+def test_compressed_streaming_argument_errors():
+    from lbm_ferrofluid_b200.distributed import SlabFerroSolver, SlabLayout, slab_shell_flags
+
+    lay = SlabLayout(24, 2, 0)
+    lf = slab_shell_flags(lay, 14, 18, device="cuda")
+    with pytest.raises(RuntimeError, match="spare planes"):
+        SlabFerroSolver(lay, lf, streaming="compressed", chunk=16)
+    with pytest.raises(ValueError):
+        SlabFerroSolver(lay, lf, streaming="esoteric")
