@@ -251,6 +251,19 @@ int lbmff_stream_collide_d3q19(const float* f_in, float* f_out, const uint8_t* f
                                float* rho, float* vel, double tau, double dx, double dt, int B, int D, int H, int W,
                                lbmff_stream_t stream);
 
+/* Shan-Chen multiphase step on D2Q9 in two passes (demo_2d_LBM_multiphase_SC.py:113-131: propagation, macro_compute,
+ * rebounce_obstacle, LBMCollisionSC2d.collision = calculate_force + BGK, LBM_collision_SC_2d.py:22-137).
+ * lbmff_sc_moments_d2q9: rho <- sum of the pulled f on non-OBSTACLE cells (in place), density = affine(rho)
+ * (LBM_macro_compute_2d.py:85-106), psi = C-S pseudopotential of density, the wall value on OBSTACLE cells.
+ * lbmff_sc_collide_stream_d2q9: pull, full-way bounce-back on OBSTACLE, vel (in place on non-OBSTACLE cells),
+ * interaction force on FLUID cells from the psi field (zero outside the array), BGK with p->tau.  force_out may be
+ * NULL.  p supplies dx, dt, tau and the density map (density_liquid / density_gas / rho_liquid / rho_gas). */
+int lbmff_sc_moments_d2q9(const float* f, const uint8_t* flags, float* rho, float* density, float* psi,
+                          const lbmff_fluid_params* p, int B, int H, int W, lbmff_stream_t stream);
+int lbmff_sc_collide_stream_d2q9(const float* f_in, float* f_out, const uint8_t* flags, const float* psi,
+                                 const float* rho, float* vel, float* force_out, const lbmff_fluid_params* p, int B,
+                                 int H, int W, lbmff_stream_t stream);
+
 /* =====================================================================================
  * SLAB TIER -- z-slab domain decomposition of the fused 3-D step (one process per GPU).
  * No reference counterpart: the reference is single-device ("Parallelism").

@@ -1,6 +1,7 @@
 // Drop-in tier, part 2: collision operators (a9, a10, a11, a15).
 #include "capi.cuh"
 #include "collide.cuh"
+#include "sc.cuh"
 
 namespace lbmff {
 
@@ -68,16 +69,7 @@ __global__ void __launch_bounds__(kThreads) k_kbc_s(const float* __restrict__ f,
   for (int q = 0; q < 9; ++q) out[(b * 9 + q) * g.N + i] = s[q];
 }
 
-// ---- a11 Shan-Chen force (LBM_collision_SC_2d.py:22-97)
-struct ScConsts {
-  float RT, a, cs2, G1, negG1, c, psx_wall;
-};
-__device__ __forceinline__ float sc_psi(float d, const ScConsts& S) {
-  const float t = d;  // density * b / 4 with b = 4
-  const float om = 1.0f - t;
-  const float v = S.RT * (1.0f + (4.0f * t - 2.0f * t * t) / (om * om * om)) - S.a * d - S.cs2;
-  return sqrtf(2.0f * d * v / S.G1 / S.cs2);
-}
+// ---- a11 Shan-Chen force (LBM_collision_SC_2d.py:22-97); ScConsts / sc_psi / make_sc: sc.cuh
 template <int DIM>
 __global__ void __launch_bounds__(kThreads) k_sc_force(const float* __restrict__ density,
                                                        const uint8_t* __restrict__ flags, float* __restrict__ out,
@@ -202,18 +194,6 @@ int lbmff_collision_kbc_d2q9(const float* f, const float* rho, const float* vel,
   k_collide_single<2, true><<<grid, kThreads, 0, st>>>(f, rho, vel, flags, force, f_out, kbc,
                                                        make_consts(dx, dt, tau), make_kbc(tau), g);
   return check_launch(__func__);
-}
-
-static ScConsts make_sc(double density_liquid, double density_gas, double dx, double dt) {
-  const double c = dx / dt, cs2 = c * c / 3.0, RT = cs2, a = 12.0 * cs2, bb = 4.0, G1 = -1.0 / 3.0;
-  const double dw = 0.5 * (density_gas + density_liquid);
-  double pw = dw * bb / 4.0;
-  pw = RT * (1.0 + (4.0 * pw - 2.0 * pw * pw) / ((1.0 - pw) * (1.0 - pw) * (1.0 - pw))) - a * dw - cs2;
-  pw = sqrt(2.0 * dw * pw / G1 / cs2);
-  ScConsts S;
-  S.RT = (float)RT; S.a = (float)a; S.cs2 = (float)cs2; S.G1 = (float)G1; S.negG1 = (float)(-G1); S.c = (float)c;
-  S.psx_wall = (float)pw;
-  return S;
 }
 
 int lbmff_sc_force_d2q9(const float* density, const uint8_t* flags, double density_liquid, double density_gas,

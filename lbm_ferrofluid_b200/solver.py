@@ -483,3 +483,64 @@ class SinglePhaseSolver:
             self._cur = nxt
             self.steps_done += 1
         return self
+
+
+class ShanChenSolver:
+    """Shan-Chen pseudopotential two-phase flow on D2Q9: the loop of demo_2d_LBM_multiphase_SC.py:113-131
+    (propagation, macro_compute, rebounce_obstacle, LBMCollisionSC2d.collision) in two kernels per step --
+    lbmff_sc_moments_d2q9 (rho, density, psi) and lbmff_sc_collide_stream_d2q9 (bounce, interaction force, BGK).
+    The op-by-op class LBMCollisionSC2d stays the drop-in API."""
+
+    def __init__(self, flags: torch.Tensor, *, tau: float = 1.0, density_liquid=0.265, density_gas=0.038,
+                 rho_liquid=0.265, rho_gas=0.038, dx=1.0, dt=1.0, keep_force: bool = False):
+        self.flags = H.need_cuda(flags, "flags", torch.uint8)
+        self.device = self.flags.device
+        self.dim, self.B, _, self.D, self.Hh, self.W = H.dims(self.flags)
+        if self.dim != 2:
+            raise RuntimeError("the reference's Shan-Chen model is 2-D (simulation_runner.py:107-108); "
+                               "extensions.LBMCollisionSC3d is the 3-D extension")
+        self.res = _res(self.flags)
+        self.dx, self.dt = float(dx), float(dt)
+        self._tau, self._density_liquid, self._density_gas = float(tau), density_liquid, density_gas
+        self._rho_liquid, self._rho_gas = rho_liquid, rho_gas
+        self.params = H.fluid_params(self, self.dx, self.dt)
+        opts = dict(dtype=torch.float32, device=self.device)
+        sc = lambda c: torch.zeros((self.B, c, *self.res), **opts)  # noqa: E731
+        self.rho, self.density, self.psi, self.vel = sc(1), sc(1), sc(1), sc(2)
+        self.force = sc(2) if keep_force else None
+        self._f = [sc(9), sc(9)]
+        self._cur = 0
+        self.steps_done = 0
+
+    @property
+    def f(self):
+        return self._f[self._cur]
+
+    def initialize(self, rho: torch.Tensor, density: Optional[torch.Tensor] = None,
+                   vel: Optional[torch.Tensor] = None):
+        """f = feq(density, vel, force = 0) as the demo does (demo_2d_LBM_multiphase_SC.py:111)."""
+        self.rho.copy_(H.need_cuda(rho, "rho"))
+        self.density.copy_(self.rho if density is None else H.need_cuda(density, "density"))
+        if vel is None:
+            self.vel.zero_()
+        else:
+            self.vel.copy_(H.need_cuda(vel, "vel"))
+        col = LBMCollision2d(tau=self._tau, device=self.device)
+        self._cur = 0
+        self._f[0].copy_(col.get_feq_(dx=self.dx, dt=self.dt, rho=self.density, vel=self.vel,
+                                      force=torch.zeros_like(self.vel)))
+        self.steps_done = 0
+        return self
+
+    def step(self, n: int = 1):
+        sz = (self.B, self.Hh, self.W)
+        for _ in range(int(n)):
+            cur, nxt = self._cur, 1 - self._cur
+            H.launch("lbmff_sc_moments_d2q9", self.device, H.ptr(self._f[cur]), H.ptr(self.flags), H.ptr(self.rho),
+                     H.ptr(self.density), H.ptr(self.psi), self.params, *sz)
+            H.launch("lbmff_sc_collide_stream_d2q9", self.device, H.ptr(self._f[cur]), H.ptr(self._f[nxt]),
+                     H.ptr(self.flags), H.ptr(self.psi), H.ptr(self.rho), H.ptr(self.vel), H.ptr(self.force),
+                     self.params, *sz)
+            self._cur = nxt
+            self.steps_done += 1
+        return self

@@ -427,3 +427,38 @@ def test_tma_kernel_falls_back_where_it_does_not_apply(monkeypatch):
     monkeypatch.setenv("LBMFF_HCZ_TMA", "2")
     with pytest.raises(RuntimeError, match="TMA kernel does not apply"):
         make_solver(G).step(1)
+
+
+def test_fused_shan_chen_step_vs_reference_golden():
+    """ShanChenSolver (lbmff_sc_moments_d2q9 + lbmff_sc_collide_stream_d2q9: two kernels per step) against the
+    10-step trajectory of the unmodified reference's LBMCollisionSC2d loop (traj_sc2d), and against the op-by-op
+    drop-in API (propagation / macro_compute / rebounce_obstacle / LBMCollisionSC2d.collision) on the same state."""
+    from lbm_ferrofluid_b200.collision import LBMCollisionSC2d
+    from lbm_ferrofluid_b200.macro_compute import LBMMacroCompute2d
+    from lbm_ferrofluid_b200.propagation import LBMPropagation2d
+    from lbm_ferrofluid_b200.solver import ShanChenSolver
+
+    G = load_golden("traj_sc2d")
+    steps = int(G["steps"])
+    s = ShanChenSolver(G["flags"].cuda(), tau=1.0, keep_force=True).initialize(G["rho0"].cuda(), vel=G["vel0"].cuda())
+    s.step(steps)
+    for k, t in (("f", s.f), ("rho", s.rho), ("vel", s.vel)):
+        e = rel_l2(t.cpu(), G[k])
+        assert e <= 2e-5, f"traj_sc2d {k}: rel-L2 {e:.3e}"
+    # op by op through the drop-in classes
+    kw = dict(density_liquid=0.265, density_gas=0.038, rho_liquid=0.265, rho_gas=0.038, device=torch.device("cuda"))
+    prop, macro, col = LBMPropagation2d(**kw), LBMMacroCompute2d(**kw), LBMCollisionSC2d(tau=1.0, **kw)
+    flags, rho, vel = G["flags"].cuda(), G["rho0"].cuda(), G["vel0"].cuda()
+    density, force = rho.clone(), torch.zeros_like(vel)
+    f = col.get_feq_(dx=1.0, dt=1.0, rho=density, vel=vel, force=force)
+    for _ in range(steps):
+        f = prop.propagation(f=f)
+        rho, vel, density = macro.macro_compute(dx=1.0, dt=1.0, f=f, rho=rho, vel=vel, flags=flags, density=density)
+        f = prop.rebounce_obstacle(f=f, flags=flags)
+        f = col.collision(dx=1.0, dt=1.0, f=f, rho=rho, density=density, vel=vel, flags=flags, force=force)
+    assert rel_l2(s.f, f) <= 5e-6 and rel_l2(s.rho, rho) <= 5e-6 and rel_l2(s.density, density) <= 5e-6
+    # the force the fused kernel applied in its last step == calculate_force on the density it saw
+    F = col.calculate_force(dx=1.0, dt=1.0, density=s.density, flags=flags, force=force)
+    assert (s.force - F).abs().max() <= 2e-6 * F.abs().max()
+    with pytest.raises(RuntimeError):
+        ShanChenSolver(torch.ones((1, 1, 8, 8, 8), dtype=torch.uint8, device="cuda"))
