@@ -418,10 +418,10 @@ k_hcz_collide_stream_pf(const float* __restrict__ fi, const float* __restrict__ 
 //  * the 20 populations with e_x = +-1 are shifted by one float and cannot be a box without widening every tile to
 //    72 (which no longer fits two blocks per SM): they keep the 4-byte cp.async copies of the _pf kernel.
 // Both kinds land in the same [2Q][4][64] stage (a thread's own slot is [q][ty][tx] either way).  Completion: two
-// mbarriers (expect_tx) for the boxes, cp.async.wait_group for the thread's own copies.  There is NO block barrier in
-// the plane loop (a __syncthreads per plane cost 11 % of the stall samples with two 8-warp blocks per SM): a warp
-// that has finished a plane bumps a shared counter, and the LAST warp to arrive issues the boxes that refill the
-// stage and the ring slot just freed -- nobody waits for the slowest warp except through the data it needs.
+// mbarriers (expect_tx) for the boxes, cp.async.wait_group for the thread's own copies; one __syncthreads per plane
+// frees the stage and the ring slot for refill.  (Measured and not kept: replacing that barrier by an arrival counter
+// whose last warp issues the refill -- the barrier shows as 11 % of the stall samples in the 512^3 capture, but with
+// two blocks per SM the other block fills those slots: 10.46 ms against 10.39 ms.)
 // TMA zero-fills outside the tensor while the lattice is periodic: a cell whose box-loaded pull wraps around the
 // array (y = 0 / H-1, local z = 0 / D-1; wall cells in the named configurations) re-reads those populations
 // directly.  Stencil centres are clamped to the interior exactly as in GlobalStencil: in x / y the clamp is an index
@@ -435,8 +435,7 @@ constexpr int kStSc = 448;                            // one scalar field, padde
 constexpr int kStSlot = kStWs + 2 * kStSc;            // 2208 floats = 8832 B per z plane
 constexpr int kPullStage = 2 * 19 * kThreads;         // 9728 floats = 38912 B
 constexpr int kTmaSmemFloats = 2 * kPullStage + 4 * kStSlot;
-constexpr int kTmaSmemBytes = kTmaSmemFloats * 4 + 16 /* two mbarriers */ + 16 /* two arrival counters */ +
-                              128 /* alignment slack */;
+constexpr int kTmaSmemBytes = kTmaSmemFloats * 4 + 16 /* two mbarriers */ + 128 /* alignment slack */;
 
 struct SmemField {   // sampler around the thread's (clamped) centre: offsets are compile-time after inlining
   const float* c;    // centre element in the slot of plane z
@@ -490,8 +489,6 @@ k_hcz_collide_stream_tma(const __grid_constant__ TmaMaps M, const float* __restr
     tma::mbar_init(bar0, 1);
     tma::mbar_init(bar0 + 8, 1);
     tma::fence_barrier_init();
-    reinterpret_cast<unsigned*>(ring + 4 * kStSlot + 4)[0] = 0u;
-    reinterpret_cast<unsigned*>(ring + 4 * kStSlot + 4)[1] = 0u;
   }
   __syncthreads();
   const PopIndex<IDX32> at(g);
@@ -539,11 +536,7 @@ k_hcz_collide_stream_tma(const __grid_constant__ TmaMaps M, const float* __restr
     }
     cp_async_commit();
   };
-  unsigned* cnt = reinterpret_cast<unsigned*>(ring + 4 * kStSlot + 4);   // after the two mbarriers
-  if (tid == 0) {
-    issue(z0, z0 - 1, 3);
-    if (z0 + 1 < z1) issue(z0 + 1, z0 + 2, 1);
-  }
+  if (tid == 0) issue(z0, z0 - 1, 3);
   prefetch(z0);
   // stencil centre of this thread inside the rim-extended tile (x / y clamp = index shift, see above)
   const int ccx = tx + kStX0 + (interior(c.x, g.W) - c.x), ccy = ty + 1 + (interior(c.y, g.H) - c.y);
@@ -552,8 +545,10 @@ k_hcz_collide_stream_tma(const __grid_constant__ TmaMaps M, const float* __restr
   float rho_next = c.live ? A.rho_[cell0] : 0.f;
   const bool sy0 = c.y == 0, sy1 = c.y == g.H - 1;
   for (int z = z0; z < z1; ++z) {
+    __syncthreads();   // every thread is done with the stage and the ring slot about to be refilled
     if (z + 1 < z1) {
-      prefetch(z + 1);          // own slots of the other stage: last read by this thread one plane ago
+      if (tid == 0) issue(z + 1, z + 2, 1);
+      prefetch(z + 1);
       cp_async_wait<1>();
     } else {
       cp_async_wait<0>();
@@ -564,51 +559,38 @@ k_hcz_collide_stream_tma(const __grid_constant__ TmaMaps M, const float* __restr
       fl_next = A.flags[((z + 1) * g.H + c.y) * g.W + c.x];
       rho_next = A.rho_[((z + 1) * g.H + c.y) * g.W + c.x];
     }
-    if (c.live) {
-      tma::mbar_wait(bar0 + 8 * (z & 1), ((z - z0) >> 1) & 1);
-      c.z = z;
-      c.i = (z * g.H + c.y) * g.W + c.x;
-      float* s = pull + (z & 1) * kPullStage + tid;
-      float gv[Q];
+    if (!c.live) continue;
+    tma::mbar_wait(bar0 + 8 * (z & 1), ((z - z0) >> 1) & 1);
+    c.z = z;
+    c.i = (z * g.H + c.y) * g.W + c.x;
+    float* s = pull + (z & 1) * kPullStage + tid;
+    float gv[Q];
 #pragma unroll
-      for (int q = 0; q < Q; ++q) gv[q] = s[q * kThreads];
-      const bool sz0 = z == 0, sz1 = z == g.D - 1;
-      if (sy0 | sy1 | sz0 | sz1) {   // periodic seam: the box was zero-filled where the pull wraps
-        const Nbr nb(c, g);
+    for (int q = 0; q < Q; ++q) gv[q] = s[q * kThreads];
+    const bool sz0 = z == 0, sz1 = z == g.D - 1;
+    if (sy0 | sy1 | sz0 | sz1) {   // periodic seam: the box was zero-filled where the pull wraps
+      const Nbr nb(c, g);
 #pragma unroll
-        for (int q = 1; q < Q; ++q) {
-          const int ex = Lat<3>::ex(q), ey = Lat<3>::ey(q), ez = Lat<3>::ez(q);
-          if (ex != 0) continue;
-          const bool wraps = (ey == 1 && sy0) || (ey == -1 && sy1) || (ez == 1 && sz0) || (ez == -1 && sz1);
-          if (wraps) {
-            const auto j = at(q, c.i + nb.at<DIM>(q, 1));
-            gv[q] = ld_spec(gi + j);
-            s[(Q + q) * kThreads] = ld_spec(fi + j);
-          }
+      for (int q = 1; q < Q; ++q) {
+        const int ex = Lat<3>::ex(q), ey = Lat<3>::ey(q), ez = Lat<3>::ez(q);
+        if (ex != 0) continue;
+        const bool wraps = (ey == 1 && sy0) || (ey == -1 && sy1) || (ez == 1 && sz0) || (ez == -1 && sz1);
+        if (wraps) {
+          const auto j = at(q, c.i + nb.at<DIM>(q, 1));
+          gv[q] = ld_spec(gi + j);
+          s[(Q + q) * kThreads] = ld_spec(fi + j);
         }
-        tma::fence_proxy_async();   // generic writes to a stage the TMA unit refills later
       }
-      const SmemPop fv{s + Q * kThreads};
-      if (interior_z(g, z) == z) {
-        const float* slot = ring + (z & 3) * kStSlot;
-        const SmemStencil<MAGNETIC> st{slot + ccy * kStW + ccx, (((z - 1) & 3) - (z & 3)) * kStSlot,
-                                       (((z + 1) & 3) - (z & 3)) * kStSlot};
-        hcz_cs_cell<DIM, MAGNETIC, IDX32>(c, at, RegPop{gv}, fv, fl, rho, A, k, K, g, st);
-      } else {
-        hcz_cs_cell<DIM, MAGNETIC, IDX32>(c, at, RegPop{gv}, fv, fl, rho, A, k, K, g, GlobalStencil<DIM, MAGNETIC>{});
-      }
+      tma::fence_proxy_async();   // generic writes to a stage the TMA unit refills later
     }
-    // this warp is done with stage z & 1 and with ring plane z - 1: the last warp to say so refills them
-    if (z + 2 < z1) {
-      __syncwarp();
-      if ((tid & 31) == 0) {
-        __threadfence_block();
-        if (atomicAdd(&cnt[z & 1], 1u) == kThreads / 32 - 1) {
-          atomicExch(&cnt[z & 1], 0u);
-          __threadfence_block();
-          issue(z + 2, z + 3, 1);
-        }
-      }
+    const SmemPop fv{s + Q * kThreads};
+    if (interior_z(g, z) == z) {
+      const float* slot = ring + (z & 3) * kStSlot;
+      const SmemStencil<MAGNETIC> st{slot + ccy * kStW + ccx, (((z - 1) & 3) - (z & 3)) * kStSlot,
+                                     (((z + 1) & 3) - (z & 3)) * kStSlot};
+      hcz_cs_cell<DIM, MAGNETIC, IDX32>(c, at, RegPop{gv}, fv, fl, rho, A, k, K, g, st);
+    } else {
+      hcz_cs_cell<DIM, MAGNETIC, IDX32>(c, at, RegPop{gv}, fv, fl, rho, A, k, K, g, GlobalStencil<DIM, MAGNETIC>{});
     }
   }
 }
