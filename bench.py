@@ -315,6 +315,22 @@ def reference_eager_on_gpu(res=(256, 256, 256)):
         return {"value": None, "error": str(e)[:200]}
 
 
+def bind_to_gpu_numa_node(index):
+    """Pin this rank's host threads to the CPU cores next to its GPU (NVML's ideal affinity) BEFORE any pinned buffer
+    is allocated, so the e2e path's staging memory is first-touched on the GPU's own NUMA node instead of wherever the
+    launcher started the process.  Returns the number of cores bound to, or None if NVML does not cooperate."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        n = len(os.sched_getaffinity(0))
+        pynvml.nvmlShutdown()
+        return n
+    except Exception:
+        return None
+
+
 def run_ours(args):
     import torch.distributed as dist
 
@@ -326,6 +342,7 @@ def run_ours(args):
                          "(use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
+    numa = bind_to_gpu_numa_node(local) if world > 1 else None
     if world > 1:
         # halo messages ride NCCL's own stream: make it high priority so its few CTAs are scheduled ahead of
         # the interior-plane kernel they overlap with
@@ -507,6 +524,7 @@ def run_ours(args):
             line["slab_bit_identical"] = None if slab_verify is None else slab_verify["slab_bit_identical"]
             line["slab_verify"] = slab_verify
             line["exchange"] = exch
+            line["numa_bound_cores"] = numa
         if cfgs is not None:
             line["configs"] = cfgs
         if eager is not None:

@@ -243,7 +243,11 @@ __device__ __forceinline__ void hcz_cs_cell(const PlaneCell& c, const PopIndex<I
   // get_grad shell rule in their data, so the 18-point stencils are plain constant-offset loads
   float glap[3], gfai[3], gprho[3], gchi[3], gpsi[3];
   stencil(c, g, ws, chi, psi, k.inv12dx, glap, gfai, gprho, gchi, gpsi);
+#ifdef LBMFF_HCZ_FEQ_IEEE
   const float dn = affine_density(rho, k.aff);
+#else
+  const float dn = k.aff.dg + k.aff.ddiff * ((rho - k.aff.rg) * k.aff.inv_rdiff);   // as CentredDensity above
+#endif
   float F[DIM];
 #pragma unroll
   for (int a = 0; a < DIM; ++a) {
@@ -271,7 +275,11 @@ __device__ __forceinline__ void hcz_cs_cell(const PlaneCell& c, const PopIndex<I
     if (DIM == 3) { if (L::ez(q) == 1) m[2] += gq; else if (L::ez(q) == -1) m[2] -= gq; }
   }
   float u[DIM], dot = 0.f;
+#ifdef LBMFF_HCZ_FEQ_IEEE
   const float inv_dn = k.vel_scale / dn;  // 1 / (cs2 density)
+#else
+  const float inv_dn = k.vel_scale * nr_rcp(dn);
+#endif
 #pragma unroll
   for (int a = 0; a < DIM; ++a) {
     u[a] = (m[a] * k.c + k.half_dt_RT * F[a]) * inv_dn;
@@ -294,13 +302,25 @@ __device__ __forceinline__ void hcz_cs_cell(const PlaneCell& c, const PopIndex<I
       relaxed = true;
     }
   }
+  {   // the rest population, then opposite pairs (hcz_collide_pair shares what e_p = -e_q makes common)
+    float f0 = fv(0);
+    float g0 = (DIM == 2 && relaxed) ? gk[0] : gv(0);
+    hcz_collide_q<DIM>(0, C, k, f0, g0, relaxed);
+    fo[at(0, i)] = f0;
+    go[at(0, i)] = g0;
+  }
 #pragma unroll
-  for (int q = 0; q < L::Q; ++q) {
-    float fq = fv(q);
+  for (int q = 1; q < L::Q; ++q) {
+    const int p = L::opp(q);
+    if (q > p) continue;
+    float fq = fv(q), fp = fv(p);
     float gq = (DIM == 2 && relaxed) ? gk[DIM == 2 ? q : 0] : gv(q);
-    hcz_collide_q<DIM>(q, C, k, fq, gq, relaxed);
+    float gp = (DIM == 2 && relaxed) ? gk[DIM == 2 ? p : 0] : gv(p);
+    hcz_collide_pair<DIM>(q, C, k, fq, gq, fp, gp, relaxed);
     fo[at(q, i)] = fq;
     go[at(q, i)] = gq;
+    fo[at(p, i)] = fp;
+    go[at(p, i)] = gp;
   }
 }
 

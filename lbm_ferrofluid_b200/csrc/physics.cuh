@@ -114,6 +114,42 @@ __device__ __forceinline__ FeqFactors<DIM> feq_factors_fast(const float* u, floa
   return F;
 }
 
+// Division and square root for the speed-ordered fused HCZ kernels: the MUFU approximation refined by one Newton
+// step and a residual correction -- faithfully rounded (<= 1 ulp) for the O(1) operands that occur here (1 - u,
+// 2u + s, density, rho), 6 instructions, and none of the slow-path checks (FCHK + branch + call) that an IEEE `/` or
+// sqrtf drags along: 9 divisions + 3 square roots were ~100 of the ~1400 instructions per cell of
+// k_hcz_collide_stream_tma.  Only the fused tier uses them; the drop-in operators keep IEEE division.
+__device__ __forceinline__ float nr_rcp(float b) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(b));
+  return fmaf(fmaf(-b, r, 1.0f), r, r);
+}
+__device__ __forceinline__ float nr_div(float a, float b) {
+  const float r = nr_rcp(b), q = a * r;
+  return fmaf(fmaf(-b, q, a), r, q);
+}
+__device__ __forceinline__ float nr_sqrt(float x) {
+  float r;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  const float s = x * r;
+  return fmaf(fmaf(-s, s, x), 0.5f * r, s);
+}
+template <int DIM>
+__device__ __forceinline__ FeqFactors<DIM> feq_factors_nr(const float* u, float inv_c) {
+  FeqFactors<DIM> F;
+  F.base = 1.0f;
+#pragma unroll
+  for (int a = 0; a < DIM; ++a) {
+    const float ul = u[a] * inv_c;
+    const float s = nr_sqrt(fmaf(3.0f * ul, ul, 1.0f));
+    const float num = fmaf(2.0f, ul, s), den = 1.0f - ul;
+    F.base *= 2.0f - s;
+    F.A[a] = nr_div(num, den);
+    F.invA[a] = nr_div(den, num);
+  }
+  return F;
+}
+
 template <int DIM>
 __device__ __forceinline__ float feq_q(const FeqFactors<DIM>& F, float rho, int q) {
   using L = Lat<DIM>;
