@@ -347,6 +347,20 @@ int lbmff_poisson_cg_3d(const float* rhs, const uint8_t* mflags, float* psi, flo
                         int max_iters, double tol, double tau, double dx, double dt, float* res_hist, double* info,
                         int B, int D, int H, int W, lbmff_stream_t stream);
 
+/* The same solve with a geometric-multigrid preconditioner (csrc/poisson_mg.cuh): one V(2,2) cycle per iteration --
+ * 2 x 2 (x 2) cell aggregation, piecewise-constant transfer, Galerkin coarse operators on the same lattice directions
+ * (walls = zero-weight links), damped-Jacobi smoothing, the whole cycle inside the same device-side WHILE loop.
+ *   work     [B][7][N] floats (the five of lbmff_poisson_cg_* + z + one smoother buffer)
+ *   mg_work  [B][lbmff_poisson_mg_workspace_floats(D,H,W)] floats (levels >= 1: weights, diagonal, x, t, b)
+ * Everything else as lbmff_poisson_cg_*; the stopping test is on the unpreconditioned residual |r|. */
+long long lbmff_poisson_mg_workspace_floats(int D, int H, int W);
+int lbmff_poisson_pcg_2d(const float* rhs, const uint8_t* mflags, float* psi, float* work, float* mg_work,
+                         double* scratch, int max_iters, double tol, double tau, double dx, double dt, float* res_hist,
+                         double* info, int B, int H, int W, lbmff_stream_t stream);
+int lbmff_poisson_pcg_3d(const float* rhs, const uint8_t* mflags, float* psi, float* work, float* mg_work,
+                         double* scratch, int max_iters, double tol, double tau, double dx, double dt, float* res_hist,
+                         double* info, int B, int D, int H, int W, lbmff_stream_t stream);
+
 /* ---- iso-surface of the order parameter on the device (replaces the host round trip
  *      mcubes.marching_cubes((-phi * s).cpu().numpy()[0, 0], 0) of src/LBM/utils/io.py:50-63).
  * u [D][H][W] fp32 (device).  Marching cubes with a case table derived at load time (csrc/iso_surface.cu; PyMCubes is

@@ -47,7 +47,7 @@ def parse_header(path: str = HEADER):
     text = open(path).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
     protos = {}
-    for m in re.finditer(r"\b(int|const char\s*\*)\s+(lbmff_\w+)\s*\(([^)]*)\)\s*;", text):
+    for m in re.finditer(r"\b(long long|int|const char\s*\*)\s+(lbmff_\w+)\s*\(([^)]*)\)\s*;", text):
         ret, name, args = m.group(1), m.group(2), m.group(3).strip()
         argtypes = []
         if args and args != "void":
@@ -65,7 +65,8 @@ def parse_header(path: str = HEADER):
                         break
                 else:
                     raise RuntimeError(f"lbmff.h: cannot map C type '{ty}' of {name}")
-        protos[name] = (ctypes.c_char_p if "char" in ret else ctypes.c_int, argtypes)
+        protos[name] = (ctypes.c_char_p if "char" in ret else (ctypes.c_longlong if "long" in ret else ctypes.c_int),
+                        argtypes)
     return protos
 
 

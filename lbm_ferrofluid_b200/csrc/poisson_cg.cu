@@ -27,6 +27,7 @@
 // it is opt-in (FerroSolver(magnetic_path="converged")) and validated against the sweeps run to convergence.
 #include "capi.cuh"
 #include "magnetic.cuh"
+#include "poisson_mg.cuh"
 
 #include <stdlib.h>
 
@@ -454,6 +455,326 @@ static int poisson_cg_impl(const float* rhs, const uint8_t* mflags, float* psi, 
   return check_launch(where);
 }
 
+// ================================================================================================================
+// Preconditioned conjugate gradients: the same system, M^-1 = one multigrid V-cycle (poisson_mg.cuh).
+// ================================================================================================================
+
+// level-0 smoother / residual on the mask-based operator.  MODE 0: xo = xi + omega / diag (b - L xi); 1: xo = b - L xi
+template <int DIM, int MODE>
+__global__ void __launch_bounds__(kThreads) k_mg0_sweep(const unsigned* __restrict__ mask, const float* __restrict__ b,
+                                                        const float* __restrict__ xi, float* __restrict__ xo, Grid g) {
+  LBMFF_CG_PLANES(c) {
+    const unsigned m = mask[c.i];
+    float out = 0.f;
+    if (!(m & kWallSelf)) {
+      const Nbr nb(c, g);
+      const float xc = __ldg(xi + c.i);
+      const float r = b[c.i] - laplace<DIM>(xi, xc, c.i, nb, m);
+      const float d = diag_of<DIM>(m);
+      out = MODE == 0 ? (d > 0.f ? fmaf(mg::kOmega / d, r, xc) : xc) : r;
+    }
+    xo[c.i] = out;
+  }
+}
+template <int DIM>
+__global__ void __launch_bounds__(kThreads) k_mg0_jacobi0(const unsigned* __restrict__ mask, const float* __restrict__ b,
+                                                          float* __restrict__ x, Grid g) {
+  LBMFF_CG_PLANES(c) {
+    const unsigned m = mask[c.i];
+    float out = 0.f;
+    if (!(m & kWallSelf)) {
+      const float d = diag_of<DIM>(m);
+      out = d > 0.f ? (mg::kOmega / d) * b[c.i] : 0.f;
+    }
+    x[c.i] = out;
+  }
+}
+// partials: r.z, r.r
+__global__ void __launch_bounds__(kThreads) k_cg_dot2(const float* __restrict__ r, const float* __restrict__ z,
+                                                      long long n, double* __restrict__ partials, int nblocks) {
+  double acc[3] = {0.0, 0.0, 0.0};
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const float rv = r[i];
+    acc[0] += (double)rv * z[i];
+    acc[1] += (double)rv * rv;
+  }
+  block_partials<3>(acc, partials, nblocks);
+}
+// what = 4 of the finish step: rz = v0 (start of PCG: p = z)
+__global__ void k_pcg_set_rz(const double* __restrict__ partials, int nblocks, CgScalars* __restrict__ sc) {
+  __shared__ double sm[32];
+  double a = 0.0;
+  for (int i = threadIdx.x; i < nblocks; i += blockDim.x) a += partials[i];
+  a = warp_sum(a);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = a;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    a = warp_sum(threadIdx.x < (blockDim.x >> 5) ? sm[threadIdx.x] : 0.0);
+    if (threadIdx.x == 0) sc->rz = a;
+  }
+}
+// p = z + beta p  (beta = 0 at the start)
+__global__ void __launch_bounds__(kThreads) k_pcg_direction(float* __restrict__ p, const float* __restrict__ z,
+                                                            long long n, const CgScalars* __restrict__ sc, int first) {
+  if (sc->done != 0.0) return;
+  const float beta = first ? 0.f : (float)sc->beta;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    p[i] = first ? z[i] : fmaf(beta, p[i], z[i]);
+}
+
+// Launches kernels directly, or records them as a chain of kernel nodes of a graph (the WHILE body).
+struct Launcher {
+  cudaStream_t st;
+  cudaGraph_t body = nullptr;
+  cudaGraphNode_t prev = nullptr;
+  cudaError_t err = cudaSuccess;
+  template <class... A>
+  void operator()(const void* fn, dim3 grid, dim3 block, A... a) {
+    if (err != cudaSuccess) return;
+    void* args[] = {(void*)&a...};
+    if (!body) {
+      err = cudaLaunchKernel(fn, grid, block, args, 0, st);
+      return;
+    }
+    cudaKernelNodeParams kp = {};
+    kp.func = const_cast<void*>(fn); kp.gridDim = grid; kp.blockDim = block; kp.sharedMemBytes = 0; kp.kernelParams = args;
+    cudaGraphNode_t n;
+    err = cudaGraphAddKernelNode(&n, body, prev ? &prev : nullptr, prev ? 1 : 0, &kp);
+    prev = n;
+  }
+};
+
+static PlaneLaunch mg_launch(const Grid& g) {
+  PlaneLaunch pl = plane_launch(g, 64);
+  pl.grid.z = pl.grid.z > 16u ? 16u : pl.grid.z;
+  return pl;
+}
+static unsigned flat_blocks(long long n) {
+  const long long b = (n + kThreads - 1) / kThreads;
+  return (unsigned)(b > 4096 ? 4096 : (b < 1 ? 1 : b));
+}
+
+// extents of the hierarchy below a D x H x W fine grid; returns the number of coarse levels
+template <int DIM>
+static int mg_levels(const Grid& g0, Grid* out) {
+  int n = 0;
+  Grid g = g0;
+  while (n < mg::kMaxLevels - 1) {
+    const int W = (g.W + 1) / 2, H = (g.H + 1) / 2, D = DIM == 3 ? (g.D + 1) / 2 : 1;
+    if (W < 3 || H < 3 || (DIM == 3 && D < 3)) break;
+    g = make_grid(1, D, H, W);
+    out[n++] = g;
+  }
+  return n;
+}
+template <int DIM>
+static long long mg_workspace_floats(const Grid& g0) {
+  Grid lv[mg::kMaxLevels];
+  const int n = mg_levels<DIM>(g0, lv);
+  long long total = 0;
+  for (int l = 0; l < n; ++l) total += (long long)(Lat<DIM>::Q - 1 + 4) * ((lv[l].N + 3) / 4 * 4);
+  return total;
+}
+template <int DIM>
+static int mg_carve(const Grid& g0, float* ws, mg::Level* L) {
+  Grid lv[mg::kMaxLevels];
+  const int n = mg_levels<DIM>(g0, lv);
+  for (int l = 0; l < n; ++l) {
+    const long long N = (lv[l].N + 3) / 4 * 4;
+    L[l].g = lv[l];
+    L[l].w = ws; ws += (Lat<DIM>::Q - 1) * N;
+    L[l].invd = ws; ws += N;
+    L[l].x = ws; ws += N;
+    L[l].t = ws; ws += N;
+    L[l].b = ws; ws += N;
+  }
+  return n;
+}
+// the Galerkin hierarchy depends on the flags only: built once per solve (cheap: sum over levels of N / 7 cells)
+template <int DIM>
+static void mg_setup(const unsigned* mask, const Grid& g0, mg::Level* L, int n, cudaStream_t st) {
+  for (int l = 0; l < n; ++l) {
+    const PlaneLaunch pl = mg_launch(L[l].g);
+    if (l == 0)
+      mg::k_mg_coarsen<DIM, mg::MaskLinks<DIM>><<<pl.grid, pl.block, 0, st>>>(mg::MaskLinks<DIM>{mask}, g0, L[0].w,
+                                                                             L[0].invd, L[0].g);
+    else
+      mg::k_mg_coarsen<DIM, mg::ArrayLinks><<<pl.grid, pl.block, 0, st>>>(mg::ArrayLinks{L[l - 1].w}, L[l - 1].g,
+                                                                         L[l].w, L[l].invd, L[l].g);
+  }
+}
+// z = M^-1 r: one V(2,2) cycle.  Level 0 works in (z, t0) with `res0` as residual scratch; result in z.
+template <int DIM>
+static void mg_vcycle(Launcher& K, const unsigned* mask, const Grid& g0, const float* r, float* z, float* t0,
+                      float* res0, mg::Level* L, int n) {
+  const PlaneLaunch p0 = cg_launch(g0);
+  K((const void*)k_mg0_jacobi0<DIM>, p0.grid, p0.block, mask, r, t0, g0);
+  K((const void*)k_mg0_sweep<DIM, 0>, p0.grid, p0.block, mask, r, (const float*)t0, z, g0);
+  if (n > 0) {
+    K((const void*)k_mg0_sweep<DIM, 1>, p0.grid, p0.block, mask, r, (const float*)z, res0, g0);
+    {
+      const PlaneLaunch pc = mg_launch(L[0].g);
+      K((const void*)mg::k_mg_restrict<DIM>, pc.grid, pc.block, (const float*)res0, g0, L[0].b, L[0].g);
+    }
+    for (int l = 0; l < n; ++l) {   // down
+      const Grid g = L[l].g;
+      const PlaneLaunch pl = mg_launch(g);
+      const float *w = L[l].w, *invd = L[l].invd, *b = L[l].b;
+      if (l == n - 1) {             // coarsest: Jacobi from zero, ending in x
+        K((const void*)mg::k_mg_jacobi0, dim3(flat_blocks(g.N)), dim3(kThreads), b, invd, L[l].t, g.N);
+        for (int s = 1; s < mg::kCoarsestSweeps; ++s) {
+          float* xi = (s & 1) ? L[l].t : L[l].x;
+          float* xo = (s & 1) ? L[l].x : L[l].t;
+          K((const void*)mg::k_mg_sweep<DIM, 0>, pl.grid, pl.block, w, invd, b, (const float*)xi, xo, g);
+        }
+        static_assert(mg::kCoarsestSweeps % 2 == 0, "the coarsest solve must end in x");
+        break;
+      }
+      K((const void*)mg::k_mg_jacobi0, dim3(flat_blocks(g.N)), dim3(kThreads), b, invd, L[l].t, g.N);
+      K((const void*)mg::k_mg_sweep<DIM, 0>, pl.grid, pl.block, w, invd, b, (const float*)L[l].t, L[l].x, g);
+      K((const void*)mg::k_mg_sweep<DIM, 1>, pl.grid, pl.block, w, invd, b, (const float*)L[l].x, L[l].t, g);
+      const PlaneLaunch pc = mg_launch(L[l + 1].g);
+      K((const void*)mg::k_mg_restrict<DIM>, pc.grid, pc.block, (const float*)L[l].t, g, L[l + 1].b, L[l + 1].g);
+    }
+    for (int l = n - 2; l >= 0; --l) {   // up
+      const Grid g = L[l].g;
+      const PlaneLaunch pl = mg_launch(g);
+      const float *w = L[l].w, *invd = L[l].invd, *b = L[l].b;
+      K((const void*)mg::k_mg_prolong_add<DIM>, pl.grid, pl.block, L[l].x, g, (const float*)L[l + 1].x, L[l + 1].g,
+        (const unsigned*)nullptr);
+      K((const void*)mg::k_mg_sweep<DIM, 0>, pl.grid, pl.block, w, invd, b, (const float*)L[l].x, L[l].t, g);
+      K((const void*)mg::k_mg_sweep<DIM, 0>, pl.grid, pl.block, w, invd, b, (const float*)L[l].t, L[l].x, g);
+    }
+    const PlaneLaunch pf = mg_launch(g0);
+    K((const void*)mg::k_mg_prolong_add<DIM>, pf.grid, pf.block, z, g0, (const float*)L[0].x, L[0].g, mask);
+  }
+  K((const void*)k_mg0_sweep<DIM, 0>, p0.grid, p0.block, mask, r, (const float*)z, t0, g0);
+  K((const void*)k_mg0_sweep<DIM, 0>, p0.grid, p0.block, mask, r, (const float*)t0, z, g0);
+}
+
+struct PcgExtra {
+  float *z, *t;          // preconditioned residual, Jacobi scratch of the fine level
+  mg::Level L[mg::kMaxLevels];
+  int nlev;
+};
+
+// body of one PCG iteration, recorded into K (direct launches or graph nodes)
+template <int DIM, bool GRAPH>
+static void pcg_body(Launcher& K, const CgBuffers& B, PcgExtra& X, const PlaneLaunch& pl, int nb, int max_iters,
+                     double tol2, const Grid& g, cudaGraphConditionalHandle handle) {
+  const bool vec4 = cg_vec4(B, g);
+  float* nohist = nullptr;
+  K((const void*)k_cg_apply<DIM>, pl.grid, pl.block, (const float*)B.p, (const unsigned*)B.mask, B.Ap, B.part, nb,
+    (const CgScalars*)B.sc, g);
+  K((const void*)k_cg_finish<GRAPH>, dim3(1), dim3(1024), (const double*)B.part, nb, 2, B.sc, nohist, 0.0, max_iters,
+    handle);
+  K(vec4 ? (const void*)k_cg_update<true> : (const void*)k_cg_update<false>, dim3(nb), dim3(kThreads), B.psi, B.r,
+    (const float*)B.p, (const float*)B.Ap, (long long)g.N, B.part, nb, (const CgScalars*)B.sc);
+  mg_vcycle<DIM>(K, B.mask, g, B.r, X.z, X.t, B.Ap, X.L, X.nlev);
+  K((const void*)k_cg_dot2, dim3(nb), dim3(kThreads), (const float*)B.r, (const float*)X.z, (long long)g.N, B.part, nb);
+  K((const void*)k_cg_finish<GRAPH>, dim3(1), dim3(1024), (const double*)B.part, nb, 3, B.sc, B.hist, tol2, max_iters,
+    handle);
+  K((const void*)k_pcg_direction, dim3(flat_blocks(g.N)), dim3(kThreads), B.p, (const float*)X.z, (long long)g.N,
+    (const CgScalars*)B.sc, 0);
+}
+
+template <int DIM>
+static cudaError_t iterate_pcg(bool use_graph, const CgBuffers& B, PcgExtra& X, const PlaneLaunch& pl, int nb,
+                               int max_iters, double tol2, const Grid& g, cudaStream_t st) {
+  if (!use_graph) {
+    Launcher K{st};
+    for (int it = 0; it < max_iters && K.err == cudaSuccess; ++it)
+      pcg_body<DIM, false>(K, B, X, pl, nb, max_iters, tol2, g, 0);
+    return K.err != cudaSuccess ? K.err : cudaGetLastError();
+  }
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  cudaError_t e = cudaGraphCreate(&graph, 0);
+  if (e != cudaSuccess) return e;
+  auto fail = [&](cudaError_t err) {
+    if (exec) cudaGraphExecDestroy(exec);
+    if (graph) cudaGraphDestroy(graph);
+    return err;
+  };
+  cudaGraphConditionalHandle handle;
+  if ((e = cudaGraphConditionalHandleCreate(&handle, graph, 1, cudaGraphCondAssignDefault)) != cudaSuccess) return fail(e);
+  cudaGraphNodeParams np = {};
+  np.type = cudaGraphNodeTypeConditional;
+  np.conditional.handle = handle;
+  np.conditional.type = cudaGraphCondTypeWhile;
+  np.conditional.size = 1;
+  cudaGraphNode_t loop;
+  if ((e = cudaGraphAddNode(&loop, graph, nullptr, 0, &np)) != cudaSuccess) return fail(e);
+  Launcher K{st};
+  K.body = np.conditional.phGraph_out[0];
+  pcg_body<DIM, true>(K, B, X, pl, nb, max_iters, tol2, g, handle);
+  if (K.err != cudaSuccess) return fail(K.err);
+  if ((e = cudaGraphInstantiate(&exec, graph, 0)) != cudaSuccess) return fail(e);
+  if ((e = cudaGraphLaunch(exec, st)) != cudaSuccess) return fail(e);
+  cudaGraphExecDestroy(exec);
+  cudaGraphDestroy(graph);
+  return cudaSuccess;
+}
+
+template <int DIM>
+static int poisson_pcg_impl(const float* rhs, const uint8_t* mflags, float* psi, float* work, float* mg_work,
+                            double* scratch, int max_iters, double tol, double tau, double dx, double dt,
+                            float* res_hist, double* info, const Grid& g, cudaStream_t st, const char* where) {
+  if (!(rhs && mflags && psi && work && mg_work && scratch)) return bad_arg(where, "null pointer");
+  if (max_iters < 0) return bad_arg(where, "max_iters must be >= 0");
+  if (!(tol >= 0)) return bad_arg(where, "tol must be >= 0");
+  if (tau != 1.0) return bad_arg(where, "the converged solve is the fixed point of the tau == 1 sweeps only");
+  if (g.N > 0x7fffffffLL) return bad_arg(where, "more than 2^31-1 cells per batch item");
+  const Consts k = make_consts(dx, dt, tau);
+  const PlaneLaunch pl = cg_launch(g);
+  const int nb = cg_blocks(pl);
+  const long long stride = cg_scratch_doubles(pl);
+  const long long mgf = mg_workspace_floats<DIM>(g);
+  const char* env = getenv("LBMFF_CG_NO_GRAPH");
+  const bool use_graph = !(env && env[0] == '1');
+  for (long long b = 0; b < g.B; ++b) {
+    const float* rb = rhs + b * g.N;
+    const uint8_t* fl = mflags + b * g.N;
+    CgBuffers B;
+    B.psi = psi + b * g.N;
+    B.b = work + (7 * b + 0) * g.N;
+    B.r = work + (7 * b + 1) * g.N;
+    B.p = work + (7 * b + 2) * g.N;
+    B.Ap = work + (7 * b + 3) * g.N;
+    B.mask = reinterpret_cast<unsigned*>(work + (7 * b + 4) * g.N);
+    PcgExtra X;
+    X.z = work + (7 * b + 5) * g.N;
+    X.t = work + (7 * b + 6) * g.N;
+    X.nlev = mg_carve<DIM>(g, mg_work + b * mgf, X.L);
+    B.sc = reinterpret_cast<CgScalars*>(scratch + b * stride);
+    B.part = scratch + b * stride + 16;
+    B.hist = res_hist ? res_hist + b * (max_iters + 1LL) : nullptr;
+    k_cg_rhs<DIM><<<pl.grid, pl.block, 0, st>>>(rb, fl, B.b, B.mask, B.part, nb, k, g);
+    k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, nb, 0, B.sc, nullptr, 0.0, max_iters, 0);
+    mg_setup<DIM>(B.mask, g, X.L, X.nlev, st);
+    k_cg_start<DIM><<<pl.grid, pl.block, 0, st>>>(B.b, B.psi, B.mask, B.r, B.p, B.part, nb, B.sc, g);
+    k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, nb, 1, B.sc, B.hist, tol * tol, max_iters, 0);
+    if (max_iters > 0) {
+      Launcher K{st};
+      mg_vcycle<DIM>(K, B.mask, g, B.r, X.z, X.t, B.Ap, X.L, X.nlev);
+      K((const void*)k_cg_dot2, dim3(nb), dim3(kThreads), (const float*)B.r, (const float*)X.z, (long long)g.N, B.part, nb);
+      K((const void*)k_pcg_set_rz, dim3(1), dim3(1024), (const double*)B.part, nb, B.sc);
+      K((const void*)k_pcg_direction, dim3(flat_blocks(g.N)), dim3(kThreads), B.p, (const float*)X.z, (long long)g.N,
+        (const CgScalars*)B.sc, 1);
+      cudaError_t e = K.err;
+      if (e == cudaSuccess) e = iterate_pcg<DIM>(use_graph, B, X, pl, nb, max_iters, tol * tol, g, st);
+      if (e != cudaSuccess) {
+        set_last_error(where, e);
+        return (int)e;
+      }
+    }
+    if (info) cudaMemcpyAsync(info + 5 * b, B.sc, 5 * sizeof(double), cudaMemcpyDeviceToDevice, st);
+  }
+  return check_launch(where);
+}
+
 }  // namespace lbmff
 
 using namespace lbmff;
@@ -480,6 +801,27 @@ int lbmff_poisson_cg_3d(const float* rhs, const uint8_t* mflags, float* psi, flo
   LBMFF_REQUIRE(B >= 1 && D >= 1 && H >= 1 && W >= 1, "non-positive extent");
   return poisson_cg_impl<3>(rhs, mflags, psi, work, scratch, max_iters, tol, tau, dx, dt, res_hist, info,
                             make_grid(B, D, H, W), (cudaStream_t)stream, __func__);
+}
+
+long long lbmff_poisson_mg_workspace_floats(int D, int H, int W) {
+  if (D < 1 || H < 1 || W < 1) return -1;
+  return D == 1 ? mg_workspace_floats<2>(make_grid(1, 1, H, W)) : mg_workspace_floats<3>(make_grid(1, D, H, W));
+}
+
+int lbmff_poisson_pcg_2d(const float* rhs, const uint8_t* mflags, float* psi, float* work, float* mg_work,
+                         double* scratch, int max_iters, double tol, double tau, double dx, double dt, float* res_hist,
+                         double* info, int B, int H, int W, lbmff_stream_t stream) {
+  LBMFF_REQUIRE(B >= 1 && H >= 1 && W >= 1, "non-positive extent");
+  return poisson_pcg_impl<2>(rhs, mflags, psi, work, mg_work, scratch, max_iters, tol, tau, dx, dt, res_hist, info,
+                             make_grid(B, 1, H, W), (cudaStream_t)stream, __func__);
+}
+
+int lbmff_poisson_pcg_3d(const float* rhs, const uint8_t* mflags, float* psi, float* work, float* mg_work,
+                         double* scratch, int max_iters, double tol, double tau, double dx, double dt, float* res_hist,
+                         double* info, int B, int D, int H, int W, lbmff_stream_t stream) {
+  LBMFF_REQUIRE(B >= 1 && D >= 1 && H >= 1 && W >= 1, "non-positive extent");
+  return poisson_pcg_impl<3>(rhs, mflags, psi, work, mg_work, scratch, max_iters, tol, tau, dx, dt, res_hist, info,
+                             make_grid(B, D, H, W), (cudaStream_t)stream, __func__);
 }
 
 }  // extern "C"

@@ -18,7 +18,7 @@ class PoissonCG:
     """Workspace + launcher.  ``solve`` is asynchronous on torch's current stream; ``info()`` synchronises."""
 
     def __init__(self, mflags: torch.Tensor, *, dx=1.0, dt=1.0, tol: float = 1e-4, max_iters: int = 200,
-                 keep_history: bool = False):
+                 keep_history: bool = False, precondition: Optional[str] = None):
         self.mflags = H.need_cuda(mflags, "magnetic_flags", torch.uint8)
         self.device = self.mflags.device
         self.dim, self.B, _, self.D, self.Hh, self.W = H.dims(self.mflags)
@@ -28,7 +28,14 @@ class PoissonCG:
         if n <= 0:
             raise RuntimeError("lbmff_poisson_cg_scratch_doubles: bad extents")
         N = self.D * self.Hh * self.W
-        self._work = torch.empty((self.B, 5, N), dtype=torch.float32, device=self.device)
+        if precondition not in (None, "mg"):
+            raise ValueError("precondition must be None or 'mg'")
+        self.precondition = precondition
+        self._mg = None
+        if precondition == "mg":   # geometric-multigrid V(2,2) cycle per iteration (csrc/poisson_mg.cuh)
+            m = _lib.load().lbmff_poisson_mg_workspace_floats(self.D, self.Hh, self.W)
+            self._mg = torch.empty((self.B, max(1, m)), dtype=torch.float32, device=self.device)
+        self._work = torch.empty((self.B, 7 if precondition else 5, N), dtype=torch.float32, device=self.device)
         self._scratch = torch.zeros((self.B, n), dtype=torch.float64, device=self.device)
         self._info = torch.zeros((self.B, 5), dtype=torch.float64, device=self.device)
         self._hist = (torch.zeros((self.B, self.max_iters + 1), dtype=torch.float32, device=self.device)
@@ -49,6 +56,11 @@ class PoissonCG:
         if it > self.max_iters:
             raise RuntimeError("max_iters above the one the workspace was sized for")
         self._last_iters = it
+        if self.precondition == "mg":
+            H.launch(f"lbmff_poisson_pcg_{self.dim}d", self.device, H.ptr(rhs), H.ptr(self.mflags), H.ptr(psi),
+                     H.ptr(self._work), H.ptr(self._mg), H.ptr(self._scratch), it, self.tol, 1.0, self.dx, self.dt,
+                     H.ptr(self._hist), H.ptr(self._info), *H.sizes(self.dim, self.B, self.D, self.Hh, self.W))
+            return psi
         H.launch(f"lbmff_poisson_cg_{self.dim}d", self.device, H.ptr(rhs), H.ptr(self.mflags), H.ptr(psi),
                  H.ptr(self._work), H.ptr(self._scratch), it, self.tol, 1.0, self.dx, self.dt,
                  H.ptr(self._hist), H.ptr(self._info), *H.sizes(self.dim, self.B, self.D, self.Hh, self.W))

@@ -165,3 +165,58 @@ def test_converged_path_matches_many_sweeps_in_the_full_step():
     assert abs(cg.total_mass() - ref.total_mass()) <= 1e-5 * abs(ref.total_mass())
     assert cg.launches_per_step == 1 + (1 + 5) + 5 + 1 + 6 + 1
     assert math.isfinite(cg.total_mass())
+
+
+@pytest.mark.parametrize("res", [(40, 36), (90, 70), (18, 20, 22), (40, 36, 44), (33, 47, 29)])
+@pytest.mark.parametrize("graph", [True, False])
+def test_multigrid_pcg_solves_the_same_system_in_far_fewer_iterations(res, graph, monkeypatch):
+    """precondition="mg": one geometric-multigrid V(2,2) cycle per CG iteration (Galerkin coarse operators on cell
+    aggregates, walls as zero-weight links; csrc/poisson_mg.cuh).  Same system, so the solution equals the plain CG
+    one (up to the constant) and is a fixed point of the reference's sweep; iterations must drop by a large factor and
+    stay nearly independent of the grid (odd / ragged extents and an interior wall included)."""
+    from lbm_ferrofluid_b200.poisson import PoissonCG
+
+    monkeypatch.setenv("LBMFF_CG_NO_GRAPH", "0" if graph else "1")
+    mflags, rhs, dim = _case(res, seed=2)
+    mf, r = mflags.cuda(), rhs.cuda()
+    plain = PoissonCG(mf, tol=1e-6, max_iters=2000)
+    psi0 = torch.zeros((1, 1, *res), device="cuda")
+    plain.solve(r, psi0)
+    pcg = PoissonCG(mf, tol=1e-6, max_iters=100, keep_history=True, precondition="mg")
+    psi = torch.zeros_like(psi0)
+    pcg.solve(r, psi)
+    i0, i1 = plain.info()[0], pcg.info()[0]
+    assert i1["converged"], i1
+    assert i1["iters"] <= 40 and i1["iters"] * 4 <= i0["iters"], (i0["iters"], i1["iters"])
+    hist = pcg.history()[0]
+    assert hist[-1] <= 1e-6 * i1["rhs_norm"] * 1.001 and all(h == h for h in hist)
+    fluid = (mf != 2)
+    a, b = psi0[fluid].double(), psi[fluid].double()
+    a, b = a - a.mean(), b - b.mean()
+    assert (a - b).norm().item() <= 2e-5 * a.norm().item(), (a - b).norm().item() / a.norm().item()
+    assert torch.equal(psi[~fluid], torch.zeros_like(psi[~fluid]))      # wall cells untouched
+    # deterministic
+    psi2 = torch.zeros_like(psi0)
+    pcg.solve(r, psi2)
+    assert torch.equal(psi, psi2)
+
+
+def test_multigrid_pcg_warm_start_and_batch():
+    from lbm_ferrofluid_b200.poisson import PoissonCG
+
+    res = (24, 20, 28)
+    m0, r0, _ = _case(res, seed=3)
+    m1, r1, _ = _case(res, seed=4, interior_wall=False)
+    mf, r = torch.cat([m0, m1]).cuda(), torch.cat([r0, r1]).cuda()
+    pcg = PoissonCG(mf, tol=1e-5, max_iters=60, precondition="mg")
+    psi = torch.zeros((2, 1, *res), device="cuda")
+    pcg.solve(r, psi)
+    first = [i["iters"] for i in pcg.info()]
+    single = PoissonCG(m1.cuda(), tol=1e-5, max_iters=60, precondition="mg")
+    ps = torch.zeros((1, 1, *res), device="cuda")
+    single.solve(r1.cuda(), ps)
+    assert torch.equal(ps[0], psi[1])                 # batch items are independent
+    pcg.solve(r, psi)                                 # warm start: already converged
+    assert all(i["iters"] <= 1 for i in pcg.info()) and all(f >= 3 for f in first)
+    with pytest.raises(ValueError):
+        PoissonCG(mf, precondition="ilu")
