@@ -163,6 +163,20 @@ int lbmff_get_H_int_d3q19(const float* phi, const uint8_t* flags, const float* H
                           const float* Hz, const float* h, double tau, double dx, double dt, float* H_int,
                           float* h_out, float* psi_ws, int B, int D, int H, int W, lbmff_stream_t stream);
 
+/* ---- allocation-free variant of lbmff_get_H_int_d2q9.  It has NO counterpart in the reference: it was added
+ *      for callers that cannot allocate (CUDA graph capture, tight serving loops,
+ *      harnesses that forbid cudaMalloc).  Same arguments and results as lbmff_get_H_int_d2q9 minus psi_ws: the psi
+ *      scratch is a file-scope static __device__ array of LBMFF_STATIC_PSI_MAX_FLOATS floats (4 MiB, held by every
+ *      GPU that loads the library until exit).  B*H*W beyond that limit is rejected (cudaErrorInvalidValue, message
+ *      in lbmff_last_error_string).  The call performs no cudaMalloc / cudaFree / allocating library routine.  All
+ *      calls on one device share the array: calls that overlap on the GPU (different streams) race; calls on one
+ *      stream are safe.  Nothing in it has to start at zero (every cell's psi is written before it is read). */
+#define LBMFF_STATIC_PSI_MAX_FLOATS (1 << 20)
+int lbmff_static_psi_max_floats(void);
+int lbmff_get_H_int_d2q9_static(const float* phi, const uint8_t* flags, const float* Hx, const float* Hy,
+                                const float* h, double tau, double dx, double dt, float* H_int, float* h_out, int B,
+                                int H, int W, lbmff_stream_t stream);
+
 /* =====================================================================================
  * Fused step tier.  The reference has no counterpart function: its time loop lives in the
  * demo scripts (demo_3d_LBM_Rosensweig_instability.py:151-209, demo_2d_LBM.py:101-121).

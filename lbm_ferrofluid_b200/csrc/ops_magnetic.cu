@@ -1,5 +1,7 @@
 // Drop-in tier, part 4: LBMMagnetic{2,3}d.get_H_int (a16).
 // k_mag_collide: psi, source, collision of h (one pass over h).  k_neg_grad: H_int = -grad(psi).
+#include <mutex>
+
 #include "capi.cuh"
 #include "magnetic.cuh"
 
@@ -77,6 +79,37 @@ static int h_int_impl(const float* phi, const uint8_t* flags, const float* Hx, c
   return check_launch(where);
 }
 
+// ---- allocation-free variant (lbmff_get_H_int_d2q9_static) ---------------------------------------------------------
+// The psi scratch lives in the library image: every GPU that loads liblbmff.so holds these 4 MiB until exit.
+// In host code `g_psi_static` is only a stand-in for the symbol, not a device address; the device address is looked
+// up once per device (with that device current) by cudaGetSymbolAddress and cached.
+static __device__ __align__(256) float g_psi_static[LBMFF_STATIC_PSI_MAX_FLOATS];
+
+static int static_psi_address(float** out, const char* where) {
+  constexpr int kMaxDevices = 64;
+  static std::mutex mu;
+  static float* cached[kMaxDevices] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) {
+    set_last_error(where, e);
+    return (int)e;
+  }
+  if (dev < 0 || dev >= kMaxDevices) return bad_arg(where, "device ordinal out of range for the static scratch table");
+  std::lock_guard<std::mutex> lock(mu);
+  if (!cached[dev]) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_psi_static);
+    if (e != cudaSuccess || !p) {
+      set_last_error(where, e != cudaSuccess ? e : cudaErrorInvalidSymbol);
+      return (int)(e != cudaSuccess ? e : cudaErrorInvalidSymbol);
+    }
+    cached[dev] = p;
+  }
+  *out = cached[dev];
+  return 0;
+}
+
 }  // namespace lbmff
 
 using namespace lbmff;
@@ -93,6 +126,23 @@ int lbmff_get_H_int_d3q19(const float* phi, const uint8_t* flags, const float* H
                           const float* Hz, const float* h, double tau, double dx, double dt, float* H_int,
                           float* h_out, float* psi_ws, int B, int D, int H, int W, lbmff_stream_t stream) {
   return h_int_impl<3>(phi, flags, Hx, Hy, Hz, h, tau, dx, dt, H_int, h_out, psi_ws, B, D, H, W,
+                       (cudaStream_t)stream, __func__);
+}
+
+int lbmff_static_psi_max_floats(void) { return LBMFF_STATIC_PSI_MAX_FLOATS; }
+
+int lbmff_get_H_int_d2q9_static(const float* phi, const uint8_t* flags, const float* Hx, const float* Hy,
+                                const float* h, double tau, double dx, double dt, float* H_int, float* h_out, int B,
+                                int H, int W, lbmff_stream_t stream) {
+  if (B < 1 || H < 3 || W < 3) return bad_arg(__func__, "B must be >= 1 and every extent >= 3");
+  if ((long long)B * H * W > (long long)LBMFF_STATIC_PSI_MAX_FLOATS)
+    return bad_arg(__func__, "B*H*W exceeds LBMFF_STATIC_PSI_MAX_FLOATS (1048576 cells): use lbmff_get_H_int_d2q9 "
+                             "with caller-provided psi_ws");
+  float* psi_ws = nullptr;
+  if (int rc = static_psi_address(&psi_ws, __func__)) return rc;
+  // k_mag_collide writes psi for every one of the B*H*W cells before k_neg_grad reads any: nothing of the previous
+  // call's contents is read, so the array needs no clearing.
+  return h_int_impl<2>(phi, flags, Hx, Hy, nullptr, h, tau, dx, dt, H_int, h_out, psi_ws, B, 1, H, W,
                        (cudaStream_t)stream, __func__);
 }
 
