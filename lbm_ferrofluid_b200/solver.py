@@ -38,14 +38,16 @@ class FerroSolver:
     the shell only; bit-identical psi) or "auto" (scalar when valid).  "converged" is NOT the reference's
     algorithm: instead of n_sweeps relaxation sweeps it solves for their fixed point with conjugate gradients
     (poisson.PoissonCG; tau == 1 only) to relative residual ``cg_tol`` in at most ``cg_max_iters`` iterations,
-    warm-started from the previous step.
+    warm-started from the previous step; ``cg_precondition="mg"`` adds one geometric-multigrid V(2,2) cycle per
+    iteration (csrc/poisson_mg.cuh).
     """
 
     def __init__(self, flags: torch.Tensor, *, density_liquid=0.2508, density_gas=0.02381, rho_liquid=0.2508,
                  rho_gas=0.02381, kappa=0.01, tau_f=0.68, tau_g=0.68, tau=1.0, contact_angle=0.5 * math.pi,
                  gravity=1e-4, dx=1.0, dt=1.0, magnetic_flags: Optional[torch.Tensor] = None,
                  H_ext=None, n_sweeps: int = 30, KBC_type: Optional[int] = None, magnetic_path: str = "auto",
-                 keep_force: bool = True, cg_tol: float = 1e-4, cg_max_iters: int = 60):
+                 keep_force: bool = True, cg_tol: float = 1e-4, cg_max_iters: int = 60,
+                 cg_precondition: Optional[str] = None):
         self.flags = H.need_cuda(flags, "flags", torch.uint8)
         self.device = self.flags.device
         self.dim, self.B, _, self.D, self.Hh, self.W = H.dims(self.flags)
@@ -117,7 +119,8 @@ class FerroSolver:
             else:
                 from .poisson import PoissonCG
                 self._h = self._a = ()
-                self.cg = PoissonCG(self.mflags, dx=self.dx, dt=self.dt, tol=cg_tol, max_iters=cg_max_iters)
+                self.cg = PoissonCG(self.mflags, dx=self.dx, dt=self.dt, tol=cg_tol, max_iters=cg_max_iters,
+                                    precondition=cg_precondition)
             self._mcur = 0
         else:
             self.magnetic_path = None

@@ -135,6 +135,52 @@ def cg(res, steps=6, tol=1e-4):
     print(f"30-sweep scalar step: {ms30:.2f} ms", flush=True)
 
 
+def pcg(res, tol=1e-4):
+    """Cold solve of the first Rosensweig step's magnetic potential: plain CG against multigrid-preconditioned CG
+    (iterations, ms, residual history), and the warm-started steps of a converged-path solver with each."""
+    import math
+    from lbm_ferrofluid_b200.poisson import PoissonCG
+    from lbm_ferrofluid_b200.solver import FerroSolver
+    dev = torch.device("cuda")
+    flags = I.shell_flags(res, device=dev)
+    mflags = I.shell_flags(res, open_axes=(1,), device=dev)
+    rho = I.rosensweig_rho(res, flags)
+    mk = lambda **kw: FerroSolver(flags, magnetic_flags=mflags, H_ext=[0.0, 100.0, 0.0], magnetic_path="converged",  # noqa
+                                  contact_angle=0.5 * math.pi, gravity=1e-4, keep_force=False, cg_tol=tol,
+                                  **kw).initialize(rho)
+    s = mk(cg_max_iters=3000)
+    s.step()
+    rhs = s._rhs.clone()
+    del s
+    for name, kw in (("cg", dict(max_iters=3000)), ("pcg-mg", dict(max_iters=200, precondition="mg"))):
+        sol = PoissonCG(mflags, tol=tol, keep_history=True, **kw)
+        psi = torch.zeros_like(rhs)
+        sol.solve(rhs, psi)                      # builds the hierarchy / graph
+        torch.cuda.synchronize()
+        psi.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); sol.solve(rhs, psi); b.record()
+        torch.cuda.synchronize()
+        i = sol.info()[0]
+        h = sol.history()[0]
+        hist = [f"{float(v) / i['rhs_norm']:.1e}" for v in h[: i["iters"] + 1]]
+        print(f"{name} cold res={res} tol={tol}: iters={i['iters']} converged={i['converged']} "
+              f"{a.elapsed_time(b):.2f} ms ({a.elapsed_time(b) / max(1, i['iters']):.3f} ms/iter)", flush=True)
+        print(f"  |r|/|b| history: {hist if len(hist) <= 40 else hist[:20] + ['...'] + hist[-5:]}", flush=True)
+        del sol
+    for name, kw in (("cg", dict(cg_max_iters=3000)), ("pcg-mg", dict(cg_max_iters=200, cg_precondition="mg"))):
+        s = mk(**kw)
+        its = []
+        for _ in range(6):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); s.step(); b.record()
+            torch.cuda.synchronize()
+            i = s.cg.info()[0]
+            its.append((i["iters"], i["converged"], round(a.elapsed_time(b), 2)))
+        print(f"{name} steps res={res}: (iters, converged, ms) = {its}", flush=True)
+        del s
+
+
 def ext(res, steps=20, reps=3):
     """single-phase BGK on D3Q19 / D3Q27, forcing none / Guo, A/B pull vs esoteric pull in place."""
     from lbm_ferrofluid_b200.extensions import ExtSinglePhaseSolver
@@ -250,6 +296,8 @@ if __name__ == "__main__":
         cs(tuple(int(v) for v in sys.argv[2:5]))
     if sys.argv[1] == "ext":
         ext(tuple(int(v) for v in sys.argv[2:5]), *( [int(sys.argv[5]), 1] if len(sys.argv) > 5 else []))
+    if sys.argv[1] == "pcg":
+        pcg(tuple(int(v) for v in sys.argv[2:5]), tol=float(sys.argv[5]) if len(sys.argv) > 5 else 1e-4)
     if sys.argv[1] == "cg":
         cg(tuple(int(v) for v in sys.argv[2:5]), tol=float(sys.argv[5]) if len(sys.argv) > 5 else 1e-4)
     if sys.argv[1] == "single2d":
