@@ -476,6 +476,123 @@ __global__ void __launch_bounds__(kThreads) k_mg0_sweep(const unsigned* __restri
     xo[c.i] = out;
   }
 }
+// The same smoother / residual in 3-D, shared-memory tiled and marching along z (the level-0 passes are 60 % of a
+// V-cycle).  A 32 x 8 column of cells walks zc planes; every plane of xi is staged ONCE, with its one-cell periodic
+// rim (34 x 10), into a two-slot ring.  From the staged plane a thread forms, for its own (x, y), the centre value, the
+// sum A of the 4 in-plane axis neighbours and the sum C of the 4 in-plane corners, and keeps them in registers for
+// the three live planes; then
+//     sum over the 6 axis neighbours      = A(z) + centre(z-1) + centre(z+1)
+//     sum over the 12 diagonal neighbours = C(z) + A(z-1) + A(z+1)
+// i.e. 9 shared-memory reads and ~20 adds per cell instead of 19 global loads.  The sum form (diag * v - sum w v) loses
+// the exact-difference property laplace() has, which matters for the CG residual at 512^3 but not for a
+// preconditioner: M^-1 only has to be one fixed symmetric operator, and it is (every cell uses the same formula in
+// every cycle).  Cells with a wall among their neighbours (mask != 0: the shell-adjacent planes / rows only) take the
+// mask-aware global path of k_mg0_sweep; wall cells get 0.
+constexpr int kMgTX = 32, kMgTY = 8, kMgTW = kMgTX + 2, kMgTH = kMgTY + 2;
+
+template <int MODE>
+__global__ void __launch_bounds__(kMgTX* kMgTY) k_mg0_sweep_tiled(const unsigned* __restrict__ mask,
+                                                                 const float* __restrict__ b,
+                                                                 const float* __restrict__ xi, float* __restrict__ xo,
+                                                                 Grid g, int zc) {
+  using L = Lat<3>;
+  __shared__ float sv[2][kMgTH][kMgTW];
+  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * kMgTX + tx;
+  const int x0 = blockIdx.x * kMgTX, y0 = blockIdx.y * kMgTY;
+  const int zs = blockIdx.z * zc, ze = min(zs + zc, g.D);
+  const int HW = g.H * g.W;
+  int off[2], sy[2], sx[2];
+#pragma unroll
+  for (int t = 0; t < 2; ++t) {
+    const int e = tid + t * kMgTX * kMgTY;
+    sy[t] = e / kMgTW; sx[t] = e - sy[t] * kMgTW;
+    int gx = x0 - 1 + sx[t], gy = y0 - 1 + sy[t];
+    gx = gx < 0 ? gx + g.W : gx; gy = gy < 0 ? gy + g.H : gy;
+    while (gx >= g.W) gx -= g.W;
+    while (gy >= g.H) gy -= g.H;
+    off[t] = e < kMgTW * kMgTH ? gy * g.W + gx : -1;
+  }
+  float rv[2] = {0.f, 0.f};
+  auto fetch = [&](int z) {   // plane z (periodic) -> registers
+    const int zz = z < 0 ? z + g.D : (z >= g.D ? z - g.D : z);
+#pragma unroll
+    for (int t = 0; t < 2; ++t)
+      if (off[t] >= 0) rv[t] = __ldg(xi + zz * HW + off[t]);
+  };
+  auto put = [&](int z) {     // registers -> ring slot of plane z
+    const int slot = (z - zs + 1) & 1;
+#pragma unroll
+    for (int t = 0; t < 2; ++t)
+      if (off[t] >= 0) sv[slot][sy[t]][sx[t]] = rv[t];
+  };
+  struct PlaneSums { float c, A, C; };
+  auto sums = [&](int z) {
+    const float(*s)[kMgTW] = sv[(z - zs + 1) & 1];
+    PlaneSums r;
+    r.c = s[ty + 1][tx + 1];
+    r.A = (s[ty + 1][tx] + s[ty + 1][tx + 2]) + (s[ty][tx + 1] + s[ty + 2][tx + 1]);
+    r.C = (s[ty][tx] + s[ty][tx + 2]) + (s[ty + 2][tx] + s[ty + 2][tx + 2]);
+    return r;
+  };
+  const int x = x0 + tx, y = y0 + ty;
+  const bool live = x < g.W && y < g.H;
+  fetch(zs - 1); put(zs - 1);
+  __syncthreads();
+  PlaneSums pm = sums(zs - 1);
+  fetch(zs); put(zs);
+  __syncthreads();
+  PlaneSums pc = sums(zs);
+  fetch(zs + 1);
+  int i = live ? zs * HW + y * g.W + x : 0;
+  unsigned m_next = live ? mask[i] : kWallSelf;
+  float b_next = live ? b[i] : 0.f;
+  constexpr float wa = L::w(1) / (1.0f - L::w(0)), wd = L::w(5) / (1.0f - L::w(0));
+  for (int z = zs; z < ze; ++z) {
+    put(z + 1);
+    if (z + 1 < ze) fetch(z + 2);
+    const unsigned m = m_next;
+    const float bc = b_next;
+    if (live && z + 1 < ze) {
+      m_next = mask[i + HW];
+      b_next = b[i + HW];
+    }
+    __syncthreads();
+    const PlaneSums pp = sums(z + 1);
+    if (live) {
+      float out = 0.f;
+      if (m == 0) {
+        const float s_axis = pc.A + (pm.c + pp.c), s_diag = pc.C + (pm.A + pp.A);
+        const float Lx = wa * (6.0f * pc.c - s_axis) + wd * (12.0f * pc.c - s_diag);
+        const float r = bc - Lx;
+        out = MODE == 0 ? fmaf(mg::kOmega, r, pc.c) : r;
+      } else if (!(m & kWallSelf)) {
+        PlaneCell c;
+        c.x = x; c.y = y; c.z = z; c.i = i; c.live = true;
+        const Nbr nb(c, g);
+        const float r = bc - laplace<3>(xi, pc.c, i, nb, m);
+        const float d = diag_of<3>(m);
+        out = MODE == 0 ? (d > 0.f ? fmaf(mg::kOmega / d, r, pc.c) : pc.c) : r;
+      }
+      xo[i] = out;
+    }
+    pm = pc;
+    pc = pp;
+    i += HW;
+  }
+}
+struct TiledLaunch {
+  dim3 grid, block;
+  int zc;
+};
+static TiledLaunch mg0_tiled_launch(const Grid& g) {
+  TiledLaunch t;
+  t.zc = g.D >= 64 ? 32 : (g.D >= 16 ? 8 : g.D);
+  t.block = dim3(kMgTX, kMgTY, 1);
+  t.grid = dim3((unsigned)((g.W + kMgTX - 1) / kMgTX), (unsigned)((g.H + kMgTY - 1) / kMgTY),
+                (unsigned)((g.D + t.zc - 1) / t.zc));
+  return t;
+}
+
 template <int DIM>
 __global__ void __launch_bounds__(kThreads) k_mg0_jacobi0(const unsigned* __restrict__ mask, const float* __restrict__ b,
                                                           float* __restrict__ x, Grid g) {
@@ -605,15 +722,30 @@ static void mg_setup(const unsigned* mask, const Grid& g0, mg::Level* L, int n, 
                                                                          L[l].w, L[l].invd, L[l].g);
   }
 }
+static bool mg_tiled_enabled() {
+  const char* e = getenv("LBMFF_MG_TILED");
+  return !(e && e[0] == '0');
+}
 // z = M^-1 r: one V(2,2) cycle.  Level 0 works in (z, t0) with `res0` as residual scratch; result in z.
 template <int DIM>
 static void mg_vcycle(Launcher& K, const unsigned* mask, const Grid& g0, const float* r, float* z, float* t0,
                       float* res0, mg::Level* L, int n) {
   const PlaneLaunch p0 = cg_launch(g0);
   K((const void*)k_mg0_jacobi0<DIM>, p0.grid, p0.block, mask, r, t0, g0);
-  K((const void*)k_mg0_sweep<DIM, 0>, p0.grid, p0.block, mask, r, (const float*)t0, z, g0);
+  // level-0 Jacobi sweep / residual: the tiled kernel in 3-D (LBMFF_MG_TILED=0 selects the generic one)
+  const TiledLaunch tl = mg0_tiled_launch(g0);
+  auto sweep0 = [&](int mode, const float* xi, float* xo) {
+    if (DIM == 3 && mg_tiled_enabled() && g0.zb == 0 && g0.zn == g0.D) {
+      K(mode == 0 ? (const void*)k_mg0_sweep_tiled<0> : (const void*)k_mg0_sweep_tiled<1>, tl.grid, tl.block, mask, r,
+        xi, xo, g0, tl.zc);
+    } else {
+      K(mode == 0 ? (const void*)k_mg0_sweep<DIM, 0> : (const void*)k_mg0_sweep<DIM, 1>, p0.grid, p0.block, mask, r,
+        xi, xo, g0);
+    }
+  };
+  sweep0(0, t0, z);
   if (n > 0) {
-    K((const void*)k_mg0_sweep<DIM, 1>, p0.grid, p0.block, mask, r, (const float*)z, res0, g0);
+    sweep0(1, z, res0);
     {
       const PlaneLaunch pc = mg_launch(L[0].g);
       K((const void*)mg::k_mg_restrict<DIM>, pc.grid, pc.block, (const float*)res0, g0, L[0].b, L[0].g);
@@ -650,8 +782,8 @@ static void mg_vcycle(Launcher& K, const unsigned* mask, const Grid& g0, const f
     const PlaneLaunch pf = mg_launch(g0);
     K((const void*)mg::k_mg_prolong_add<DIM>, pf.grid, pf.block, z, g0, (const float*)L[0].x, L[0].g, mask);
   }
-  K((const void*)k_mg0_sweep<DIM, 0>, p0.grid, p0.block, mask, r, (const float*)z, t0, g0);
-  K((const void*)k_mg0_sweep<DIM, 0>, p0.grid, p0.block, mask, r, (const float*)t0, z, g0);
+  sweep0(0, z, t0);
+  sweep0(0, t0, z);
 }
 
 struct PcgExtra {

@@ -187,7 +187,7 @@ def test_multigrid_pcg_solves_the_same_system_in_far_fewer_iterations(res, graph
     pcg.solve(r, psi)
     i0, i1 = plain.info()[0], pcg.info()[0]
     assert i1["converged"], i1
-    assert i1["iters"] <= 40 and i1["iters"] * 4 <= i0["iters"], (i0["iters"], i1["iters"])
+    assert i1["iters"] <= 20 and i1["iters"] * 4 <= i0["iters"], (i0["iters"], i1["iters"])
     hist = pcg.history()[0]
     assert hist[-1] <= 1e-6 * i1["rhs_norm"] * 1.001 and all(h == h for h in hist)
     fluid = (mf != 2)
@@ -220,3 +220,32 @@ def test_multigrid_pcg_warm_start_and_batch():
     assert all(i["iters"] <= 1 for i in pcg.info()) and all(f >= 3 for f in first)
     with pytest.raises(ValueError):
         PoissonCG(mf, precondition="ilu")
+
+
+@pytest.mark.parametrize("res", [(18, 20, 22), (33, 47, 29), (70, 24, 72), (64, 40, 96)])
+def test_tiled_multigrid_smoother_equals_the_generic_one(res, monkeypatch):
+    """k_mg0_sweep_tiled (32 x 8 column marching along z, plane sums out of a shared-memory ring) against the generic
+    level-0 smoother k_mg0_sweep (LBMFF_MG_TILED=0): the same preconditioner up to fp32 summation order, so the same
+    solution, the same iteration count (+-1) and matching residual histories -- ragged x / y / z extents, z chunks that
+    do not divide D, and an interior wall included."""
+    from lbm_ferrofluid_b200.poisson import PoissonCG
+
+    mflags, rhs, dim = _case(res, seed=5)
+    mf, r = mflags.cuda(), rhs.cuda()
+    out = {}
+    for tiled in ("1", "0"):
+        monkeypatch.setenv("LBMFF_MG_TILED", tiled)
+        pcg = PoissonCG(mf, tol=1e-6, max_iters=60, keep_history=True, precondition="mg")
+        psi = torch.zeros((1, 1, *res), device="cuda")
+        pcg.solve(r, psi)
+        out[tiled] = (psi, pcg.info()[0], pcg.history()[0])
+    (pa, ia, ha), (pb, ib, hb) = out["1"], out["0"]
+    assert ia["converged"] and ib["converged"], (ia, ib)
+    assert abs(ia["iters"] - ib["iters"]) <= 1 and ia["iters"] <= 20, (ia["iters"], ib["iters"])
+    for k in range(1, min(4, len(ha), len(hb))):      # early history: the two preconditioners are the same operator
+        assert abs(ha[k] - hb[k]) <= 1e-3 * hb[0], (k, ha[k], hb[k])
+    fluid = (mf != 2)
+    a, b = pa[fluid].double(), pb[fluid].double()
+    a, b = a - a.mean(), b - b.mean()
+    assert (a - b).norm().item() <= 2e-5 * b.norm().item(), (a - b).norm().item() / b.norm().item()
+    assert torch.equal(pa[~fluid], torch.zeros_like(pa[~fluid]))

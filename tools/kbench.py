@@ -181,6 +181,28 @@ def pcg(res, tol=1e-4):
         del s
 
 
+def pcgprof(res, iters=4):
+    """A fixed number of multigrid-PCG iterations on the first Rosensweig step's right-hand side (for ncu launch lists;
+    run with LBMFF_CG_NO_GRAPH=1 so that every kernel is a plain launch)."""
+    import math
+    from lbm_ferrofluid_b200.poisson import PoissonCG
+    from lbm_ferrofluid_b200.solver import FerroSolver
+    dev = torch.device("cuda")
+    flags = I.shell_flags(res, device=dev)
+    mflags = I.shell_flags(res, open_axes=(1,), device=dev)
+    rho = I.rosensweig_rho(res, flags)
+    s = FerroSolver(flags, magnetic_flags=mflags, H_ext=[0.0, 100.0, 0.0], magnetic_path="scalar",
+                    contact_angle=0.5 * math.pi, gravity=1e-4, keep_force=False).initialize(rho)
+    s.step()
+    rhs = s._rhs.clone()
+    del s
+    sol = PoissonCG(mflags, tol=0.0, max_iters=iters, precondition="mg")
+    psi = torch.zeros_like(rhs)
+    sol.solve(rhs, psi)
+    torch.cuda.synchronize()
+    print("pcgprof", sol.info()[0], flush=True)
+
+
 def ext(res, steps=20, reps=3):
     """single-phase BGK on D3Q19 / D3Q27, forcing none / Guo, A/B pull vs esoteric pull in place."""
     from lbm_ferrofluid_b200.extensions import ExtSinglePhaseSolver
@@ -296,6 +318,8 @@ if __name__ == "__main__":
         cs(tuple(int(v) for v in sys.argv[2:5]))
     if sys.argv[1] == "ext":
         ext(tuple(int(v) for v in sys.argv[2:5]), *( [int(sys.argv[5]), 1] if len(sys.argv) > 5 else []))
+    if sys.argv[1] == "pcgprof":
+        pcgprof(tuple(int(v) for v in sys.argv[2:5]))
     if sys.argv[1] == "pcg":
         pcg(tuple(int(v) for v in sys.argv[2:5]), tol=float(sys.argv[5]) if len(sys.argv) > 5 else 1e-4)
     if sys.argv[1] == "cg":
