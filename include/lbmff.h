@@ -366,14 +366,18 @@ int lbmff_poisson_cg_3d(const float* rhs, const uint8_t* mflags, float* psi, flo
  * (walls = zero-weight links), damped-Jacobi smoothing, the whole cycle inside the same device-side WHILE loop.
  *   work     [B][7][N] floats (the five of lbmff_poisson_cg_* + z + one smoother buffer)
  *   mg_work  [B][lbmff_poisson_mg_workspace_floats(D,H,W)] floats (levels >= 1: weights, diagonal, x, t, b)
+ *   reuse_hierarchy: the coarse operators depend on mflags only; non-zero = mg_work still holds the hierarchy an
+ *            earlier call built for the SAME mflags and extents (skips the set-up kernels), 0 = build it.
+ * Coarse operators carry the over-correction factor 1/2 per level (unsmoothed aggregation); the level-0 smoother in
+ * 3-D is a shared-memory tiled kernel marching along z (LBMFF_MG_TILED=0 selects the generic one).
  * Everything else as lbmff_poisson_cg_*; the stopping test is on the unpreconditioned residual |r|. */
 long long lbmff_poisson_mg_workspace_floats(int D, int H, int W);
 int lbmff_poisson_pcg_2d(const float* rhs, const uint8_t* mflags, float* psi, float* work, float* mg_work,
                          double* scratch, int max_iters, double tol, double tau, double dx, double dt, float* res_hist,
-                         double* info, int B, int H, int W, lbmff_stream_t stream);
+                         double* info, int reuse_hierarchy, int B, int H, int W, lbmff_stream_t stream);
 int lbmff_poisson_pcg_3d(const float* rhs, const uint8_t* mflags, float* psi, float* work, float* mg_work,
                          double* scratch, int max_iters, double tol, double tau, double dx, double dt, float* res_hist,
-                         double* info, int B, int D, int H, int W, lbmff_stream_t stream);
+                         double* info, int reuse_hierarchy, int B, int D, int H, int W, lbmff_stream_t stream);
 
 /* ---- iso-surface of the order parameter on the device (replaces the host round trip
  *      mcubes.marching_cubes((-phi * s).cpu().numpy()[0, 0], 0) of src/LBM/utils/io.py:50-63).

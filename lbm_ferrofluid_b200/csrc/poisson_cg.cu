@@ -477,8 +477,8 @@ __global__ void __launch_bounds__(kThreads) k_mg0_sweep(const unsigned* __restri
   }
 }
 // The same smoother / residual in 3-D, shared-memory tiled and marching along z (the level-0 passes are 60 % of a
-// V-cycle).  A 32 x 8 column of cells walks zc planes; every plane of xi is staged ONCE, with its one-cell periodic
-// rim (34 x 10), into a two-slot ring.  From the staged plane a thread forms, for its own (x, y), the centre value, the
+// V-cycle).  A 32 x 32 column of cells (32 x 8 threads, four consecutive rows each) walks zc planes; every plane of
+// xi is staged ONCE, with its one-cell periodic rim (34 x 34), into a two-slot ring.  From the staged plane a thread forms, for its own (x, y), the centre value, the
 // sum A of the 4 in-plane axis neighbours and the sum C of the 4 in-plane corners, and keeps them in registers for
 // the three live planes; then
 //     sum over the 6 axis neighbours      = A(z) + centre(z-1) + centre(z+1)
@@ -488,107 +488,159 @@ __global__ void __launch_bounds__(kThreads) k_mg0_sweep(const unsigned* __restri
 // preconditioner: M^-1 only has to be one fixed symmetric operator, and it is (every cell uses the same formula in
 // every cycle).  Cells with a wall among their neighbours (mask != 0: the shell-adjacent planes / rows only) take the
 // mask-aware global path of k_mg0_sweep; wall cells get 0.
-constexpr int kMgTX = 32, kMgTY = 8, kMgTW = kMgTX + 2, kMgTH = kMgTY + 2;
+constexpr int kMgTX = 32, kMgTY = 8;   // 32 x 8 threads; kMgR consecutive rows per thread (template parameter)
 
-template <int MODE>
-__global__ void __launch_bounds__(kMgTX* kMgTY) k_mg0_sweep_tiled(const unsigned* __restrict__ mask,
-                                                                 const float* __restrict__ b,
-                                                                 const float* __restrict__ xi, float* __restrict__ xo,
-                                                                 Grid g, int zc) {
+// the rare cell with a wall among its neighbours: mask-aware global path, kept out of line so that the marching loop
+// keeps its registers
+__device__ __noinline__ float mg0_wall_adjacent_cell(const float* __restrict__ xi, float xc, float bc, int x, int y,
+                                                     int z, int i, unsigned m, const Grid& g, int mode) {
+  PlaneCell c;
+  c.x = x; c.y = y; c.z = z; c.i = i; c.live = true;
+  const Nbr nb(c, g);
+  const float res = bc - laplace<3>(xi, xc, i, nb, m);
+  const float d = diag_of<3>(m);
+  return mode == 0 ? (d > 0.f ? fmaf(mg::kOmega / d, res, xc) : xc) : res;
+}
+
+template <int MODE, int kMgR>
+__global__ void __launch_bounds__(kMgTX* kMgTY, kMgR == 4 ? 2 : 3) k_mg0_sweep_tiled(const unsigned* __restrict__ mask,
+                                                                    const float* __restrict__ b,
+                                                                    const float* __restrict__ xi,
+                                                                    float* __restrict__ xo,
+                                                                    const __grid_constant__ Grid g, int zc) {
   using L = Lat<3>;
-  __shared__ float sv[2][kMgTH][kMgTW];
+  constexpr int kMgRows = kMgTY * kMgR;                         // 32 x (8 kMgR) cells per block and plane
+  constexpr int kMgTW = kMgTX + 2, kMgTH = kMgRows + 2;         // staged tile with its rim
+  constexpr int kMgTile = kMgTW * kMgTH;
+  constexpr int kMgStage = (kMgTile + kMgTX * kMgTY - 1) / (kMgTX * kMgTY);   // staged elements per thread
+  __shared__ float sv[2][kMgTile];
   const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * kMgTX + tx;
-  const int x0 = blockIdx.x * kMgTX, y0 = blockIdx.y * kMgTY;
+  const int x0 = blockIdx.x * kMgTX, y0 = blockIdx.y * kMgRows;
   const int zs = blockIdx.z * zc, ze = min(zs + zc, g.D);
   const int HW = g.H * g.W;
-  int off[2], sy[2], sx[2];
+  // the (up to) kMgStage rim-tile elements this thread stages per plane: tile element e = tid + t * 256 lives at
+  // sv[slot][e]; its in-plane global position is periodic in x and y.  Only the last one can fall outside the tile.
+  // Addresses: one 64-bit pointer per staged element (plane 0), plus a block-uniform 32-bit plane offset.
+  const float* __restrict__ src[kMgStage];
+  bool last_ok = true;
 #pragma unroll
-  for (int t = 0; t < 2; ++t) {
+  for (int t = 0; t < kMgStage; ++t) {
     const int e = tid + t * kMgTX * kMgTY;
-    sy[t] = e / kMgTW; sx[t] = e - sy[t] * kMgTW;
-    int gx = x0 - 1 + sx[t], gy = y0 - 1 + sy[t];
+    const int sy = e / kMgTW, sx = e - sy * kMgTW;
+    int gx = x0 - 1 + sx, gy = y0 - 1 + sy;
     gx = gx < 0 ? gx + g.W : gx; gy = gy < 0 ? gy + g.H : gy;
     while (gx >= g.W) gx -= g.W;
     while (gy >= g.H) gy -= g.H;
-    off[t] = e < kMgTW * kMgTH ? gy * g.W + gx : -1;
+    const bool ok = e < kMgTile;
+    if (t == kMgStage - 1) last_ok = ok;
+    src[t] = xi + (ok ? gy * g.W + gx : 0);
   }
-  float rv[2] = {0.f, 0.f};
+  float rv[kMgStage];
   auto fetch = [&](int z) {   // plane z (periodic) -> registers
     const int zz = z < 0 ? z + g.D : (z >= g.D ? z - g.D : z);
+    const int zo = zz * HW;
 #pragma unroll
-    for (int t = 0; t < 2; ++t)
-      if (off[t] >= 0) rv[t] = __ldg(xi + zz * HW + off[t]);
+    for (int t = 0; t < kMgStage; ++t) rv[t] = __ldg(src[t] + zo);
   };
-  auto put = [&](int z) {     // registers -> ring slot of plane z
-    const int slot = (z - zs + 1) & 1;
+  auto put = [&](int slot) {  // registers -> ring slot
 #pragma unroll
-    for (int t = 0; t < 2; ++t)
-      if (off[t] >= 0) sv[slot][sy[t]][sx[t]] = rv[t];
+    for (int t = 0; t < kMgStage; ++t)
+      if (t < kMgStage - 1 || last_ok) sv[slot][tid + t * kMgTX * kMgTY] = rv[t];
   };
-  struct PlaneSums { float c, A, C; };
-  auto sums = [&](int z) {
-    const float(*s)[kMgTW] = sv[(z - zs + 1) & 1];
-    PlaneSums r;
-    r.c = s[ty + 1][tx + 1];
-    r.A = (s[ty + 1][tx] + s[ty + 1][tx + 2]) + (s[ty][tx + 1] + s[ty + 2][tx + 1]);
-    r.C = (s[ty][tx] + s[ty][tx + 2]) + (s[ty + 2][tx] + s[ty + 2][tx + 2]);
-    return r;
+  // per row r of this thread: centre value, A = sum of the 4 in-plane axis neighbours, C = sum of the 4 corners.
+  // Row sums h(j) = left + right of tile row j are shared between the rows: 3 reads per tile row, kMgR + 2 tile rows.
+  struct PlaneSums { float c[kMgR], A[kMgR], C[kMgR]; };
+  auto sums = [&](int slot, PlaneSums& P) {
+    const float* s = sv[slot] + (ty * kMgR) * kMgTW + tx;
+    float h[kMgR + 2], m[kMgR + 2];
+#pragma unroll
+    for (int j = 0; j < kMgR + 2; ++j) {
+      h[j] = s[j * kMgTW] + s[j * kMgTW + 2];
+      m[j] = s[j * kMgTW + 1];
+    }
+#pragma unroll
+    for (int r = 0; r < kMgR; ++r) {
+      P.c[r] = m[r + 1];
+      P.A[r] = h[r + 1] + (m[r] + m[r + 2]);
+      P.C[r] = h[r] + h[r + 2];
+    }
   };
-  const int x = x0 + tx, y = y0 + ty;
-  const bool live = x < g.W && y < g.H;
-  fetch(zs - 1); put(zs - 1);
+  const int x = x0 + tx, yb = y0 + ty * kMgR;
+  bool live[kMgR];
+#pragma unroll
+  for (int r = 0; r < kMgR; ++r) live[r] = x < g.W && yb + r < g.H;
+  PlaneSums pm, pc, pp;
+  fetch(zs - 1); put(0);
   __syncthreads();
-  PlaneSums pm = sums(zs - 1);
-  fetch(zs); put(zs);
+  sums(0, pm);
+  fetch(zs); put(1);
   __syncthreads();
-  PlaneSums pc = sums(zs);
+  sums(1, pc);
   fetch(zs + 1);
-  int i = live ? zs * HW + y * g.W + x : 0;
-  unsigned m_next = live ? mask[i] : kWallSelf;
-  float b_next = live ? b[i] : 0.f;
+  int i0 = zs * HW + yb * g.W + x;          // cell of row 0 in plane z (only dereferenced where live)
+  unsigned m_next[kMgR];
+  float b_next[kMgR];
+#pragma unroll
+  for (int r = 0; r < kMgR; ++r) {
+    m_next[r] = live[r] ? mask[i0 + r * g.W] : kWallSelf;
+    b_next[r] = live[r] ? b[i0 + r * g.W] : 0.f;
+  }
   constexpr float wa = L::w(1) / (1.0f - L::w(0)), wd = L::w(5) / (1.0f - L::w(0));
-  for (int z = zs; z < ze; ++z) {
-    put(z + 1);
+  // plane z; SLOT = ring slot of plane z + 1 (compile-time: the z loop is unrolled by the ring size)
+  auto plane = [&](int z, auto SLOT_) {
+    constexpr int SLOT = decltype(SLOT_)::value;
+    put(SLOT);
     if (z + 1 < ze) fetch(z + 2);
-    const unsigned m = m_next;
-    const float bc = b_next;
-    if (live && z + 1 < ze) {
-      m_next = mask[i + HW];
-      b_next = b[i + HW];
+    unsigned m[kMgR];
+    float bc[kMgR];
+#pragma unroll
+    for (int r = 0; r < kMgR; ++r) {
+      m[r] = m_next[r];
+      bc[r] = b_next[r];
+      if (live[r] && z + 1 < ze) {
+        m_next[r] = mask[i0 + HW + r * g.W];
+        b_next[r] = b[i0 + HW + r * g.W];
+      }
     }
     __syncthreads();
-    const PlaneSums pp = sums(z + 1);
-    if (live) {
+    sums(SLOT, pp);
+#pragma unroll
+    for (int r = 0; r < kMgR; ++r) {
+      if (!live[r]) continue;
+      const int i = i0 + r * g.W;
       float out = 0.f;
-      if (m == 0) {
-        const float s_axis = pc.A + (pm.c + pp.c), s_diag = pc.C + (pm.A + pp.A);
-        const float Lx = wa * (6.0f * pc.c - s_axis) + wd * (12.0f * pc.c - s_diag);
-        const float r = bc - Lx;
-        out = MODE == 0 ? fmaf(mg::kOmega, r, pc.c) : r;
-      } else if (!(m & kWallSelf)) {
-        PlaneCell c;
-        c.x = x; c.y = y; c.z = z; c.i = i; c.live = true;
-        const Nbr nb(c, g);
-        const float r = bc - laplace<3>(xi, pc.c, i, nb, m);
-        const float d = diag_of<3>(m);
-        out = MODE == 0 ? (d > 0.f ? fmaf(mg::kOmega / d, r, pc.c) : pc.c) : r;
+      if (m[r] == 0) {
+        const float s_axis = pc.A[r] + (pm.c[r] + pp.c[r]), s_diag = pc.C[r] + (pm.A[r] + pp.A[r]);
+        const float Lx = wa * (6.0f * pc.c[r] - s_axis) + wd * (12.0f * pc.c[r] - s_diag);
+        const float res = bc[r] - Lx;
+        out = MODE == 0 ? fmaf(mg::kOmega, res, pc.c[r]) : res;
+      } else if (!(m[r] & kWallSelf)) {
+        out = mg0_wall_adjacent_cell(xi, pc.c[r], bc[r], x, yb + r, z, i, m[r], g, MODE);
       }
       xo[i] = out;
     }
     pm = pc;
     pc = pp;
-    i += HW;
+    i0 += HW;
+  };
+  for (int z = zs; z < ze; z += 2) {   // plane zs - 1 sits in slot 0, zs in slot 1, zs + 1 in slot 0, ...
+    plane(z, std::integral_constant<int, 0>{});
+    if (z + 1 < ze) plane(z + 1, std::integral_constant<int, 1>{});
   }
 }
 struct TiledLaunch {
   dim3 grid, block;
-  int zc;
+  int zc, rows;
 };
 static TiledLaunch mg0_tiled_launch(const Grid& g) {
   TiledLaunch t;
+  const char* e = getenv("LBMFF_MG_ROWS");
+  t.rows = (e && e[0] == '4') ? 4 : 2;
   t.zc = g.D >= 64 ? 32 : (g.D >= 16 ? 8 : g.D);
+  if (const char* z = getenv("LBMFF_MG_ZC")) t.zc = atoi(z) > 0 ? atoi(z) : t.zc;
   t.block = dim3(kMgTX, kMgTY, 1);
-  t.grid = dim3((unsigned)((g.W + kMgTX - 1) / kMgTX), (unsigned)((g.H + kMgTY - 1) / kMgTY),
+  const int rows = kMgTY * t.rows;
+  t.grid = dim3((unsigned)((g.W + kMgTX - 1) / kMgTX), (unsigned)((g.H + rows - 1) / rows),
                 (unsigned)((g.D + t.zc - 1) / t.zc));
   return t;
 }
@@ -736,8 +788,9 @@ static void mg_vcycle(Launcher& K, const unsigned* mask, const Grid& g0, const f
   const TiledLaunch tl = mg0_tiled_launch(g0);
   auto sweep0 = [&](int mode, const float* xi, float* xo) {
     if (DIM == 3 && mg_tiled_enabled() && g0.zb == 0 && g0.zn == g0.D) {
-      K(mode == 0 ? (const void*)k_mg0_sweep_tiled<0> : (const void*)k_mg0_sweep_tiled<1>, tl.grid, tl.block, mask, r,
-        xi, xo, g0, tl.zc);
+      const void* fn = tl.rows == 4 ? (mode == 0 ? (const void*)k_mg0_sweep_tiled<0, 4> : (const void*)k_mg0_sweep_tiled<1, 4>)
+                                    : (mode == 0 ? (const void*)k_mg0_sweep_tiled<0, 2> : (const void*)k_mg0_sweep_tiled<1, 2>);
+      K(fn, tl.grid, tl.block, mask, r, xi, xo, g0, tl.zc);
     } else {
       K(mode == 0 ? (const void*)k_mg0_sweep<DIM, 0> : (const void*)k_mg0_sweep<DIM, 1>, p0.grid, p0.block, mask, r,
         xi, xo, g0);
@@ -853,7 +906,8 @@ static cudaError_t iterate_pcg(bool use_graph, const CgBuffers& B, PcgExtra& X, 
 template <int DIM>
 static int poisson_pcg_impl(const float* rhs, const uint8_t* mflags, float* psi, float* work, float* mg_work,
                             double* scratch, int max_iters, double tol, double tau, double dx, double dt,
-                            float* res_hist, double* info, const Grid& g, cudaStream_t st, const char* where) {
+                            float* res_hist, double* info, int reuse_hierarchy, const Grid& g, cudaStream_t st,
+                            const char* where) {
   if (!(rhs && mflags && psi && work && mg_work && scratch)) return bad_arg(where, "null pointer");
   if (max_iters < 0) return bad_arg(where, "max_iters must be >= 0");
   if (!(tol >= 0)) return bad_arg(where, "tol must be >= 0");
@@ -885,7 +939,7 @@ static int poisson_pcg_impl(const float* rhs, const uint8_t* mflags, float* psi,
     B.hist = res_hist ? res_hist + b * (max_iters + 1LL) : nullptr;
     k_cg_rhs<DIM><<<pl.grid, pl.block, 0, st>>>(rb, fl, B.b, B.mask, B.part, nb, k, g);
     k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, nb, 0, B.sc, nullptr, 0.0, max_iters, 0);
-    mg_setup<DIM>(B.mask, g, X.L, X.nlev, st);
+    if (!reuse_hierarchy) mg_setup<DIM>(B.mask, g, X.L, X.nlev, st);   // depends on the flags only
     k_cg_start<DIM><<<pl.grid, pl.block, 0, st>>>(B.b, B.psi, B.mask, B.r, B.p, B.part, nb, B.sc, g);
     k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, nb, 1, B.sc, B.hist, tol * tol, max_iters, 0);
     if (max_iters > 0) {
@@ -942,18 +996,18 @@ long long lbmff_poisson_mg_workspace_floats(int D, int H, int W) {
 
 int lbmff_poisson_pcg_2d(const float* rhs, const uint8_t* mflags, float* psi, float* work, float* mg_work,
                          double* scratch, int max_iters, double tol, double tau, double dx, double dt, float* res_hist,
-                         double* info, int B, int H, int W, lbmff_stream_t stream) {
+                         double* info, int reuse_hierarchy, int B, int H, int W, lbmff_stream_t stream) {
   LBMFF_REQUIRE(B >= 1 && H >= 1 && W >= 1, "non-positive extent");
   return poisson_pcg_impl<2>(rhs, mflags, psi, work, mg_work, scratch, max_iters, tol, tau, dx, dt, res_hist, info,
-                             make_grid(B, 1, H, W), (cudaStream_t)stream, __func__);
+                             reuse_hierarchy, make_grid(B, 1, H, W), (cudaStream_t)stream, __func__);
 }
 
 int lbmff_poisson_pcg_3d(const float* rhs, const uint8_t* mflags, float* psi, float* work, float* mg_work,
                          double* scratch, int max_iters, double tol, double tau, double dx, double dt, float* res_hist,
-                         double* info, int B, int D, int H, int W, lbmff_stream_t stream) {
+                         double* info, int reuse_hierarchy, int B, int D, int H, int W, lbmff_stream_t stream) {
   LBMFF_REQUIRE(B >= 1 && D >= 1 && H >= 1 && W >= 1, "non-positive extent");
   return poisson_pcg_impl<3>(rhs, mflags, psi, work, mg_work, scratch, max_iters, tol, tau, dx, dt, res_hist, info,
-                             make_grid(B, D, H, W), (cudaStream_t)stream, __func__);
+                             reuse_hierarchy, make_grid(B, D, H, W), (cudaStream_t)stream, __func__);
 }
 
 }  // extern "C"

@@ -32,6 +32,7 @@ class PoissonCG:
             raise ValueError("precondition must be None or 'mg'")
         self.precondition = precondition
         self._mg = None
+        self._hierarchy_built = False
         if precondition == "mg":   # geometric-multigrid V(2,2) cycle per iteration (csrc/poisson_mg.cuh)
             m = _lib.load().lbmff_poisson_mg_workspace_floats(self.D, self.Hh, self.W)
             self._mg = torch.empty((self.B, max(1, m)), dtype=torch.float32, device=self.device)
@@ -59,7 +60,9 @@ class PoissonCG:
         if self.precondition == "mg":
             H.launch(f"lbmff_poisson_pcg_{self.dim}d", self.device, H.ptr(rhs), H.ptr(self.mflags), H.ptr(psi),
                      H.ptr(self._work), H.ptr(self._mg), H.ptr(self._scratch), it, self.tol, 1.0, self.dx, self.dt,
-                     H.ptr(self._hist), H.ptr(self._info), *H.sizes(self.dim, self.B, self.D, self.Hh, self.W))
+                     H.ptr(self._hist), H.ptr(self._info), int(self._hierarchy_built),
+                     *H.sizes(self.dim, self.B, self.D, self.Hh, self.W))
+            self._hierarchy_built = True     # mflags and the workspace belong to this object: build once
             return psi
         H.launch(f"lbmff_poisson_cg_{self.dim}d", self.device, H.ptr(rhs), H.ptr(self.mflags), H.ptr(psi),
                  H.ptr(self._work), H.ptr(self._scratch), it, self.tol, 1.0, self.dx, self.dt,

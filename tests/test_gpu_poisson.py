@@ -222,8 +222,9 @@ def test_multigrid_pcg_warm_start_and_batch():
         PoissonCG(mf, precondition="ilu")
 
 
+@pytest.mark.parametrize("rows", ["2", "4"])
 @pytest.mark.parametrize("res", [(18, 20, 22), (33, 47, 29), (70, 24, 72), (64, 40, 96)])
-def test_tiled_multigrid_smoother_equals_the_generic_one(res, monkeypatch):
+def test_tiled_multigrid_smoother_equals_the_generic_one(res, rows, monkeypatch):
     """k_mg0_sweep_tiled (32 x 8 column marching along z, plane sums out of a shared-memory ring) against the generic
     level-0 smoother k_mg0_sweep (LBMFF_MG_TILED=0): the same preconditioner up to fp32 summation order, so the same
     solution, the same iteration count (+-1) and matching residual histories -- ragged x / y / z extents, z chunks that
@@ -233,6 +234,7 @@ def test_tiled_multigrid_smoother_equals_the_generic_one(res, monkeypatch):
     mflags, rhs, dim = _case(res, seed=5)
     mf, r = mflags.cuda(), rhs.cuda()
     out = {}
+    monkeypatch.setenv("LBMFF_MG_ROWS", rows)          # rows of the tile per thread: 2 (default) or 4
     for tiled in ("1", "0"):
         monkeypatch.setenv("LBMFF_MG_TILED", tiled)
         pcg = PoissonCG(mf, tol=1e-6, max_iters=60, keep_history=True, precondition="mg")

@@ -135,7 +135,7 @@ def cg(res, steps=6, tol=1e-4):
     print(f"30-sweep scalar step: {ms30:.2f} ms", flush=True)
 
 
-def pcg(res, tol=1e-4):
+def pcg(res, tol=1e-4, steps=True):
     """Cold solve of the first Rosensweig step's magnetic potential: plain CG against multigrid-preconditioned CG
     (iterations, ms, residual history), and the warm-started steps of a converged-path solver with each."""
     import math
@@ -153,6 +153,8 @@ def pcg(res, tol=1e-4):
     rhs = s._rhs.clone()
     del s
     for name, kw in (("cg", dict(max_iters=3000)), ("pcg-mg", dict(max_iters=200, precondition="mg"))):
+        if name == "cg" and not steps:
+            continue
         sol = PoissonCG(mflags, tol=tol, keep_history=True, **kw)
         psi = torch.zeros_like(rhs)
         sol.solve(rhs, psi)                      # builds the hierarchy / graph
@@ -169,6 +171,8 @@ def pcg(res, tol=1e-4):
         print(f"  |r|/|b| history: {hist if len(hist) <= 40 else hist[:20] + ['...'] + hist[-5:]}", flush=True)
         del sol
     for name, kw in (("cg", dict(cg_max_iters=3000)), ("pcg-mg", dict(cg_max_iters=200, cg_precondition="mg"))):
+        if not steps:
+            break
         s = mk(**kw)
         its = []
         for _ in range(6):
@@ -318,6 +322,8 @@ if __name__ == "__main__":
         cs(tuple(int(v) for v in sys.argv[2:5]))
     if sys.argv[1] == "ext":
         ext(tuple(int(v) for v in sys.argv[2:5]), *( [int(sys.argv[5]), 1] if len(sys.argv) > 5 else []))
+    if sys.argv[1] == "pcgcold":
+        pcg(tuple(int(v) for v in sys.argv[2:5]), steps=False)
     if sys.argv[1] == "pcgprof":
         pcgprof(tuple(int(v) for v in sys.argv[2:5]))
     if sys.argv[1] == "pcg":
