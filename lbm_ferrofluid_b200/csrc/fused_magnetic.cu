@@ -270,6 +270,204 @@ __global__ void __launch_bounds__(kTX* kTY, 5) k_mag_sweep_scalar_tiled(const fl
   }
 }
 
+// ---- tau == 1 scalar sweep in psi-only form (3-D, inside one multi-sweep call) ------------------------------------
+// The two values a cell keeps are both functions of its psi and its source: a = mag_collide_q(1 | 5, 0, psi, rhs).
+// Inside a call that runs n >= 3 sweeps the intermediate states therefore need not be stored as two floats per cell:
+// the sweep reads psi (+ the sweep-invariant rhs) of the neighbours, rebuilds their two values WHILE STAGING the plane
+// into shared memory (once per staged element, not once per use), and writes psi only -- 12 B per cell and sweep
+// (psi read, rhs read, psi written) instead of 20, and no per-cell collision / second store.  The arithmetic is the
+// same uncontracted mag_collide_q / psi_of sequence, so every psi is bit-identical to k_mag_sweep_scalar_tiled's.
+//   NBR  = 0: neighbour values from the two-float state arrays `src` = [2][N]       (first sweep of a call)
+//        = 1: rebuilt from psi `src` = [N] and rhs
+//   WALL = 0: the cell's own values of two sweeps ago from the state arrays `dst` = [2][N] (first two sweeps)
+//        = 1: rebuilt from psi `dst` = [N] (the buffer this sweep overwrites) and rhs
+// Output: psi -> dst[i] (same-thread read-before-write, as in k_mag_sweep_scalar).  sweeps_scalar_impl chains
+// (0,0) -> (1,0) -> (1,1)... and k_mag_psi_expand turns the last two psi fields back into the state arrays the next
+// call, the slab exchange and materialize_h expect -- bit-identical to what n old-style sweeps leave behind.
+//   MASK = 0: the wall mask of a shell-adjacent cell is built from 18 flag loads (~250 instructions executed by the
+//             whole warp for its one or two shell-adjacent lanes: 40 % of all instructions of a 512^3 sweep) and
+//             parked, as a bit pattern, in wmask[i] -- the diagonal half of the older state array, dead from the
+//             first sweep of the call until k_mag_psi_expand rewrites it;
+//        = 1: the mask is read back from wmask[i] (one load).
+template <int NBR, int WALL, int MASK, int R>
+__global__ void __launch_bounds__(kTX* kTY, R == 1 ? 4 : 3) k_mag_sweep_psi_tiled(const float* __restrict__ src, float* dst,
+                                                                               const uint8_t* __restrict__ fl,
+                                                                               const float* __restrict__ rhs,
+                                                                               float* wmask, Consts k, Grid g, int zc) {
+  using L = Lat<3>;
+  // 32 x 8 threads, R rows per thread (rows ty, ty + 8, ...): the per-plane bookkeeping (staging addresses, loop
+  // control, barrier) is shared by R cells -- it was two thirds of the instructions with one row per thread
+  constexpr int kRows = kTY * R, kTH = kRows + 2, kTile = kTH * kTileW;
+  constexpr int kStage = (kTile + kTX * kTY - 1) / (kTX * kTY);   // staged tile elements per thread
+  __shared__ float sA[kRing][kTile];  // axis-class value
+  __shared__ float sD[kRing][kTile];  // diagonal-class value
+  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * kTX + tx;
+  const int x0 = blockIdx.x * kTX, y0 = blockIdx.y * kRows;
+  const int zs = g.zb + blockIdx.z * zc;
+  const int ze = min(zs + zc, g.zb + g.zn);
+  const int HW = g.H * g.W, N = (int)g.N;
+  // tile element e = tid + t * 256 of the row-major rim-extended tile: in-plane offset, periodic in x and y
+  int off[kStage];
+#pragma unroll
+  for (int t = 0; t < kStage; ++t) {
+    const int e = tid + t * kTX * kTY;
+    const int sy = e / kTileW, sx = e - sy * kTileW;
+    int gx = x0 - 1 + sx, gy = y0 - 1 + sy;
+    gx = gx < 0 ? gx + g.W : gx; gy = gy < 0 ? gy + g.H : gy;
+    while (gx >= g.W) gx -= g.W;
+    while (gy >= g.H) gy -= g.H;
+    off[t] = e < kTile ? gy * g.W + gx : -1;
+  }
+  // raw registers of the planes in flight, TWO register sets (planes z + 1 and z + 2 are on their way while plane z is
+  // computed: with one set the top stall was the wait for the plane fetched one iteration earlier): (axis, diagonal)
+  // values when NBR == 0, (psi, rhs) when NBR == 1.  The set is a compile-time function of the ring phase.
+  float ra[2][kStage], rd[2][kStage];
+  auto fetch = [&](int z, auto SET_) {
+    constexpr int SET = decltype(SET_)::value;
+    const int zz = z < 0 ? z + g.D : (z >= g.D ? z - g.D : z);
+    const int zo = zz * HW;
+#pragma unroll
+    for (int t = 0; t < kStage; ++t)
+      if (t < kStage - 1 || off[t] >= 0) {
+        const int j = zo + off[t];
+        ra[SET][t] = __ldg(src + j);
+        rd[SET][t] = NBR == 0 ? __ldg(src + N + j) : __ldg(rhs + j);
+      }
+  };
+  auto put_slot = [&](int slot, auto SET_) {
+    constexpr int SET = decltype(SET_)::value;
+#pragma unroll
+    for (int t = 0; t < kStage; ++t)
+      if (t < kStage - 1 || off[t] >= 0) {
+        const int e = tid + t * kTX * kTY;
+        sA[slot][e] = NBR == 0 ? ra[SET][t] : mag_collide_q<3>(1, 0.0f, ra[SET][t], rd[SET][t], k);
+        sD[slot][e] = NBR == 0 ? rd[SET][t] : mag_collide_q<3>(5, 0.0f, ra[SET][t], rd[SET][t], k);
+      }
+  };
+  using Set0 = std::integral_constant<int, 0>;
+  using Set1 = std::integral_constant<int, 1>;
+  fetch(zs - 1, Set0{}); put_slot(0, Set0{});
+  fetch(zs, Set0{}); put_slot(1, Set0{});
+  fetch(zs + 1, Set1{});   // phase S puts plane z + 1 from set (S + 1) & 1 and refills it with plane z + 3
+  fetch(zs + 2, Set0{});
+  const int x = x0 + tx;
+  bool live[R], shell_xy[R];
+  uint8_t f_next[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int y = y0 + ty + kTY * r;
+    live[r] = x < g.W && y < g.H;
+    shell_xy[r] = x <= 1 || x >= g.W - 2 || y <= 1 || y >= g.H - 2;
+    f_next[r] = live[r] ? fl[zs * HW + y * g.W + x] : (uint8_t)LBMFF_OBSTACLE;
+  }
+  int i0 = zs * HW + (y0 + ty) * g.W + x;   // cell of row 0 in plane z (dereferenced only where live)
+  const int rowstep = kTY * g.W;
+  // rows next to the x / y shell (thread-constant) need, on every plane, their parked wall mask and their own state of
+  // two sweeps ago: three dependent DRAM round trips if loaded at the point of use, and the blocks on the x rim (one
+  // in eight) consist of such warps only.  They ride one plane ahead like the flag.
+  float wm_next[R], wa_next[R], wb_next[R];
+  auto wall_prefetch = [&](int r, int i) {
+    if (MASK == 1) wm_next[r] = wmask[i];
+    wa_next[r] = dst[i];
+    wb_next[r] = WALL == 0 ? dst[N + i] : __ldg(rhs + i);
+  };
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    wm_next[r] = 0.f; wa_next[r] = 0.f; wb_next[r] = 0.f;
+    if (live[r] && shell_xy[r]) wall_prefetch(r, i0 + r * rowstep);
+  }
+  auto plane = [&](int z, auto S_) {
+    constexpr int S = decltype(S_)::value;
+    using Set = std::integral_constant<int, (S + 1) & 1>;
+    put_slot((S + 2) & (kRing - 1), Set{});   // plane z + 1
+    if (z + 2 < ze) fetch(z + 3, Set{});
+    uint8_t fcell[R];
+    float wm[R], wa[R], wb[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      fcell[r] = f_next[r];
+      wm[r] = wm_next[r]; wa[r] = wa_next[r]; wb[r] = wb_next[r];
+      if (live[r] && z + 1 < ze) {
+        f_next[r] = fl[i0 + HW + r * rowstep];
+        if (shell_xy[r]) wall_prefetch(r, i0 + HW + r * rowstep);
+      }
+    }
+    __syncthreads();
+    constexpr int sl[3] = {S & (kRing - 1), (S + 1) & (kRing - 1), (S + 2) & (kRing - 1)};  // planes z-1, z, z+1
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if (fcell[r] == LBMFF_OBSTACLE) continue;   // also rows that are not live
+      const int i = i0 + r * rowstep;
+      float hv[L::Q];
+      hv[0] = 0.0f;
+#pragma unroll
+      for (int q = 1; q < L::Q; ++q) {
+        const bool axis = (L::ex(q) != 0) + (L::ey(q) != 0) + (L::ez(q) != 0) == 1;
+        const int e = (ty + kTY * r + 1 - L::ey(q)) * kTileW + (tx + 1 - L::ex(q));
+        const int ps = sl[1 - L::ez(q)];
+        hv[q] = axis ? sA[ps][e] : sD[ps][e];
+      }
+      if (shell_xy[r] || near_z_shell(g, z)) {
+        unsigned wall_mask = 0;
+        // own state of two sweeps ago: prefetched for rows next to the x / y shell, loaded here on the two planes
+        // next to the z shell
+        const float va = shell_xy[r] ? wa[r] : dst[i];
+        const float vb = shell_xy[r] ? wb[r] : (WALL == 0 ? dst[N + i] : __ldg(rhs + i));
+        if (MASK == 0) {
+          const Nbr nb(PlaneCell{x, y0 + ty + kTY * r, z, i, true}, g);
+#pragma unroll
+          for (int q = 1; q < L::Q; ++q)
+            if (fl[i + nb.at<3>(q, 1)] == LBMFF_OBSTACLE) wall_mask |= 1u << q;
+          wmask[i] = __uint_as_float(wall_mask);   // aliases dst + N in the first sweep: vb was read above
+        } else {
+          wall_mask = __float_as_uint(shell_xy[r] ? wm[r] : wmask[i]);
+        }
+        if (wall_mask) {
+          float p_axis, p_diag;
+          if (WALL == 0) {
+            p_axis = va; p_diag = vb;
+          } else {
+            p_axis = mag_collide_q<3>(1, 0.0f, va, vb, k);
+            p_diag = mag_collide_q<3>(5, 0.0f, va, vb, k);
+          }
+#pragma unroll
+          for (int q = 1; q < L::Q; ++q) {
+            const bool axis = (L::ex(q) != 0) + (L::ey(q) != 0) + (L::ez(q) != 0) == 1;
+            if ((wall_mask >> q) & 1u) hv[q] = axis ? p_axis : p_diag;
+          }
+        }
+      }
+      dst[i] = psi_of<3>(hv);
+    }
+    i0 += HW;
+  };
+  for (int z = zs; z < ze; z += kRing) {
+    plane(z, std::integral_constant<int, 0>{});
+    if (z + 1 < ze) plane(z + 1, std::integral_constant<int, 1>{});
+    if (z + 2 < ze) plane(z + 2, std::integral_constant<int, 2>{});
+    if (z + 3 < ze) plane(z + 3, std::integral_constant<int, 3>{});
+  }
+}
+
+// psi of the last two sweeps (newest in cur[0:N], the one before in prev[0:N]) -> the two-float state arrays, psi_out.
+// OBSTACLE cells keep what the arrays held (the old-style sweeps never write them either).
+__global__ void __launch_bounds__(kThreads) k_mag_psi_expand(float* __restrict__ cur, float* __restrict__ prev,
+                                                             const uint8_t* __restrict__ fl,
+                                                             const float* __restrict__ rhs,
+                                                             float* __restrict__ psi_out, Consts k, long long i0,
+                                                             long long i1, long long N) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = i0 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < i1; i += stride) {
+    if (fl[i] == LBMFF_OBSTACLE) continue;
+    const float pn = cur[i], pm = prev[i], r = rhs[i];
+    cur[i] = mag_collide_q<3>(1, 0.0f, pn, r, k);
+    cur[N + i] = mag_collide_q<3>(5, 0.0f, pn, r, k);
+    prev[i] = mag_collide_q<3>(1, 0.0f, pm, r, k);
+    prev[N + i] = mag_collide_q<3>(5, 0.0f, pm, r, k);
+    if (psi_out) psi_out[i] = pn;
+  }
+}
+
 // Rebuild the population-faithful h from the scalar state (for API users that ask for h).
 // cur = state after the last sweep, prev = one sweep earlier, psi = psi of the last sweep.
 template <int DIM>
@@ -349,6 +547,44 @@ static int sweeps_scalar_impl(float* aA, float* aB, const uint8_t* mflags, const
   if (g.N > 0x7fffffffLL / 2) return bad_arg(where, "more than (2^31-1)/2 cells per batch item");
   const Consts k = make_consts(dx, dt, 1.0);
   const PlaneLaunch pl = plane_launch(g);
+  if constexpr (DIM == 3) {
+    // n >= 3 sweeps of a whole (non-slab) lattice in one call: psi-only intermediate states (k_mag_sweep_psi_tiled),
+    // 12 instead of 20 B per cell and sweep; LBMFF_MAG_PSI=0 keeps the two-float sweeps
+    const char* e = getenv("LBMFF_MAG_PSI");
+    if (n >= 3 && g.W >= 4 && g.H >= 4 && g.zb == 0 && g.zn == g.D && g.Dg == g.D && !(e && e[0] == '0')) {
+      const int zc = g.zn < 32 ? g.zn : 32;
+      const char* er = getenv("LBMFF_MAG_PSI_ROWS");
+      const int R = er ? atoi(er) : 2;
+      const int rows = kTY * (R == 1 || R == 2 ? R : 4);
+      const dim3 tg((g.W + kTX - 1) / kTX, (g.H + rows - 1) / rows, (g.zn + zc - 1) / zc), tb(kTX, kTY);
+#define LBMFF_PSI_SWEEP(NB, WL, MK, SRC, DST)                                                                    \
+  do {                                                                                                          \
+    if (R == 1) k_mag_sweep_psi_tiled<NB, WL, MK, 1><<<tg, tb, 0, st>>>(SRC, DST, fl, r, wm, k, g, zc);        \
+    else if (R == 2) k_mag_sweep_psi_tiled<NB, WL, MK, 2><<<tg, tb, 0, st>>>(SRC, DST, fl, r, wm, k, g, zc);   \
+    else k_mag_sweep_psi_tiled<NB, WL, MK, 4><<<tg, tb, 0, st>>>(SRC, DST, fl, r, wm, k, g, zc);               \
+  } while (0)
+      for (long long b = 0; b < g.B; ++b) {
+        float* A = aA + b * 2 * g.N;
+        float* B = aB + b * 2 * g.N;
+        const uint8_t* fl = mflags + b * g.N;
+        const float* r = rhs + b * g.N;
+        float* wm = B + g.N;   // diagonal half of the older state array: dead after the first sweep reads it
+        LBMFF_PSI_SWEEP(0, 0, 0, A, B);   // state in A (B: one older) -> psi_1 in B
+        LBMFF_PSI_SWEEP(1, 0, 1, B, A);   // psi_1, walls from state 0 in A -> psi_2 in A
+        for (int s = 2; s < n; ++s) {     // psi_{s+1} over psi_{s-1}
+          if (s & 1) LBMFF_PSI_SWEEP(1, 1, 1, B, A);
+          else LBMFF_PSI_SWEEP(1, 1, 1, A, B);
+        }
+#undef LBMFF_PSI_SWEEP
+        float* cur = (n & 1) ? B : A;       // newest psi: sweep 1 wrote B, sweep 2 A, ...
+        float* prev = (n & 1) ? A : B;
+        const unsigned eb = blocks_for(g.N) > 8192u ? 8192u : blocks_for(g.N);
+        k_mag_psi_expand<<<eb, kThreads, 0, st>>>(
+            cur, prev, fl, r, psi_out ? psi_out + b * g.N : nullptr, k, 0, g.N, g.N);
+      }
+      return check_launch(where);
+    }
+  }
   for (int s = 0; s < n; ++s) {
     const float* cur = (s & 1) ? aB : aA;
     float* prev = (s & 1) ? aA : aB;

@@ -462,3 +462,39 @@ def test_fused_shan_chen_step_vs_reference_golden():
     assert (s.force - F).abs().max() <= 2e-6 * F.abs().max()
     with pytest.raises(RuntimeError):
         ShanChenSolver(torch.ones((1, 1, 8, 8, 8), dtype=torch.uint8, device="cuda"))
+
+
+@pytest.mark.parametrize("rows", ["4", "2", "1"])
+@pytest.mark.parametrize("res", [(20, 18, 24), (37, 22, 45), (70, 24, 72), (36, 70, 40)])
+@pytest.mark.parametrize("n", [3, 4, 7, 30])
+def test_psi_only_scalar_sweeps_are_bit_identical_to_the_two_float_sweeps(res, n, rows, monkeypatch):
+    """lbmff_magnetic_sweeps_scalar_3d with n >= 3 runs its intermediate sweeps in psi-only form
+    (k_mag_sweep_psi_tiled: the neighbours' two values are rebuilt from psi and rhs while the plane is staged; 12
+    instead of 20 B per cell and sweep) and expands the last two psi fields back into the two-float state.  Against
+    LBMFF_MAG_PSI=0 (n two-float sweeps) from a random state: both state arrays and psi must be equal bit for bit,
+    wall cells untouched -- odd and even n (buffer parity), ragged extents, z chunks that do not divide D."""
+    from lbm_ferrofluid_b200 import _host as H
+    from lbm_ferrofluid_b200 import initializers as I
+
+    dev = torch.device("cuda:0")
+    D, Hh, W = res
+    g = torch.Generator(device="cpu").manual_seed(n * 1000 + W)
+    mflags = I.shell_flags(res, open_axes=(1,), device=dev)
+    rhs = (0.3 * torch.randn((1, 1, *res), generator=g)).to(dev)
+    a0 = torch.randn((1, 2, *res), generator=g).to(dev)
+    b0 = torch.randn((1, 2, *res), generator=g).to(dev)
+    out = {}
+    monkeypatch.setenv("LBMFF_MAG_PSI_ROWS", rows)     # rows of the tile per thread (default 4)
+    for mode in ("1", "0"):
+        monkeypatch.setenv("LBMFF_MAG_PSI", mode)
+        aA, aB = a0.clone(), b0.clone()
+        psi = torch.full((1, 1, *res), 7.0, device=dev)
+        H.launch("lbmff_magnetic_sweeps_scalar_3d", dev, H.ptr(aA), H.ptr(aB), H.ptr(mflags), H.ptr(rhs), H.ptr(psi),
+                 n, 1.0, 1.0, 1, D, Hh, W)
+        torch.cuda.synchronize()
+        out[mode] = (aA, aB, psi)
+    for x, y, name in zip(out["1"], out["0"], ("aA", "aB", "psi")):
+        assert torch.isfinite(x).all(), name
+        assert torch.equal(x, y), f"{name}: {(x != y).sum().item()} cells differ, max |d| {(x - y).abs().max().item():.3e}"
+    wall = (mflags == 2)
+    assert torch.equal(out["1"][2][wall], torch.full_like(out["1"][2][wall], 7.0))     # psi untouched on walls

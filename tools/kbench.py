@@ -36,6 +36,30 @@ def sweep(res, n=30, reps=3):
           f"GB/s={152 * N / best / 1e6:.1f} pages/pop={N * 4 / 2**21:.2f}", flush=True)
 
 
+def ssweep(res, n=30, reps=3):
+    """tau = 1 scalar sweeps through lbmff_magnetic_sweeps_scalar_3d: psi-only intermediate states (default) against
+    the two-float sweeps (LBMFF_MAG_PSI=0), ms per sweep (the expand kernel included in the psi-only figure)."""
+    D, Hh, W = res
+    dev = torch.device("cuda")
+    N = D * Hh * W
+    aA = torch.rand((1, 2, D, Hh, W), device=dev) * 1e-3
+    aB = torch.rand((1, 2, D, Hh, W), device=dev) * 1e-3
+    mfl = I.shell_flags(res, open_axes=(1,), device=dev)
+    rhs = torch.rand((1, 1, D, Hh, W), device=dev) * 1e-3
+    psi = torch.zeros_like(rhs)
+    run = lambda: H.launch("lbmff_magnetic_sweeps_scalar_3d", dev, H.ptr(aA), H.ptr(aB), H.ptr(mfl), H.ptr(rhs),  # noqa
+                           H.ptr(psi), n, 1.0, 1.0, 1, D, Hh, W)
+    for mode, rows in (("1", "4"), ("1", "2"), ("1", "1"), ("0", "-")):
+        os.environ["LBMFF_MAG_PSI"] = mode
+        os.environ["LBMFF_MAG_PSI_ROWS"] = rows
+        ms = timed(run, reps) / n
+        model = 12 if mode == "1" else 20
+        print(f"scalar sweeps psi_only={mode} rows={rows} res={res} n={n}: {ms:.4f} ms per sweep, "
+              f"{model * N / ms / 1e6:.0f} GB/s of the {model} B/cell model", flush=True)
+    os.environ.pop("LBMFF_MAG_PSI", None)
+    os.environ.pop("LBMFF_MAG_PSI_ROWS", None)
+
+
 def timed(fn, reps=5):
     fn()
     torch.cuda.synchronize()
@@ -336,5 +360,7 @@ if __name__ == "__main__":
         ros2d(int(sys.argv[2]))
     if sys.argv[1] == "streams":
         streams(tuple(int(v) for v in sys.argv[2:5]))
+    if sys.argv[1] == "ssweep":
+        ssweep(tuple(int(v) for v in sys.argv[2:5]), int(sys.argv[5]) if len(sys.argv) > 5 else 30)
     if sys.argv[1] == "sweep":
         sweep(tuple(int(v) for v in sys.argv[2:5]), int(sys.argv[5]) if len(sys.argv) > 5 else 30)
