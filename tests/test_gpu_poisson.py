@@ -251,3 +251,38 @@ def test_tiled_multigrid_smoother_equals_the_generic_one(res, rows, monkeypatch)
     a, b = a - a.mean(), b - b.mean()
     assert (a - b).norm().item() <= 2e-5 * b.norm().item(), (a - b).norm().item() / b.norm().item()
     assert torch.equal(pa[~fluid], torch.zeros_like(pa[~fluid]))
+
+
+def test_ferrosolver_with_multigrid_preconditioner_follows_the_plain_cg_trajectory():
+    """FerroSolver(magnetic_path="converged", cg_precondition="mg"): the same converged step with the V-cycle inside
+    the solve (hierarchy built by the first solve, reused afterwards) -- psi and the flow fields follow the plain-CG
+    solver to the tolerance of the two iterative solves, in a third of the iterations or fewer on the cold steps."""
+    from lbm_ferrofluid_b200.solver import FerroSolver
+    from oracle.make_golden import perturbed_interface, shell_flags
+
+    res, steps = (24, 28, 24), 4
+    flags = shell_flags(res)
+    mflags = shell_flags(res, open_axes=(1,))
+    rho0 = perturbed_interface(res, 0.5, 0.2508, 0.02381, torch.float32, False)
+    out = {}
+    for pre in (None, "mg"):
+        s = FerroSolver(flags.cuda(), magnetic_flags=mflags.cuda(), H_ext=[0.0, 60.0, 0.0], magnetic_path="converged",
+                        cg_tol=1e-6, cg_max_iters=300, cg_precondition=pre)
+        s.initialize(rho0.cuda())
+        iters = []
+        for _ in range(steps):
+            s.step()
+            i = s.cg.info()[0]
+            assert i["converged"], (pre, i)
+            iters.append(i["iters"])
+        out[pre] = (s, iters)
+    (a, ia), (b, ib) = out[None], out["mg"]
+    assert b.cg._hierarchy_built
+    assert ib[0] * 3 <= ia[0], (ia, ib)
+    fluid = (mflags != 2).cuda()
+    pa, pb = a.psi[fluid].double(), b.psi[fluid].double()
+    pa, pb = pa - pa.mean(), pb - pb.mean()
+    assert ((pa - pb).norm() / pa.norm()).item() <= 2e-5
+    for k in ("rho", "pressure", "vel"):
+        x, y = getattr(a, k).double(), getattr(b, k).double()
+        assert ((x - y).norm() / x.norm()).item() <= (1e-4 if k == "vel" else 1e-6), k
