@@ -472,9 +472,9 @@ def run_ours(args):
         fs = build_solver(res, "scalar", device, world, rank, args.workload, **slab_kw)
         fs.step(args.warmup)
         ms_fast = timed(fs.step, args.steps)
-        # one GPU: the sweeps of a step run in psi-only form (psi read + written, rhs read: 12 B/cell/sweep, SURVEY 8d's
-        # own 664 B/cell model); slabs exchange the two-float state every sweep and keep the 20 B/cell/sweep form
-        own_bytes = BYTES_HCZ + N_SWEEPS * (12 if world == 1 else BYTES_SCALAR_SWEEP)
+        # the sweeps of a step run in psi-only form (psi read + written, rhs read: 12 B/cell/sweep, SURVEY 8d's own
+        # 664 B/cell model), on one GPU and on slabs (whose per-sweep halo is then one psi plane per direction)
+        own_bytes = BYTES_HCZ + N_SWEEPS * 12
         v = cells * args.steps / (ms_fast * 1e-3) / 1e6
         fast = {"magnetic_path": "scalar", "value": v, "unit": "MLUPS", "ms_per_step": ms_fast / args.steps,
                 "model_bytes_per_cell": own_bytes,

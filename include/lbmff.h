@@ -312,6 +312,22 @@ int lbmff_slab_magnetic_sweep_d3q19(const float* h_in, float* h_out, const uint8
 int lbmff_slab_magnetic_sweep_scalar_3d(const float* a_cur, float* a_prev_out, const uint8_t* mflags,
                                         const float* rhs, float* psi_out, double dx, double dt,
                                         const lbmff_slab* slab, int B, int D, int H, int W, lbmff_stream_t stream);
+/* The same sweeps in psi-only form: the intermediate states of a step are psi alone (first half of
+ * the two-float arrays), the neighbours' two values being rebuilt from psi and rhs while a plane is staged.  ONE sweep
+ * on a plane range; src / dst alternate between the two state arrays like a_cur / a_prev_out above.  The caller chains
+ *   sweep 1: (nbr, wall, mask) = (0, 0, 0)   reads the two-float state src, wall returns from the two-float dst
+ *   sweep 2: (1, 0, 1)                       reads psi + rhs, wall returns from the two-float dst
+ *   sweep 3..n: (1, 1, 1)                    reads psi + rhs, wall returns rebuilt from the psi in dst
+ * and needs psi (first half of dst) and rhs valid one halo plane around the range.  wmask: the second half of the
+ * array sweep 1 writes (dead until the expand call); sweep 1 parks the wall masks of shell-adjacent cells there.
+ * lbmff_slab_magnetic_psi_expand_3d turns the last two psi fields (a_cur newest) back into the two-float state and
+ * writes psi_out (may be NULL) -- bit-identical to n calls of lbmff_slab_magnetic_sweep_scalar_3d. */
+int lbmff_slab_magnetic_sweep_psi_3d(const float* src, float* dst, const uint8_t* mflags, const float* rhs,
+                                     float* wmask, int nbr_mode, int wall_mode, int mask_mode, double dx, double dt,
+                                     const lbmff_slab* slab, int B, int D, int H, int W, lbmff_stream_t stream);
+int lbmff_slab_magnetic_psi_expand_3d(float* a_cur, float* a_prev, const uint8_t* mflags, const float* rhs,
+                                      float* psi_out, double dx, double dt, const lbmff_slab* slab, int B, int D,
+                                      int H, int W, lbmff_stream_t stream);
 /* get_grad shell rule folded into the data, in place: OBSTACLE shell cells take the nearest interior value
  * (LBM_collision_3d.py:217-218). */
 int lbmff_slab_shell_rule_3d(float* field, const uint8_t* flags, const lbmff_slab* slab, int B, int D, int H, int W,

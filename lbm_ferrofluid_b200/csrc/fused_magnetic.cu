@@ -539,6 +539,28 @@ static int sweeps_impl(float* hA, float* hB, const uint8_t* mflags, const float*
   return check_launch(where);
 }
 
+// one psi-only sweep (3-D) on the plane range of g; nbr / wall / mask: the template modes of k_mag_sweep_psi_tiled
+static int psi_sweep_launch(const float* src, float* dst, const uint8_t* fl, const float* rhs, float* wmask, int nbr,
+                            int wall, int mask, const Consts& k, const Grid& g, cudaStream_t st, const char* where) {
+  const int zc = g.zn < 32 ? g.zn : 32;
+  const char* er = getenv("LBMFF_MAG_PSI_ROWS");
+  const int R = er ? atoi(er) : 2;
+  const int rows = kTY * (R == 1 || R == 4 ? R : 2);
+  const dim3 tg((g.W + kTX - 1) / kTX, (g.H + rows - 1) / rows, (g.zn + zc - 1) / zc), tb(kTX, kTY);
+#define LBMFF_PSI_R(NB, WL, MK)                                                                              \
+  do {                                                                                                      \
+    if (R == 1) k_mag_sweep_psi_tiled<NB, WL, MK, 1><<<tg, tb, 0, st>>>(src, dst, fl, rhs, wmask, k, g, zc); \
+    else if (R == 4) k_mag_sweep_psi_tiled<NB, WL, MK, 4><<<tg, tb, 0, st>>>(src, dst, fl, rhs, wmask, k, g, zc); \
+    else k_mag_sweep_psi_tiled<NB, WL, MK, 2><<<tg, tb, 0, st>>>(src, dst, fl, rhs, wmask, k, g, zc);      \
+  } while (0)
+  if (nbr == 0 && wall == 0 && mask == 0) LBMFF_PSI_R(0, 0, 0);
+  else if (nbr == 1 && wall == 0 && mask == 1) LBMFF_PSI_R(1, 0, 1);
+  else if (nbr == 1 && wall == 1 && mask == 1) LBMFF_PSI_R(1, 1, 1);
+  else return bad_arg(where, "psi sweep: (nbr, wall, mask) must be (0,0,0), (1,0,1) or (1,1,1)");
+#undef LBMFF_PSI_R
+  return 0;
+}
+
 template <int DIM>
 static int sweeps_scalar_impl(float* aA, float* aB, const uint8_t* mflags, const float* rhs, float* psi_out, int n,
                               double dx, double dt, const Grid& g, cudaStream_t st, const char* where) {
@@ -552,30 +574,18 @@ static int sweeps_scalar_impl(float* aA, float* aB, const uint8_t* mflags, const
     // 12 instead of 20 B per cell and sweep; LBMFF_MAG_PSI=0 keeps the two-float sweeps
     const char* e = getenv("LBMFF_MAG_PSI");
     if (n >= 3 && g.W >= 4 && g.H >= 4 && g.zb == 0 && g.zn == g.D && g.Dg == g.D && !(e && e[0] == '0')) {
-      const int zc = g.zn < 32 ? g.zn : 32;
-      const char* er = getenv("LBMFF_MAG_PSI_ROWS");
-      const int R = er ? atoi(er) : 2;
-      const int rows = kTY * (R == 1 || R == 2 ? R : 4);
-      const dim3 tg((g.W + kTX - 1) / kTX, (g.H + rows - 1) / rows, (g.zn + zc - 1) / zc), tb(kTX, kTY);
-#define LBMFF_PSI_SWEEP(NB, WL, MK, SRC, DST)                                                                    \
-  do {                                                                                                          \
-    if (R == 1) k_mag_sweep_psi_tiled<NB, WL, MK, 1><<<tg, tb, 0, st>>>(SRC, DST, fl, r, wm, k, g, zc);        \
-    else if (R == 2) k_mag_sweep_psi_tiled<NB, WL, MK, 2><<<tg, tb, 0, st>>>(SRC, DST, fl, r, wm, k, g, zc);   \
-    else k_mag_sweep_psi_tiled<NB, WL, MK, 4><<<tg, tb, 0, st>>>(SRC, DST, fl, r, wm, k, g, zc);               \
-  } while (0)
       for (long long b = 0; b < g.B; ++b) {
         float* A = aA + b * 2 * g.N;
         float* B = aB + b * 2 * g.N;
         const uint8_t* fl = mflags + b * g.N;
         const float* r = rhs + b * g.N;
         float* wm = B + g.N;   // diagonal half of the older state array: dead after the first sweep reads it
-        LBMFF_PSI_SWEEP(0, 0, 0, A, B);   // state in A (B: one older) -> psi_1 in B
-        LBMFF_PSI_SWEEP(1, 0, 1, B, A);   // psi_1, walls from state 0 in A -> psi_2 in A
-        for (int s = 2; s < n; ++s) {     // psi_{s+1} over psi_{s-1}
-          if (s & 1) LBMFF_PSI_SWEEP(1, 1, 1, B, A);
-          else LBMFF_PSI_SWEEP(1, 1, 1, A, B);
+        psi_sweep_launch(A, B, fl, r, wm, 0, 0, 0, k, g, st, where);   // state in A (B: one older) -> psi_1 in B
+        psi_sweep_launch(B, A, fl, r, wm, 1, 0, 1, k, g, st, where);   // psi_1, walls from state 0 in A -> psi_2 in A
+        for (int s = 2; s < n; ++s) {                                  // psi_{s+1} over psi_{s-1}
+          if (s & 1) psi_sweep_launch(B, A, fl, r, wm, 1, 1, 1, k, g, st, where);
+          else psi_sweep_launch(A, B, fl, r, wm, 1, 1, 1, k, g, st, where);
         }
-#undef LBMFF_PSI_SWEEP
         float* cur = (n & 1) ? B : A;       // newest psi: sweep 1 wrote B, sweep 2 A, ...
         float* prev = (n & 1) ? A : B;
         const unsigned eb = blocks_for(g.N) > 8192u ? 8192u : blocks_for(g.N);
@@ -715,6 +725,35 @@ int lbmff_slab_magnetic_sweep_scalar_3d(const float* a_cur, float* a_prev_out, c
   if (int rc = slab_grid_m(slab, B, D, H, W, &g, __func__)) return rc;
   return sweeps_scalar_impl<3>(const_cast<float*>(a_cur), a_prev_out, mflags, rhs, psi_out, 1, dx, dt, g,
                                (cudaStream_t)stream, __func__);
+}
+
+/* psi-only form of the tau == 1 sweeps on a plane range (see k_mag_sweep_psi_tiled): ONE sweep; the caller chains the
+ * modes (0,0,0) -> (1,0,1) -> (1,1,1)... and exchanges the psi halves between sweeps */
+int lbmff_slab_magnetic_sweep_psi_3d(const float* src, float* dst, const uint8_t* mflags, const float* rhs,
+                                     float* wmask, int nbr_mode, int wall_mode, int mask_mode, double dx, double dt,
+                                     const lbmff_slab* slab, int B, int D, int H, int W, lbmff_stream_t stream) {
+  Grid g;
+  if (int rc = slab_grid_m(slab, B, D, H, W, &g, __func__)) return rc;
+  if (!(src && dst && src != dst && mflags && rhs && wmask)) return bad_arg(__func__, "null or aliased pointer");
+  if (B != 1) return bad_arg(__func__, "B must be 1");
+  if (W < 4 || H < 4) return bad_arg(__func__, "W and H must be >= 4");
+  if (g.N > 0x7fffffffLL / 2) return bad_arg(__func__, "more than (2^31-1)/2 cells per batch item");
+  if (int rc = psi_sweep_launch(src, dst, mflags, rhs, wmask, nbr_mode, wall_mode, mask_mode,
+                                make_consts(dx, dt, 1.0), g, (cudaStream_t)stream, __func__))
+    return rc;
+  return check_launch(__func__);
+}
+int lbmff_slab_magnetic_psi_expand_3d(float* a_cur, float* a_prev, const uint8_t* mflags, const float* rhs,
+                                      float* psi_out, double dx, double dt, const lbmff_slab* slab, int B, int D,
+                                      int H, int W, lbmff_stream_t stream) {
+  Grid g;
+  if (int rc = slab_grid_m(slab, B, D, H, W, &g, __func__)) return rc;
+  if (!(a_cur && a_prev && a_cur != a_prev && mflags && rhs)) return bad_arg(__func__, "null or aliased pointer");
+  if (B != 1) return bad_arg(__func__, "B must be 1");
+  const unsigned eb = blocks_for(g.i1 - g.i0) > 8192u ? 8192u : blocks_for(g.i1 - g.i0);
+  k_mag_psi_expand<<<eb, kThreads, 0, (cudaStream_t)stream>>>(a_cur, a_prev, mflags, rhs, psi_out,
+                                                            make_consts(dx, dt, 1.0), g.i0, g.i1, g.N);
+  return check_launch(__func__);
 }
 
 int lbmff_magnetic_materialize_h_2d(const float* a_cur, const float* a_prev, const float* psi, const float* rhs,

@@ -22,6 +22,7 @@ from __future__ import annotations
 
 import ctypes
 import math
+import os
 from dataclasses import dataclass
 from typing import Callable, List, Optional, Sequence
 
@@ -498,30 +499,46 @@ class SlabFerroSolver:
         if self.magnetic:
             if self._hook_before_source is not None:
                 self._hook_before_source()
+            # psi-only form of the tau == 1 sweeps: the intermediate states are psi alone, so a
+            # sweep moves 12 instead of 20 B per cell and its halo is ONE plane of psi per direction instead of two
+            # state planes.  rhs is then needed one plane beyond the owned block (chi is valid two planes out).
+            psi_only = (self.magnetic_path == "scalar" and self.n_sweeps >= 3 and self.W >= 4 and self.Hh >= 4
+                        and os.environ.get("LBMFF_MAG_PSI", "1") != "0")
             self._launch("lbmff_slab_magnetic_source_3d", p(chi), p(self.mflags), *[p(t) for t in self.H_ext_mac],
-                         self.dx, p(self._rhs), planes=own)
+                         self.dx, p(self._rhs), planes=d1 if psi_only else own)
             if self._hook_after_source is not None:
                 self._hook_after_source()
             t0 = self._mark()
             sweep = ("lbmff_slab_magnetic_sweep_d3q19" if self.magnetic_path == "faithful"
                      else "lbmff_slab_magnetic_sweep_scalar_3d")
+            wm = self._h[1 - self._mcur][:, 1:]   # psi-only: second half of the array the first sweep writes
             for s in range(self.n_sweeps):
                 m = self._mcur
                 src, dst = self._h[m], self._h[1 - m]
                 psi = p(self.psi if s == self.n_sweeps - 1 else None)
                 tail = (float(self._tau), self.dx, self.dt) if self.magnetic_path == "faithful" else (self.dx, self.dt)
 
-                def run(planes, src=src, dst=dst, psi=psi, tail=tail):
-                    self._launch(sweep, p(src), p(dst), p(self.mflags), p(self._rhs), psi, *tail, planes=planes)
+                if psi_only:
+                    modes = (0, 0, 0) if s == 0 else ((1, 0, 1) if s == 1 else (1, 1, 1))
+
+                    def run(planes, src=src, dst=dst, modes=modes):
+                        self._launch("lbmff_slab_magnetic_sweep_psi_3d", p(src), p(dst), p(self.mflags), p(self._rhs),
+                                     p(wm), *modes, self.dx, self.dt, planes=planes)
+                else:
+                    def run(planes, src=src, dst=dst, psi=psi, tail=tail):
+                        self._launch(sweep, p(src), p(dst), p(self.mflags), p(self._rhs), psi, *tail, planes=planes)
 
                 def boundary(run=run):
                     for e in edges:
                         run(e)
 
                 self._mcur = 1 - m
-                yield HaloRequest([dst], 1, overlap=lambda run=run: run(interior), pre=boundary, pipelined=True,
-                                  pops=self.magnetic_path == "faithful")
+                yield HaloRequest([dst[:, :1] if psi_only else dst], 1, overlap=lambda run=run: run(interior),
+                                  pre=boundary, pipelined=True, pops=self.magnetic_path == "faithful")
             yield HaloRequest([], 0)      # join: the caller's stream waits for the last boundary planes and halos
+            if psi_only:   # back to the two-float state (owned planes + the halo plane the next step's first sweep reads)
+                self._launch("lbmff_slab_magnetic_psi_expand_3d", p(self._h[self._mcur]), p(self._h[1 - self._mcur]),
+                             p(self.mflags), p(self._rhs), p(self.psi), self.dx, self.dt, planes=d1)
             t1 = self._mark()
             if self._timing is not None:
                 self._timing["sweeps"].append((t0, t1))
