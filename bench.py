@@ -443,6 +443,8 @@ def run_ours(args):
         done = max(1, solver.steps_done)
         exch = {"exchanges_per_step": ex.calls / done, "bytes_per_direction_per_step": ex.bytes_per_direction / done,
                 "transport": getattr(ex, "transport", "nccl p2p (batch_isend_irecv)")}
+        if hasattr(ex, "pushes"):     # sweeps whose halo exchange was fused into the boundary-plane kernels
+            exch["fused_pushes_per_step"] = ex.pushes / done
     # ---- end to end through host buffers
     e2e = None
     if not args.no_e2e:

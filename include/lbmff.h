@@ -308,6 +308,14 @@ int lbmff_slab_magnetic_source_3d(const float* chi, const uint8_t* mflags, const
 int lbmff_slab_magnetic_sweep_d3q19(const float* h_in, float* h_out, const uint8_t* mflags, const float* rhs,
                                     float* psi_out, double tau, double dx, double dt, const lbmff_slab* slab, int B,
                                     int D, int H, int W, lbmff_stream_t stream);
+/* The same sweep for a BOUNDARY plane range with the halo "send" fused in: the populations with e_z = direction (+1:
+ * top owned plane -> upper neighbour's lower halo, -1: bottom owned plane -> lower neighbour's upper halo) are also
+ * stored into peer_out, the neighbour's h_out array mapped into this process over NVLink (e.g. torch symmetric
+ * memory), at cell index + peer_shift_cells.  No reference counterpart; distributed.SymmPushExchanger is the caller. */
+int lbmff_slab_magnetic_sweep_push_d3q19(const float* h_in, float* h_out, const uint8_t* mflags, const float* rhs,
+                                         float* psi_out, double tau, double dx, double dt, float* peer_out,
+                                         int direction, long long peer_shift_cells, const lbmff_slab* slab, int B,
+                                         int D, int H, int W, lbmff_stream_t stream);
 /* ONE tau == 1 scalar sweep (a_cur latest state, a_prev_out the one before, overwritten with the new state). */
 int lbmff_slab_magnetic_sweep_scalar_3d(const float* a_cur, float* a_prev_out, const uint8_t* mflags,
                                         const float* rhs, float* psi_out, double dx, double dt,

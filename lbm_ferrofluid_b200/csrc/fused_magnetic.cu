@@ -41,11 +41,16 @@ __global__ void __launch_bounds__(kThreads) k_mag_source(const float* __restrict
 // other cells:     h_q = in_q(x - e_q); psi = sum_{q>=1} h_q / (1 - w0); out_q = collide(h_q, psi, rhs)
 // Register cap: five resident blocks per SM in 3-D (48 registers, 1280 threads/SM) measured fastest -- 3.17 ms per
 // 512^3 sweep against 3.29 ms uncapped (64 registers) and 3.38 ms at six blocks (40 registers, spills).
-template <int DIM, bool WRITE_PSI, bool IDX32>
+// PUSH = +1 / -1 (slab boundary planes, multi-GPU): the populations with e_z = PUSH are ALSO stored into `peer`, the
+// neighbour rank's output array mapped over NVLink (symmetric memory), `peer_shift` cells away -- the halo plane that
+// neighbour pulls them from.  The sweep of a boundary plane and its halo "send" are then one kernel: no pack, no
+// staging buffer, no communication kernel (distributed.SymmPushExchanger).
+template <int DIM, bool WRITE_PSI, bool IDX32, int PUSH = 0>
 __global__ void __launch_bounds__(kThreads, DIM == 3 ? 5 : 1) k_mag_sweep(const float* __restrict__ hin, float* __restrict__ hout,
                                                         const uint8_t* __restrict__ mflags,
                                                         const float* __restrict__ rhs, float* __restrict__ psi_out,
-                                                        Consts k, Grid g) {
+                                                        Consts k, Grid g, float* __restrict__ peer = nullptr,
+                                                        int peer_shift = 0) {
   using L = Lat<DIM>;
   const PlaneCell c = plane_cell(g);
   if (!c.live) return;
@@ -80,6 +85,11 @@ __global__ void __launch_bounds__(kThreads, DIM == 3 ? 5 : 1) k_mag_sweep(const 
   }
 #pragma unroll
   for (int q = 0; q < L::Q; ++q) out[at(q, i)] = hv[q];
+  if constexpr (PUSH != 0 && DIM == 3) {
+#pragma unroll
+    for (int q = 0; q < L::Q; ++q)
+      if (L::ez(q) == PUSH) peer[at(q, i + peer_shift)] = hv[q];
+  }
 }
 
 // ---- tau == 1 scalar sweep ---------------------------------------------------------------------
@@ -717,6 +727,29 @@ int lbmff_slab_magnetic_sweep_d3q19(const float* h_in, float* h_out, const uint8
   if (int rc = slab_grid_m(slab, B, D, H, W, &g, __func__)) return rc;
   return sweeps_impl<3>(const_cast<float*>(h_in), h_out, mflags, rhs, psi_out, 1, tau, dx, dt, g,
                         (cudaStream_t)stream, __func__);
+}
+int lbmff_slab_magnetic_sweep_push_d3q19(const float* h_in, float* h_out, const uint8_t* mflags, const float* rhs,
+                                         float* psi_out, double tau, double dx, double dt, float* peer_out,
+                                         int direction, long long peer_shift_cells, const lbmff_slab* slab, int B,
+                                         int D, int H, int W, lbmff_stream_t stream) {
+  Grid g;
+  if (int rc = slab_grid_m(slab, B, D, H, W, &g, __func__)) return rc;
+  if (!(h_in && h_out && h_in != h_out && mflags && rhs && peer_out)) return bad_arg(__func__, "null or aliased pointer");
+  if (B != 1) return bad_arg(__func__, "B must be 1");
+  if (direction != 1 && direction != -1) return bad_arg(__func__, "direction must be +1 or -1");
+  if (!(tau > 0)) return bad_arg(__func__, "tau must be positive");
+  if (19 * g.N >= 0xffffffffLL) return bad_arg(__func__, "lattice too large for 32-bit population indices");
+  if (peer_shift_cells <= -g.N || peer_shift_cells >= g.N) return bad_arg(__func__, "peer shift outside the array");
+  const Consts k = make_consts(dx, dt, tau);
+  const PlaneLaunch pl = plane_launch(g);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int sh = (int)peer_shift_cells;
+#define LBMFF_PUSH(WP, DIR) \
+  k_mag_sweep<3, WP, true, DIR><<<pl.grid, pl.block, 0, st>>>(h_in, h_out, mflags, rhs, psi_out, k, g, peer_out, sh)
+  if (psi_out) { if (direction > 0) LBMFF_PUSH(true, 1); else LBMFF_PUSH(true, -1); }
+  else { if (direction > 0) LBMFF_PUSH(false, 1); else LBMFF_PUSH(false, -1); }
+#undef LBMFF_PUSH
+  return check_launch(__func__);
 }
 int lbmff_slab_magnetic_sweep_scalar_3d(const float* a_cur, float* a_prev_out, const uint8_t* mflags,
                                         const float* rhs, float* psi_out, double dx, double dt,

@@ -245,6 +245,116 @@ class DistExchanger:
             self._pipe = None
 
 
+class SymmPushExchanger(DistExchanger):
+    """DistExchanger whose per-sweep halo exchange of the magnetic lattice is FUSED into the boundary-plane sweep
+    kernels: the h buffers live in torch symmetric memory (every rank maps its neighbours' buffers over NVLink), the
+    kernel that sweeps a boundary plane stores the five z-moving populations into the neighbour's halo plane as it
+    stores its own (lbmff_slab_magnetic_sweep_push_d3q19), and a signal-pad handshake replaces the message: 30 x per
+    step there is no NCCL kernel, no copy, no staging.  Everything else (the once-per-step halos of f, g, rho, ...)
+    stays on DistExchanger's grouped NCCL point-to-point path.
+
+    Ordering.  The neighbour may overwrite my halo plane of buffer X in its sweep s only after my boundary kernels of
+    sweep s-1 (the last readers of that plane) are done: it starts sweep s only after it has seen my signal of sweep
+    s-1, which I raise behind those kernels in stream order -- the data dependence already gives the WAR order.  Two
+    signal channels (0: to the upper neighbour, 1: to the lower one) keep the two messages between the same pair of
+    ranks apart when world == 2."""
+
+    transport = ("fused boundary-plane sweep + halo push over NVLink peer memory (torch symmetric memory, signal pads) "
+                 "for the 30 magnetic sweeps; nccl p2p, in place, for the once-per-step halos")
+    SIGNAL_TIMEOUT_MS = 60000
+
+    def __init__(self, layout: SlabLayout, device, group=None):
+        super().__init__(layout, device, group)
+        import torch.distributed._symmetric_memory as symm
+
+        self._symm = symm
+        self._peers = {}          # data_ptr of a local symmetric tensor -> (handle, ptr on `up`, ptr on `down`)
+        self._handle = None
+        self._signals_pending = False
+        self.pushes = 0
+
+    def alloc(self, shape) -> torch.Tensor:
+        """Zero-filled fp32 tensor in symmetric memory, mapped on both neighbours (collective: every rank calls it
+        with the same shape, in the same order)."""
+        t = self._symm.empty(tuple(shape), dtype=torch.float32, device=self.device)
+        t.zero_()
+        hdl = self._symm.rendezvous(t, self.group if self.group is not None else self.dist.group.WORLD)
+        lay = self.layout
+        up = hdl.get_buffer(lay.up, tuple(shape), torch.float32)
+        down = hdl.get_buffer(lay.down, tuple(shape), torch.float32)
+        self._peers[t.data_ptr()] = (hdl, up, down)     # the views keep the mappings alive
+        if self._handle is None:
+            self._handle = hdl
+        return t
+
+    def _wait_signals(self):
+        if self._signals_pending:
+            lay, h = self.layout, self._handle
+            h.wait_signal(lay.down, 0, self.SIGNAL_TIMEOUT_MS)   # the lower neighbour's "to up" message
+            h.wait_signal(lay.up, 1, self.SIGNAL_TIMEOUT_MS)     # the upper neighbour's "to down" message
+            self._signals_pending = False
+
+    def pipelined(self, req: "HaloRequest"):
+        ent = None
+        if req.push is not None and len(req.tensors) == 1 and self.stream is not None:
+            ent = self._peers.get(req.tensors[0].data_ptr())   # the solver's views start at element 0 of the buffer
+        if ent is None:
+            with torch.cuda.stream(self.stream) if self.stream is not None else _nullcontext():
+                self._wait_signals()
+            return super().pipelined(req)
+        _, up, down = ent
+        off = 0
+        cur, side = torch.cuda.current_stream(self.device), self.stream
+        if self._pipe is None:
+            side.wait_stream(cur)
+        else:
+            side.wait_event(self._pipe[0])         # boundary(s) reads interior(s-1) and overwrites what it read
+        with torch.cuda.stream(side):
+            self._wait_signals()                   # my halos of sweep s-1 have landed
+            req.push(up.data_ptr() + off, down.data_ptr() + off)
+            e_bnd = torch.cuda.Event()
+            e_bnd.record(side)
+            self._handle.put_signal(self.layout.up, 0, self.SIGNAL_TIMEOUT_MS)
+            self._handle.put_signal(self.layout.down, 1, self.SIGNAL_TIMEOUT_MS)
+            self._signals_pending = True
+        if self._pipe is not None:
+            cur.wait_event(self._pipe[1])          # interior(s) reads boundary(s-1) and overwrites what it read
+        req.overlap()
+        e_int = torch.cuda.Event()
+        e_int.record(cur)
+        self._pipe = (e_int, e_bnd)
+        self.calls += 1
+        self.pushes += 1
+        self.bytes_per_direction += 4 * 5 * req.tensors[0].shape[0] * req.tensors[0].shape[3] * req.tensors[0].shape[4]
+
+    def flush(self):
+        if self.stream is not None and self._signals_pending:
+            with torch.cuda.stream(self.stream):
+                self._wait_signals()
+        super().flush()
+
+
+class _nullcontext:
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *exc):
+        return False
+
+
+def make_exchanger(layout: SlabLayout, device, group=None):
+    """The exchanger the benchmark and the hardware check use: the fused push exchanger on GPUs (LBMFF_SLAB_PUSH=0 or
+    an unavailable symmetric-memory backend selects plain DistExchanger)."""
+    dev = torch.device(device)
+    if dev.type == "cuda" and os.environ.get("LBMFF_SLAB_PUSH", "1") != "0":
+        try:
+            return SymmPushExchanger(layout, dev, group)
+        except Exception as e:   # the NCCL path is complete on its own
+            import warnings
+            warnings.warn(f"SymmPushExchanger unavailable ({type(e).__name__}: {e}); using NCCL point-to-point")
+    return DistExchanger(layout, dev, group)
+
+
 def loopback_exchange(layouts: Sequence[SlabLayout], tensor_sets: Sequence[Sequence[torch.Tensor]], depth: int,
                       pops: bool = False):
     """Halo exchange between P virtual ranks living in one process (tensor_sets[r] = rank r's tensors); with
@@ -272,6 +382,10 @@ class HaloRequest:
     pops: bool = False
     pre: Optional[Callable[[], None]] = None
     pipelined: bool = False
+    # fused alternative to `pre` + exchange: push(ptr_up, ptr_down) launches the boundary planes with kernels that store
+    # the z-moving populations straight into the neighbours' arrays (raw device pointers of the SAME tensor on the
+    # upper / lower neighbour, mapped into this process); only exchangers that own such mappings use it
+    push: Optional[Callable[[int, int], None]] = None
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -372,8 +486,20 @@ class SlabFerroSolver:
             self.magnetic_path = magnetic_path
             self.psi, self._rhs, self._chi = sc(1), sc(1), sc(1)
             # the magnetic lattice stays A/B in both modes (its sweeps alternate boundary-first on two streams)
-            self._h = [mc(19)[:, :, :self.D] for _ in range(2)] if magnetic_path == "faithful" else \
-                      [mc(2)[:, :, :self.D] for _ in range(2)]
+            alloc = getattr(exchanger, "alloc", None)
+            self._h = None
+            if magnetic_path == "faithful" and alloc is not None:
+                # buffers the neighbours can store into (SymmPushExchanger): same shape and views as mc(19)
+                try:
+                    self._h = [alloc((self.B, 19, self.Dk, self.Hh, self.W))[:, :, :self.D] for _ in range(2)]
+                except Exception as e:   # no symmetric memory here: ordinary buffers, the exchanger's NCCL path
+                    import warnings
+                    warnings.warn(f"symmetric-memory allocation failed ({type(e).__name__}: {e}); "
+                                  "the magnetic sweeps exchange their halos over NCCL")
+                    self._h = None
+            if self._h is None:
+                self._h = [mc(19)[:, :, :self.D] for _ in range(2)] if magnetic_path == "faithful" else \
+                          [mc(2)[:, :, :self.D] for _ in range(2)]
             self._mcur = 0
         else:
             self.magnetic_path, self.mflags = None, None
@@ -532,9 +658,19 @@ class SlabFerroSolver:
                     for e in edges:
                         run(e)
 
+                push = None
+                if self.magnetic_path == "faithful" and self.B == 1:
+                    # bottom owned plane -> the lower neighbour's upper halo (e_z = -1 populations, Dl planes up in ITS
+                    # array); top owned plane -> the upper neighbour's lower halo (e_z = +1, Dl planes down)
+                    def push(ptr_up, ptr_down, src=src, dst=dst, psi=psi, tail=tail):
+                        cells = L.Dl * self.Hh * self.W
+                        for e, ptr, direction, shift in ((edges[0], ptr_down, -1, cells), (edges[1], ptr_up, 1, -cells)):
+                            self._launch("lbmff_slab_magnetic_sweep_push_d3q19", p(src), p(dst), p(self.mflags),
+                                         p(self._rhs), psi, *tail, ctypes.c_void_p(ptr), direction, shift, planes=e)
+
                 self._mcur = 1 - m
                 yield HaloRequest([dst[:, :1] if psi_only else dst], 1, overlap=lambda run=run: run(interior),
-                                  pre=boundary, pipelined=True, pops=self.magnetic_path == "faithful")
+                                  pre=boundary, pipelined=True, pops=self.magnetic_path == "faithful", push=push)
             yield HaloRequest([], 0)      # join: the caller's stream waits for the last boundary planes and halos
             if psi_only:   # back to the two-float state (owned planes + the halo plane the next step's first sweep reads)
                 self._launch("lbmff_slab_magnetic_psi_expand_3d", p(self._h[self._mcur]), p(self._h[1 - self._mcur]),
@@ -696,7 +832,7 @@ class SlabFerroSolver:
         flags = slab_shell_flags(lay, Hh, W, device=device)
         mflags = slab_shell_flags(lay, Hh, W, open_axes=(1,), device=device)
         rho = I.rosensweig_rho((lay.D, Hh, W), flags, global_depth=lay.Dg, z_offset=lay.zoff)
-        s = cls(lay, flags, exchanger=DistExchanger(lay, device), magnetic_flags=mflags, H_ext=[0.0, mag, 0.0],
+        s = cls(lay, flags, exchanger=make_exchanger(lay, device), magnetic_flags=mflags, H_ext=[0.0, mag, 0.0],
                 n_sweeps=n_sweeps, magnetic_path=path, contact_angle=0.5 * math.pi, gravity=1e-4, **kw)
         return s.initialize(rho)
 
@@ -712,7 +848,7 @@ def _two_droplets(cls, res_per_rank, path, device, world, rank, mag=1.0, n_sweep
     flags = slab_shell_flags(lay, Hh, W, device=device)
     mflags = slab_shell_flags(lay, Hh, W, device=device)
     rho = I.two_droplets_rho((lay.D, Hh, W), flags, global_depth=lay.Dg, z_offset=lay.zoff)
-    s = cls(lay, flags, exchanger=DistExchanger(lay, device), magnetic_flags=mflags, H_ext=[0.0, mag, 0.0],
+    s = cls(lay, flags, exchanger=make_exchanger(lay, device), magnetic_flags=mflags, H_ext=[0.0, mag, 0.0],
             n_sweeps=n_sweeps, magnetic_path=path, contact_angle=0.5 * math.pi, gravity=1e-4, kappa=0.5, **kw)
     return s.initialize(rho)
 
@@ -720,9 +856,11 @@ def _two_droplets(cls, res_per_rank, path, device, world, rank, mag=1.0, n_sweep
 SlabFerroSolver.two_droplets = classmethod(_two_droplets)
 
 
-def step_virtual_ranks(solvers: Sequence[SlabFerroSolver], n: int = 1):
+def step_virtual_ranks(solvers: Sequence[SlabFerroSolver], n: int = 1, push: bool = False):
     """Advance P slab solvers living in ONE process (one GPU) in lockstep, halos by device copies.
-    This is the bit-for-bit test vehicle of the decomposition."""
+    This is the bit-for-bit test vehicle of the decomposition.  ``push``: requests that offer the
+    fused boundary-sweep + halo-push kernels use them, the "peer" arrays being the neighbour virtual ranks' tensors
+    (what SymmPushExchanger does across GPUs over symmetric memory)."""
     layouts = [s.layout for s in solvers]
     for _ in range(int(n)):
         gens = [s._step_gen() for s in solvers]
@@ -733,6 +871,13 @@ def step_virtual_ranks(solvers: Sequence[SlabFerroSolver], n: int = 1):
             if any(r is None for r in reqs):
                 raise RuntimeError("virtual ranks fell out of lockstep")
             if not reqs[0].tensors:
+                continue
+            if push and all(r.push is not None for r in reqs):
+                for k, r in enumerate(reqs):
+                    r.push(reqs[layouts[k].up].tensors[0].data_ptr(), reqs[layouts[k].down].tensors[0].data_ptr())
+                for r in reqs:
+                    if r.overlap is not None:
+                        r.overlap()
                 continue
             for r in reqs:
                 if r.pre is not None:
@@ -773,7 +918,7 @@ def verify_against_single_gpu(device, world: int, rank: int, res_global=(64, 48,
     ok_all = True
     for path in paths:
         lay = SlabLayout(Dg, world, rank)
-        ex = (exchanger_factory or DistExchanger)(lay, dev) if group is None else DistExchanger(lay, dev, group)
+        ex = (exchanger_factory or make_exchanger)(lay, dev) if group is None else DistExchanger(lay, dev, group)
         slab = SlabFerroSolver(lay, lay.take(flags), exchanger=ex, magnetic_flags=lay.take(mflags),
                                magnetic_path=path, **kw).initialize(lay.take(rho))
         slab.step(steps)

@@ -7,7 +7,7 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-def build(res, P, path, walls_open, steps, kappa=0.01, gravity=1e-4, droplets=False, **slab_kw):
+def build(res, P, path, walls_open, steps, kappa=0.01, gravity=1e-4, droplets=False, push=False, **slab_kw):
     from lbm_ferrofluid_b200 import initializers as I
     from lbm_ferrofluid_b200.distributed import SlabFerroSolver, SlabLayout, slab_shell_flags, step_virtual_ranks
     from lbm_ferrofluid_b200.solver import FerroSolver
@@ -29,7 +29,7 @@ def build(res, P, path, walls_open, steps, kappa=0.01, gravity=1e-4, droplets=Fa
         lm = slab_shell_flags(lay, res[1], res[2], open_axes=walls_open, device=dev)
         assert torch.equal(lf, lay.take(flags)) and torch.equal(lm, lay.take(mflags))
         slabs.append(SlabFerroSolver(lay, lf, magnetic_flags=lm, **kw, **slab_kw).initialize(lay.take(rho)))
-    step_virtual_ranks(slabs, steps)
+    step_virtual_ranks(slabs, steps, push=push)
     torch.cuda.synchronize()
     return one, slabs
 
@@ -51,6 +51,24 @@ def test_virtual_ranks_bit_identical_to_one_gpu(P, path, walls_open):
     if path == "faithful":
         got = torch.cat([s.owned("h") for s in slabs], dim=2)
         assert torch.equal(got, one.h)
+
+
+@pytest.mark.parametrize("P", [2, 3])
+@pytest.mark.parametrize("walls_open", [(1,), ()])
+def test_fused_boundary_sweep_and_halo_push_is_bit_identical(P, walls_open):
+    """lbmff_slab_magnetic_sweep_push_d3q19: the boundary-plane sweep stores the z-moving populations straight into the
+    neighbour's halo plane (here: the neighbour virtual rank's tensor; across GPUs the same pointer arithmetic runs on
+    symmetric-memory mappings, SymmPushExchanger) -- no exchange of h at all, and still the one-GPU result bit for bit,
+    h included."""
+    res = (24, 14, 18)
+    one, slabs = build(res, P, "faithful", walls_open, steps=3, push=True)
+    fluid = (one.mflags != 2)
+    for name in ("f", "g", "rho", "pressure", "vel", "psi", "h"):
+        got = torch.cat([s.owned(name) for s in slabs], dim=2)
+        want = getattr(one, name)
+        if name == "psi":
+            got, want = got * fluid, want * fluid
+        assert torch.equal(got, want), f"{name}: P={P} differs (max {float((got - want).abs().max()):.3e})"
 
 
 def test_virtual_ranks_two_droplets_no_gravity():
