@@ -87,6 +87,12 @@ int lbmff_compute_gamma_d3q19(const float* vel, double dx, double dt, float* gam
 /* ---- a13  smooth_phi (HCZ_3d.py:265-269, LBM_magnetic_3d.py:119-123) */
 int lbmff_smooth_phi(const float* phi, float* out, long long n, double eps, lbmff_stream_t stream);
 
+/* ---- a19  the demos' order-parameter line phi = -(2 (density - dg) / (dl - dg) - 1) on density = affine(rho)
+ *      (demo_3d_LBM_Rosensweig_instability.py:162, HCZ_3d.py:213-215): nine elementwise torch kernels in one pass,
+ *      bit-identical to the torch expression evaluated on CUDA. */
+int lbmff_order_parameter(const float* rho, double rho_gas, double rho_liquid, double density_gas,
+                          double density_liquid, float* phi_out, long long n, lbmff_stream_t stream);
+
 /* ---- a7/a8  get_grad (static) / get_laplacian
  *      (LBM_collision_3d.py:209-318, LBM_collision_2d.py:183-256); out of grad is [B][dim][...] */
 int lbmff_get_grad_2d(const float* in, const uint8_t* flags, float* out, double dx, int B, int H, int W,

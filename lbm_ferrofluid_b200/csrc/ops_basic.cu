@@ -293,6 +293,42 @@ int lbmff_equation_of_states(const float* rho, float* out, long long n, double d
   return check_launch(__func__);
 }
 
+// phi = -(2 (density - dg) / (dl - dg) - 1), density = dg + (dl - dg) ((rho - rg) / (rl - rg)): the nine elementwise torch
+// kernels of the demos' order-parameter line (demo_3d_LBM_Rosensweig_instability.py:162 on top of the affine density
+// map, HCZ_3d.py:213-215) in ONE pass, each operation rounded separately and the two divisions by Python scalars taken
+// as multiplications by the reciprocal (formed in double, rounded to fp32) -- which is how torch evaluates
+// tensor / python_scalar on CUDA (tools/probe/torch_scalar_ops_probe.py, phi_probe.py) -- so the result
+// equals the torch expression bit for bit (tests/test_gpu_ops.py).
+struct PhiConsts {
+  float rg, inv_rdiff, ddiff, dg, inv_ddiff;
+};
+__global__ void __launch_bounds__(kThreads) k_order_parameter(const float* __restrict__ rho, float* __restrict__ out,
+                                                              long long n, PhiConsts c) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const float t = __fmul_rn(__fsub_rn(rho[i], c.rg), c.inv_rdiff);
+    const float density = __fadd_rn(__fmul_rn(c.ddiff, t), c.dg);
+    const float u = __fmul_rn(__fmul_rn(2.0f, __fsub_rn(density, c.dg)), c.inv_ddiff);
+    out[i] = -__fsub_rn(u, 1.0f);
+  }
+}
+
+int lbmff_order_parameter(const float* rho, double rho_gas, double rho_liquid, double density_gas,
+                          double density_liquid, float* phi_out, long long n, lbmff_stream_t stream) {
+  LBMFF_REQUIRE(rho && phi_out && n >= 0, "bad arguments");
+  LBMFF_REQUIRE(rho_liquid != rho_gas && density_liquid != density_gas, "liquid and gas values must differ");
+  if (n == 0) return 0;
+  PhiConsts c;
+  c.rg = (float)rho_gas;
+  c.inv_rdiff = (float)(1.0 / (rho_liquid - rho_gas));   // torch forms the reciprocal of a Python scalar in double
+  c.ddiff = (float)(density_liquid - density_gas);
+  c.dg = (float)density_gas;
+  c.inv_ddiff = (float)(1.0 / (density_liquid - density_gas));
+  const unsigned nb = blocks_for(n) > 16384u ? 16384u : blocks_for(n);
+  k_order_parameter<<<nb, kThreads, 0, (cudaStream_t)stream>>>(rho, phi_out, n, c);
+  return check_launch(__func__);
+}
+
 int lbmff_smooth_phi(const float* phi, float* out, long long n, double eps, lbmff_stream_t stream) {
   LBMFF_REQUIRE(phi && out && n >= 0 && eps > 0, "bad arguments");
   if (n == 0) return 0;

@@ -752,9 +752,13 @@ class SlabFerroSolver:
     @property
     def phi(self):
         """Order parameter of the owned planes (demo_3d...Rosensweig...py:162)."""
-        dg, dl, rg, rl = self._density_gas, self._density_liquid, self._rho_gas, self._rho_liquid
-        density = dg + (dl - dg) * ((self.layout.owned(self.rho) - rg) / (rl - rg))
-        return -(2.0 * (density - dg) / (dl - dg) - 1.0)
+        rho = self.layout.owned(self.rho)          # a contiguous block of planes (B = 1, one channel)
+        if not rho.is_contiguous():
+            rho = rho.contiguous()
+        out = torch.empty_like(rho)
+        H.launch("lbmff_order_parameter", self.device, H.ptr(rho), float(self._rho_gas), float(self._rho_liquid),
+                 float(self._density_gas), float(self._density_liquid), H.ptr(out), rho.numel())
+        return out
 
     def step_host(self, faces_host, phi_host):
         """One outer step through host buffers (same contract and copy/compute overlap as FerroSolver.step_host):

@@ -143,7 +143,16 @@ class FerroSolver:
 
     @property
     def phi(self):
-        """Order parameter the demos render (demo_3d...Rosensweig...py:162)."""
+        """Order parameter the demos render (demo_3d...Rosensweig...py:162): one fused pass over rho
+        (lbmff_order_parameter), bit-identical to the nine torch kernels of ``phi_torch``."""
+        out = torch.empty_like(self.rho)
+        H.launch("lbmff_order_parameter", self.device, H.ptr(self.rho), float(self._rho_gas), float(self._rho_liquid),
+                 float(self._density_gas), float(self._density_liquid), H.ptr(out), self.rho.numel())
+        return out
+
+    @property
+    def phi_torch(self):
+        """The same field as the demos' own torch expression (the checker of ``phi``)."""
         dg, dl = self._density_gas, self._density_liquid
         return -(2.0 * (self.density - dg) / (dl - dg) - 1.0)
 

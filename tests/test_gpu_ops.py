@@ -218,3 +218,23 @@ def test_rejects_cpu_and_fp64():
         prop.propagation(torch.zeros(1, 19, 4, 4, 4))
     with pytest.raises(TypeError):
         prop.propagation(torch.zeros(1, 19, 4, 4, 4, dtype=torch.float64, device="cuda"))
+
+
+def test_order_parameter_kernel_equals_the_torch_expression_bit_for_bit():
+    """lbmff_order_parameter (FerroSolver.phi) against the demos' own line evaluated by torch on the same GPU
+    (demo_3d_LBM_Rosensweig_instability.py:162 on the affine density map): nine elementwise kernels in one pass, equal
+    bit for bit -- random rho over and beyond the gas .. liquid range, default and non-default fluid constants."""
+    from lbm_ferrofluid_b200 import initializers as I
+    from lbm_ferrofluid_b200.solver import FerroSolver
+
+    dev = torch.device("cuda")
+    res = (12, 20, 36)
+    flags = I.shell_flags(res, device=dev)
+    g = torch.Generator(device="cpu").manual_seed(5)
+    for kw in ({}, dict(density_liquid=0.31, density_gas=0.017, rho_liquid=0.29, rho_gas=0.02)):
+        s = FerroSolver(flags, **kw)
+        s.rho.copy_((0.3 * torch.rand((1, 1, *res), generator=g) - 0.02).to(dev))
+        a, b = s.phi, s.phi_torch
+        assert torch.isfinite(a).all()
+        assert torch.equal(a, b), f"{(a != b).sum().item()} of {a.numel()} values differ, max |d| = " \
+                                  f"{(a - b).abs().max().item():.3e}"
