@@ -253,6 +253,128 @@ __global__ void __launch_bounds__(kThreads) k_cg_apply(const float* __restrict__
   block_partials<3>(acc, partials, nblocks);
 }
 
+// Ap = L p in 3-D, shared-memory tiled and marching along z: a 32 x 16 column of cells (32 x 8 threads, two rows each)
+// walks zc planes; every plane of p is staged once with its periodic rim (34 x 18) into a four-slot ring (planes z-1, z,
+// z+1 readable while z+2 lands), two planes ahead in two register sets.  The 18 neighbour values of a cell are then
+// shared-memory reads instead of L1/L2 round trips behind per-load address arithmetic.  The arithmetic is laplace()'s:
+// differences first, accumulated in the same q order, so Ap is bit-identical to k_cg_apply's (only the block partition
+// of the p.Ap partials differs).  Cells with a wall among their neighbours (mask != 0) take laplace() itself.
+constexpr int kApTX = 32, kApTY = 8, kApR = 2, kApRing = 4;
+constexpr int kApRows = kApTY * kApR, kApTW = kApTX + 2, kApTH = kApRows + 2, kApTile = kApTW * kApTH;
+constexpr int kApStage = (kApTile + kApTX * kApTY - 1) / (kApTX * kApTY);
+
+__device__ __noinline__ float cg_apply_wall_adjacent(const float* __restrict__ p, float pc, int x, int y, int z, int i,
+                                                     unsigned m, const Grid& g) {
+  PlaneCell c;
+  c.x = x; c.y = y; c.z = z; c.i = i; c.live = true;
+  const Nbr nb(c, g);
+  return laplace<3>(p, pc, i, nb, m);
+}
+
+__global__ void __launch_bounds__(kApTX* kApTY, 3) k_cg_apply_tiled(const float* __restrict__ p,
+                                                                   const unsigned* __restrict__ mask,
+                                                                   float* __restrict__ Ap, double* __restrict__ partials,
+                                                                   int nblocks, const CgScalars* __restrict__ sc,
+                                                                   const __grid_constant__ Grid g, int zc) {
+  using L = Lat<3>;
+  if (sc->done != 0.0) return;
+  __shared__ float sP[kApRing][kApTile];
+  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * kApTX + tx;
+  const int x0 = blockIdx.x * kApTX, y0 = blockIdx.y * kApRows;
+  const int zs = blockIdx.z * zc, ze = min(zs + zc, g.D);
+  const int HW = g.H * g.W;
+  int off[kApStage];
+#pragma unroll
+  for (int t = 0; t < kApStage; ++t) {
+    const int e = tid + t * kApTX * kApTY;
+    const int sy = e / kApTW, sx = e - sy * kApTW;
+    int gx = x0 - 1 + sx, gy = y0 - 1 + sy;
+    gx = gx < 0 ? gx + g.W : gx; gy = gy < 0 ? gy + g.H : gy;
+    while (gx >= g.W) gx -= g.W;
+    while (gy >= g.H) gy -= g.H;
+    off[t] = e < kApTile ? gy * g.W + gx : -1;
+  }
+  float rv[2][kApStage];
+  auto fetch = [&](int z, auto SET_) {
+    constexpr int SET = decltype(SET_)::value;
+    const int zz = z < 0 ? z + g.D : (z >= g.D ? z - g.D : z);
+    const int zo = zz * HW;
+#pragma unroll
+    for (int t = 0; t < kApStage; ++t)
+      if (t < kApStage - 1 || off[t] >= 0) rv[SET][t] = __ldg(p + zo + off[t]);
+  };
+  auto put_slot = [&](int slot, auto SET_) {
+    constexpr int SET = decltype(SET_)::value;
+#pragma unroll
+    for (int t = 0; t < kApStage; ++t)
+      if (t < kApStage - 1 || off[t] >= 0) sP[slot][tid + t * kApTX * kApTY] = rv[SET][t];
+  };
+  using Set0 = std::integral_constant<int, 0>;
+  using Set1 = std::integral_constant<int, 1>;
+  fetch(zs - 1, Set0{}); put_slot(0, Set0{});
+  fetch(zs, Set0{}); put_slot(1, Set0{});
+  fetch(zs + 1, Set1{});
+  fetch(zs + 2, Set0{});
+  const int x = x0 + tx;
+  bool live[kApR];
+  unsigned m_next[kApR];
+#pragma unroll
+  for (int r = 0; r < kApR; ++r) {
+    const int y = y0 + ty + kApTY * r;
+    live[r] = x < g.W && y < g.H;
+    m_next[r] = live[r] ? mask[zs * HW + y * g.W + x] : kWallSelf;
+  }
+  int i0 = zs * HW + (y0 + ty) * g.W + x;
+  const int rowstep = kApTY * g.W;
+  double acc[3] = {0.0, 0.0, 0.0};
+  auto plane = [&](int z, auto S_) {
+    constexpr int S = decltype(S_)::value;
+    using Set = std::integral_constant<int, (S + 1) & 1>;
+    put_slot((S + 2) & (kApRing - 1), Set{});   // plane z + 1
+    if (z + 2 < ze) fetch(z + 3, Set{});
+    unsigned m[kApR];
+#pragma unroll
+    for (int r = 0; r < kApR; ++r) {
+      m[r] = m_next[r];
+      if (live[r] && z + 1 < ze) m_next[r] = mask[i0 + HW + r * rowstep];
+    }
+    __syncthreads();
+    constexpr int sl[3] = {S & (kApRing - 1), (S + 1) & (kApRing - 1), (S + 2) & (kApRing - 1)};  // planes z-1, z, z+1
+#pragma unroll
+    for (int r = 0; r < kApR; ++r) {
+      if (!live[r]) continue;
+      const int i = i0 + r * rowstep;
+      float out = 0.f;
+      if (!(m[r] & kWallSelf)) {
+        const int ec = (ty + kApTY * r + 1) * kApTW + (tx + 1);
+        const float pc = sP[sl[1]][ec];
+        if (m[r] == 0) {
+          float s_axis = 0.f, s_diag = 0.f;
+#pragma unroll
+          for (int q = 1; q < L::Q; ++q) {
+            const bool axis = (L::ex(q) != 0) + (L::ey(q) != 0) + (L::ez(q) != 0) == 1;
+            const float d = pc - sP[sl[1 - L::ez(q)]][ec - L::ey(q) * kApTW - L::ex(q)];
+            if (axis) s_axis += d; else s_diag += d;
+          }
+          out = (L::w(1) * s_axis + L::w(5) * s_diag) / (1.0f - L::w(0));
+        } else {
+          out = cg_apply_wall_adjacent(p, pc, x, y0 + ty + kApTY * r, z, i, m[r], g);
+        }
+        acc[0] += (double)pc * out;
+      }
+      Ap[i] = out;
+    }
+    i0 += HW;
+  };
+  for (int z = zs; z < ze; z += kApRing) {
+    plane(z, std::integral_constant<int, 0>{});
+    if (z + 1 < ze) plane(z + 1, std::integral_constant<int, 1>{});
+    if (z + 2 < ze) plane(z + 2, std::integral_constant<int, 2>{});
+    if (z + 3 < ze) plane(z + 3, std::integral_constant<int, 3>{});
+  }
+  block_partials<3>(acc, partials, nblocks);
+}
+
 // The two vector updates are flat streaming kernels (no stencil, no flags: r, p and Ap are kept at exactly 0 on wall
 // cells, so psi is untouched there), float4 when the item is 16-byte aligned, grid-stride over `nblocks` blocks.
 // psi += alpha p; r -= alpha Ap; partials: r.r (twice: the unpreconditioned r.z is r.r)
@@ -315,7 +437,30 @@ static PlaneLaunch cg_launch(const Grid& g) {
   return pl;
 }
 static int cg_blocks(const PlaneLaunch& pl) { return (int)(pl.grid.x * pl.grid.y * pl.grid.z); }
-static long long cg_scratch_doubles(const PlaneLaunch& pl) { return 3LL * cg_blocks(pl) + 16; }
+// launch of the operator kernel: k_cg_apply_tiled in 3-D (LBMFF_CG_TILED=0 keeps k_cg_apply), with its own block count
+struct ApplyLaunch {
+  bool tiled;
+  dim3 grid, block;
+  int zc, nb;
+};
+static ApplyLaunch apply_launch(const Grid& g, const PlaneLaunch& pl, bool allow_env = true) {
+  ApplyLaunch a;
+  a.tiled = false; a.grid = pl.grid; a.block = pl.block; a.zc = 0; a.nb = cg_blocks(pl);
+  const char* e = allow_env ? getenv("LBMFF_CG_TILED") : nullptr;
+  if (g.D > 1 && g.W >= 4 && g.H >= 4 && g.D >= 3 && !(e && e[0] == '0')) {
+    a.tiled = true;
+    a.zc = g.D >= 64 ? 32 : (g.D >= 16 ? 8 : g.D);
+    a.block = dim3(kApTX, kApTY, 1);
+    a.grid = dim3((unsigned)((g.W + kApTX - 1) / kApTX), (unsigned)((g.H + kApRows - 1) / kApRows),
+                  (unsigned)((g.D + a.zc - 1) / a.zc));
+    a.nb = (int)(a.grid.x * a.grid.y * a.grid.z);
+  }
+  return a;
+}
+static long long cg_scratch_doubles(const PlaneLaunch& pl, const Grid& g) {
+  const int nt = apply_launch(g, pl, false).nb, np = cg_blocks(pl);
+  return 3LL * (nt > np ? nt : np) + 16;
+}
 
 struct CgBuffers {
   float *b, *r, *p, *Ap, *psi;
@@ -336,9 +481,13 @@ template <int DIM>
 static cudaError_t iterate_plain(const CgBuffers& B, const PlaneLaunch& pl, int nb, int max_iters, double tol2,
                                  const Grid& g, cudaStream_t st) {
   const bool vec4 = cg_vec4(B, g);
+  const ApplyLaunch al = apply_launch(g, pl);
   for (int it = 0; it < max_iters; ++it) {
-    k_cg_apply<DIM><<<pl.grid, pl.block, 0, st>>>(B.p, B.mask, B.Ap, B.part, nb, B.sc, g);
-    k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, nb, 2, B.sc, nullptr, 0.0, max_iters, 0);
+    if (DIM == 3 && al.tiled)
+      k_cg_apply_tiled<<<al.grid, al.block, 0, st>>>(B.p, B.mask, B.Ap, B.part, al.nb, B.sc, g, al.zc);
+    else
+      k_cg_apply<DIM><<<pl.grid, pl.block, 0, st>>>(B.p, B.mask, B.Ap, B.part, al.nb, B.sc, g);
+    k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, al.nb, 2, B.sc, nullptr, 0.0, max_iters, 0);
     if (vec4) k_cg_update<true><<<nb, kThreads, 0, st>>>(B.psi, B.r, B.p, B.Ap, g.N, B.part, nb, B.sc);
     else k_cg_update<false><<<nb, kThreads, 0, st>>>(B.psi, B.r, B.p, B.Ap, g.N, B.part, nb, B.sc);
     k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, nb, 3, B.sc, B.hist, tol2, max_iters, 0);
@@ -386,14 +535,21 @@ static cudaError_t iterate_graph(const CgBuffers& B, const PlaneLaunch& pl, int 
   float* nohist = nullptr;
   Grid gv = g;
   CgBuffers b = B;
-  void* a_apply[] = {&b.p, &b.mask, &b.Ap, &b.part, &nbv, &b.sc, &gv};
-  void* a_fin2[] = {&b.part, &nbv, &what2, &b.sc, &nohist, &zero, &mi, &handle};
+  const ApplyLaunch al = apply_launch(g, pl);
+  int nba = al.nb, zcv = al.zc;
+  void* a_apply[] = {&b.p, &b.mask, &b.Ap, &b.part, &nba, &b.sc, &gv};
+  void* a_apply_t[] = {&b.p, &b.mask, &b.Ap, &b.part, &nba, &b.sc, &gv, &zcv};
+  void* a_fin2[] = {&b.part, &nba, &what2, &b.sc, &nohist, &zero, &mi, &handle};
   long long nv = g.N;
   const bool vec4 = cg_vec4(B, g);
   void* a_update[] = {&b.psi, &b.r, &b.p, &b.Ap, &nv, &b.part, &nbv, &b.sc};
   void* a_fin3[] = {&b.part, &nbv, &what3, &b.sc, &b.hist, &t2, &mi, &handle};
   void* a_dir[] = {&b.p, &b.r, &nv, &b.sc};
-  if ((e = add((void*)k_cg_apply<DIM>, pl.grid, pl.block, a_apply)) != cudaSuccess) return fail(e);
+  if (DIM == 3 && al.tiled) {
+    if ((e = add((void*)k_cg_apply_tiled, al.grid, al.block, a_apply_t)) != cudaSuccess) return fail(e);
+  } else if ((e = add((void*)k_cg_apply<DIM>, pl.grid, pl.block, a_apply)) != cudaSuccess) {
+    return fail(e);
+  }
   if ((e = add((void*)k_cg_finish<true>, dim3(1), dim3(1024), a_fin2)) != cudaSuccess) return fail(e);
   if ((e = add(vec4 ? (void*)k_cg_update<true> : (void*)k_cg_update<false>, dim3(nb), dim3(kThreads), a_update)) !=
       cudaSuccess)
@@ -422,7 +578,7 @@ static int poisson_cg_impl(const float* rhs, const uint8_t* mflags, float* psi, 
   const Consts k = make_consts(dx, dt, tau);
   const PlaneLaunch pl = cg_launch(g);
   const int nb = cg_blocks(pl);
-  const long long stride = cg_scratch_doubles(pl);
+  const long long stride = cg_scratch_doubles(pl, g);
   const char* env = getenv("LBMFF_CG_NO_GRAPH");
   const bool use_graph = !(env && env[0] == '1');
   for (long long b = 0; b < g.B; ++b) {
@@ -851,9 +1007,14 @@ static void pcg_body(Launcher& K, const CgBuffers& B, PcgExtra& X, const PlaneLa
                      double tol2, const Grid& g, cudaGraphConditionalHandle handle) {
   const bool vec4 = cg_vec4(B, g);
   float* nohist = nullptr;
-  K((const void*)k_cg_apply<DIM>, pl.grid, pl.block, (const float*)B.p, (const unsigned*)B.mask, B.Ap, B.part, nb,
-    (const CgScalars*)B.sc, g);
-  K((const void*)k_cg_finish<GRAPH>, dim3(1), dim3(1024), (const double*)B.part, nb, 2, B.sc, nohist, 0.0, max_iters,
+  const ApplyLaunch al = apply_launch(g, pl);
+  if (DIM == 3 && al.tiled)
+    K((const void*)k_cg_apply_tiled, al.grid, al.block, (const float*)B.p, (const unsigned*)B.mask, B.Ap, B.part, al.nb,
+      (const CgScalars*)B.sc, g, al.zc);
+  else
+    K((const void*)k_cg_apply<DIM>, pl.grid, pl.block, (const float*)B.p, (const unsigned*)B.mask, B.Ap, B.part, al.nb,
+      (const CgScalars*)B.sc, g);
+  K((const void*)k_cg_finish<GRAPH>, dim3(1), dim3(1024), (const double*)B.part, al.nb, 2, B.sc, nohist, 0.0, max_iters,
     handle);
   K(vec4 ? (const void*)k_cg_update<true> : (const void*)k_cg_update<false>, dim3(nb), dim3(kThreads), B.psi, B.r,
     (const float*)B.p, (const float*)B.Ap, (long long)g.N, B.part, nb, (const CgScalars*)B.sc);
@@ -916,7 +1077,7 @@ static int poisson_pcg_impl(const float* rhs, const uint8_t* mflags, float* psi,
   const Consts k = make_consts(dx, dt, tau);
   const PlaneLaunch pl = cg_launch(g);
   const int nb = cg_blocks(pl);
-  const long long stride = cg_scratch_doubles(pl);
+  const long long stride = cg_scratch_doubles(pl, g);
   const long long mgf = mg_workspace_floats<DIM>(g);
   const char* env = getenv("LBMFF_CG_NO_GRAPH");
   const bool use_graph = !(env && env[0] == '1');
@@ -969,7 +1130,8 @@ extern "C" {
 
 int lbmff_poisson_cg_scratch_doubles(int D, int H, int W) {
   if (D < 1 || H < 1 || W < 1) return -1;
-  const long long n = cg_scratch_doubles(cg_launch(make_grid(1, D, H, W)));
+  const Grid g1 = make_grid(1, D, H, W);
+  const long long n = cg_scratch_doubles(cg_launch(g1), g1);
   return n > 0x7fffffffLL ? -1 : (int)n;
 }
 

@@ -286,3 +286,31 @@ def test_ferrosolver_with_multigrid_preconditioner_follows_the_plain_cg_trajecto
     for k in ("rho", "pressure", "vel"):
         x, y = getattr(a, k).double(), getattr(b, k).double()
         assert ((x - y).norm() / x.norm()).item() <= (1e-4 if k == "vel" else 1e-6), k
+
+
+@pytest.mark.parametrize("res", [(18, 20, 22), (33, 47, 29), (70, 24, 72)])
+def test_tiled_cg_operator_equals_the_generic_one(res, monkeypatch):
+    """k_cg_apply_tiled (3-D, plane ring in shared memory, laplace()'s differences in the same order) against
+    k_cg_apply (LBMFF_CG_TILED=0): Ap is the same bit for bit, only the block partition of the p.Ap partial sums
+    differs, so the two solves follow each other to rounding -- same iteration count (+-1), same solution -- on
+    ragged extents with an interior wall."""
+    from lbm_ferrofluid_b200.poisson import PoissonCG
+
+    mflags, rhs, dim = _case(res, seed=7)
+    mf, r = mflags.cuda(), rhs.cuda()
+    out = {}
+    for tiled in ("1", "0"):
+        monkeypatch.setenv("LBMFF_CG_TILED", tiled)
+        cg = PoissonCG(mf, tol=1e-6, max_iters=1500, keep_history=True)
+        psi = torch.zeros((1, 1, *res), device="cuda")
+        cg.solve(r, psi)
+        out[tiled] = (psi, cg.info()[0], cg.history()[0])
+    (pa, ia, ha), (pb, ib, hb) = out["1"], out["0"]
+    assert ia["converged"] and ib["converged"], (ia, ib)
+    assert abs(ia["iters"] - ib["iters"]) <= 1, (ia["iters"], ib["iters"])
+    assert abs(ha[1] - hb[1]) <= 1e-5 * hb[0] and abs(ha[3] - hb[3]) <= 1e-4 * hb[0]
+    fluid = (mf != 2)
+    a, b = pa[fluid].double(), pb[fluid].double()
+    a, b = a - a.mean(), b - b.mean()
+    assert (a - b).norm().item() <= 2e-5 * b.norm().item()
+    assert torch.equal(pa[~fluid], torch.zeros_like(pa[~fluid]))
