@@ -271,13 +271,19 @@ __device__ __noinline__ float cg_apply_wall_adjacent(const float* __restrict__ p
   return laplace<3>(p, pc, i, nb, m);
 }
 
+// MODE 0: Ap = L p, partial p.Ap (k_cg_apply).  MODE 1: the start of a solve (k_cg_start): `p` is psi, r = p_out =
+// (b - c (1 + omega)) - L psi, partials r.r (twice) and |b - c (1 + omega)|^2; Ap is r, bvec is b, out2 is the direction p.
+template <int MODE>
 __global__ void __launch_bounds__(kApTX* kApTY, 3) k_cg_apply_tiled(const float* __restrict__ p,
                                                                    const unsigned* __restrict__ mask,
                                                                    float* __restrict__ Ap, double* __restrict__ partials,
                                                                    int nblocks, const CgScalars* __restrict__ sc,
-                                                                   const __grid_constant__ Grid g, int zc) {
+                                                                   const __grid_constant__ Grid g, int zc,
+                                                                   const float* __restrict__ bvec = nullptr,
+                                                                   float* __restrict__ out2 = nullptr) {
   using L = Lat<3>;
-  if (sc->done != 0.0) return;
+  if (MODE == 0 && sc->done != 0.0) return;
+  const float drift = MODE == 1 ? (float)sc->mean : 0.f;
   __shared__ float sP[kApRing][kApTile];
   const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * kApTX + tx;
   const int x0 = blockIdx.x * kApTX, y0 = blockIdx.y * kApRows;
@@ -360,9 +366,16 @@ __global__ void __launch_bounds__(kApTX* kApTY, 3) k_cg_apply_tiled(const float*
         } else {
           out = cg_apply_wall_adjacent(p, pc, x, y0 + ty + kApTY * r, z, i, m[r], g);
         }
-        acc[0] += (double)pc * out;
+        if (MODE == 0) {
+          acc[0] += (double)pc * out;
+        } else {
+          const float bz = bvec[i] - drift * (2.0f - diag_of<3>(m[r]));
+          out = bz - out;
+          acc[0] += (double)out * out; acc[1] += (double)out * out; acc[2] += (double)bz * bz;
+        }
       }
       Ap[i] = out;
+      if (MODE == 1) out2[i] = out;
     }
     i0 += HW;
   };
@@ -484,7 +497,7 @@ static cudaError_t iterate_plain(const CgBuffers& B, const PlaneLaunch& pl, int 
   const ApplyLaunch al = apply_launch(g, pl);
   for (int it = 0; it < max_iters; ++it) {
     if (DIM == 3 && al.tiled)
-      k_cg_apply_tiled<<<al.grid, al.block, 0, st>>>(B.p, B.mask, B.Ap, B.part, al.nb, B.sc, g, al.zc);
+      k_cg_apply_tiled<0><<<al.grid, al.block, 0, st>>>(B.p, B.mask, B.Ap, B.part, al.nb, B.sc, g, al.zc, nullptr, nullptr);
     else
       k_cg_apply<DIM><<<pl.grid, pl.block, 0, st>>>(B.p, B.mask, B.Ap, B.part, al.nb, B.sc, g);
     k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, al.nb, 2, B.sc, nullptr, 0.0, max_iters, 0);
@@ -538,7 +551,9 @@ static cudaError_t iterate_graph(const CgBuffers& B, const PlaneLaunch& pl, int 
   const ApplyLaunch al = apply_launch(g, pl);
   int nba = al.nb, zcv = al.zc;
   void* a_apply[] = {&b.p, &b.mask, &b.Ap, &b.part, &nba, &b.sc, &gv};
-  void* a_apply_t[] = {&b.p, &b.mask, &b.Ap, &b.part, &nba, &b.sc, &gv, &zcv};
+  const float* nob = nullptr;
+  float* noo = nullptr;
+  void* a_apply_t[] = {&b.p, &b.mask, &b.Ap, &b.part, &nba, &b.sc, &gv, &zcv, &nob, &noo};
   void* a_fin2[] = {&b.part, &nba, &what2, &b.sc, &nohist, &zero, &mi, &handle};
   long long nv = g.N;
   const bool vec4 = cg_vec4(B, g);
@@ -546,7 +561,7 @@ static cudaError_t iterate_graph(const CgBuffers& B, const PlaneLaunch& pl, int 
   void* a_fin3[] = {&b.part, &nbv, &what3, &b.sc, &b.hist, &t2, &mi, &handle};
   void* a_dir[] = {&b.p, &b.r, &nv, &b.sc};
   if (DIM == 3 && al.tiled) {
-    if ((e = add((void*)k_cg_apply_tiled, al.grid, al.block, a_apply_t)) != cudaSuccess) return fail(e);
+    if ((e = add((void*)k_cg_apply_tiled<0>, al.grid, al.block, a_apply_t)) != cudaSuccess) return fail(e);
   } else if ((e = add((void*)k_cg_apply<DIM>, pl.grid, pl.block, a_apply)) != cudaSuccess) {
     return fail(e);
   }
@@ -596,8 +611,14 @@ static int poisson_cg_impl(const float* rhs, const uint8_t* mflags, float* psi, 
     B.hist = res_hist ? res_hist + b * (max_iters + 1LL) : nullptr;
     k_cg_rhs<DIM><<<pl.grid, pl.block, 0, st>>>(rb, fl, B.b, B.mask, B.part, nb, k, g);
     k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, nb, 0, B.sc, nullptr, 0.0, max_iters, 0);
-    k_cg_start<DIM><<<pl.grid, pl.block, 0, st>>>(B.b, B.psi, B.mask, B.r, B.p, B.part, nb, B.sc, g);
-    k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, nb, 1, B.sc, B.hist, tol * tol, max_iters, 0);
+    {
+      const ApplyLaunch al = apply_launch(g, pl);
+      if (DIM == 3 && al.tiled)
+        k_cg_apply_tiled<1><<<al.grid, al.block, 0, st>>>(B.psi, B.mask, B.r, B.part, al.nb, B.sc, g, al.zc, B.b, B.p);
+      else
+        k_cg_start<DIM><<<pl.grid, pl.block, 0, st>>>(B.b, B.psi, B.mask, B.r, B.p, B.part, al.nb, B.sc, g);
+      k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, al.nb, 1, B.sc, B.hist, tol * tol, max_iters, 0);
+    }
     if (max_iters > 0) {
       const cudaError_t e = use_graph ? iterate_graph<DIM>(B, pl, nb, max_iters, tol * tol, g, st)
                                       : iterate_plain<DIM>(B, pl, nb, max_iters, tol * tol, g, st);
@@ -1009,8 +1030,8 @@ static void pcg_body(Launcher& K, const CgBuffers& B, PcgExtra& X, const PlaneLa
   float* nohist = nullptr;
   const ApplyLaunch al = apply_launch(g, pl);
   if (DIM == 3 && al.tiled)
-    K((const void*)k_cg_apply_tiled, al.grid, al.block, (const float*)B.p, (const unsigned*)B.mask, B.Ap, B.part, al.nb,
-      (const CgScalars*)B.sc, g, al.zc);
+    K((const void*)k_cg_apply_tiled<0>, al.grid, al.block, (const float*)B.p, (const unsigned*)B.mask, B.Ap, B.part, al.nb,
+      (const CgScalars*)B.sc, g, al.zc, (const float*)nullptr, (float*)nullptr);
   else
     K((const void*)k_cg_apply<DIM>, pl.grid, pl.block, (const float*)B.p, (const unsigned*)B.mask, B.Ap, B.part, al.nb,
       (const CgScalars*)B.sc, g);
@@ -1101,8 +1122,14 @@ static int poisson_pcg_impl(const float* rhs, const uint8_t* mflags, float* psi,
     k_cg_rhs<DIM><<<pl.grid, pl.block, 0, st>>>(rb, fl, B.b, B.mask, B.part, nb, k, g);
     k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, nb, 0, B.sc, nullptr, 0.0, max_iters, 0);
     if (!reuse_hierarchy) mg_setup<DIM>(B.mask, g, X.L, X.nlev, st);   // depends on the flags only
-    k_cg_start<DIM><<<pl.grid, pl.block, 0, st>>>(B.b, B.psi, B.mask, B.r, B.p, B.part, nb, B.sc, g);
-    k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, nb, 1, B.sc, B.hist, tol * tol, max_iters, 0);
+    {
+      const ApplyLaunch al = apply_launch(g, pl);
+      if (DIM == 3 && al.tiled)
+        k_cg_apply_tiled<1><<<al.grid, al.block, 0, st>>>(B.psi, B.mask, B.r, B.part, al.nb, B.sc, g, al.zc, B.b, B.p);
+      else
+        k_cg_start<DIM><<<pl.grid, pl.block, 0, st>>>(B.b, B.psi, B.mask, B.r, B.p, B.part, al.nb, B.sc, g);
+      k_cg_finish<false><<<1, 1024, 0, st>>>(B.part, al.nb, 1, B.sc, B.hist, tol * tol, max_iters, 0);
+    }
     if (max_iters > 0) {
       Launcher K{st};
       mg_vcycle<DIM>(K, B.mask, g, B.r, X.z, X.t, B.Ap, X.L, X.nlev);
