@@ -335,10 +335,13 @@ int lbmff_slab_magnetic_sweep_scalar_3d(const float* a_cur, float* a_prev_out, c
  * and needs psi (first half of dst) and rhs valid one halo plane around the range.  wmask: the second half of the
  * array sweep 1 writes (dead until the expand call); sweep 1 parks the wall masks of shell-adjacent cells there.
  * lbmff_slab_magnetic_psi_expand_3d turns the last two psi fields (a_cur newest) back into the two-float state and
- * writes psi_out (may be NULL) -- bit-identical to n calls of lbmff_slab_magnetic_sweep_scalar_3d. */
+ * writes psi_out (may be NULL) -- bit-identical to n calls of lbmff_slab_magnetic_sweep_scalar_3d.
+ * peer_dst (may be NULL): psi is also stored at cell + peer_shift_cells of the neighbour rank's dst array mapped into
+ * this process (boundary planes; the fused halo push of lbmff_slab_magnetic_sweep_push_d3q19 for this form). */
 int lbmff_slab_magnetic_sweep_psi_3d(const float* src, float* dst, const uint8_t* mflags, const float* rhs,
                                      float* wmask, int nbr_mode, int wall_mode, int mask_mode, double dx, double dt,
-                                     const lbmff_slab* slab, int B, int D, int H, int W, lbmff_stream_t stream);
+                                     float* peer_dst, long long peer_shift_cells, const lbmff_slab* slab, int B, int D,
+                                     int H, int W, lbmff_stream_t stream);
 int lbmff_slab_magnetic_psi_expand_3d(float* a_cur, float* a_prev, const uint8_t* mflags, const float* rhs,
                                       float* psi_out, double dx, double dt, const lbmff_slab* slab, int B, int D,
                                       int H, int W, lbmff_stream_t stream);

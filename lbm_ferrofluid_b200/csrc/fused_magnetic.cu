@@ -303,8 +303,11 @@ template <int NBR, int WALL, int MASK, int R>
 __global__ void __launch_bounds__(kTX* kTY, R == 1 ? 4 : 3) k_mag_sweep_psi_tiled(const float* __restrict__ src, float* dst,
                                                                                const uint8_t* __restrict__ fl,
                                                                                const float* __restrict__ rhs,
-                                                                               float* wmask, Consts k, Grid g, int zc) {
+                                                                               float* wmask, Consts k, Grid g, int zc,
+                                                                               float* peer = nullptr, int peer_shift = 0) {
   using L = Lat<3>;
+  // peer != nullptr (slab boundary planes, multi-GPU): psi is also stored into the neighbour rank's array, peer_shift
+  // cells away -- its halo plane (the fused halo push of distributed.SymmPushExchanger)
   // 32 x 8 threads, R rows per thread (rows ty, ty + 8, ...): the per-plane bookkeeping (staging addresses, loop
   // control, barrier) is shared by R cells -- it was two thirds of the instructions with one row per thread
   constexpr int kRows = kTY * R, kTH = kRows + 2, kTile = kTH * kTileW;
@@ -447,7 +450,9 @@ __global__ void __launch_bounds__(kTX* kTY, R == 1 ? 4 : 3) k_mag_sweep_psi_tile
           }
         }
       }
-      dst[i] = psi_of<3>(hv);
+      const float psi_new = psi_of<3>(hv);
+      dst[i] = psi_new;
+      if (peer) peer[i + peer_shift] = psi_new;
     }
     i0 += HW;
   };
@@ -551,7 +556,8 @@ static int sweeps_impl(float* hA, float* hB, const uint8_t* mflags, const float*
 
 // one psi-only sweep (3-D) on the plane range of g; nbr / wall / mask: the template modes of k_mag_sweep_psi_tiled
 static int psi_sweep_launch(const float* src, float* dst, const uint8_t* fl, const float* rhs, float* wmask, int nbr,
-                            int wall, int mask, const Consts& k, const Grid& g, cudaStream_t st, const char* where) {
+                            int wall, int mask, const Consts& k, const Grid& g, cudaStream_t st, const char* where,
+                            float* peer = nullptr, int peer_shift = 0) {
   const int zc = g.zn < 32 ? g.zn : 32;
   const char* er = getenv("LBMFF_MAG_PSI_ROWS");
   const int R = er ? atoi(er) : 2;
@@ -559,9 +565,9 @@ static int psi_sweep_launch(const float* src, float* dst, const uint8_t* fl, con
   const dim3 tg((g.W + kTX - 1) / kTX, (g.H + rows - 1) / rows, (g.zn + zc - 1) / zc), tb(kTX, kTY);
 #define LBMFF_PSI_R(NB, WL, MK)                                                                              \
   do {                                                                                                      \
-    if (R == 1) k_mag_sweep_psi_tiled<NB, WL, MK, 1><<<tg, tb, 0, st>>>(src, dst, fl, rhs, wmask, k, g, zc); \
-    else if (R == 4) k_mag_sweep_psi_tiled<NB, WL, MK, 4><<<tg, tb, 0, st>>>(src, dst, fl, rhs, wmask, k, g, zc); \
-    else k_mag_sweep_psi_tiled<NB, WL, MK, 2><<<tg, tb, 0, st>>>(src, dst, fl, rhs, wmask, k, g, zc);      \
+    if (R == 1) k_mag_sweep_psi_tiled<NB, WL, MK, 1><<<tg, tb, 0, st>>>(src, dst, fl, rhs, wmask, k, g, zc, peer, peer_shift); \
+    else if (R == 4) k_mag_sweep_psi_tiled<NB, WL, MK, 4><<<tg, tb, 0, st>>>(src, dst, fl, rhs, wmask, k, g, zc, peer, peer_shift); \
+    else k_mag_sweep_psi_tiled<NB, WL, MK, 2><<<tg, tb, 0, st>>>(src, dst, fl, rhs, wmask, k, g, zc, peer, peer_shift);      \
   } while (0)
   if (nbr == 0 && wall == 0 && mask == 0) LBMFF_PSI_R(0, 0, 0);
   else if (nbr == 1 && wall == 0 && mask == 1) LBMFF_PSI_R(1, 0, 1);
@@ -764,15 +770,18 @@ int lbmff_slab_magnetic_sweep_scalar_3d(const float* a_cur, float* a_prev_out, c
  * modes (0,0,0) -> (1,0,1) -> (1,1,1)... and exchanges the psi halves between sweeps */
 int lbmff_slab_magnetic_sweep_psi_3d(const float* src, float* dst, const uint8_t* mflags, const float* rhs,
                                      float* wmask, int nbr_mode, int wall_mode, int mask_mode, double dx, double dt,
-                                     const lbmff_slab* slab, int B, int D, int H, int W, lbmff_stream_t stream) {
+                                     float* peer_dst, long long peer_shift_cells, const lbmff_slab* slab, int B, int D,
+                                     int H, int W, lbmff_stream_t stream) {
   Grid g;
   if (int rc = slab_grid_m(slab, B, D, H, W, &g, __func__)) return rc;
   if (!(src && dst && src != dst && mflags && rhs && wmask)) return bad_arg(__func__, "null or aliased pointer");
   if (B != 1) return bad_arg(__func__, "B must be 1");
   if (W < 4 || H < 4) return bad_arg(__func__, "W and H must be >= 4");
   if (g.N > 0x7fffffffLL / 2) return bad_arg(__func__, "more than (2^31-1)/2 cells per batch item");
+  if (peer_dst && (peer_shift_cells <= -g.N || peer_shift_cells >= g.N)) return bad_arg(__func__, "peer shift outside the array");
   if (int rc = psi_sweep_launch(src, dst, mflags, rhs, wmask, nbr_mode, wall_mode, mask_mode,
-                                make_consts(dx, dt, 1.0), g, (cudaStream_t)stream, __func__))
+                                make_consts(dx, dt, 1.0), g, (cudaStream_t)stream, __func__, peer_dst,
+                                (int)peer_shift_cells))
     return rc;
   return check_launch(__func__);
 }

@@ -325,7 +325,8 @@ class SymmPushExchanger(DistExchanger):
         self._pipe = (e_int, e_bnd)
         self.calls += 1
         self.pushes += 1
-        self.bytes_per_direction += 4 * 5 * req.tensors[0].shape[0] * req.tensors[0].shape[3] * req.tensors[0].shape[4]
+        t = req.tensors[0]    # five z-moving populations of a D3Q19 lattice, or one plane of psi
+        self.bytes_per_direction += 4 * (5 if t.shape[1] == 19 else t.shape[1]) * t.shape[0] * t.shape[3] * t.shape[4]
 
     def flush(self):
         if self.stream is not None and self._signals_pending:
@@ -488,10 +489,11 @@ class SlabFerroSolver:
             # the magnetic lattice stays A/B in both modes (its sweeps alternate boundary-first on two streams)
             alloc = getattr(exchanger, "alloc", None)
             self._h = None
-            if magnetic_path == "faithful" and alloc is not None:
-                # buffers the neighbours can store into (SymmPushExchanger): same shape and views as mc(19)
+            if alloc is not None:
+                # buffers the neighbours can store into (SymmPushExchanger): same shape and views as mc(19) / mc(2)
                 try:
-                    self._h = [alloc((self.B, 19, self.Dk, self.Hh, self.W))[:, :, :self.D] for _ in range(2)]
+                    nch = 19 if magnetic_path == "faithful" else 2
+                    self._h = [alloc((self.B, nch, self.Dk, self.Hh, self.W))[:, :, :self.D] for _ in range(2)]
                 except Exception as e:   # no symmetric memory here: ordinary buffers, the exchanger's NCCL path
                     import warnings
                     warnings.warn(f"symmetric-memory allocation failed ({type(e).__name__}: {e}); "
@@ -647,9 +649,9 @@ class SlabFerroSolver:
                 if psi_only:
                     modes = (0, 0, 0) if s == 0 else ((1, 0, 1) if s == 1 else (1, 1, 1))
 
-                    def run(planes, src=src, dst=dst, modes=modes):
+                    def run(planes, src=src, dst=dst, modes=modes, peer=None, shift=0):
                         self._launch("lbmff_slab_magnetic_sweep_psi_3d", p(src), p(dst), p(self.mflags), p(self._rhs),
-                                     p(wm), *modes, self.dx, self.dt, planes=planes)
+                                     p(wm), *modes, self.dx, self.dt, ctypes.c_void_p(peer or 0), shift, planes=planes)
                 else:
                     def run(planes, src=src, dst=dst, psi=psi, tail=tail):
                         self._launch(sweep, p(src), p(dst), p(self.mflags), p(self._rhs), psi, *tail, planes=planes)
@@ -667,6 +669,12 @@ class SlabFerroSolver:
                         for e, ptr, direction, shift in ((edges[0], ptr_down, -1, cells), (edges[1], ptr_up, 1, -cells)):
                             self._launch("lbmff_slab_magnetic_sweep_push_d3q19", p(src), p(dst), p(self.mflags),
                                          p(self._rhs), psi, *tail, ctypes.c_void_p(ptr), direction, shift, planes=e)
+
+                if psi_only and self.B == 1:     # the psi plane of each boundary plane goes straight to the neighbour
+                    def push(ptr_up, ptr_down, run=run):
+                        cells = L.Dl * self.Hh * self.W
+                        run(edges[0], peer=ptr_down, shift=cells)
+                        run(edges[1], peer=ptr_up, shift=-cells)
 
                 self._mcur = 1 - m
                 yield HaloRequest([dst[:, :1] if psi_only else dst], 1, overlap=lambda run=run: run(interior),

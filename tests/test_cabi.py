@@ -26,8 +26,11 @@ def test_no_undeclared_exports():
 
 
 def test_library_is_sm100a_and_torch_free():
-    out = subprocess.run(["cuobjdump", "-lelf", build.LIB], capture_output=True, text=True).stdout
-    assert "sm_100a" in out
+    for _ in range(3):     # cuobjdump has been seen to come back empty once on a loaded build machine
+        r = subprocess.run(["cuobjdump", "-lelf", build.LIB], capture_output=True, text=True)
+        if "sm_100a" in r.stdout:
+            break
+    assert "sm_100a" in r.stdout, (r.returncode, r.stdout[-300:], r.stderr[-300:])
     ldd = subprocess.run(["ldd", build.LIB], capture_output=True, text=True).stdout
     assert "torch" not in ldd and "c10" not in ldd
 

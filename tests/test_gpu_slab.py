@@ -54,16 +54,17 @@ def test_virtual_ranks_bit_identical_to_one_gpu(P, path, walls_open):
 
 
 @pytest.mark.parametrize("P", [2, 3])
+@pytest.mark.parametrize("path", ["faithful", "scalar"])
 @pytest.mark.parametrize("walls_open", [(1,), ()])
-def test_fused_boundary_sweep_and_halo_push_is_bit_identical(P, walls_open):
+def test_fused_boundary_sweep_and_halo_push_is_bit_identical(P, path, walls_open):
     """lbmff_slab_magnetic_sweep_push_d3q19: the boundary-plane sweep stores the z-moving populations straight into the
     neighbour's halo plane (here: the neighbour virtual rank's tensor; across GPUs the same pointer arithmetic runs on
     symmetric-memory mappings, SymmPushExchanger) -- no exchange of h at all, and still the one-GPU result bit for bit,
-    h included."""
+    h included.  "scalar": the psi-only sweeps push their one psi plane the same way (lbmff_slab_magnetic_sweep_psi_3d)."""
     res = (24, 14, 18)
-    one, slabs = build(res, P, "faithful", walls_open, steps=3, push=True)
+    one, slabs = build(res, P, path, walls_open, steps=3, push=True)
     fluid = (one.mflags != 2)
-    for name in ("f", "g", "rho", "pressure", "vel", "psi", "h"):
+    for name in ("f", "g", "rho", "pressure", "vel", "psi") + (("h",) if path == "faithful" else ()):
         got = torch.cat([s.owned(name) for s in slabs], dim=2)
         want = getattr(one, name)
         if name == "psi":
