@@ -296,10 +296,11 @@ class FerroSolver:
         n = int(n)
         if graph and n >= 2:
             g = self._step_graph()
-            for _ in range(n // 2):
-                g.replay()
-            self.steps_done += 2 * (n // 2)
-            n -= 2 * (n // 2)
+            if g is not None:                 # None: the capture failed (see _step_graph); eager launches below
+                for _ in range(n // 2):
+                    g.replay()
+                self.steps_done += 2 * (n // 2)
+                n -= 2 * (n // 2)
         for _ in range(n):
             self._step_once()
         return self
@@ -314,15 +315,39 @@ class FerroSolver:
         graphs = self.__dict__.setdefault("_graphs", {})
         key = (self._cur, getattr(self, "_mcur", 0))
         if key not in graphs:
-            torch.cuda.synchronize(self.device)
+            import gc
             saved = (self._cur, getattr(self, "_mcur", 0), self.steps_done)
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):                      # capture only records: nothing below executes now
-                self._step_once()
-                self._step_once()
-            self._cur, self.steps_done = saved[0], saved[2]
-            if self.magnetic:
-                self._mcur = saved[1]
+            g = None
+            # A capture is invalidated by any capture-unsafe CUDA call made while it is open -- in "global" mode by ANY
+            # thread, and in this thread by whatever a garbage-collection pass happens to finalise (a pinned buffer, an
+            # event of an earlier solver): seen once in four full test-suite runs.  So: thread-local capture mode, the
+            # collector off for the duration, one retry, and if the capture still fails the caller steps eagerly -- a
+            # graph is an optimisation, never a reason for step() to raise.
+            for _attempt in range(2):
+                torch.cuda.synchronize(self.device)
+                gc_on = gc.isenabled()
+                gc.collect()
+                gc.disable()
+                try:
+                    cand = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(cand, capture_error_mode="thread_local"):   # records only: nothing executes
+                        self._step_once()
+                        self._step_once()
+                    g = cand
+                except Exception as e:                     # noqa: BLE001 -- any capture failure means "no graph"
+                    import warnings
+                    warnings.warn(f"CUDA graph capture of the step failed ({type(e).__name__}); "
+                                  f"{'retrying' if _attempt == 0 else 'stepping eagerly'}")
+                    g = None
+                finally:
+                    if gc_on:
+                        gc.enable()
+                    self._cur, self.steps_done = saved[0], saved[2]
+                    if self.magnetic:
+                        self._mcur = saved[1]
+                if g is not None:
+                    break
+                torch.cuda.synchronize(self.device)
             graphs[key] = g
         return graphs[key]
 
