@@ -69,6 +69,11 @@ class PoissonCG:
                  H.ptr(self._hist), H.ptr(self._info), *H.sizes(self.dim, self.B, self.D, self.Hh, self.W))
         return psi
 
+    def invalidate_hierarchy(self):
+        """Call after changing ``mflags`` in place: the multigrid hierarchy (built by the first solve from the flags)
+        is rebuilt by the next one."""
+        self._hierarchy_built = False
+
     def info(self):
         """Per batch item: dict(iters, converged, residual, rhs_norm, drift) of the last solve (synchronises).
         ``drift`` is the constant the reference's sweeps would add to psi per sweep in their stationary state."""
