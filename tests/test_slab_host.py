@@ -118,3 +118,17 @@ def test_dist_exchanger_gloo(world):
             p.join(120)
             assert p.exitcode == 0
         assert dict(out) == {r: True for r in range(world)}
+
+
+def test_make_exchanger_picks_the_plain_exchanger_off_gpu(monkeypatch):
+    """distributed.make_exchanger: the fused push exchanger needs CUDA + symmetric memory; on the CPU (the gloo tests) and
+    with LBMFF_SLAB_PUSH=0 it must hand back the plain point-to-point DistExchanger.  HaloRequest.push stays optional."""
+    from lbm_ferrofluid_b200.distributed import DistExchanger, HaloRequest, SlabLayout, SymmPushExchanger, make_exchanger
+
+    lay = SlabLayout(16, 2, 0)
+    ex = make_exchanger(lay, "cpu")
+    assert type(ex) is DistExchanger and not hasattr(ex, "alloc")
+    monkeypatch.setenv("LBMFF_SLAB_PUSH", "0")
+    assert type(make_exchanger(lay, "cpu")) is DistExchanger
+    assert issubclass(SymmPushExchanger, DistExchanger)
+    assert HaloRequest([], 0).push is None
